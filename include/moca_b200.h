@@ -1,0 +1,185 @@
+/*
+ * moca_b200.h — C-ABI of libmoca_b200.so, the B200 (sm_100a) implementation of the MoCA-Video hot path.
+ *
+ * The reference (ZhangT-tech/MoCA-Video) is pure Python: its "operator API" for this path is the Python
+ * method surface listed in SURVEY.md §8(b).  Each entry point below names the reference method whose body
+ * it replaces (paths relative to the reference tree).  The Python shim in moca_video_b200/ binds these with
+ * ctypes; INTEGRATION.md shows the binding a maintainer of the reference would add.
+ *
+ * Conventions
+ *   - every function returns int32 status: MOCA_OK or a negative MOCA_E_* code; moca_last_error() gives the
+ *     message of the last failure on the calling thread.  No C++ exception crosses this boundary.
+ *   - all tensor pointers are DEVICE pointers unless the parameter is documented "host"; tensors are dense
+ *     fp32 in the reference's own layout (latents [B,C,F,H,W]).  The library never frees caller memory.
+ *   - `stream` is a cudaStream_t passed as void*; every call is asynchronous on it (no hidden sync), and
+ *     kernels never draw random numbers: noise is always an input (RNG parity with the reference).
+ *   - there is no CPU fallback: on a device that is not sm_100 moca_ctx_create fails with MOCA_E_ARCH.
+ */
+#ifndef MOCA_B200_H
+#define MOCA_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MOCA_OK 0
+#define MOCA_E_SHAPE (-1)
+#define MOCA_E_DTYPE (-2)
+#define MOCA_E_ALIGN (-3)
+#define MOCA_E_ARCH (-4)
+#define MOCA_E_CUDA (-5)
+#define MOCA_E_NCCL (-6)
+#define MOCA_E_ARG (-7)
+#define MOCA_E_STATE (-8)
+
+#define MOCA_MAX_FRAMES 64
+
+typedef struct moca_ctx moca_ctx;       /* one per process / GPU; not thread-safe */
+typedef struct moca_unet moca_unet;     /* packed bf16 weights + execution plan of one UNet */
+
+const char* moca_last_error(void);
+int32_t moca_abi_version(void);
+
+/* ---- context ------------------------------------------------------------------------------------------ */
+int32_t moca_ctx_create(int32_t device, moca_ctx** out);
+int32_t moca_ctx_destroy(moca_ctx* ctx);
+
+/* ---- K13: DDIMSampler.unet CFG combine (lvdm/models/samplers/ddim.py:362-374) fused with
+ *           DDIMSampler.ddim_step (ddim.py:377-649; exact math in SURVEY.md Appendix B) -------------------
+ * x, e_c, e_u, noise, x_prev, pred_x0: [B,C,F,H,W] fp32.  e_u may be NULL (no guidance; ddim.py:366).
+ * coef: HOST float[4*F] rows A, A_prev, sigma, sqrt(1-A) for each frame's table index (ddim.py:409-412).
+ * ts:   HOST int32[F] DDPM timestep of each frame (ddim.py:428).
+ * mask: [B,1,Fm,H,W] fp32 or NULL; mask_idx: HOST int32[F], mask frame used by frame f, <0 = no blend
+ *       (the reference's clobbered loop index, SURVEY Q3, is expressed by the caller through this table).
+ * cond_img: [B,C,1,H,W] fp32 (ignored when mask is NULL).
+ * enh_lo / enh_hi: blend gain for t <= t_thresh / t > t_thresh (ddim.py:584: 1.5 / 1.0; SAM branch :845: 2 / 0=off).
+ * cover_max: masks whose sum exceeds cover_max*H*W*B are skipped (ddim.py:826); >= 1 disables the test.
+ * F <= MOCA_MAX_FRAMES. */
+int32_t moca_cfg_ddim_step(moca_ctx* ctx, const float* x, const float* e_c, const float* e_u, const float* noise,
+                           float cfg_scale, const float* coef, const int32_t* ts, const float* mask, int32_t Fm,
+                           const int32_t* mask_idx, const float* cond_img, double gamma, float enh_lo, float enh_hi,
+                           int32_t t_thresh, float cover_max, int32_t B, int32_t C, int32_t F, int32_t H, int32_t W,
+                           float* x_prev, float* pred_x0, void* stream);
+
+/* ---- DDIMSampler.p_sample_ddim (ddim.py:274-359): CFG + plain DDIM update, scalar table index -------------
+ * n = B*C*F*H*W elements.  coef: A, A_prev, sigma, sqrt(1-A).  use_scale selects ddim.py:349-355. */
+int32_t moca_p_sample_ddim(moca_ctx* ctx, const float* x, const float* e_c, const float* e_u, const float* noise,
+                           float cfg_scale, float A, float A_prev, float sigma, float sqrt_one_minus_A,
+                           int32_t use_scale, float scale, float scale_prev, int64_t n, float* x_prev,
+                           float* pred_x0, void* stream);
+
+/* ---- K15: prepare_latents (scripts/evaluation/funcs.py:55-80): diagonal re-noising into the FIFO queue ----
+ * z [B,C,Fz,H,W] clean latents, noise/queue [B,C,Q,H,W]; src_frame HOST int32[Q] (frame of z for queue slot q),
+ * alpha HOST float[Q] (ddim_alphas of slot q).  queue[q] = alpha^0.5 * z[src] + (1-alpha)^0.5 * noise[q]. */
+int32_t moca_renoise(moca_ctx* ctx, const float* z, const float* noise, const int32_t* src_frame, const float* alpha,
+                     int32_t B, int32_t C, int32_t Fz, int32_t Q, int32_t H, int32_t W, float* queue, void* stream);
+
+/* ---- K15: shift_latents (funcs.py:86-99): queue[:, :, :-1] = queue[:, :, 1:]; queue[:, :, -1] = tail -------
+ * out may not alias queue.  tail [B,C,1,H,W]. */
+int32_t moca_queue_shift(moca_ctx* ctx, const float* queue, const float* tail, int32_t B, int32_t C, int32_t Q,
+                         int32_t H, int32_t W, float* out, void* stream);
+
+/* ---- FIFO window gather / look-ahead write-back (funcs.py:307-316, 351-352) -------------------------------
+ * gather:  win[B,C,Fw,H,W] = queue[:, :, start:start+Fw]
+ * scatter: queue[:, :, start:start+Fw] = win[:, :, win_off:win_off+Fw] for a window of Fwin frames. */
+int32_t moca_window_gather(moca_ctx* ctx, const float* queue, int32_t B, int32_t C, int32_t Q, int32_t H, int32_t W,
+                           int32_t start, int32_t Fw, float* win, void* stream);
+int32_t moca_window_scatter(moca_ctx* ctx, const float* win, int32_t Fwin, int32_t win_off, int32_t B, int32_t C,
+                            int32_t Q, int32_t H, int32_t W, int32_t start, int32_t Fw, float* queue, void* stream);
+
+/* ---- K14: FreeInit (utils/freeinit_utils.py) ---------------------------------------------------------------
+ * moca_freeinit_filter: get_freq_filter (freeinit_utils.py:51-70) -> lpf [T,H,W] fp32.
+ *   type: 0 gaussian (:73-91), 1 butterworth (:94-113), 2 ideal (:116-134), 3 box (:137-157).
+ * moca_freeinit_mix: freq_mix_3d (freeinit_utils.py:7-47): y = Re IFFT3( ifftshift( fftshift(FFT3 x)*lpf
+ *   + fftshift(FFT3 noise)*(1-lpf) ) ) over the last three dims; x, noise, y [NV,T,H,W] (NV = B*C volumes).
+ *   work: device scratch of moca_freeinit_work_bytes(NV,T,H,W) bytes. */
+int32_t moca_freeinit_filter(moca_ctx* ctx, int32_t type, int32_t n, double d_s, double d_t, int32_t T, int32_t H,
+                             int32_t W, float* lpf, void* stream);
+int64_t moca_freeinit_work_bytes(int32_t NV, int32_t T, int32_t H, int32_t W);
+int32_t moca_freeinit_mix(moca_ctx* ctx, const float* x, const float* noise, const float* lpf, int32_t NV, int32_t T,
+                          int32_t H, int32_t W, float* y, void* work, void* stream);
+
+/* ---- UNet: UNetModel (lvdm/modules/networks/openaimodel3d.py:279-578) ---------------------------------------
+ * moca_unet_create: architecture integers of the yaml (configs/inference_t2v_512_v2.0.yaml:22-50).
+ * moca_unet_load:   one call per state_dict tensor (name = state_dict key, fp32 DEVICE pointer, element count);
+ *                   the library converts to its packed bf16 layouts and keeps its own copy.
+ * moca_unet_finalize: checks every parameter arrived.
+ * moca_unet_forward: UNetModel.forward (openaimodel3d.py:534-578).
+ *   x, y      [B,Cin,T,H,W] fp32 (reference layout)
+ *   timesteps HOST int32[B*T]: per-(b,t) timestep (the reference's is_fifo case has B=1, openaimodel3d.py:535,548;
+ *             the plain case repeats each sample's t over its T frames, :545-549)
+ *   context   [B,Lmax,ctx_dim] fp32, ctx_len HOST int32[B] valid tokens per sample
+ *   fps       HOST int32[B]
+ * Shapes (B,T,H,W,Lmax) select a cached execution plan (workspace + CUDA graph), built on first use. */
+int32_t moca_unet_create(moca_ctx* ctx, int32_t in_channels, int32_t out_channels, int32_t model_channels,
+                         int32_t num_res_blocks, const int32_t* channel_mult, int32_t n_mult,
+                         const int32_t* attention_resolutions, int32_t n_attn_res, int32_t num_head_channels,
+                         int32_t context_dim, int32_t init_attn_heads, moca_unet** out);
+int32_t moca_unet_destroy(moca_unet* net);
+int32_t moca_unet_load(moca_unet* net, const char* name, const float* data, int64_t numel, void* stream);
+int32_t moca_unet_finalize(moca_unet* net);
+int32_t moca_unet_forward(moca_unet* net, const float* x, const int32_t* timesteps, const float* context,
+                          const int32_t* ctx_len, int32_t Lmax, const int32_t* fps, int32_t B, int32_t T, int32_t H,
+                          int32_t W, float* y, void* stream);
+/* Debug/parity taps: number of recorded taps of the last forward built with taps enabled, and a copy of tap i as
+ * fp32 [rows, channels] channels-last tokens (rows = B*T*H_l*W_l).  Enable with moca_unet_set_taps(net, 1)
+ * before the first forward of a shape; taps disable CUDA-graph replay. */
+int32_t moca_unet_set_taps(moca_unet* net, int32_t enable);
+int32_t moca_unet_num_taps(moca_unet* net);
+int32_t moca_unet_tap_info(moca_unet* net, int32_t i, char* name, int32_t name_cap, int64_t* rows, int64_t* channels);
+int32_t moca_unet_tap_read(moca_unet* net, int32_t i, float* dst, void* stream);
+/* Count of kernels one forward launches (for bench.py's gpu_launches). */
+int32_t moca_unet_launches(moca_unet* net);
+/* Algorithmic FLOPs (2*MAC, as the reference computes them) of the last planned forward. */
+double moca_unet_flops(moca_unet* net);
+
+/* Host-only architecture listing: moca_unet_create with ctx == NULL builds the parameter table without touching a
+ * device; param_count / param_info enumerate the state_dict keys the loader expects (CPU tests compare them with
+ * the reference's own state_dict listing). */
+int32_t moca_unet_param_count(moca_unet* net);
+int32_t moca_unet_param_info(moca_unet* net, int32_t i, char* name, int32_t name_cap, int64_t* numel);
+int64_t moca_unet_workspace_bytes(moca_unet* net);
+int64_t moca_unet_weight_bytes(moca_unet* net);
+
+/* ---- primitives exposed for unit parity tests (tests/test_gpu_ops.py): the same kernels the UNet plan launches ----
+ * moca_gemm_bf16: D[M,N] = A[M,K] * W[N,K]^T (+bias[N]) on the tcgen05 core; A, W bf16 row-major (K contiguous),
+ *   D fp32 or bf16 (out_bf16).  K % 64 == 0.                                    (nn.Linear, attention.py:54-57)
+ * moca_geglu_f32: FeedForward's GEGLU projection (attention.py:376-383) with the gate fused in the GEMM epilogue.
+ * moca_conv3x3_f32: Conv2d 3x3 padding 1 stride 1|2 on channels-last tokens  (openaimodel3d.py:149-153, 66-70)
+ * moca_tconv_f32:   Conv3d (3,1,1) padding (1,0,0) on tokens [B,T,HW,C]       (openaimodel3d.py:252-263)
+ * moca_groupnorm_bf16 / moca_layernorm_bf16: normalisation (+SiLU) producing the bf16 GEMM operand
+ *                                                          (basics.py:76-87; attention.py:199-201)
+ * moca_attention_bf16: softmax(q k^T / 8) v, head dim 64                      (attention.py:92-114)
+ * These helpers allocate scratch and synchronise; they are a test surface, not the hot path. */
+int32_t moca_gemm_bf16(moca_ctx* ctx, const void* A, const void* Wt, const float* bias, int32_t M, int32_t N, int32_t K,
+                       void* D, int32_t out_bf16, void* stream);
+int32_t moca_geglu_f32(moca_ctx* ctx, const void* A_bf16, const float* w, const float* bias, int32_t M, int32_t N, int32_t K,
+                       void* out_bf16, void* stream);
+int32_t moca_conv3x3_f32(moca_ctx* ctx, const float* x_nhwc, const float* w_oihw, const float* bias, int32_t NF,
+                         int32_t H, int32_t W, int32_t Cin, int32_t Cout, int32_t stride, float* y_nhwc, void* stream);
+int32_t moca_tconv_f32(moca_ctx* ctx, const float* x, const float* w, const float* bias, int32_t B, int32_t T, int32_t HW,
+                       int32_t Cin, int32_t Cout, float* y, void* stream);
+int32_t moca_groupnorm_bf16(moca_ctx* ctx, const float* x, const float* gamma, const float* beta, int64_t rows, int32_t C,
+                            int32_t rows_per_stat, float eps, int32_t silu, void* out_bf16, void* stream);
+int32_t moca_layernorm_bf16(moca_ctx* ctx, const float* x, const float* gamma, const float* beta, int64_t rows, int32_t C,
+                            void* out_bf16, void* stream);
+int32_t moca_attention_bf16(moca_ctx* ctx, const void* q, const void* k, const void* v, int32_t batch, int32_t heads,
+                            int32_t Lq, int32_t Lk, int32_t Lk_valid, int32_t q_stride, int32_t kv_stride, void* out,
+                            int32_t o_stride, int32_t temporal_inner, void* stream);
+
+/* ---- multi-GPU queue hand-off (replaces the mp.Queue/CUDA-IPC exchange of
+ *      scripts/evaluation/funcs_mp.py:197-236) -----------------------------------------------------------------
+ * The exchange itself is issued by the host shim through torch.distributed (NCCL all_gather of the updated
+ * half-windows); these two kernels pack / unpack the half-windows of the windows a rank owns. */
+int32_t moca_halfwin_pack(moca_ctx* ctx, const float* xprev, int32_t Fwin, int32_t half, int32_t B, int32_t C, int32_t H,
+                          int32_t W, float* packed, void* stream);
+int32_t moca_halfwin_unpack(moca_ctx* ctx, const float* packed, int32_t n_windows, const int32_t* window_start,
+                            int32_t half, int32_t B, int32_t C, int32_t Q, int32_t H, int32_t W, float* queue,
+                            void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MOCA_B200_H */

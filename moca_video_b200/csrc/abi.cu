@@ -1,0 +1,47 @@
+// Context object and error plumbing of the C-ABI (include/moca_b200.h).
+#include "common.cuh"
+
+namespace moca {
+static thread_local char g_err[1024] = "";
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+}  // namespace moca
+
+using namespace moca;
+
+extern "C" const char* moca_last_error(void) { return g_err; }
+extern "C" int32_t moca_abi_version(void) { return 1; }
+
+extern "C" int32_t moca_ctx_create(int32_t device, moca_ctx** out) {
+    MOCA_REQUIRE(out != nullptr, MOCA_E_ARG, "moca_ctx_create: out is NULL");
+    *out = nullptr;
+    int ndev = 0;
+    MOCA_CHECK_CUDA(cudaGetDeviceCount(&ndev));
+    MOCA_REQUIRE(device >= 0 && device < ndev, MOCA_E_ARG, "moca_ctx_create: device %d of %d", device, ndev);
+    cudaDeviceProp prop;
+    MOCA_CHECK_CUDA(cudaGetDeviceProperties(&prop, device));
+    // no fallback by design: the kernels are sm_100a SASS (tcgen05 / TMEM / TMA)
+    MOCA_REQUIRE(prop.major == 10, MOCA_E_ARCH, "moca_ctx_create: device %d is sm_%d%d; this library is built for sm_100a only",
+                 device, prop.major, prop.minor);
+    MOCA_CHECK_CUDA(cudaSetDevice(device));
+    moca_ctx* c = new moca_ctx();
+    c->c.device = device;
+    c->c.num_sms = prop.multiProcessorCount;
+    c->c.cc_major = prop.major;
+    c->c.cc_minor = prop.minor;
+    MOCA_CHECK_CUDA(cudaMalloc(&c->c.d_mask_sums, sizeof(double) * MOCA_MAX_FRAMES));
+    MOCA_CHECK_CUDA(cudaMemset(c->c.d_mask_sums, 0, sizeof(double) * MOCA_MAX_FRAMES));
+    *out = c;
+    return MOCA_OK;
+}
+
+extern "C" int32_t moca_ctx_destroy(moca_ctx* ctx) {
+    if (!ctx) return MOCA_OK;
+    cudaFree(ctx->c.d_mask_sums);
+    delete ctx;
+    return MOCA_OK;
+}

@@ -1,0 +1,56 @@
+// Shared helpers of libmoca_b200.so: status/error plumbing across the C-ABI, context object, launch checks.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <stdarg.h>
+#include "../../include/moca_b200.h"
+
+namespace moca {
+
+void set_error(const char* fmt, ...);
+
+struct Ctx {
+    int device = 0;
+    int num_sms = 148;
+    int cc_major = 0, cc_minor = 0;
+    double* d_mask_sums = nullptr;      // [MOCA_MAX_FRAMES] scratch of the K13 mask pre-pass
+    float* d_twiddle = nullptr;         // FreeInit DFT twiddles (cos,sin) for up to 3 axes
+    int tw_T = 0, tw_H = 0, tw_W = 0;
+};
+
+#define MOCA_CHECK_CUDA(expr)                                                                         \
+    do {                                                                                              \
+        cudaError_t _e = (expr);                                                                      \
+        if (_e != cudaSuccess) {                                                                      \
+            ::moca::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+            return MOCA_E_CUDA;                                                                       \
+        }                                                                                             \
+    } while (0)
+
+#define MOCA_REQUIRE(cond, code, ...)          \
+    do {                                       \
+        if (!(cond)) {                         \
+            ::moca::set_error(__VA_ARGS__);    \
+            return (code);                     \
+        }                                      \
+    } while (0)
+
+#define MOCA_LAUNCH_CHECK()                                                                          \
+    do {                                                                                             \
+        cudaError_t _e = cudaGetLastError();                                                         \
+        if (_e != cudaSuccess) {                                                                     \
+            ::moca::set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e), __FILE__, __LINE__); \
+            return MOCA_E_CUDA;                                                                      \
+        }                                                                                            \
+    } while (0)
+
+static inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
+
+}  // namespace moca
+
+struct moca_ctx {
+    moca::Ctx c;
+};

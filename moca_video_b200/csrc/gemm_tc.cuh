@@ -1,0 +1,78 @@
+// tcgen05 / TMEM / TMA GEMM core of the UNet.
+//
+//   acc[m, n] = sum_tap sum_k A[m + shift[tap], k] * Wt[n, tap*Kp + k]          (fp32 accumulate in TMEM)
+//
+// A is a bf16 channels-last token matrix [rows, K]; Wt the packed bf16 weight [N, ntaps*Kp] (K contiguous).
+// One kernel serves
+//   * nn.Linear / 1x1 conv           ntaps = 1
+//   * 3x3 conv (ResBlock, Up/Down)   ntaps = 9 over a zero-bordered [NF, H+2, W+2, C] buffer: tap (dy,dx) is the row
+//                                    shift (dy-1)*(W+2) + (dx-1); border rows are computed and dropped by the epilogue
+//   * Conv3d (3,1,1) (TemporalConv)  ntaps = 3 over a [B, T+2, H*W, C] buffer with zero first/last frame: shift (dt-1)*H*W
+// so the convolutions are implicit GEMMs whose "im2col" is nothing but the TMA row coordinate (rows outside the
+// buffer are zero-filled by TMA).  The epilogue maps an input-space row to its output token row, adds bias /
+// per-frame embedding bias / fp32 residual, or applies GEGLU, and stores fp32 or bf16.
+//
+// Kernel shape: persistent, 192 threads = warp 0 TMA producer, warp 1 MMA issuer (+TMEM alloc), warps 2-5 epilogue.
+// 128 x BN output tile, BK = 64 (one 128-byte swizzled row), STAGES-deep smem ring, two TMEM accumulator stages so the
+// epilogue of tile i overlaps the main loop of tile i+1.
+#pragma once
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace moca {
+
+enum GemmMode { GEMM_LINEAR = 0, GEMM_SPATIAL_PAD = 1, GEMM_TIME_PAD = 2 };
+enum GemmEpi { EPI_F32 = 0, EPI_BF16 = 1, EPI_GEGLU = 2 };
+
+struct GemmParams {
+    CUtensorMap tmA, tmB;
+    int M, N;                 // rows computed (input-row space), accumulator columns
+    int ntaps, kblocks, Kp;   // kblocks = Kp / 64 per tap
+    int tap_shift[9];
+    int mode;
+    int g_rows;               // SPATIAL: (H+2)*(W+2)   TIME: (T+2)*HW
+    int g_w;                  // SPATIAL: W+2           TIME: HW
+    int g_H, g_W;             // SPATIAL: H, W          TIME: g_H = T
+    int stride;               // SPATIAL: 1 or 2 (Downsample)
+    float* outf;
+    __nv_bfloat16* outb;
+    int ldo;                  // output row pitch (elements)
+    const float* bias;        // [N] or null
+    const float* rowbias;     // [frames, rb_ld] or null (ResBlock emb_layers output, openaimodel3d.py:221-226)
+    int rb_ld, rows_per_frame;
+    const float* residual;    // fp32 [out_rows, ldo] or null
+    int epi;
+    int num_m_tiles, num_n_tiles;
+};
+
+struct GemmDesc {
+    const void* A = nullptr;          // bf16 [a_rows, a_cols], pitch a_pitch elements
+    int64_t a_rows = 0;
+    int a_cols = 0, a_pitch = 0;
+    const void* Wt = nullptr;         // bf16 [N, ntaps*Kp]
+    int N = 0, ntaps = 1, Kp = 0;
+    int tap_shift[9] = {0};
+    int mode = GEMM_LINEAR;
+    int g_rows = 0, g_w = 0, g_H = 0, g_W = 0, stride = 1;
+    int M = 0;
+    int epi = EPI_F32;
+    void* out = nullptr;
+    int ldo = 0;
+    const float* bias = nullptr;
+    const float* rowbias = nullptr;
+    int rb_ld = 0, rows_per_frame = 1;
+    const float* residual = nullptr;
+};
+
+struct GemmLaunch {
+    GemmParams p;
+    int BN = 128;
+    int grid = 0;
+    size_t smem = 0;
+    double flops = 0;
+};
+
+int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out);
+int gemm_run(const GemmLaunch& l, cudaStream_t st);
+
+}  // namespace moca

@@ -1,0 +1,320 @@
+// See unet.cuh.  Part 1: architecture enumeration and weight packing (moca_unet_create / _load / _finalize).
+#include "unet.cuh"
+
+using namespace moca;
+
+namespace moca {
+
+static int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+static void* dalloc(moca_unet* n, size_t bytes) {
+    void* p = nullptr;
+    if (n->dry) {                       // architecture listing only (CPU tests): never dereferenced
+        n->weight_bytes += bytes;
+        return (void*)(uintptr_t)0x1000;
+    }
+    if (cudaMalloc(&p, bytes ? bytes : 16) != cudaSuccess) return nullptr;
+    cudaMemset(p, 0, bytes ? bytes : 16);
+    n->allocs.push_back(p);
+    n->weight_bytes += bytes;
+    return p;
+}
+
+static float* reg_f32(moca_unet* n, const std::string& name, int64_t numel, float* into = nullptr, int geglu_bn = 0) {
+    float* p = into ? into : (float*)dalloc(n, numel * sizeof(float));
+    LoadSlot s;
+    s.kind = LoadSlot::COPY_F32;
+    s.dst_f32 = p;
+    s.numel = numel;
+    s.geglu_bn = geglu_bn;
+    n->slots[name] = s;
+    return p;
+}
+
+static NormW reg_norm(moca_unet* n, const std::string& prefix, int C) {
+    NormW w;
+    w.g = reg_f32(n, prefix + ".weight", C);
+    w.b = reg_f32(n, prefix + ".bias", C);
+    return w;
+}
+
+static PackedW alloc_packed(moca_unet* n, int N, int K, int taps, bool bias) {
+    PackedW w;
+    w.N = N; w.K = K; w.taps = taps; w.Kp = round_up(K, 64);
+    w.w = (__nv_bfloat16*)dalloc(n, (size_t)N * taps * w.Kp * sizeof(__nv_bfloat16));
+    if (bias) w.b = (float*)dalloc(n, (size_t)N * sizeof(float));
+    return w;
+}
+
+// registers state_dict tensor `name` ([rowsN, K, taps]) to be packed into rows [row0, row0+rowsN) of pw
+static void reg_pack(moca_unet* n, const std::string& name, const PackedW& pw, int row0, int rowsN, int geglu_bn = 0) {
+    LoadSlot s;
+    s.kind = LoadSlot::PACK;
+    s.dst = pw.w;
+    s.N = rowsN; s.K = pw.K; s.taps = pw.taps; s.Kp = pw.Kp; s.row0 = row0; s.geglu_bn = geglu_bn;
+    s.pitch = (int64_t)pw.taps * pw.Kp;
+    s.numel = (int64_t)rowsN * pw.K * pw.taps;
+    n->slots[name] = s;
+}
+
+static PackedW reg_linear(moca_unet* n, const std::string& prefix, int N, int K, int taps, bool bias, int geglu_bn = 0) {
+    PackedW w = alloc_packed(n, N, K, taps, bias);
+    reg_pack(n, prefix + ".weight", w, 0, N, geglu_bn);
+    if (bias) reg_f32(n, prefix + ".bias", N, w.b, geglu_bn);
+    return w;
+}
+
+static void build_res(moca_unet* n, LayerW& L, int te) {
+    ResW& r = L.res;
+    const std::string& p = L.name;
+    r.cin = L.cin; r.cout = L.cout;
+    r.gn1 = reg_norm(n, p + ".in_layers.0", r.cin);
+    r.conv1 = reg_linear(n, p + ".in_layers.2", r.cout, r.cin, 9, true);
+    r.emb_off = n->n_emb;
+    n->n_emb += r.cout;
+    r.gn2 = reg_norm(n, p + ".out_layers.0", r.cout);
+    r.conv2 = reg_linear(n, p + ".out_layers.3", r.cout, r.cout, 9, true);
+    r.has_skip = r.cin != r.cout;
+    if (r.has_skip) r.skip = reg_linear(n, p + ".skip_connection", r.cout, r.cin, 1, true);
+    for (int i = 0; i < 4; ++i) {
+        const std::string q = p + ".temopral_conv.conv" + std::to_string(i + 1);
+        r.tgn[i] = reg_norm(n, q + ".0", r.cout);
+        r.tconv[i] = reg_linear(n, q + (i == 0 ? ".2" : ".3"), r.cout, r.cout, 3, true);
+    }
+    (void)te;
+}
+
+static void build_tf(moca_unet* n, LayerW& L, bool spatial, int heads, int inner, bool linear) {
+    TfW& t = L.tf;
+    const std::string& p = L.name;
+    t.spatial = spatial; t.linear = linear; t.C = L.cin; t.inner = inner; t.heads = heads;
+    t.gn = reg_norm(n, p + ".norm", t.C);
+    t.proj_in = reg_linear(n, p + ".proj_in", inner, t.C, 1, true);
+    t.proj_out = reg_linear(n, p + ".proj_out", t.C, inner, 1, true);
+    const std::string b = p + ".transformer_blocks.0";
+    t.ln1 = reg_norm(n, b + ".norm1", inner);
+    t.ln2 = reg_norm(n, b + ".norm2", inner);
+    t.ln3 = reg_norm(n, b + ".norm3", inner);
+    t.qkv1 = alloc_packed(n, 3 * inner, inner, 1, false);
+    reg_pack(n, b + ".attn1.to_q.weight", t.qkv1, 0, inner);
+    reg_pack(n, b + ".attn1.to_k.weight", t.qkv1, inner, inner);
+    reg_pack(n, b + ".attn1.to_v.weight", t.qkv1, 2 * inner, inner);
+    t.out1 = reg_linear(n, b + ".attn1.to_out.0", inner, inner, 1, true);
+    if (spatial) {
+        t.q2 = reg_linear(n, b + ".attn2.to_q", inner, inner, 1, false);
+        t.kv_off = n->n_kv;
+        n->n_kv += 2 * inner;          // k rows then v rows, registered once kv_all is allocated
+    } else {
+        t.qkv2 = alloc_packed(n, 3 * inner, inner, 1, false);
+        reg_pack(n, b + ".attn2.to_q.weight", t.qkv2, 0, inner);
+        reg_pack(n, b + ".attn2.to_k.weight", t.qkv2, inner, inner);
+        reg_pack(n, b + ".attn2.to_v.weight", t.qkv2, 2 * inner, inner);
+    }
+    t.out2 = reg_linear(n, b + ".attn2.to_out.0", inner, inner, 1, true);
+    t.ff1 = reg_linear(n, b + ".ff.net.0.proj", 8 * inner, inner, 1, true, 256);
+    t.ff2 = reg_linear(n, b + ".ff.net.2", inner, 4 * inner, 1, true);
+}
+
+static bool has(const std::vector<int>& v, int x) {
+    for (int e : v)
+        if (e == x) return true;
+    return false;
+}
+
+// Enumerates blocks exactly like UNetModel.__init__ (openaimodel3d.py:373-526); same walk as moca_video_b200/arch.py.
+static void build_arch(moca_unet* n) {
+    const int mc = n->mc, dh = n->dh, te = 4 * mc;
+    n->time0 = reg_linear(n, "time_embed.0", te, mc, 1, true);
+    n->time2 = reg_linear(n, "time_embed.2", te, te, 1, true);
+    n->fps0 = reg_linear(n, "fps_embedding.0", te, mc, 1, true);
+    n->fps2 = reg_linear(n, "fps_embedding.2", te, te, 1, true);
+    auto mk = [](const char* kind, const std::string& name, int cin, int cout) {
+        LayerW L; L.kind = kind; L.name = name; L.cin = cin; L.cout = cout; return L;
+    };
+    {
+        BlockW b;
+        LayerW L = mk("conv_in", "input_blocks.0.0", n->in_ch, mc);
+        L.conv = reg_linear(n, L.name, mc, n->in_ch, 9, true);
+        b.layers.push_back(L);
+        n->inp.push_back(b);
+    }
+    {
+        LayerW L = mk("tt", "init_attn.0", mc, mc);
+        build_tf(n, L, false, n->init_heads, n->init_heads * dh, false);
+        n->init_attn.layers.push_back(L);
+    }
+    std::vector<int> chans{mc};
+    int ch = mc, ds = 1, bi = 1;
+    for (size_t level = 0; level < n->mult.size(); ++level) {
+        const int mult = n->mult[level];
+        for (int r = 0; r < n->nres; ++r) {
+            BlockW b;
+            const std::string pre = "input_blocks." + std::to_string(bi);
+            LayerW L = mk("res", pre + ".0", ch, mult * mc);
+            build_res(n, L, te);
+            b.layers.push_back(L);
+            ch = mult * mc;
+            if (has(n->attn_res, ds)) {
+                LayerW S = mk("st", pre + ".1", ch, ch);
+                build_tf(n, S, true, ch / dh, ch, true);
+                b.layers.push_back(S);
+                LayerW T = mk("tt", pre + ".2", ch, ch);
+                build_tf(n, T, false, ch / dh, ch, true);
+                b.layers.push_back(T);
+            }
+            n->inp.push_back(b);
+            chans.push_back(ch);
+            ++bi;
+        }
+        if (level != n->mult.size() - 1) {
+            BlockW b;
+            LayerW L = mk("down", "input_blocks." + std::to_string(bi) + ".0", ch, ch);
+            L.conv = reg_linear(n, L.name + ".op", ch, ch, 9, true);
+            b.layers.push_back(L);
+            n->inp.push_back(b);
+            chans.push_back(ch);
+            ++bi;
+            ds *= 2;
+        }
+    }
+    {
+        LayerW A = mk("res", "middle_block.0", ch, ch); build_res(n, A, te); n->mid.layers.push_back(A);
+        LayerW S = mk("st", "middle_block.1", ch, ch); build_tf(n, S, true, ch / dh, ch, true); n->mid.layers.push_back(S);
+        LayerW T = mk("tt", "middle_block.2", ch, ch); build_tf(n, T, false, ch / dh, ch, true); n->mid.layers.push_back(T);
+        LayerW B2 = mk("res", "middle_block.3", ch, ch); build_res(n, B2, te); n->mid.layers.push_back(B2);
+    }
+    int oi = 0;
+    for (int level = (int)n->mult.size() - 1; level >= 0; --level) {
+        const int mult = n->mult[level];
+        for (int i = 0; i <= n->nres; ++i) {
+            const int ich = chans.back();
+            chans.pop_back();
+            BlockW b;
+            b.skip_cin = ich;
+            const std::string pre = "output_blocks." + std::to_string(oi);
+            LayerW L = mk("res", pre + ".0", ch + ich, mc * mult);
+            build_res(n, L, te);
+            b.layers.push_back(L);
+            ch = mc * mult;
+            int li = 1;
+            if (has(n->attn_res, ds)) {
+                LayerW S = mk("st", pre + ".1", ch, ch);
+                build_tf(n, S, true, ch / dh, ch, true);
+                b.layers.push_back(S);
+                LayerW T = mk("tt", pre + ".2", ch, ch);
+                build_tf(n, T, false, ch / dh, ch, true);
+                b.layers.push_back(T);
+                li = 3;
+            }
+            if (level && i == n->nres) {
+                LayerW U = mk("up", pre + "." + std::to_string(li), ch, ch);
+                U.conv = reg_linear(n, U.name + ".conv", ch, ch, 9, true);
+                b.layers.push_back(U);
+                ds /= 2;
+            }
+            n->outb.push_back(b);
+            ++oi;
+        }
+    }
+    n->gn_out = reg_norm(n, "out.0", mc);
+    n->conv_out = reg_linear(n, "out.2", n->out_ch, mc, 9, true);
+    // stacked matrices: all ResBlock emb_layers (one GEMM per step) and all cross-attention to_k/to_v (one GEMM per step)
+    n->emb_all = alloc_packed(n, n->n_emb, te, 1, true);
+    n->kv_all = alloc_packed(n, n->n_kv > 0 ? n->n_kv : 16, n->ctx_dim, 1, false);
+    auto visit = [&](BlockW& b) {
+        for (LayerW& L : b.layers) {
+            if (L.kind == "res") {
+                reg_pack(n, L.name + ".emb_layers.1.weight", n->emb_all, L.res.emb_off, L.res.cout);
+                reg_f32(n, L.name + ".emb_layers.1.bias", L.res.cout, n->emb_all.b + L.res.emb_off);
+            } else if (L.kind == "st") {
+                const std::string a = L.name + ".transformer_blocks.0.attn2";
+                reg_pack(n, a + ".to_k.weight", n->kv_all, L.tf.kv_off, L.tf.inner);
+                reg_pack(n, a + ".to_v.weight", n->kv_all, L.tf.kv_off + L.tf.inner, L.tf.inner);
+            }
+        }
+    };
+    for (auto& b : n->inp) visit(b);
+    visit(n->mid);
+    for (auto& b : n->outb) visit(b);
+}
+
+__global__ void copy_bias_kernel(const float* __restrict__ src, float* __restrict__ dst, int N, int geglu_bn) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    int r = i;
+    if (geglu_bn > 0) {
+        const int half = N / 2, hb = geglu_bn / 2;
+        const int j = i < half ? i : i - half;
+        r = (j / hb) * geglu_bn + (i < half ? 0 : hb) + (j % hb);
+    }
+    dst[r] = src[i];
+}
+
+}  // namespace moca
+
+extern "C" int32_t moca_unet_create(moca_ctx* ctx, int32_t in_channels, int32_t out_channels, int32_t model_channels,
+                                    int32_t num_res_blocks, const int32_t* channel_mult, int32_t n_mult,
+                                    const int32_t* attention_resolutions, int32_t n_attn_res, int32_t num_head_channels,
+                                    int32_t context_dim, int32_t init_attn_heads, moca_unet** out) {
+    MOCA_REQUIRE(out && channel_mult && attention_resolutions, MOCA_E_ARG, "moca_unet_create: NULL argument");
+    MOCA_REQUIRE(num_head_channels == 64, MOCA_E_SHAPE, "moca_unet_create: attention kernels are built for head dim 64 (got %d)", num_head_channels);
+    MOCA_REQUIRE(model_channels % 64 == 0 && context_dim % 8 == 0, MOCA_E_SHAPE,
+                 "moca_unet_create: model_channels %d must be a multiple of 64 and context_dim %d of 8", model_channels, context_dim);
+    MOCA_REQUIRE(in_channels <= 64 && out_channels <= 128, MOCA_E_SHAPE, "moca_unet_create: in/out channels too large");
+    moca_unet* n = new moca_unet();
+    n->ctx = ctx;
+    n->dry = (ctx == nullptr);          // ctx == NULL: host-only architecture listing (moca_unet_param_*)
+    n->in_ch = in_channels; n->out_ch = out_channels; n->mc = model_channels; n->nres = num_res_blocks;
+    n->dh = num_head_channels; n->ctx_dim = context_dim; n->init_heads = init_attn_heads;
+    n->mult.assign(channel_mult, channel_mult + n_mult);
+    n->attn_res.assign(attention_resolutions, attention_resolutions + n_attn_res);
+    build_arch(n);
+    for (void* p : n->allocs)
+        if (!p) {
+            set_error("moca_unet_create: device allocation failed");
+            return MOCA_E_CUDA;
+        }
+    *out = n;
+    return MOCA_OK;
+}
+
+extern "C" int32_t moca_unet_param_count(moca_unet* n) { return n ? (int32_t)n->slots.size() : 0; }
+
+extern "C" int32_t moca_unet_param_info(moca_unet* n, int32_t i, char* name, int32_t name_cap, int64_t* numel) {
+    MOCA_REQUIRE(n && name && numel && i >= 0 && i < (int)n->slots.size(), MOCA_E_ARG, "moca_unet_param_info: bad argument");
+    auto it = n->slots.begin();
+    std::advance(it, i);
+    snprintf(name, name_cap, "%s", it->first.c_str());
+    *numel = it->second.numel;
+    return MOCA_OK;
+}
+
+extern "C" int32_t moca_unet_load(moca_unet* n, const char* name, const float* data, int64_t numel, void* stream) {
+    MOCA_REQUIRE(n && name && data, MOCA_E_ARG, "moca_unet_load: NULL argument");
+    MOCA_REQUIRE(!n->dry, MOCA_E_STATE, "moca_unet_load: network was created without a context (listing only)");
+    auto it = n->slots.find(name);
+    MOCA_REQUIRE(it != n->slots.end(), MOCA_E_ARG, "moca_unet_load: unknown parameter '%s'", name);
+    LoadSlot& s = it->second;
+    MOCA_REQUIRE(s.numel == numel, MOCA_E_SHAPE, "moca_unet_load: '%s' has %lld elements, expected %lld", name, (long long)numel,
+                 (long long)s.numel);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (s.kind == LoadSlot::COPY_F32) {
+        copy_bias_kernel<<<cdiv(numel, 256), 256, 0, st>>>(data, s.dst_f32, (int)numel, s.geglu_bn);
+        MOCA_LAUNCH_CHECK();
+    } else {
+        int rc = pack_weight(data, s.N, s.K, s.taps, s.Kp, s.dst, s.pitch, s.row0, s.geglu_bn, st);
+        if (rc) return rc;
+    }
+    s.loaded = true;
+    n->finalized = false;
+    return MOCA_OK;
+}
+
+extern "C" int32_t moca_unet_finalize(moca_unet* n) {
+    MOCA_REQUIRE(n, MOCA_E_ARG, "moca_unet_finalize: NULL");
+    for (auto& kv : n->slots)
+        MOCA_REQUIRE(kv.second.loaded, MOCA_E_STATE, "moca_unet_finalize: parameter '%s' was never loaded", kv.first.c_str());
+    MOCA_CHECK_CUDA(cudaDeviceSynchronize());
+    n->finalized = true;
+    return MOCA_OK;
+}

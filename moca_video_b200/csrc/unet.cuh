@@ -1,0 +1,98 @@
+// UNet runner: packed weights + per-shape execution plan (ops list, workspace, CUDA graph).
+// Mirrors UNetModel (lvdm/modules/networks/openaimodel3d.py:279-578) for the option set of
+// configs/inference_t2v_512_v2.0.yaml (use_linear, temporal_conv, temporal_attention, temporal_selfatt_only,
+// addition_attention, fps_cond, num_head_channels heads, no relative position, no image cross-attention).
+#pragma once
+#include <functional>
+#include <map>
+#include <memory>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "attn.cuh"
+#include "common.cuh"
+#include "gemm_tc.cuh"
+#include "norm.cuh"
+
+namespace moca {
+
+struct PackedW {               // bf16 [N, taps*Kp]
+    __nv_bfloat16* w = nullptr;
+    float* b = nullptr;        // fp32 [N] or null
+    int N = 0, K = 0, Kp = 0, taps = 1;
+};
+
+struct NormW {
+    float* g = nullptr;
+    float* b = nullptr;
+};
+
+struct ResW {
+    int cin = 0, cout = 0;
+    NormW gn1, gn2;
+    PackedW conv1, conv2, skip;
+    bool has_skip = false;
+    int emb_off = 0;           // column offset into the stacked emb_layers output
+    NormW tgn[4];
+    PackedW tconv[4];
+};
+
+struct TfW {
+    bool spatial = true;
+    bool linear = true;
+    int C = 0, inner = 0, heads = 0;
+    NormW gn, ln1, ln2, ln3;
+    PackedW proj_in, proj_out;
+    PackedW qkv1, out1;        // attn1: fused q|k|v [3*inner, inner], to_out
+    PackedW q2, out2;          // attn2 (spatial): to_q ; k|v live in the stacked context projection at kv_off
+    PackedW qkv2;              // attn2 (temporal): fused self-attention
+    int kv_off = 0;
+    PackedW ff1, ff2;
+};
+
+struct LayerW {
+    std::string kind, name;
+    int cin = 0, cout = 0;
+    ResW res;
+    TfW tf;
+    PackedW conv;              // conv_in / down / up
+};
+
+struct BlockW {
+    std::vector<LayerW> layers;
+    int skip_cin = 0;
+};
+
+struct LoadSlot {
+    enum Kind { COPY_F32, PACK } kind = COPY_F32;
+    float* dst_f32 = nullptr;
+    __nv_bfloat16* dst = nullptr;
+    int N = 0, K = 0, taps = 1, Kp = 0, row0 = 0, geglu_bn = 0;
+    int64_t pitch = 0;
+    int64_t numel = 0;
+    bool loaded = false;
+};
+
+struct Plan;
+
+}  // namespace moca
+
+struct moca_unet {
+    moca_ctx* ctx = nullptr;
+    int in_ch = 4, out_ch = 4, mc = 320, nres = 2, dh = 64, ctx_dim = 1024, init_heads = 8;
+    std::vector<int> mult, attn_res;
+    std::vector<moca::BlockW> inp, outb;
+    moca::BlockW init_attn, mid;
+    moca::PackedW time0, time2, fps0, fps2, emb_all, kv_all, conv_out;
+    moca::NormW gn_out;
+    int n_emb = 0, n_kv = 0;
+    std::unordered_map<std::string, moca::LoadSlot> slots;
+    std::vector<void*> allocs;
+    bool finalized = false;
+    bool dry = false;
+    bool taps = false;
+    std::map<std::vector<int>, std::shared_ptr<moca::Plan>> plans;
+    moca::Plan* last = nullptr;
+    size_t weight_bytes = 0;
+};

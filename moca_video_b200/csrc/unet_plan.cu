@@ -1,0 +1,522 @@
+// See unet.cuh.  Part 2: per-shape execution plan of UNetModel.forward (openaimodel3d.py:534-578) and its modules.
+//
+// Activation layout: channels-last token matrix [B*T*H*W, C], token order (b, t, h, w) at every level.  The residual
+// stream and every GroupNorm/LayerNorm input stay fp32; every GEMM operand is a bf16 copy produced by the norm that
+// precedes it (fused normalise + SiLU + layout scatter), so no rearrange/permute/contiguous copy of the reference
+// (openaimodel3d.py:42-45,230-233,552; attention.py:264-277,333-372) exists here: temporal modules address the same
+// matrix with a row stride of H*W.
+#include "unet.cuh"
+
+namespace moca {
+
+typedef std::function<int(cudaStream_t)> Op;
+
+struct Tap {
+    std::string name;
+    float* buf = nullptr;
+    int64_t rows = 0;
+    int C = 0;
+};
+
+struct Plan {
+    int B = 0, T = 0, H = 0, W = 0, Lmax = 0;
+    std::vector<Op> ops;
+    int launches = 0;
+    double flops = 0;
+    std::vector<void*> allocs;
+    float* x_in = nullptr;
+    float* ctx_in = nullptr;
+    int* d_ts = nullptr;
+    int* d_fps = nullptr;
+    int* d_ctxlen = nullptr;
+    float* out_tok = nullptr;
+    double* stats = nullptr;
+    size_t stats_bytes = 0;
+    cudaGraphExec_t gexec = nullptr;
+    std::vector<Tap> taps;
+    bool with_taps = false;
+    size_t workspace_bytes = 0;
+    ~Plan() {
+        if (gexec) cudaGraphExecDestroy(gexec);
+        for (void* p : allocs) cudaFree(p);
+    }
+};
+
+struct Act {
+    float* p = nullptr;
+    int C = 0, H = 0, W = 0;
+};
+
+enum ScratchId { S_PAD = 0, S_RAW, S_LIN, S_QKV, S_ATT, S_FFH, S_F32A, S_F32B, S_Y, S_COUNT };
+
+struct Builder {
+    moca_unet* net;
+    Plan* plan;
+    bool dry;
+    int rc = MOCA_OK;
+    size_t need[S_COUNT] = {0};
+    void* sptr[S_COUNT] = {nullptr};
+    int stat_slots = 0;
+    int B, T, H0, W0, NF, Lmax;
+
+    void fail(int code) { if (rc == MOCA_OK) rc = code; }
+
+    void* palloc(size_t bytes) {
+        if (dry) { plan->workspace_bytes += bytes; return nullptr; }
+        void* p = nullptr;
+        if (cudaMalloc(&p, bytes ? bytes : 16) != cudaSuccess) { set_error("plan: cudaMalloc of %zu bytes failed", bytes); fail(MOCA_E_CUDA); return nullptr; }
+        plan->allocs.push_back(p);
+        return p;
+    }
+    template <typename Tp>
+    Tp* scratch(int id, size_t elems) {
+        const size_t bytes = elems * sizeof(Tp);
+        if (dry) { if (bytes > need[id]) need[id] = bytes; return nullptr; }
+        return (Tp*)sptr[id];
+    }
+    void push(Op op, int nlaunch = 1) {
+        plan->launches += nlaunch;
+        if (!dry) plan->ops.push_back(std::move(op));
+    }
+    double* stat_slot() {
+        const int s = stat_slots++;
+        return dry ? nullptr : plan->stats + (size_t)s * NF * 64;
+    }
+
+    // ---- GEMM flavours -------------------------------------------------------------------------------------
+    void gemm(GemmDesc d, double useful_flops) {
+        plan->launches += 1;
+        plan->flops += useful_flops;
+        if (dry || rc) return;
+        GemmLaunch L;
+        int r = gemm_plan(net->ctx->c, d, &L);
+        if (r) { fail(r); return; }
+        plan->ops.push_back([L](cudaStream_t st) { return gemm_run(L, st); });
+    }
+    void linear(const __nv_bfloat16* A, int64_t rows, int K, const PackedW& w, int epi, void* out, int ldo, const float* residual,
+                int n_override = 0) {
+        GemmDesc d;
+        d.A = A; d.a_rows = rows; d.a_cols = K; d.a_pitch = K;
+        d.Wt = w.w; d.N = n_override ? n_override : w.N; d.ntaps = 1; d.Kp = w.Kp;
+        d.mode = GEMM_LINEAR; d.M = (int)rows; d.epi = epi; d.out = out; d.ldo = ldo; d.bias = w.b; d.residual = residual;
+        gemm(d, 2.0 * rows * d.N * K);
+    }
+    void conv3x3(const __nv_bfloat16* pad, int H, int W, int Cin, const PackedW& w, int stride, float* out, const float* rowbias,
+                 int rb_ld, const float* residual) {
+        GemmDesc d;
+        const int Hp = H + 2, Wp = W + 2;
+        d.A = pad; d.a_rows = (int64_t)NF * Hp * Wp; d.a_cols = Cin; d.a_pitch = Cin;
+        d.Wt = w.w; d.N = w.N; d.ntaps = 9; d.Kp = w.Kp;
+        for (int ky = 0; ky < 3; ++ky)
+            for (int kx = 0; kx < 3; ++kx) d.tap_shift[ky * 3 + kx] = (ky - 1) * Wp + (kx - 1);
+        d.mode = GEMM_SPATIAL_PAD; d.g_rows = Hp * Wp; d.g_w = Wp; d.g_H = H; d.g_W = W; d.stride = stride;
+        d.M = (int)d.a_rows; d.epi = EPI_F32; d.out = out; d.ldo = w.N; d.bias = w.b;
+        d.rowbias = rowbias; d.rb_ld = rb_ld; d.rows_per_frame = (H / stride) * (W / stride); d.residual = residual;
+        gemm(d, 2.0 * NF * (H / stride) * (W / stride) * w.N * 9.0 * w.K);
+    }
+    void tconv(const __nv_bfloat16* padT, int HW, int C, const PackedW& w, float* out, const float* residual) {
+        GemmDesc d;
+        d.A = padT; d.a_rows = (int64_t)B * (T + 2) * HW; d.a_cols = C; d.a_pitch = C;
+        d.Wt = w.w; d.N = w.N; d.ntaps = 3; d.Kp = w.Kp;
+        for (int dt = 0; dt < 3; ++dt) d.tap_shift[dt] = (dt - 1) * HW;
+        d.mode = GEMM_TIME_PAD; d.g_rows = (T + 2) * HW; d.g_w = HW; d.g_H = T;
+        d.M = (int)d.a_rows; d.epi = EPI_F32; d.out = out; d.ldo = w.N; d.bias = w.b; d.residual = residual;
+        gemm(d, 2.0 * NF * HW * w.N * 3.0 * C);
+    }
+
+    // ---- normalisation flavours ----------------------------------------------------------------------------
+    void gnorm(const float* x1, int C1, const float* x2, int C2, int64_t rows, int rows_per_stat, const NormW& w, float eps, int silu,
+               int dst_mode, int H, int W, __nv_bfloat16* dst, __nv_bfloat16* raw) {
+        double* acc = stat_slot();
+        ApplyArgs a;
+        a.x1 = x1; a.C1 = C1; a.x2 = x2; a.C2 = C2; a.rows = rows; a.rows_per_stat = rows_per_stat; a.acc = acc;
+        a.gamma = w.g; a.beta = w.b; a.eps = eps; a.silu = silu; a.dst_mode = dst_mode;
+        a.NF = NF; a.H = H; a.W = W; a.B = B; a.T = T; a.HW = H * W; a.dst = dst; a.raw = raw;
+        push([=](cudaStream_t st) {
+            int r = gn_stats(x1, C1, x2, C2, rows, rows_per_stat, 32, acc, st);
+            return r ? r : gn_apply(a, st);
+        }, 2);
+    }
+    void convert(const float* x, int C, int64_t rows, int dst_mode, int H, int W, __nv_bfloat16* dst) {
+        ApplyArgs a;
+        a.x1 = x; a.C1 = C; a.rows = rows; a.rows_per_stat = 0; a.dst_mode = dst_mode;
+        a.NF = NF; a.H = H; a.W = W; a.B = B; a.T = T; a.HW = H * W; a.dst = dst;
+        push([=](cudaStream_t st) { return gn_apply(a, st); });
+    }
+    void lnorm(const float* x, const NormW& w, int64_t rows, int C, __nv_bfloat16* out) {
+        push([=](cudaStream_t st) { return layernorm_bf16(x, w.g, w.b, rows, C, out, st); });
+    }
+    void tap(const std::string& name, const Act& a) {
+        if (!plan->with_taps) return;
+        const int64_t rows = (int64_t)NF * a.H * a.W;
+        Tap t;
+        t.name = name; t.rows = rows; t.C = a.C;
+        t.buf = (float*)palloc((size_t)rows * a.C * sizeof(float));
+        if (dry) return;
+        plan->taps.push_back(t);
+        const float* src = a.p;
+        float* dst = t.buf;
+        const size_t bytes = (size_t)rows * a.C * sizeof(float);
+        plan->ops.push_back([=](cudaStream_t st) {
+            return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, st) == cudaSuccess ? MOCA_OK : MOCA_E_CUDA;
+        });
+    }
+
+    Act res_block(const LayerW& L, const Act& x, const Act* skip, const float* embout);
+    void transformer(const LayerW& L, const Act& x, const __nv_bfloat16* kv);
+    void build();
+};
+
+// ResBlock._forward (openaimodel3d.py:208-234) followed by its TemporalConvBlock (:269-276)
+Act Builder::res_block(const LayerW& L, const Act& x, const Act* skip, const float* embout) {
+    const ResW& r = L.res;
+    const int H = x.H, W = x.W, HW = H * W;
+    const int64_t rows = (int64_t)NF * HW;
+    const int C2 = skip ? skip->C : 0;
+    const int Cin = x.C + C2;
+    if (Cin != r.cin) { set_error("plan: %s expects %d input channels, got %d", L.name.c_str(), r.cin, Cin); fail(MOCA_E_SHAPE); }
+    if (skip && !r.has_skip) { set_error("plan: %s concatenates a skip tensor but has an identity skip_connection", L.name.c_str()); fail(MOCA_E_SHAPE); }
+    const size_t pad_elems = (size_t)NF * (H + 2) * (W + 2);
+    __nv_bfloat16* pad = scratch<__nv_bfloat16>(S_PAD, pad_elems * (Cin > r.cout ? Cin : r.cout));
+    __nv_bfloat16* raw = r.has_skip ? scratch<__nv_bfloat16>(S_RAW, (size_t)rows * Cin) : nullptr;
+    float* t1 = scratch<float>(S_F32A, (size_t)rows * r.cout);
+    float* t2 = scratch<float>(S_F32B, (size_t)rows * r.cout);
+    Act out;
+    out.C = r.cout; out.H = H; out.W = W;
+    out.p = (float*)palloc((size_t)rows * r.cout * sizeof(float));
+    // in_layers: GN(fp32, eps 1e-5) -> SiLU -> conv3x3 ; + emb_layers(emb)[:, :, None, None]
+    gnorm(x.p, x.C, skip ? skip->p : nullptr, C2, rows, HW, r.gn1, 1e-5f, 1, DST_SPATIAL_PAD, H, W, pad, raw);
+    conv3x3(pad, H, W, Cin, r.conv1, 1, t1, embout + r.emb_off, net->n_emb, nullptr);
+    // out_layers: GN -> SiLU -> (dropout) -> conv3x3 ; + skip_connection(x)
+    gnorm(t1, r.cout, nullptr, 0, rows, HW, r.gn2, 1e-5f, 1, DST_SPATIAL_PAD, H, W, pad, nullptr);
+    if (r.has_skip) {
+        linear(raw, rows, Cin, r.skip, EPI_F32, out.p, r.cout, nullptr);
+        conv3x3(pad, H, W, r.cout, r.conv2, 1, out.p, nullptr, 0, out.p);
+    } else {
+        conv3x3(pad, H, W, r.cout, r.conv2, 1, out.p, nullptr, 0, x.p);
+    }
+    // TemporalConvBlock: 4 x [GN over (C/32, T, H, W) -> SiLU -> Conv3d (3,1,1)] + identity
+    const size_t padt_elems = (size_t)B * (T + 2) * HW * r.cout;
+    __nv_bfloat16* padT = scratch<__nv_bfloat16>(S_PAD, padt_elems);
+    const float* src = out.p;
+    float* dsts[4] = {t1, t2, t1, out.p};
+    for (int i = 0; i < 4; ++i) {
+        gnorm(src, r.cout, nullptr, 0, rows, T * HW, r.tgn[i], 1e-5f, 1, DST_TIME_PAD, H, W, padT, nullptr);
+        tconv(padT, HW, r.cout, r.tconv[i], dsts[i], i == 3 ? out.p : nullptr);
+        src = dsts[i];
+    }
+    return out;
+}
+
+
+// SpatialTransformer.forward (attention.py:262-278) / TemporalTransformer.forward (:331-373) with one
+// BasicTransformerBlock (:216-220): x += attn1(LN1 x); x += attn2(LN2 x, ctx); x += ff(LN3 x).  Runs in place on x.
+void Builder::transformer(const LayerW& L, const Act& x, const __nv_bfloat16* kv) {
+    const TfW& t = L.tf;
+    const int H = x.H, W = x.W, HW = H * W;
+    const int64_t rows = (int64_t)NF * HW;
+    const int C = t.C, I = t.inner;
+    if (x.C != C) { set_error("plan: %s expects %d channels, got %d", L.name.c_str(), C, x.C); fail(MOCA_E_SHAPE); }
+    __nv_bfloat16* lin = scratch<__nv_bfloat16>(S_LIN, (size_t)rows * (C > I ? C : I));
+    __nv_bfloat16* qkv = scratch<__nv_bfloat16>(S_QKV, (size_t)rows * 3 * I);
+    __nv_bfloat16* att = scratch<__nv_bfloat16>(S_ATT, (size_t)rows * I);
+    __nv_bfloat16* ffh = scratch<__nv_bfloat16>(S_FFH, (size_t)rows * 4 * I);
+    float* y = scratch<float>(S_Y, (size_t)rows * I);
+    // norm (GroupNorm eps 1e-6; spatial: per frame, temporal: 5-D input so statistics span all T frames)
+    gnorm(x.p, C, nullptr, 0, rows, t.spatial ? HW : T * HW, t.gn, 1e-6f, 0, DST_LINEAR, H, W, lin, nullptr);
+    linear(lin, rows, C, t.proj_in, EPI_F32, y, I, nullptr);
+
+    AttnArgs self;
+    self.q = qkv; self.k = qkv + I; self.v = qkv + 2 * I; self.ldq = 3 * I; self.ldkv = 3 * I;
+    self.out = att; self.ldo = I; self.heads = t.heads; self.scale = 0.125f;
+    if (t.spatial) {
+        self.n_outer = NF; self.Lq = HW; self.Lk = HW;
+        self.qmap.div = 1; self.qmap.mul_a = HW; self.qmap.mul_b = 0; self.qmap.step = 1;
+    } else {
+        self.n_outer = B * HW; self.Lq = T; self.Lk = T;
+        self.qmap.div = HW; self.qmap.mul_a = T * HW; self.qmap.mul_b = 1; self.qmap.step = HW;
+    }
+    self.kvmap = self.qmap;
+    const double attn_flops = 4.0 * (double)self.n_outer * t.heads * self.Lq * self.Lk * 64.0;
+    const bool spatial = t.spatial;
+    auto run_self = [=](cudaStream_t st) { return spatial ? attention_flash(self, st) : attention_short(self, st); };
+
+    // attn1: self-attention
+    lnorm(y, t.ln1, rows, I, lin);
+    linear(lin, rows, I, t.qkv1, EPI_BF16, qkv, 3 * I, nullptr);
+    push(run_self); plan->flops += attn_flops;
+    linear(att, rows, I, t.out1, EPI_F32, y, I, y);
+    // attn2: cross-attention on the text context (spatial) or a second self-attention (temporal_selfatt_only, attention.py:313-314)
+    lnorm(y, t.ln2, rows, I, lin);
+    if (t.spatial) {
+        linear(lin, rows, I, t.q2, EPI_BF16, qkv, I, nullptr);
+        AttnArgs ca;
+        ca.q = qkv; ca.ldq = I; ca.qmap = self.qmap;
+        ca.k = kv + t.kv_off; ca.v = kv + t.kv_off + I; ca.ldkv = net->n_kv;
+        ca.kvmap.div = T; ca.kvmap.mul_a = Lmax; ca.kvmap.mul_b = 0; ca.kvmap.step = 1;     // frame o uses the context of sample o / T
+        ca.out = att; ca.ldo = I; ca.n_outer = NF; ca.heads = t.heads; ca.Lq = HW; ca.Lk = Lmax;
+        ca.kv_len = plan->d_ctxlen; ca.kv_len_div = T; ca.scale = 0.125f;
+        push([=](cudaStream_t st) { return attention_flash(ca, st); });
+        plan->flops += 4.0 * (double)NF * t.heads * HW * Lmax * 64.0;
+    } else {
+        linear(lin, rows, I, t.qkv2, EPI_BF16, qkv, 3 * I, nullptr);
+        push(run_self); plan->flops += attn_flops;
+    }
+    linear(att, rows, I, t.out2, EPI_F32, y, I, y);
+    // feed-forward: Linear(C -> 8C) with the GEGLU gate fused into the GEMM epilogue, Linear(4C -> C) + residual
+    lnorm(y, t.ln3, rows, I, lin);
+    linear(lin, rows, I, t.ff1, EPI_GEGLU, ffh, 4 * I, nullptr);
+    linear(ffh, rows, 4 * I, t.ff2, EPI_F32, y, I, y);
+    // proj_out + x_in
+    convert(y, I, rows, DST_LINEAR, H, W, lin);
+    linear(lin, rows, I, t.proj_out, EPI_F32, x.p, C, x.p);
+}
+
+
+struct IntPack {
+    int ts[128];
+    int fps[128];
+    int ctxlen[16];
+};
+
+__global__ void set_ints_kernel(const __grid_constant__ IntPack P, int nf, int nb, int* __restrict__ ts, int* __restrict__ fps,
+                                int* __restrict__ ctxlen) {
+    const int i = threadIdx.x;
+    if (i < nf) { ts[i] = P.ts[i]; fps[i] = P.fps[i]; }
+    if (i < nb) ctxlen[i] = P.ctxlen[i];
+}
+
+// UNetModel.forward (openaimodel3d.py:534-578)
+void Builder::build() {
+    moca_unet* n = net;
+    const int mc = n->mc, te = 4 * mc;
+    const int64_t rows0 = (int64_t)NF * H0 * W0;
+    // ---- fixed input staging (the graph reads these; the caller's pointers are copied in before every launch)
+    plan->x_in = (float*)palloc((size_t)B * n->in_ch * T * H0 * W0 * sizeof(float));
+    plan->ctx_in = (float*)palloc((size_t)B * Lmax * n->ctx_dim * sizeof(float));
+    plan->d_ts = (int*)palloc(128 * sizeof(int));
+    plan->d_fps = (int*)palloc(128 * sizeof(int));
+    plan->d_ctxlen = (int*)palloc(16 * sizeof(int));
+    plan->out_tok = (float*)palloc((size_t)rows0 * n->out_ch * sizeof(float));
+    __nv_bfloat16* te_bf = (__nv_bfloat16*)palloc((size_t)NF * mc * 2);
+    __nv_bfloat16* fe_bf = (__nv_bfloat16*)palloc((size_t)NF * mc * 2);
+    float* e1 = (float*)palloc((size_t)NF * te * 4);
+    __nv_bfloat16* e1_bf = (__nv_bfloat16*)palloc((size_t)NF * te * 2);
+    float* temb = (float*)palloc((size_t)NF * te * 4);
+    float* femb = (float*)palloc((size_t)NF * te * 4);
+    __nv_bfloat16* semb = (__nv_bfloat16*)palloc((size_t)NF * te * 2);
+    float* embout = (float*)palloc((size_t)NF * n->n_emb * 4);
+    __nv_bfloat16* ctx_bf = (__nv_bfloat16*)palloc((size_t)B * Lmax * n->ctx_dim * 2);
+    __nv_bfloat16* kv = (__nv_bfloat16*)palloc((size_t)B * Lmax * (n->n_kv > 0 ? n->n_kv : 16) * 2);
+    if (!dry) {
+        double* stats = plan->stats;
+        const size_t sb = plan->stats_bytes;
+        plan->ops.push_back([=](cudaStream_t st) { return cudaMemsetAsync(stats, 0, sb, st) == cudaSuccess ? MOCA_OK : MOCA_E_CUDA; });
+    }
+    plan->launches += 1;
+    // ---- time / fps embeddings (openaimodel3d.py:536-543) and all 22 emb_layers in one GEMM (:166-172, 221-226)
+    {
+        const int* d_ts = plan->d_ts; const int* d_fps = plan->d_fps; const int nf = NF;
+        push([=](cudaStream_t st) { return timestep_embedding_bf16(d_ts, nf, mc, te_bf, st); });
+        push([=](cudaStream_t st) { return timestep_embedding_bf16(d_fps, nf, mc, fe_bf, st); });
+        const int64_t ne = (int64_t)NF * te;
+        linear(te_bf, NF, mc, n->time0, EPI_F32, e1, te, nullptr);
+        push([=](cudaStream_t st) { return silu_add_bf16(e1, nullptr, ne, e1_bf, st); });
+        linear(e1_bf, NF, te, n->time2, EPI_F32, temb, te, nullptr);
+        linear(fe_bf, NF, mc, n->fps0, EPI_F32, e1, te, nullptr);
+        push([=](cudaStream_t st) { return silu_add_bf16(e1, nullptr, ne, e1_bf, st); });
+        linear(e1_bf, NF, te, n->fps2, EPI_F32, femb, te, nullptr);
+        push([=](cudaStream_t st) { return silu_add_bf16(temb, femb, ne, semb, st); });       // SiLU(emb), emb = t_emb + fps_emb
+        linear(semb, NF, te, n->emb_all, EPI_F32, embout, n->n_emb, nullptr);
+    }
+    // ---- cross-attention keys / values of every SpatialTransformer in one GEMM (context is the same for all frames)
+    if (n->n_kv > 0) {
+        const float* ctx_in = plan->ctx_in;
+        const int64_t nc = (int64_t)B * Lmax * n->ctx_dim;
+        push([=](cudaStream_t st) { return f32_to_bf16(ctx_in, nc, ctx_bf, st); });
+        linear(ctx_bf, (int64_t)B * Lmax, n->ctx_dim, n->kv_all, EPI_BF16, kv, n->n_kv, nullptr, n->n_kv);
+    }
+    // ---- input conv
+    Act cur;
+    cur.C = mc; cur.H = H0; cur.W = W0;
+    {
+        __nv_bfloat16* pad = scratch<__nv_bfloat16>(S_PAD, (size_t)NF * (H0 + 2) * (W0 + 2) * 64);
+        const float* x_in = plan->x_in;
+        const int b = B, c = n->in_ch, t = T, h = H0, w = W0;
+        push([=](cudaStream_t st) { return ncthw_to_pad(x_in, b, c, t, h, w, 64, pad, st); });
+        cur.p = (float*)palloc((size_t)rows0 * mc * 4);
+        conv3x3(pad, H0, W0, 64, n->inp[0].layers[0].conv, 1, cur.p, nullptr, 0, nullptr);
+        tap("input_blocks.0.0", cur);
+    }
+    auto run_layers = [&](const BlockW& blk, const Act* skip) {
+        for (size_t li = 0; li < blk.layers.size(); ++li) {
+            const LayerW& L = blk.layers[li];
+            if (L.kind == "conv_in") continue;
+            if (L.kind == "res") {
+                cur = res_block(L, cur, li == 0 ? skip : nullptr, embout);
+            } else if (L.kind == "st" || L.kind == "tt") {
+                transformer(L, cur, kv);
+            } else if (L.kind == "down") {
+                const int64_t rows = (int64_t)NF * cur.H * cur.W;
+                __nv_bfloat16* pad = scratch<__nv_bfloat16>(S_PAD, (size_t)NF * (cur.H + 2) * (cur.W + 2) * cur.C);
+                convert(cur.p, cur.C, rows, DST_SPATIAL_PAD, cur.H, cur.W, pad);
+                Act o; o.C = L.cout; o.H = cur.H / 2; o.W = cur.W / 2;
+                o.p = (float*)palloc((size_t)NF * o.H * o.W * o.C * 4);
+                conv3x3(pad, cur.H, cur.W, cur.C, L.conv, 2, o.p, nullptr, 0, nullptr);
+                cur = o;
+            } else if (L.kind == "up") {
+                const int64_t rows = (int64_t)NF * cur.H * cur.W;
+                const int H2 = cur.H * 2, W2 = cur.W * 2;
+                __nv_bfloat16* pad = scratch<__nv_bfloat16>(S_PAD, (size_t)NF * (H2 + 2) * (W2 + 2) * cur.C);
+                convert(cur.p, cur.C, rows, DST_SPATIAL_PAD_UP2, cur.H, cur.W, pad);
+                Act o; o.C = L.cout; o.H = H2; o.W = W2;
+                o.p = (float*)palloc((size_t)NF * H2 * W2 * o.C * 4);
+                conv3x3(pad, H2, W2, cur.C, L.conv, 1, o.p, nullptr, 0, nullptr);
+                cur = o;
+            }
+            tap(L.name, cur);
+        }
+    };
+    std::vector<Act> hs;
+    for (size_t i = 0; i < n->inp.size(); ++i) {
+        if (i > 0) run_layers(n->inp[i], nullptr);
+        if (i == 0) run_layers(n->init_attn, nullptr);        // openaimodel3d.py:559-560
+        hs.push_back(cur);
+    }
+    run_layers(n->mid, nullptr);
+    for (size_t i = 0; i < n->outb.size(); ++i) {
+        Act skip = hs.back();
+        hs.pop_back();
+        if (skip.H != cur.H || skip.W != cur.W) { set_error("plan: skip tensor geometry mismatch at output block %zu", i); fail(MOCA_E_SHAPE); }
+        run_layers(n->outb[i], &skip);                        // h = cat([h, hs.pop()], 1) is virtual: two-source GroupNorm
+    }
+    // ---- out: GN -> SiLU -> conv3x3 (openaimodel3d.py:528-532, 574)
+    {
+        const int64_t rows = rows0;
+        __nv_bfloat16* pad = scratch<__nv_bfloat16>(S_PAD, (size_t)NF * (H0 + 2) * (W0 + 2) * cur.C);
+        gnorm(cur.p, cur.C, nullptr, 0, rows, H0 * W0, n->gn_out, 1e-5f, 1, DST_SPATIAL_PAD, H0, W0, pad, nullptr);
+        conv3x3(pad, H0, W0, cur.C, n->conv_out, 1, plan->out_tok, nullptr, 0, nullptr);
+    }
+}
+
+}  // namespace moca
+
+using namespace moca;
+
+static int get_plan(moca_unet* n, int B, int T, int H, int W, int Lmax, Plan** out) {
+    std::vector<int> key{B, T, H, W, Lmax, n->taps ? 1 : 0};
+    auto it = n->plans.find(key);
+    if (it != n->plans.end()) { *out = it->second.get(); return MOCA_OK; }
+    int down = 1;
+    for (size_t i = 1; i < n->mult.size(); ++i) down *= 2;
+    MOCA_REQUIRE(H % down == 0 && W % down == 0, MOCA_E_SHAPE, "moca_unet_forward: H=%d W=%d must be multiples of %d", H, W, down);
+    MOCA_REQUIRE(B * T <= 128 && B <= 16 && T <= 16, MOCA_E_SHAPE, "moca_unet_forward: B=%d T=%d unsupported (B*T <= 128, T <= 16)", B, T);
+    auto plan = std::make_shared<Plan>();
+    plan->B = B; plan->T = T; plan->H = H; plan->W = W; plan->Lmax = Lmax; plan->with_taps = n->taps;
+    Builder dry;
+    dry.net = n; dry.plan = plan.get(); dry.dry = true; dry.B = B; dry.T = T; dry.H0 = H; dry.W0 = W; dry.NF = B * T; dry.Lmax = Lmax;
+    dry.build();
+    if (dry.rc) return dry.rc;
+    Builder real = dry;
+    real.dry = false; real.stat_slots = 0;
+    plan->launches = 0; plan->flops = 0;
+    plan->stats_bytes = (size_t)dry.stat_slots * B * T * 64 * sizeof(double);
+    plan->stats = (double*)real.palloc(plan->stats_bytes);
+    for (int i = 0; i < S_COUNT; ++i) {
+        real.sptr[i] = real.palloc(dry.need[i] + 256);
+        plan->workspace_bytes += dry.need[i];
+    }
+    if (real.rc) return real.rc;
+    real.build();
+    if (real.rc) return real.rc;
+    n->plans[key] = plan;
+    *out = plan.get();
+    return MOCA_OK;
+}
+
+extern "C" int32_t moca_unet_forward(moca_unet* n, const float* x, const int32_t* timesteps, const float* context,
+                                     const int32_t* ctx_len, int32_t Lmax, const int32_t* fps, int32_t B, int32_t T, int32_t H,
+                                     int32_t W, float* y, void* stream) {
+    MOCA_REQUIRE(n && x && timesteps && context && ctx_len && fps && y, MOCA_E_ARG, "moca_unet_forward: NULL argument");
+    MOCA_REQUIRE(n->finalized, MOCA_E_STATE, "moca_unet_forward: call moca_unet_finalize after loading the weights");
+    MOCA_REQUIRE(B > 0 && T > 0 && H > 0 && W > 0 && Lmax > 0, MOCA_E_SHAPE, "moca_unet_forward: bad shape");
+    MOCA_REQUIRE((Lmax * n->ctx_dim) % 8 == 0, MOCA_E_SHAPE, "moca_unet_forward: context size");
+    for (int b = 0; b < B; ++b)
+        MOCA_REQUIRE(ctx_len[b] >= 1 && ctx_len[b] <= Lmax, MOCA_E_ARG, "moca_unet_forward: ctx_len[%d]=%d outside 1..%d", b, ctx_len[b], Lmax);
+    cudaStream_t st = (cudaStream_t)stream;
+    Plan* plan = nullptr;
+    int rc = get_plan(n, B, T, H, W, Lmax, &plan);
+    if (rc) return rc;
+    n->last = plan;
+    // inputs -> fixed staging (kernel parameters carry the small integer tables, so no pinned staging is needed)
+    IntPack ip;
+    memset(&ip, 0, sizeof(ip));
+    for (int i = 0; i < B * T; ++i) { ip.ts[i] = timesteps[i]; ip.fps[i] = fps[i / T]; }
+    for (int b = 0; b < B; ++b) ip.ctxlen[b] = ctx_len[b];
+    set_ints_kernel<<<1, 128, 0, st>>>(ip, B * T, B, plan->d_ts, plan->d_fps, plan->d_ctxlen);
+    MOCA_LAUNCH_CHECK();
+    MOCA_CHECK_CUDA(cudaMemcpyAsync(plan->x_in, x, (size_t)B * n->in_ch * T * H * W * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    MOCA_CHECK_CUDA(cudaMemcpyAsync(plan->ctx_in, context, (size_t)B * Lmax * n->ctx_dim * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    const bool use_graph = !plan->with_taps && getenv("MOCA_NO_GRAPH") == nullptr;
+    if (use_graph) {
+        if (!plan->gexec) {
+            // capture on a private stream (the caller's may be the legacy default stream, which cannot be captured)
+            cudaGraph_t graph = nullptr;
+            cudaStream_t cs = nullptr;
+            MOCA_CHECK_CUDA(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
+            MOCA_CHECK_CUDA(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
+            int orc = MOCA_OK;
+            for (auto& op : plan->ops) {
+                orc = op(cs);
+                if (orc) break;
+            }
+            cudaError_t ce = cudaStreamEndCapture(cs, &graph);
+            cudaStreamDestroy(cs);
+            if (orc) { if (graph) cudaGraphDestroy(graph); return orc; }
+            MOCA_REQUIRE(ce == cudaSuccess, MOCA_E_CUDA, "moca_unet_forward: stream capture failed: %s", cudaGetErrorString(ce));
+            ce = cudaGraphInstantiate(&plan->gexec, graph, 0);
+            cudaGraphDestroy(graph);
+            MOCA_REQUIRE(ce == cudaSuccess, MOCA_E_CUDA, "moca_unet_forward: graph instantiate failed: %s", cudaGetErrorString(ce));
+        }
+        MOCA_CHECK_CUDA(cudaGraphLaunch(plan->gexec, st));
+    } else {
+        for (auto& op : plan->ops) {
+            rc = op(st);
+            if (rc) return rc;
+        }
+    }
+    return tokens_to_ncthw(plan->out_tok, n->out_ch, B, n->out_ch, T, H, W, y, st);
+}
+
+extern "C" int32_t moca_unet_destroy(moca_unet* n) {
+    if (!n) return MOCA_OK;
+    n->plans.clear();
+    for (void* p : n->allocs) cudaFree(p);
+    delete n;
+    return MOCA_OK;
+}
+
+extern "C" int32_t moca_unet_set_taps(moca_unet* n, int32_t enable) {
+    MOCA_REQUIRE(n, MOCA_E_ARG, "moca_unet_set_taps: NULL");
+    n->taps = enable != 0;
+    return MOCA_OK;
+}
+extern "C" int32_t moca_unet_num_taps(moca_unet* n) { return (n && n->last) ? (int32_t)n->last->taps.size() : 0; }
+extern "C" int32_t moca_unet_tap_info(moca_unet* n, int32_t i, char* name, int32_t name_cap, int64_t* rows, int64_t* channels) {
+    MOCA_REQUIRE(n && n->last && i >= 0 && i < (int)n->last->taps.size() && name && rows && channels, MOCA_E_ARG, "moca_unet_tap_info: bad argument");
+    const Tap& t = n->last->taps[i];
+    snprintf(name, name_cap, "%s", t.name.c_str());
+    *rows = t.rows;
+    *channels = t.C;
+    return MOCA_OK;
+}
+extern "C" int32_t moca_unet_tap_read(moca_unet* n, int32_t i, float* dst, void* stream) {
+    MOCA_REQUIRE(n && n->last && i >= 0 && i < (int)n->last->taps.size() && dst, MOCA_E_ARG, "moca_unet_tap_read: bad argument");
+    const Tap& t = n->last->taps[i];
+    MOCA_CHECK_CUDA(cudaMemcpyAsync(dst, t.buf, (size_t)t.rows * t.C * sizeof(float), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    return MOCA_OK;
+}
+extern "C" int32_t moca_unet_launches(moca_unet* n) { return (n && n->last) ? n->last->launches + 4 : 0; }
+extern "C" double moca_unet_flops(moca_unet* n) { return (n && n->last) ? n->last->flops : 0.0; }
+extern "C" int64_t moca_unet_workspace_bytes(moca_unet* n) { return (n && n->last) ? (int64_t)n->last->workspace_bytes : 0; }
+extern "C" int64_t moca_unet_weight_bytes(moca_unet* n) { return n ? (int64_t)n->weight_bytes : 0; }

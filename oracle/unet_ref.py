@@ -117,7 +117,7 @@ def resblock(x, emb, sd, p, b):
     return h5.permute(0, 2, 1, 3, 4).reshape(n, c, hh, ww)
 
 
-def _run_block(blk, h, emb, ctx, sd, b):
+def _run_block(blk, h, emb, ctx, sd, b, taps=None):
     for L in blk.layers:
         if L.kind == "conv_in":
             h = F.conv2d(h, sd[L.name + ".weight"], sd[L.name + ".bias"], padding=1)
@@ -135,11 +135,13 @@ def _run_block(blk, h, emb, ctx, sd, b):
         elif L.kind == "up":
             h = F.interpolate(h, scale_factor=2, mode="nearest")
             h = F.conv2d(h, sd[L.name + ".conv.weight"], sd[L.name + ".conv.bias"], padding=1)
+        if taps is not None:
+            taps[L.name] = h.permute(0, 2, 3, 1).reshape(-1, h.shape[1]).clone()     # channels-last tokens [rows, C]
     return h
 
 
 @torch.no_grad()
-def unet_forward(sd, cfg: UNetConfig, x, timesteps, context, fps=16):
+def unet_forward(sd, cfg: UNetConfig, x, timesteps, context, fps=16, taps=None):
     """x [b,c,t,h,w]; timesteps [b] or [b*t] (``is_fifo``, openaimodel3d.py:535); context [b,L,ctx_dim]."""
     mc = cfg.model_channels
     b, _, t, _, _ = x.shape
@@ -156,14 +158,14 @@ def unet_forward(sd, cfg: UNetConfig, x, timesteps, context, fps=16):
     inp, init_attn, mid, out = build_blocks(cfg)
     hs = []
     for i, blk in enumerate(inp):
-        h = _run_block(blk, h, emb, ctx, sd, b)
+        h = _run_block(blk, h, emb, ctx, sd, b, taps)
         if i == 0:
-            h = _run_block(init_attn, h, emb, ctx, sd, b)
+            h = _run_block(init_attn, h, emb, ctx, sd, b, taps)
         hs.append(h)
-    h = _run_block(mid, h, emb, ctx, sd, b)
+    h = _run_block(mid, h, emb, ctx, sd, b, taps)
     for blk in out:
         h = torch.cat([h, hs.pop()], dim=1)
-        h = _run_block(blk, h, emb, ctx, sd, b)
+        h = _run_block(blk, h, emb, ctx, sd, b, taps)
     y = F.conv2d(F.silu(_gn(h, sd, "out.0", 1e-5)), sd["out.2.weight"], sd["out.2.bias"], padding=1)
     n, c, hh, ww = y.shape
     return y.reshape(b, t, c, hh, ww).permute(0, 2, 1, 3, 4).contiguous()
