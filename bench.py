@@ -1,0 +1,279 @@
+"""bench.py — UNet denoise steps/s (16 frames, 320x512 px = latent [1,4,16,40,64]) on B200, BASELINE.json's metric.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+
+A "step" is one sampler step with classifier-free guidance: two UNet forwards (issued as one b=2 launch) + the fused
+step kernel.  N=1 runs BASELINE config[1] (plain DDIM text-to-video step, p_sample_ddim with use_scale, ctx 77+77);
+N>1 runs config[3]: the FIFO queue's 8 windows per iteration sharded over the ranks (window r on rank r mod N, one
+NCCL all_gather of the updated half-windows per iteration), K iterations = 8K steps.
+Prints ONE JSON line (see the keys below); nothing here imports oracle/ except the cpu_baseline / --impl reference legs.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FLOP_PER_FORWARD_77 = 12.581472337920e12      # 2*MAC of the reference forward, ctx 77 (FlopCounterMode)
+FLOP_PER_FORWARD_154 = 12.680026030080e12     # ctx 154
+CFG_SCALE = 12.0
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d.get("bf16_tflops_sustained", 1400.0), d.get("hbm_gbs", 6650.0), "measured (MEASURED_PEAKS.json, sustained)"
+    return 1400.0, 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.stop_flag, self.sm, self.reasons, self.max_mhz = index, False, [], set(), None
+
+    def run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            names = {nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown", nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                     nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown", nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap"}
+            while not self.stop_flag:
+                self.sm.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                for bit, nm in names.items():
+                    if r & bit:
+                        self.reasons.add(nm)
+                time.sleep(0.05)
+        except Exception as e:  # noqa: BLE001
+            self.reasons.add(f"nvml_unavailable:{type(e).__name__}")
+
+    def summary(self):
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+def cpu_reference_sample(steps, warmup):
+    """The reference's CPU path for this metric: oracle/unet_ref.py (plain torch fp32 restatement, pinned to the
+    unmodified reference by tests/golden) on the host cores.  One sample = ONE cond UNet forward on 2 of the 16 frames
+    ([1,4,2,40,64], ctx 77) = 1/16 of a CFG step (2 forwards x 16 frames); cost is linear in frames."""
+    from moca_video_b200.arch import UNetConfig, random_state_dict
+    from oracle.unet_ref import unet_forward
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    cfg = UNetConfig.videocrafter2()
+    sd = random_state_dict(cfg, seed=0, device="cpu")
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn((1, 4, 2, 40, 64), generator=g)
+    ctx = torch.randn((1, 77, 1024), generator=g)
+    ts = torch.tensor([500, 516])
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        unet_forward(sd, cfg, x, ts, ctx, fps=10)
+        if i >= warmup:
+            times.append(time.perf_counter() - t0)
+    t = float(np.mean(times))
+    frac = 1.0 / 16.0
+    return {"value": frac / t, "unit": "steps/s", "cores": cores, "kind": "port",
+            "sample": f"one fp32 UNet forward on 2 of 16 frames ([1,4,2,40,64], ctx 77) = 1/16 CFG step; {t:.2f} s per sample, "
+                      f"{len(times)} timed"}, t
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    cb, t = cpu_reference_sample(args.steps, args.warmup)
+    out = {"impl": "reference", "metric": "UNet denoise steps/s (16f 320x512)", "value": cb["value"], "unit": "steps/s",
+           "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True,
+           "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": "configs[1]: VideoCrafter2 UNet DDIM step, 16x320x512 (latent [1,4,16,40,64]), CFG, random-init; "
+                                  "bounded CPU sample scaled to a full step"},
+           "cpu_baseline": cb, "e2e": {"value": cb["value"], "unit": "steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "gpu_launches": 0}
+    print(json.dumps(out))
+
+
+def build_engine(dev):
+    from moca_video_b200.arch import UNetConfig, random_state_dict
+    from moca_video_b200.model import LatentDiffusionB200
+    from moca_video_b200.sampler import DDIMSampler
+    from moca_video_b200.unet import UNet3D
+    cfg = UNetConfig.videocrafter2()
+    net = UNet3D(device=dev)
+    sd = random_state_dict(cfg, seed=0, device=dev)
+    net.load_state_dict(sd)
+    del sd
+    torch.cuda.empty_cache()
+    model = LatentDiffusionB200(net, use_scale=True, fps=10)
+    return net, model, DDIMSampler(model)
+
+
+def run_ddim(args, dev):
+    """N=1: BASELINE config[1] steps (p_sample_ddim, ddim.py:274-359)."""
+    net, model, sampler = build_engine(dev)
+    sampler.make_schedule(50, ddim_eta=1.0, verbose=False)
+    g = torch.Generator(device=dev).manual_seed(1)
+    shape = (1, 4, 16, 40, 64)
+    x0 = torch.randn(shape, device=dev, generator=g)
+    cond = {"c_crossattn": [torch.randn((1, 77, 1024), device=dev, generator=g)], "fps": 10}
+    uc = {"c_crossattn": [torch.randn((1, 77, 1024), device=dev, generator=g)], "fps": 10}
+    noise = torch.randn(shape, device=dev, generator=g)
+    total = args.warmup + args.steps
+
+    def step(i, x, nz):
+        idx = 49 - (i % 50)
+        t = [int(sampler.ddim_timesteps[idx])]
+        return sampler.p_sample_ddim(x, cond, t, index=idx, unconditional_guidance_scale=CFG_SCALE, unconditional_conditioning=uc,
+                                     noise=nz)[0]
+
+    # ---- device-resident throughput ("value")
+    # every step denoises the same resident latent (random-init weights make a 50-step chain diverge numerically; the
+    # work per step is identical either way)
+    x = x0
+    for i in range(args.warmup):
+        x = step(i, x0, noise)
+    torch.cuda.synchronize()
+    clocks = ClockSampler(torch.cuda.current_device()); clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.warmup, total):
+        x = step(i, x0, noise)
+    e1.record(); torch.cuda.synchronize()
+    clocks.stop_flag = True; clocks.join()
+    ms = e0.elapsed_time(e1) / args.steps
+    assert torch.isfinite(x).all()
+    # ---- end to end through the public API with HOST buffers: pinned x / noise in, x_prev out, every step
+    hx = x0.cpu().pin_memory(); hn = noise.cpu().pin_memory(); hy = torch.empty_like(hx).pin_memory()
+    dx = torch.empty_like(x0); dn = torch.empty_like(noise)
+    for i in range(2):
+        dx.copy_(hx, non_blocking=True); dn.copy_(hn, non_blocking=True); hy.copy_(step(i, dx, dn), non_blocking=True)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        dx.copy_(hx, non_blocking=True); dn.copy_(hn, non_blocking=True)
+        hy.copy_(step(i, dx, dn), non_blocking=True)
+        torch.cuda.synchronize()
+    e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+    launches = (net.launches() + 1) * args.steps
+    return dict(ms=ms, units_per_step=1, e2e_ms=e2e_ms, h2d=2 * x0.numel() * 4, d2h=x0.numel() * 4, launches=launches,
+                flop_per_unit=2 * FLOP_PER_FORWARD_77, clocks=clocks.summary(), executed_flops=net.flops(),
+                workload="configs[1]: VideoCrafter2 UNet (inference_t2v_512_v2.0), DDIM text-to-video step at 16x320x512 "
+                         "(latent [1,4,16,40,64]), CFG 12 as one b=2 launch (ctx 77+77), use_scale, eta 1, random-init weights",
+                net=net)
+
+
+def run_fifo(args, dev, rank, world):
+    """N>1: BASELINE config[3]/[4] — FIFO windows sharded over ranks (scripts/evaluation/funcs.py:305-371)."""
+    import types
+    import torch.distributed as dist
+    from moca_video_b200 import fifo
+    net, model, sampler = build_engine(dev)
+    sampler.make_schedule(64, ddim_eta=1.0, verbose=False)
+    fa = types.SimpleNamespace(num_inference_steps=64, lookahead_denoising=True, video_length=16, num_partitions=4, new_video_length=128)
+    g = torch.Generator(device=dev).manual_seed(1)
+    cond = {"c_crossattn": [torch.randn((1, 77, 1024), device=dev, generator=g), torch.randn((1, 77, 1024), device=dev, generator=g)], "fps": 10}
+    uc = {"c_crossattn": [torch.randn((1, 77, 1024), device=dev, generator=g)], "fps": 10}
+    z = torch.randn((1, 4, 16, 40, 64), device=dev, generator=g)
+    lat = fifo.prepare_latents(fa, None, sampler, initial_latents=z, generator=g)
+    state = {"lat": lat}
+
+    def iterate(n):
+        # fifo_ddim_sampling keeps the queue it shifts; run n iterations from the current queue
+        frames = []
+        fifo.fifo_ddim_sampling(fa, model, cond, (1, 4, 16, 40, 64), sampler, cfg_scale=CFG_SCALE, unconditional_conditioning=uc,
+                                latents=state["lat"], generator=g, num_iterations=n, on_frame=lambda i, f: frames.append(f),
+                                queue_out=state)
+        state["lat"] = state["latents"]
+        return frames
+
+    iterate(args.warmup)
+    dist.barrier(); torch.cuda.synchronize()
+    clocks = ClockSampler(torch.cuda.current_device()); clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    iterate(args.steps)
+    e1.record(); torch.cuda.synchronize(); dist.barrier()
+    clocks.stop_flag = True; clocks.join()
+    ms = e0.elapsed_time(e1) / args.steps
+    t = torch.tensor([ms], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    # e2e: same loop, popped frame read back to the host every iteration
+    t0 = time.perf_counter()
+    host = [f.cpu() for f in iterate(args.steps)]
+    torch.cuda.synchronize(); dist.barrier()
+    e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+    t = torch.tensor([e2e_ms], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    per_rank = (8 + world - 1) // world
+    return dict(ms=ms, units_per_step=8, e2e_ms=float(t.item()), h2d=0, d2h=host[0].numel() * 4,
+                launches=(net.launches() + 8) * per_rank * args.steps, flop_per_unit=FLOP_PER_FORWARD_154 + FLOP_PER_FORWARD_77,
+                clocks=clocks.summary(), executed_flops=net.flops(),
+                workload=f"configs[3]: FIFO diagonal denoising, 72-frame queue, 8 windows/iteration of [1,4,16,40,64] sharded over "
+                         f"{world} GPUs (window r on rank r mod {world}), CFG 12 (ctx 154+77), NCCL all_gather hand-off + FreeInit shift per "
+                         "iteration; 1 step = 1 window step", net=net)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 1 if args.impl == "reference" else 3)
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a B200: the product has no CPU path (use --impl reference for the CPU arm)")
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+        r = run_fifo(args, dev, rank, world)
+    else:
+        r = run_ddim(args, dev)
+    if rank != 0:
+        return
+    tf_peak, hbm_peak, peak_src = peaks()
+    value = r["units_per_step"] / (r["ms"] * 1e-3)
+    achieved = value * r["flop_per_unit"] / 1e12 / max(world, 1)           # per GPU
+    out = {"metric": "UNet denoise steps/s (16f 320x512)", "value": value, "unit": "steps/s", "n_gpus": world, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": r["ms"], "higher_is_better": True, "scaling": "weak" if world == 1 else "strong",
+           "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+           "config": {"workload": r["workload"], "l2": "per-step working set (2.83 GB packed weights + >1 GB activations) exceeds the 126 MB L2; no flush needed",
+                      "tolerance": "bf16 MMA operands, fp32 accumulate/residual/norm statistics; rel-L2 vs fp32 reference <= 2e-2 (tests/test_gpu_unet.py)"},
+           "e2e": {"value": r["units_per_step"] / (r["e2e_ms"] * 1e-3), "unit": "steps/s", "h2d_bytes_per_step": r["h2d"],
+                   "d2h_bytes_per_step": r["d2h"]},
+           "gpu_launches": r["launches"], "clocks": r["clocks"],
+           "roofline": {"bound": "tensor", "achieved": achieved, "peak": tf_peak, "unit": "TFLOP/s", "frac": achieved / tf_peak,
+                        "traffic": None, "peak_source": peak_src,
+                        "note": "whole UNet step: algorithmic 2*MAC of the reference forward (SURVEY 8d) x forwards per step / step time, per GPU; "
+                                f"executed useful FLOPs per forward {r['executed_flops'] / 1e12:.3f} T"}}
+    if world == 1 and not args.no_cpu_baseline:
+        r["net"] = None
+        torch.cuda.empty_cache()
+        out["cpu_baseline"], _ = cpu_reference_sample(2, 1)
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()

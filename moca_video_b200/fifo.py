@@ -1,0 +1,153 @@
+"""Host-side mirror of the FIFO diagonal-denoising driver (scripts/evaluation/funcs.py) for one or several GPUs.
+
+  prepare_latents      funcs.py:21-82     -> moca_renoise
+  shift_latents        funcs.py:86-99     -> moca_freeinit_filter / moca_freeinit_mix / moca_queue_shift
+  fifo_ddim_sampling   funcs.py:243-371   window loop; windows of one iteration only depend on the iteration-start
+                                          queue (funcs.py:306,351-352; scripts/evaluation/funcs_mp.py:207-221), so they
+                                          are sharded over the ranks of a torch.distributed group: window r runs on rank
+                                          r mod G, the updated half-windows are exchanged with ONE all_gather per
+                                          iteration (NCCL over NVLink), every rank then applies the same shift.
+RNG parity: every rank draws the noise of ALL windows from an identically seeded generator in the reference's order
+(window 2n-1 .. 0, one draw per frame, then the shift's tail draw) and uses its own share, so 1-GPU and G-GPU runs
+produce the same queue.  VAE decode of the popped frame and PNG writing are out of scope: popped
+latent frames are returned (or handed to ``on_frame``).
+"""
+import numpy as np
+import torch
+
+from . import ops
+from .schedule import fifo_queue_tables
+
+
+def prepare_latents(args, input_path, sampler, model=None, data=None, initial_latents=None, noise=None, generator=None):
+    """funcs.py:21-82.  ``initial_latents`` replaces the reference's torch.load(f"{input_path}/{S}.pt") when given;
+    ``noise`` [B,C,Q,H,W] replaces the per-slot randn_like draws (same order: look-ahead copies first)."""
+    if data is not None:
+        raise NotImplementedError("prepare_latents: the DAVIS branch needs the VAE encoder (out of scope, SURVEY N1)")
+    if initial_latents is None:
+        initial_latents = torch.load(f"{input_path}/{args.num_inference_steps}.pt")
+    z = initial_latents.to("cuda", dtype=torch.float32).contiguous()
+    B, C, Fz, H, W = z.shape
+    S = args.num_inference_steps
+    look = args.video_length // 2 if args.lookahead_denoising else 0
+    Q = look + S
+    if noise is None:
+        noise = torch.cat([torch.randn((B, C, 1, H, W), device=z.device, generator=generator) for _ in range(Q)], dim=2)
+    src = [0] * look + [max(0, i - (S - Fz)) for i in range(S)]
+    alpha = [float(sampler.ddim_alphas[0])] * look + [float(sampler.ddim_alphas[i]) for i in range(S)]
+    return ops.renoise(z, noise, src, alpha)
+
+
+_filter_cache = {}
+
+
+def shift_latents(latents, davis_data=None, model=None, new_noise=None, generator=None):
+    """funcs.py:86-99 (non-DAVIS branch): anchor = frame 0; queue shifts left by one; the new tail frame is
+    freq_mix_3d(anchor, N(0,1), gaussian LPF(d_s=d_t=0.25)) built for a T=1 volume."""
+    if davis_data is not None:
+        raise NotImplementedError("shift_latents: the DAVIS branch needs the VAE encoder (out of scope, SURVEY N1)")
+    B, C, Q, H, W = latents.shape
+    anchor = ops.window_gather(latents, 0, 1)
+    if new_noise is None:
+        new_noise = torch.randn((B, C, H, W), device=latents.device, generator=generator).unsqueeze(2)
+    key = (H, W, latents.device.index)
+    if key not in _filter_cache:      # the reference rebuilds the filter on the CPU every call (freeinit_utils.py:73-91)
+        _filter_cache[key] = ops.freeinit_filter((1, H, W), latents.device, "gaussian", 1, 0.25, 0.25)
+    tail = ops.freq_mix_3d(anchor, new_noise.reshape(B, C, 1, H, W), _filter_cache[key])
+    return ops.queue_shift(latents, tail)
+
+
+def window_plan(args):
+    """[(start, mid, end)] for rank = 2n-1 .. 0 in the reference's (reversed) order, funcs.py:306-310."""
+    f = args.video_length
+    n = 2 * args.num_partitions if args.lookahead_denoising else args.num_partitions
+    out = []
+    for rank in reversed(range(n)):
+        start = rank * (f // 2) if args.lookahead_denoising else rank * f
+        out.append((rank, start, start + f // 2, start + f))
+    return out
+
+
+def fifo_ddim_sampling(args, model, conditioning, noise_shape, ddim_sampler, cfg_scale=1.0, output_dir=None, latents_dir=None,
+                       save_frames=False, conditioned_image=None, targets=None, gamma=0.5, use_self_attention=False,
+                       davis_data=None, anchor_frame=None, unconditional_conditioning=None, masks=None, latents=None,
+                       generator=None, group=None, on_frame=None, num_iterations=None, queue_out=None, **kwargs):
+    """funcs.py:243-371.  Returns the list of popped latent frames [B,C,1,H,W] (one per iteration).
+
+    ``unconditional_conditioning``: the reference encodes "" with CLIP here (funcs.py:267-276); CLIP is out of scope, so
+    the embedding is an input (or ``model.get_learned_conditioning`` is used when the model has it).
+    ``masks`` [B,1,Q,H,W]: per-queue-slot masks (the reference's DAVIS masks).  ``group``: torch.distributed group to
+    shard windows over (None = the default group if initialised, else single GPU).  ``queue_out``: dict that receives the
+    final queue (``latents``, ``masks``) so a caller can continue the run."""
+    import torch.distributed as dist
+    kwargs.update({"clean_cond": True})
+    cond = conditioning
+    uc = None
+    if cfg_scale != 1.0:
+        uc = unconditional_conditioning
+        if uc is None:
+            uc_emb = model.get_learned_conditioning(noise_shape[0] * [""])
+            uc = dict(cond)
+            uc["c_crossattn"] = [uc_emb]
+    if latents is None:
+        latents = prepare_latents(args, latents_dir, ddim_sampler, model, generator=generator)
+    B, C, Q, H, W = latents.shape
+    f = args.video_length
+    half = f // 2
+    ts_q, idx_q = fifo_queue_tables(args.num_inference_steps, f, args.lookahead_denoising)
+    wins = window_plan(args)
+    world = dist.get_world_size(group) if (group is not None or (dist.is_available() and dist.is_initialized())) else 1
+    rank = dist.get_rank(group) if world > 1 else 0
+    n_iter = num_iterations if num_iterations is not None else args.new_video_length + args.num_inference_steps - f
+    popped = []
+    dev = latents.device
+    for it in range(n_iter):
+        # noise of every window in the reference's draw order (identical on all ranks)
+        noises = [torch.cat([torch.randn((B, C, 1, H, W), device=dev, generator=generator) for _ in range(f)], dim=2)
+                  for _ in wins]
+        if world == 1:
+            for (w, start, mid, end), nz in zip(wins, noises):
+                x_in = ops.window_gather(latents, start, f)
+                m_in = ops.window_gather(masks, start, f) if masks is not None else None
+                x_prev, _ = ddim_sampler.fifo_onestep(cond=cond, shape=noise_shape, latents=x_in, timesteps=ts_q[start:end],
+                                                      indices=idx_q[start:end], unconditional_guidance_scale=cfg_scale,
+                                                      unconditional_conditioning=uc, cond_image=conditioned_image,
+                                                      target=targets, gamma=gamma, use_self_attention=use_self_attention,
+                                                      davis_masks=m_in, noise=nz, **kwargs)
+                if args.lookahead_denoising:
+                    ops.window_scatter(latents, x_prev, half, mid, half)
+                else:
+                    ops.window_scatter(latents, x_prev, 0, start, f)
+        else:
+            # snapshot semantics (funcs_mp.py:207): all windows read the iteration-start queue
+            keep = half if args.lookahead_denoising else f
+            mine = [(w, start, mid, end, nz) for (w, start, mid, end), nz in zip(wins, noises) if w % world == rank]
+            per = (len(wins) + world - 1) // world
+            packed = torch.zeros((per, B, C, keep, H, W), device=dev, dtype=torch.float32)
+            for j, (w, start, mid, end, nz) in enumerate(mine):
+                x_in = ops.window_gather(latents, start, f)
+                m_in = ops.window_gather(masks, start, f) if masks is not None else None
+                x_prev, _ = ddim_sampler.fifo_onestep(cond=cond, shape=noise_shape, latents=x_in, timesteps=ts_q[start:end],
+                                                      indices=idx_q[start:end], unconditional_guidance_scale=cfg_scale,
+                                                      unconditional_conditioning=uc, cond_image=conditioned_image,
+                                                      target=targets, gamma=gamma, use_self_attention=use_self_attention,
+                                                      davis_masks=m_in, noise=nz, **kwargs)
+                packed[j] = ops.window_gather(x_prev, f - keep, keep)
+            gathered = torch.empty((world, per, B, C, keep, H, W), device=dev, dtype=torch.float32)
+            dist.all_gather_into_tensor(gathered.view(-1), packed.view(-1), group=group)   # the queue hand-off
+            for (w, start, mid, end) in wins:
+                owner = w % world
+                slot = [x[0] for x in wins if x[0] % world == owner].index(w)       # same order as `mine` on the owner
+                ops.window_scatter(latents, gathered[owner, slot], 0, mid if args.lookahead_denoising else start, keep)
+        first = half if args.lookahead_denoising else 0
+        frame = ops.window_gather(latents, first, 1)
+        if on_frame is not None:
+            on_frame(it, frame)
+        popped.append(frame)
+        tail_noise = torch.randn((B, C, H, W), device=dev, generator=generator).unsqueeze(2)
+        latents = shift_latents(latents, new_noise=tail_noise)
+        if masks is not None:
+            masks = ops.queue_shift(masks, ops.window_gather(masks, Q - 1, 1))
+    if queue_out is not None:
+        queue_out["latents"], queue_out["masks"] = latents, masks
+    return popped

@@ -1,0 +1,166 @@
+"""Host-side mirror of the reference sampler for the hot path (lvdm/models/samplers/ddim.py).
+
+``DDIMSampler`` keeps the reference's method names, argument order and return values:
+  make_schedule   ddim.py:62-106     (host tables, moca_video_b200/schedule.py)
+  unet            ddim.py:362-374    (conditional + unconditional forward)
+  fifo_onestep    ddim.py:255-271
+  ddim_step       ddim.py:377-649    (MoCA momentum correction + concept blend)  -> moca_cfg_ddim_step
+  p_sample_ddim   ddim.py:274-359                                                  -> moca_p_sample_ddim
+  sample / ddim_sampling  ddim.py:109-253
+All tensor arithmetic runs in libmoca_b200.so.  Differences from the reference, all deliberate and switchable:
+  * the two apply_model calls of classifier-free guidance are issued as ONE batched UNet launch (b=2, per-sample context
+    length) when the model exposes ``apply_model_cfg``; the guidance combine happens inside the step kernel;
+  * noise is drawn by the caller-visible ``noise_fn`` in the reference's order (one N(0,1) draw per frame, ddim.py:561),
+    never inside a kernel;
+  * masks are an input (``davis_masks`` or ``masks=``): SAM-2 / Grounding-DINO mask *generation* is third-party and out
+    of scope; debug PNG dumps are dropped;
+  * reference quirks are reproduced by default and can be turned off: ``gamma`` never reaches ddim_step (Q1),
+    the clobbered mask index (Q3).
+"""
+import numpy as np
+import torch
+
+from . import ops
+from .schedule import make_ddim_tables, reference_mask_index
+
+
+def noise_like(shape, device, generator=None):
+    """lvdm/common.py:31-34 (repeat=False)."""
+    return torch.randn(shape, device=device, generator=generator)
+
+
+class DDIMSampler:
+    def __init__(self, model, schedule="linear", use_self_attention=True, parity_quirks=True, noise_fn=None, **kwargs):
+        self.model = model
+        self.ddpm_num_timesteps = model.num_timesteps
+        self.schedule = schedule
+        self.counter = 0
+        self.use_self_attention = use_self_attention
+        self.parity_quirks = parity_quirks          # True: behave like the reference as shipped
+        self.noise_fn = noise_fn or noise_like
+        self.tables = None
+
+    # ---- schedule ---------------------------------------------------------------------------------------------
+    def make_schedule(self, ddim_num_steps, ddim_discretize="uniform", ddim_eta=0.0, verbose=True):
+        if ddim_discretize != "uniform":
+            raise NotImplementedError(ddim_discretize)
+        ac = self.model.alphas_cumprod
+        ac = ac.detach().cpu().numpy() if isinstance(ac, torch.Tensor) else np.asarray(ac)
+        sa = getattr(self.model, "scale_arr", None)
+        if isinstance(sa, torch.Tensor):
+            sa = sa.detach().cpu().numpy()
+        self.tables = make_ddim_tables(ddim_num_steps, ddim_eta, ac, sa, self.ddpm_num_timesteps)
+        t = self.tables
+        self.ddim_timesteps = t.timesteps
+        self.ddim_alphas, self.ddim_alphas_prev = t.alphas, t.alphas_prev
+        self.ddim_sigmas, self.ddim_sqrt_one_minus_alphas = t.sigmas, t.sqrt_one_minus_alphas
+        self.use_scale = bool(getattr(self.model, "use_scale", False))
+        if self.use_scale:
+            self.ddim_scale_arr, self.ddim_scale_arr_prev = t.scale, t.scale_prev
+
+    # ---- UNet with classifier-free guidance -------------------------------------------------------------------
+    def _eps_pair(self, x, c, t, unconditional_guidance_scale, unconditional_conditioning, **kwargs):
+        """Returns (e_cond, e_uncond or None): the two apply_model calls of ddim.py:368-370 / :298-299."""
+        if unconditional_conditioning is None or unconditional_guidance_scale == 1.0:
+            return self.model.apply_model(x, t, c, **kwargs), None
+        if hasattr(self.model, "apply_model_cfg"):
+            return self.model.apply_model_cfg(x, t, c, unconditional_conditioning, **kwargs)
+        return self.model.apply_model(x, t, c, **kwargs), self.model.apply_model(x, t, unconditional_conditioning, **kwargs)
+
+    @torch.no_grad()
+    def unet(self, x, c, t, unconditional_guidance_scale=1.0, unconditional_conditioning=None, **kwargs):
+        e_c, e_u = self._eps_pair(x, c, t, unconditional_guidance_scale, unconditional_conditioning, **kwargs)
+        if e_u is None:
+            return e_c
+        return torch.add(e_u, e_c - e_u, alpha=float(unconditional_guidance_scale))       # ddim.py:372 (API parity only;
+        # the hot path below never calls this: the combine is fused into the step kernel)
+
+    # ---- FIFO step --------------------------------------------------------------------------------------------
+    @torch.no_grad()
+    def fifo_onestep(self, cond, shape, latents=None, timesteps=None, indices=None, unconditional_guidance_scale=1.0,
+                     unconditional_conditioning=None, cond_image=None, target=None, use_self_attention=False,
+                     davis_masks=None, noise=None, **kwargs):
+        """ddim.py:255-271.  ``gamma`` in kwargs is swallowed exactly like the reference does (it lands in the UNet's
+        **kwargs) unless parity_quirks is off, in which case it is routed to ddim_step."""
+        ts = [int(v) for v in np.asarray(timesteps).tolist()]
+        gamma = 0.5
+        if not self.parity_quirks and "gamma" in kwargs:
+            gamma = float(kwargs["gamma"])
+        kw = {k: v for k, v in kwargs.items() if k not in ("gamma", "clean_cond")}
+        e_c, e_u = self._eps_pair(latents, cond, ts, unconditional_guidance_scale, unconditional_conditioning, **kw)
+        return self._step(latents, e_c, e_u, unconditional_guidance_scale, indices, cond_image, ts, gamma, davis_masks, noise)
+
+    @torch.no_grad()
+    def ddim_step(self, sample, noise_pred, indices, cond_image, target, ts, gamma=0.5, use_self_attention=False,
+                  davis_masks=None, noise=None):
+        """ddim.py:377-649 on an already guidance-combined ``noise_pred``."""
+        ts = [int(v) for v in (ts.tolist() if isinstance(ts, torch.Tensor) else np.asarray(ts).tolist())]
+        return self._step(sample, noise_pred, None, 1.0, indices, cond_image, ts, gamma, davis_masks, noise)
+
+    def _step(self, x, e_c, e_u, cfg, indices, cond_image, ts, gamma, masks, noise):
+        B, C, F, H, W = x.shape
+        if noise is None:
+            # one draw per frame in frame order, like `noise_like(pred_x0.shape)` inside the frame loop (ddim.py:561)
+            noise = torch.cat([self.noise_fn((B, C, 1, H, W), x.device) for _ in range(F)], dim=2)
+        coef = self.tables.coef(indices)
+        mask_idx = None
+        if masks is not None:
+            Fm = masks.shape[2]
+            mask_idx = reference_mask_index(F, H) if self.parity_quirks else list(range(F))
+            mask_idx = [j if j < Fm else -1 for j in mask_idx]          # `davis_masks.shape[2] > i` guard (ddim.py:565)
+            if cond_image is not None and cond_image.shape[1] == 3:      # RGB -> RGBA with ones (ddim.py:574-577)
+                cond_image = torch.cat([cond_image, torch.ones_like(cond_image[:, :1])], dim=1)
+        return ops.cfg_ddim_step(x, e_c, e_u, noise, cfg, coef, ts, masks, mask_idx, cond_image if masks is not None else None,
+                                 gamma, 1.5, 1.0, 300, 2.0)
+
+    # ---- plain DDIM -------------------------------------------------------------------------------------------
+    @torch.no_grad()
+    def p_sample_ddim(self, x, c, t, index, repeat_noise=False, use_original_steps=False, quantize_denoised=False,
+                      temperature=1.0, noise_dropout=0.0, score_corrector=None, corrector_kwargs=None,
+                      unconditional_guidance_scale=1.0, unconditional_conditioning=None, uc_type=None,
+                      conditional_guidance_scale_temporal=None, noise=None, **kwargs):
+        if use_original_steps or quantize_denoised or score_corrector is not None or uc_type is not None \
+                or conditional_guidance_scale_temporal is not None or noise_dropout > 0.0 or repeat_noise:
+            raise NotImplementedError("p_sample_ddim: only the option set used by the driver is implemented")
+        ts = [int(v) for v in (t.tolist() if isinstance(t, torch.Tensor) else np.asarray(t).reshape(-1).tolist())]
+        e_c, e_u = self._eps_pair(x, c, ts, unconditional_guidance_scale, unconditional_conditioning, **kwargs)
+        if noise is None:
+            noise = self.noise_fn(tuple(x.shape), x.device)
+        if temperature != 1.0:
+            noise = noise * temperature
+        T = self.tables
+        i = int(index)
+        return ops.p_sample_ddim(x, e_c, e_u, noise, unconditional_guidance_scale, T.alphas[i], T.alphas_prev[i], T.sigmas[i],
+                                 T.sqrt_one_minus_alphas[i], T.scale[i] if self.use_scale else None,
+                                 T.scale_prev[i] if self.use_scale else None)
+
+    @torch.no_grad()
+    def ddim_sampling(self, cond, shape, x_T=None, timesteps=None, unconditional_guidance_scale=1.0,
+                      unconditional_conditioning=None, verbose=False, latents_dir=None, generator=None, **kwargs):
+        """ddim.py:183-253 (the latent cache files 0.pt / {S}.pt keep the reference's torch.save format)."""
+        device = self.model.device
+        b = shape[0]
+        img = torch.randn(shape, device=device, generator=generator) if x_T is None else x_T
+        steps = self.ddim_timesteps if timesteps is None else self.ddim_timesteps[:int(timesteps)]
+        total = steps.shape[0]
+        intermediates = {"x_inter": [img], "pred_x0": [img]}
+        for i, step in enumerate(np.flip(steps)):
+            if i == 0 and latents_dir is not None:
+                torch.save(img, f"{latents_dir}/{i}.pt")
+            index = total - i - 1
+            img, pred_x0 = self.p_sample_ddim(img, cond, [int(step)] * b, index=index,
+                                              unconditional_guidance_scale=unconditional_guidance_scale,
+                                              unconditional_conditioning=unconditional_conditioning, **kwargs)
+        if latents_dir is not None:
+            torch.save(img, f"{latents_dir}/{total}.pt")
+        return img, intermediates
+
+    @torch.no_grad()
+    def sample(self, S, batch_size, shape, conditioning=None, eta=0.0, x_T=None, unconditional_guidance_scale=1.0,
+               unconditional_conditioning=None, verbose=False, schedule_verbose=False, latents_dir=None, **kwargs):
+        """ddim.py:109-181."""
+        self.make_schedule(ddim_num_steps=S, ddim_eta=eta, verbose=schedule_verbose)
+        size = (batch_size, *shape) if len(shape) == 4 else (batch_size, *shape)
+        return self.ddim_sampling(conditioning, size, x_T=x_T, unconditional_guidance_scale=unconditional_guidance_scale,
+                                  unconditional_conditioning=unconditional_conditioning, verbose=verbose,
+                                  latents_dir=latents_dir, **kwargs)
