@@ -217,6 +217,39 @@ def gen_unet_small():
     np.savez_compressed(os.path.join(GOLD, "unet_small.npz"), **out)
 
 
+SMALL64 = dict(in_channels=4, out_channels=4, model_channels=64, attention_resolutions=(4, 2, 1), num_res_blocks=2,
+               channel_mult=(1, 2, 4, 4), num_head_channels=64, context_dim=64)
+
+
+def gen_unet_small64():
+    """Reference UNetModel with head dim 64 (the width the CUDA attention kernels are built for), shrunk to
+    model_channels 64: the fixture the GPU parity test compares the CUDA path with on the box (no reference there)."""
+    from moca_video_b200.arch import UNetConfig, param_shapes, random_state_dict
+    from oracle.unet_ref import unet_forward
+    cfg = UNetConfig(**SMALL64)
+    p = refimport.unet_params()
+    p.update(model_channels=64, num_head_channels=64, context_dim=64)
+    net = refimport.build_unet(p, rerandomize=False)
+    ref_shapes = {k: tuple(v.shape) for k, v in net.state_dict().items()}
+    assert ref_shapes == {k: tuple(v) for k, v in param_shapes(cfg).items()}
+    sd = random_state_dict(cfg, seed=0)
+    net.load_state_dict(sd, strict=True)
+    rng = np.random.default_rng(23)
+    out = {}
+    for tag, (b, t, h, w, L, fifo) in {"fifo": (1, 16, 8, 16, 11, True), "plain": (2, 4, 16, 8, 7, False)}.items():
+        x = torch.from_numpy(rng.standard_normal((b, 4, t, h, w)).astype(np.float32))
+        ctx = torch.from_numpy(rng.standard_normal((b, L, 64)).astype(np.float32))
+        ts = torch.from_numpy(rng.integers(0, 1000, size=(t if fifo else b,))).long()
+        with torch.no_grad():
+            y_ref = net(x, ts, context=ctx, fps=10)
+        y = unet_forward(sd, cfg, x, ts, ctx, fps=10)
+        err = float((y - y_ref).norm() / y_ref.norm())
+        print(f"unet_small64[{tag}] restatement vs reference rel-L2 = {err:.3e}, |y| = {float(y_ref.abs().mean()):.3f}")
+        assert err < 1e-5
+        out.update({f"{tag}_x": _np(x), f"{tag}_ctx": _np(ctx), f"{tag}_ts": _np(ts), f"{tag}_y": _np(y_ref)})
+    np.savez_compressed(os.path.join(GOLD, "unet_small64.npz"), **out)
+
+
 def gen_unet_full():
     """Full-size architecture: key/shape listing equality + one forward (slow, ~2 min)."""
     from moca_video_b200.arch import UNetConfig, param_shapes, random_state_dict
@@ -258,7 +291,7 @@ def gen_unet_full():
 
 if __name__ == "__main__":
     os.makedirs(GOLD, exist_ok=True)
-    which = sys.argv[1:] or ["tables", "ddim_step", "p_sample", "queue", "unet_small", "unet_full"]
+    which = sys.argv[1:] or ["tables", "ddim_step", "p_sample", "queue", "unet_small", "unet_small64", "unet_full"]
     for w in which:
         print("==", w)
         globals()["gen_" + w]()

@@ -1,0 +1,144 @@
+"""GPU parity of the UNet primitives (through the C-ABI) against plain PyTorch fp32 on the same bf16-rounded operands.
+
+Tolerances (rel-L2): fp32-output GEMM/conv vs fp32 matmul of the bf16-rounded operands <= 2e-5 (accumulation order
+only); anything whose OUTPUT is bf16 <= 4e-3 (one bf16 rounding = 2^-9 relative, measured 1.7e-3..2.3e-3); the
+north_star bar for the bf16 path end to end is 2e-2 (tests/test_gpu_unet.py).
+"""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda"
+
+
+def rel(a, b):
+    a = a.float(); b = b.float()
+    return float((a - b).norm() / (b.norm() + 1e-30))
+
+
+@pytest.fixture(autouse=True)
+def _no_tf32():
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+
+
+GEMM_SHAPES = [(128, 128, 64), (1, 16, 64), (127, 144, 192), (256, 256, 128), (1000, 320, 320), (77, 2560, 1024),
+               (16, 1280, 320), (2560, 3840, 1280), (40960, 320, 320), (3000, 640, 1920), (5000, 4, 320), (300, 160, 64),
+               (20480, 960, 320)]
+
+
+@pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
+def test_gemm_tcgen05(M, N, K):
+    from moca_video_b200 import ops
+    g = torch.Generator(device=DEV).manual_seed(M + N + K)
+    a = torch.randn(M, K, device=DEV, generator=g).bfloat16()
+    w = (torch.randn(N, K, device=DEV, generator=g) / K ** 0.5).bfloat16()
+    b = torch.randn(N, device=DEV, generator=g)
+    ref = a.float() @ w.float().t()
+    assert rel(ops.gemm_bf16(a, w, b, False), ref + b) < 2e-5
+    assert rel(ops.gemm_bf16(a, w, None, False), ref) < 2e-5
+    assert rel(ops.gemm_bf16(a, w, b, True), ref + b) < 4e-3
+
+
+def test_gemm_rejects_bad_k():
+    from moca_video_b200 import MocaError, ops
+    a = torch.zeros(8, 40, device=DEV).bfloat16()
+    with pytest.raises(MocaError):
+        ops.gemm_bf16(a, a, None, False)
+
+
+@pytest.mark.parametrize("M,N,K", [(3000, 2560, 320), (130, 512, 64), (640, 10240, 1280)])
+def test_geglu_epilogue(M, N, K):
+    from moca_video_b200 import ops
+    g = torch.Generator(device=DEV).manual_seed(5)
+    a = torch.randn(M, K, device=DEV, generator=g).bfloat16()
+    w = torch.randn(N, K, device=DEV, generator=g) / K ** 0.5
+    b = torch.randn(N, device=DEV, generator=g)
+    h = a.float() @ w.bfloat16().float().t() + b
+    v, gate = h.chunk(2, dim=-1)
+    assert rel(ops.geglu(a, w, b), v * F.gelu(gate)) < 4e-3
+
+
+CONV_CASES = [(2, 8, 8, 64, 64, 1), (3, 10, 16, 64, 128, 1), (16, 40, 64, 320, 320, 1), (4, 20, 32, 960, 640, 1), (2, 5, 8, 1280, 1280, 1),
+              (4, 40, 64, 320, 320, 2), (2, 10, 16, 1280, 1280, 2), (16, 10, 16, 64, 4, 1), (2, 8, 8, 8, 64, 1), (1, 2, 2, 64, 64, 1)]
+
+
+@pytest.mark.parametrize("NF,H,W,Ci,Co,s", CONV_CASES)
+def test_conv3x3_implicit_gemm(NF, H, W, Ci, Co, s):
+    from moca_video_b200 import ops
+    g = torch.Generator(device=DEV).manual_seed(NF * H + Ci)
+    x = torch.randn(NF, H, W, Ci, device=DEV, generator=g)
+    w = torch.randn(Co, Ci, 3, 3, device=DEV, generator=g) / (9 * Ci) ** 0.5
+    b = torch.randn(Co, device=DEV, generator=g)
+    ref = F.conv2d(x.bfloat16().float().permute(0, 3, 1, 2), w.bfloat16().float(), b, stride=s, padding=1).permute(0, 2, 3, 1)
+    assert rel(ops.conv3x3_nhwc(x, w, b, s), ref) < 2e-5
+
+
+@pytest.mark.parametrize("B,T,HW,C", [(1, 16, 40, 64), (2, 4, 100, 128), (1, 16, 2560, 320), (2, 16, 160, 1280), (1, 1, 40, 64)])
+def test_temporal_conv_implicit_gemm(B, T, HW, C):
+    from moca_video_b200 import ops
+    g = torch.Generator(device=DEV).manual_seed(B * T + C)
+    x = torch.randn(B, T, HW, C, device=DEV, generator=g)
+    w = torch.randn(C, C, 3, 1, 1, device=DEV, generator=g) / (3 * C) ** 0.5
+    b = torch.randn(C, device=DEV, generator=g)
+    x5 = x.bfloat16().float().permute(0, 3, 1, 2).reshape(B, C, T, HW, 1)
+    ref = F.conv3d(x5, w.bfloat16().float(), b, padding=(1, 0, 0)).reshape(B, C, T, HW).permute(0, 2, 3, 1)
+    assert rel(ops.tconv_tokens(x, w, b), ref) < 2e-5
+
+
+@pytest.mark.parametrize("NF,HW,C,span,eps,silu", [(16, 2560, 320, 1, 1e-5, 1), (16, 160, 1280, 16, 1e-6, 0), (4, 640, 960, 1, 1e-5, 1),
+                                                   (2, 40, 2560, 2, 1e-5, 1), (8, 64, 64, 1, 1e-5, 1), (4, 40, 1920, 1, 1e-5, 1)])
+def test_groupnorm(NF, HW, C, span, eps, silu):
+    from moca_video_b200 import ops
+    g = torch.Generator(device=DEV).manual_seed(C)
+    x = torch.randn(NF * HW, C, device=DEV, generator=g) * 2 + 0.5
+    ga = torch.randn(C, device=DEV, generator=g); be = torch.randn(C, device=DEV, generator=g)
+    y = ops.groupnorm_bf16(x, ga, be, HW * span, eps, silu)
+    ref = F.group_norm(x.reshape(NF // span, span * HW, C).permute(0, 2, 1), 32, ga, be, eps)
+    ref = (F.silu(ref) if silu else ref).permute(0, 2, 1).reshape(NF * HW, C)
+    assert rel(y, ref) < 4e-3
+
+
+@pytest.mark.parametrize("rows,C", [(1000, 320), (333, 1280), (64, 64), (4096, 640), (100, 512), (1, 320)])
+def test_layernorm(rows, C):
+    from moca_video_b200 import ops
+    g = torch.Generator(device=DEV).manual_seed(rows)
+    x = torch.randn(rows, C, device=DEV, generator=g) * 3 + 1
+    ga = torch.randn(C, device=DEV, generator=g); be = torch.randn(C, device=DEV, generator=g)
+    assert rel(ops.layernorm_bf16(x, ga, be), F.layer_norm(x, (C,), ga, be, 1e-5)) < 4e-3
+
+
+def _ref_attn(q, k, v, batch, heads, Lq, Lk, Lv):
+    q = q.float().reshape(batch, Lq, heads, 64).permute(0, 2, 1, 3)
+    k = k.float().reshape(batch, Lk, heads, 64).permute(0, 2, 1, 3)[:, :, :Lv]
+    v = v.float().reshape(batch, Lk, heads, 64).permute(0, 2, 1, 3)[:, :, :Lv]
+    s = (q @ k.transpose(-1, -2)) * 0.125
+    return (s.softmax(-1) @ v).permute(0, 2, 1, 3).reshape(batch * Lq, heads * 64)
+
+
+@pytest.mark.parametrize("batch,heads,Lq,Lk,Lv", [(2, 1, 64, 64, 64), (3, 5, 40, 40, 40), (2, 20, 160, 160, 160), (4, 10, 640, 640, 640),
+                                                  (2, 5, 2560, 2560, 2560), (4, 5, 640, 154, 77), (2, 20, 40, 77, 77), (2, 5, 100, 154, 154),
+                                                  (1, 1, 1, 1, 1), (2, 2, 65, 129, 128)])
+def test_attention_flash(batch, heads, Lq, Lk, Lv):
+    from moca_video_b200 import ops
+    g = torch.Generator(device=DEV).manual_seed(Lq + Lk)
+    q = torch.randn(batch * Lq, heads * 64, device=DEV, generator=g).bfloat16()
+    k = torch.randn(batch * Lk, heads * 64, device=DEV, generator=g).bfloat16()
+    v = torch.randn(batch * Lk, heads * 64, device=DEV, generator=g).bfloat16()
+    assert rel(ops.attention_bf16(q, k, v, batch, heads, Lq, Lk, Lv), _ref_attn(q, k, v, batch, heads, Lq, Lk, Lv)) < 5e-3
+
+
+@pytest.mark.parametrize("B,T,HW,heads", [(1, 16, 40, 5), (2, 16, 160, 20), (1, 4, 64, 1), (1, 16, 2560, 5), (1, 1, 7, 2)])
+def test_attention_temporal(B, T, HW, heads):
+    """Sequences are the T frames of one spatial position, addressed in place with a row stride of HW."""
+    from moca_video_b200 import ops
+    C = heads * 64
+    g = torch.Generator(device=DEV).manual_seed(T * HW)
+    qkv = torch.randn(B * T * HW, 3 * C, device=DEV, generator=g).bfloat16()
+    q, k, v = qkv[:, :C], qkv[:, C:2 * C], qkv[:, 2 * C:]
+    y = ops.attention_bf16(q, k, v, B * HW, heads, T, T, T, temporal_inner=HW)
+    perm = lambda t: t.float().reshape(B, T, HW, C).permute(0, 2, 1, 3).reshape(B * HW * T, C)
+    r = _ref_attn(perm(q), perm(k), perm(v), B * HW, heads, T, T, T).reshape(B, HW, T, C).permute(0, 2, 1, 3).reshape(B * T * HW, C)
+    assert rel(y, r) < 5e-3

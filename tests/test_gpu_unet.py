@@ -1,0 +1,190 @@
+"""GPU parity of the UNet forward and of one whole sampler step, through the public API (-> C-ABI).
+
+Bars (north_star): bf16 path rel-L2 <= 2e-2 against the fp32 reference.  References used here:
+  * tests/golden/unet_small64.npz — output of the UNMODIFIED reference UNetModel (generated in the authoring container);
+  * oracle/unet_ref.py in fp32 on the GPU (TF32 off) at the full inference_t2v_512_v2.0 size.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+TOL = 2e-2
+
+
+def rel(a, b):
+    a = a.float(); b = b.float()
+    return float((a - b).norm() / (b.norm() + 1e-30))
+
+
+@pytest.fixture(autouse=True)
+def _no_tf32():
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+
+
+@pytest.fixture(scope="module")
+def small():
+    from moca_video_b200.arch import UNetConfig, random_state_dict
+    from moca_video_b200.unet import UNet3D
+    cfg = UNetConfig(model_channels=64, context_dim=64)
+    sd = random_state_dict(cfg, seed=0, device=DEV)
+    net = UNet3D(model_channels=64, context_dim=64, device=DEV).load_state_dict(sd)
+    return cfg, sd, net
+
+
+@pytest.fixture(scope="module")
+def full():
+    from moca_video_b200.arch import UNetConfig, random_state_dict
+    from moca_video_b200.unet import UNet3D
+    cfg = UNetConfig.videocrafter2()
+    sd = random_state_dict(cfg, seed=0, device=DEV)
+    net = UNet3D(device=DEV).load_state_dict(sd)
+    return cfg, sd, net
+
+
+@pytest.mark.parametrize("tag", ["fifo", "plain"])
+def test_unet_small_vs_reference_golden(small, tag):
+    """Same seeded weights (arch.random_state_dict is device independent per tensor name? no: CPU and CUDA generators differ),
+    so the golden stores inputs/outputs for CPU-drawn weights; the weights are re-drawn on the CPU here."""
+    from moca_video_b200.arch import random_state_dict
+    from moca_video_b200.unet import UNet3D
+    cfg = small[0]
+    sd = random_state_dict(cfg, seed=0, device="cpu")
+    net = UNet3D(model_channels=64, context_dim=64, device=DEV).load_state_dict(sd)
+    g = np.load(os.path.join(GOLDEN, "unet_small64.npz"))
+    x, ctx, ts, y_ref = (torch.from_numpy(g[f"{tag}_{k}"]) for k in ("x", "ctx", "ts", "y"))
+    y = net(x.to(DEV), ts, ctx.to(DEV), fps=10)
+    assert rel(y.cpu(), y_ref) < TOL
+
+
+def test_unet_small_taps_vs_oracle(small):
+    """Layer-by-layer parity (channels-last token matrices after every ResBlock / transformer / resample)."""
+    from oracle.unet_ref import unet_forward
+    cfg, sd, net = small
+    g = torch.Generator(device=DEV).manual_seed(5)
+    x = torch.randn(1, 4, 16, 8, 8, device=DEV, generator=g)
+    ctx = torch.randn(1, 11, 64, device=DEV, generator=g)
+    ts = torch.randint(0, 1000, (16,), device=DEV, generator=g)
+    rt = {}
+    y_ref = unet_forward(sd, cfg, x, ts, ctx, fps=10, taps=rt)
+    net.set_taps(True)
+    y = net(x, ts, ctx, fps=10)
+    taps = net.taps()
+    net.set_taps(False)
+    assert len(taps) >= 50 and set(taps) <= set(rt)
+    for k, v in taps.items():
+        assert rel(v, rt[k]) < TOL, k
+    assert rel(y, y_ref) < TOL
+    y2 = net(x, ts, ctx, fps=10)            # CUDA-graph replay path gives the same numbers as the eager tap path
+    assert rel(y2, y) < 1e-6
+
+
+def test_unet_full_vs_oracle_fp32(full):
+    """inference_t2v_512_v2.0 architecture at [1,4,16,40,64], ctx 77, FIFO per-frame timesteps (BASELINE config 1/3)."""
+    from oracle.unet_ref import unet_forward
+    cfg, sd, net = full
+    g = torch.Generator(device=DEV).manual_seed(7)
+    x = torch.randn(1, 4, 16, 40, 64, device=DEV, generator=g)
+    ctx = torch.randn(1, 77, 1024, device=DEV, generator=g)
+    ts_q = np.concatenate([np.zeros(8, np.int64), np.round(np.linspace(0, 999, 64)).astype(np.int64)])
+    ts = torch.from_numpy(ts_q[24:40]).to(DEV)
+    y_ref = unet_forward(sd, cfg, x, ts, ctx, fps=10)
+    y = net(x, ts, ctx, fps=10)
+    assert torch.isfinite(y).all()
+    assert rel(y, y_ref) < TOL
+    assert net.launches() > 0 and net.flops() > 1.2e13
+
+
+def test_unet_full_cfg_batch_equals_separate_forwards(full):
+    """The b=2 classifier-free-guidance launch with per-sample context length (154 vs 77) must give what two
+    separate b=1 forwards give: padding tokens are never seen by the softmax."""
+    cfg, sd, net = full
+    g = torch.Generator(device=DEV).manual_seed(9)
+    x = torch.randn(1, 4, 16, 40, 64, device=DEV, generator=g)
+    c = torch.randn(1, 154, 1024, device=DEV, generator=g)
+    u = torch.randn(1, 77, 1024, device=DEV, generator=g)
+    ts = list(range(100, 900, 50))
+    e_c = net(x, ts, c, fps=10)
+    e_u = net(x, ts, u, fps=10)
+    ctx = torch.zeros(2, 154, 1024, device=DEV)
+    ctx[0] = c[0]; ctx[1, :77] = u[0]; ctx[1, 77:] = 1e4          # poison the padding
+    e2 = net(torch.cat([x, x]), ts + ts, ctx, fps=10, ctx_len=[154, 77])
+    assert rel(e2[0:1], e_c) < 2e-3 and rel(e2[1:2], e_u) < 2e-3     # same kernels, different tile schedule / atomics order
+
+
+def test_fifo_onestep_vs_oracle(small):
+    """DDIMSampler.fifo_onestep (ddim.py:255-271): batched CFG forward + fused MoCA step, against oracle UNet + numpy step."""
+    from moca_video_b200.model import LatentDiffusionB200
+    from moca_video_b200.sampler import DDIMSampler
+    from moca_video_b200.schedule import fifo_queue_tables
+    from oracle import step_ref as R
+    from oracle.unet_ref import unet_forward
+    cfg, sd, net = small
+    sampler = DDIMSampler(LatentDiffusionB200(net, fps=10))
+    sampler.make_schedule(64, ddim_eta=1.0, verbose=False)
+    g = torch.Generator(device=DEV).manual_seed(3)
+    shape = (1, 4, 16, 8, 16)
+    x = torch.randn(shape, device=DEV, generator=g)
+    c = torch.randn((1, 22, 64), device=DEV, generator=g); u = torch.randn((1, 11, 64), device=DEV, generator=g)
+    noise = torch.randn(shape, device=DEV, generator=g)
+    mask = (torch.rand((1, 1, 16, 8, 16), device=DEV, generator=g) < 0.3).float()
+    cimg = torch.rand((1, 4, 1, 8, 16), device=DEV, generator=g)
+    ts_q, idx_q = fifo_queue_tables(64, 16, True)
+    for win in (0, 3, 7):
+        t, idx = ts_q[8 * win:8 * win + 16], idx_q[8 * win:8 * win + 16]
+        xp, p0 = sampler.fifo_onestep(cond={"c_crossattn": [c], "fps": 10}, shape=shape, latents=x, timesteps=t, indices=idx,
+                                      unconditional_guidance_scale=12.0, unconditional_conditioning={"c_crossattn": [u], "fps": 10},
+                                      cond_image=cimg, target="cat", gamma=0.9, davis_masks=mask, noise=noise, clean_cond=True)
+        tt = torch.from_numpy(np.asarray(t)).to(DEV)
+        e = R.cfg_combine(unet_forward(sd, cfg, x, tt, c, fps=10).cpu().numpy(), unet_forward(sd, cfg, x, tt, u, fps=10).cpu().numpy(), 12.0)
+        xo, po = R.moca_ddim_step(x.cpu().numpy(), e, noise.cpu().numpy(), R.coef_rows(R.make_tables(64, 1.0), idx), t,
+                                  mask.cpu().numpy(), R.parity_mask_index(16, 8), cimg.cpu().numpy(), 0.5)
+        assert rel(xp.cpu(), torch.from_numpy(xo)) < TOL and rel(p0.cpu(), torch.from_numpy(po)) < TOL
+
+
+def test_fifo_iterations_vs_oracle(small):
+    """Two FIFO iterations (8 windows each + FreeInit shift) against oracle.fifo_iteration / shift_latents driven by the
+    oracle UNet; identical pre-drawn noise (funcs.py:305-371)."""
+    import types
+    from moca_video_b200 import fifo
+    from moca_video_b200.model import LatentDiffusionB200
+    from moca_video_b200.sampler import DDIMSampler
+    from oracle import step_ref as R
+    from oracle.unet_ref import unet_forward
+    cfg, sd, net = small
+    sampler = DDIMSampler(LatentDiffusionB200(net, fps=10))
+    sampler.make_schedule(64, ddim_eta=1.0, verbose=False)
+    fa = types.SimpleNamespace(num_inference_steps=64, lookahead_denoising=True, video_length=16, num_partitions=4, new_video_length=4)
+    g = torch.Generator(device=DEV).manual_seed(11)
+    H, W = 8, 8
+    z = torch.randn(1, 4, 16, H, W, device=DEV, generator=g)
+    c = torch.randn((1, 9, 64), device=DEV, generator=g); u = torch.randn((1, 9, 64), device=DEV, generator=g)
+    lat0 = fifo.prepare_latents(fa, None, sampler, initial_latents=z, generator=g)
+    # replay: the product draws 8 windows x 16 frames, then the tail, per iteration from `gen`
+    gen = torch.Generator(device=DEV).manual_seed(12)
+    out = {}
+    frames = fifo.fifo_ddim_sampling(fa, sampler.model, {"c_crossattn": [c], "fps": 10}, (1, 4, 16, H, W), sampler, cfg_scale=7.5,
+                                     unconditional_conditioning={"c_crossattn": [u], "fps": 10}, latents=lat0.clone(), generator=gen,
+                                     num_iterations=2, queue_out=out)
+    gen = torch.Generator(device=DEV).manual_seed(12)
+    tables = R.make_tables(64, 1.0)
+
+    def eps_fn(win, t):
+        xw = torch.from_numpy(win).to(DEV); tt = torch.from_numpy(np.asarray(t)).to(DEV)
+        return unet_forward(sd, cfg, xw, tt, c, fps=10).cpu().numpy(), unet_forward(sd, cfg, xw, tt, u, fps=10).cpu().numpy()
+
+    lat = lat0.cpu().numpy()
+    for it in range(2):
+        draws = [torch.cat([torch.randn((1, 4, 1, H, W), device=DEV, generator=gen) for _ in range(16)], dim=2).cpu().numpy() for _ in range(8)]
+        noise = np.stack(draws[::-1])          # draws are in window order 7..0; oracle indexes by rank
+        lat = R.fifo_iteration(lat, eps_fn, noise, tables, 7.5)
+        assert rel(frames[it].cpu(), torch.from_numpy(lat[:, :, 8:9])) < TOL
+        tail = torch.randn((1, 4, H, W), device=DEV, generator=gen).cpu().numpy()
+        lat = R.shift_latents(lat, tail)
+    assert rel(out["latents"].cpu(), torch.from_numpy(lat)) < TOL
