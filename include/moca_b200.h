@@ -141,6 +141,8 @@ double moca_unet_flops(moca_unet* net);
 int32_t moca_unet_param_count(moca_unet* net);
 int32_t moca_unet_param_info(moca_unet* net, int32_t i, char* name, int32_t name_cap, int64_t* numel);
 int64_t moca_unet_workspace_bytes(moca_unet* net);
+/* Per-op device timing of the last planned forward (CSV "idx,us,gflop,label" into buf; returns bytes needed). */
+int64_t moca_unet_profile(moca_unet* net, int32_t iters, char* buf, int64_t cap, void* stream);
 int64_t moca_unet_weight_bytes(moca_unet* net);
 
 /* ---- primitives exposed for unit parity tests (tests/test_gpu_ops.py): the same kernels the UNet plan launches ----

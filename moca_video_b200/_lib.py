@@ -41,6 +41,7 @@ SIGNATURES = {
     "moca_unet_param_count": (i32, [vp]),
     "moca_unet_param_info": (i32, [vp, i32, cp, i32, pi64]),
     "moca_unet_workspace_bytes": (i64, [vp]),
+    "moca_unet_profile": (i64, [vp, i32, cp, i64, vp]),
     "moca_unet_weight_bytes": (i64, [vp]),
     "moca_gemm_bf16": (i32, [vp, vp, vp, vp, i32, i32, i32, vp, i32, vp]),
     "moca_geglu_f32": (i32, [vp, vp, vp, vp, i32, i32, i32, vp, vp]),

@@ -93,8 +93,9 @@ int gn_stats(const float* x1, int C1, const float* x2, int C2, int64_t rows, int
                  "gn_stats: unsupported channels C1=%d C2=%d groups=%d", C1, C2, groups);
     MOCA_REQUIRE(rows % rows_per_stat == 0, MOCA_E_SHAPE, "gn_stats: rows %lld not a multiple of %d", (long long)rows, rows_per_stat);
     const int nstat = (int)(rows / rows_per_stat);
-    int chunk = 64;
-    while (chunk > 8 && (int64_t)cdiv(rows_per_stat, chunk) * nstat < 296) chunk >>= 1;
+    // fixed chunk: the fp32 partial sums (and so the statistics, bit for bit up to the order of the fp64 atomics) do not
+    // depend on how many frames are batched — a b=2 CFG launch reproduces two b=1 launches
+    const int chunk = 32;
     dim3 grid(cdiv(rows_per_stat, chunk), nstat);
     gn_stats_kernel<<<grid, kStatThreads, 0, st>>>(x1, C1, x2, C2, rows_per_stat, chunk, C / 32, acc);
     MOCA_LAUNCH_CHECK();

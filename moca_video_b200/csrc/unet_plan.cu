@@ -21,6 +21,8 @@ struct Tap {
 struct Plan {
     int B = 0, T = 0, H = 0, W = 0, Lmax = 0;
     std::vector<Op> ops;
+    std::vector<std::string> labels;      // one per op (profiling: moca_unet_profile)
+    std::vector<double> op_flops;
     int launches = 0;
     double flops = 0;
     std::vector<void*> allocs;
@@ -58,8 +60,14 @@ struct Builder {
     void* sptr[S_COUNT] = {nullptr};
     int stat_slots = 0;
     int B, T, H0, W0, NF, Lmax;
+    std::string scope;
 
     void fail(int code) { if (rc == MOCA_OK) rc = code; }
+    void raw_push(Op op, const std::string& label, double flops) {
+        plan->ops.push_back(std::move(op));
+        plan->labels.push_back(scope + " " + label);
+        plan->op_flops.push_back(flops);
+    }
 
     void* palloc(size_t bytes) {
         if (dry) { plan->workspace_bytes += bytes; return nullptr; }
@@ -74,9 +82,9 @@ struct Builder {
         if (dry) { if (bytes > need[id]) need[id] = bytes; return nullptr; }
         return (Tp*)sptr[id];
     }
-    void push(Op op, int nlaunch = 1) {
+    void push(Op op, int nlaunch = 1, const std::string& label = "op", double flops = 0) {
         plan->launches += nlaunch;
-        if (!dry) plan->ops.push_back(std::move(op));
+        if (!dry) raw_push(std::move(op), label, flops);
     }
     double* stat_slot() {
         const int s = stat_slots++;
@@ -91,7 +99,10 @@ struct Builder {
         GemmLaunch L;
         int r = gemm_plan(net->ctx->c, d, &L);
         if (r) { fail(r); return; }
-        plan->ops.push_back([L](cudaStream_t st) { return gemm_run(L, st); });
+        char buf[192];
+        snprintf(buf, sizeof(buf), "gemm M=%d N=%d K=%d taps=%d BN=%d tiles=%d epi=%d mode=%d", d.M, d.N, d.a_cols, d.ntaps, L.BN,
+                 L.p.num_m_tiles * L.p.num_n_tiles, d.epi, d.mode);
+        raw_push([L](cudaStream_t st) { return gemm_run(L, st); }, buf, useful_flops);
     }
     void linear(const __nv_bfloat16* A, int64_t rows, int K, const PackedW& w, int epi, void* out, int ldo, const float* residual,
                 int n_override = 0) {
@@ -135,16 +146,16 @@ struct Builder {
         push([=](cudaStream_t st) {
             int r = gn_stats(x1, C1, x2, C2, rows, rows_per_stat, 32, acc, st);
             return r ? r : gn_apply(a, st);
-        }, 2);
+        }, 2, "gnorm rows=" + std::to_string(rows) + " C=" + std::to_string(C1 + C2) + " dst=" + std::to_string(dst_mode));
     }
     void convert(const float* x, int C, int64_t rows, int dst_mode, int H, int W, __nv_bfloat16* dst) {
         ApplyArgs a;
         a.x1 = x; a.C1 = C; a.rows = rows; a.rows_per_stat = 0; a.dst_mode = dst_mode;
         a.NF = NF; a.H = H; a.W = W; a.B = B; a.T = T; a.HW = H * W; a.dst = dst;
-        push([=](cudaStream_t st) { return gn_apply(a, st); });
+        push([=](cudaStream_t st) { return gn_apply(a, st); }, 1, "convert rows=" + std::to_string(rows) + " C=" + std::to_string(C) + " dst=" + std::to_string(dst_mode));
     }
     void lnorm(const float* x, const NormW& w, int64_t rows, int C, __nv_bfloat16* out) {
-        push([=](cudaStream_t st) { return layernorm_bf16(x, w.g, w.b, rows, C, out, st); });
+        push([=](cudaStream_t st) { return layernorm_bf16(x, w.g, w.b, rows, C, out, st); }, 1, "layernorm rows=" + std::to_string(rows) + " C=" + std::to_string(C));
     }
     void tap(const std::string& name, const Act& a) {
         if (!plan->with_taps) return;
@@ -157,9 +168,9 @@ struct Builder {
         const float* src = a.p;
         float* dst = t.buf;
         const size_t bytes = (size_t)rows * a.C * sizeof(float);
-        plan->ops.push_back([=](cudaStream_t st) {
+        raw_push([=](cudaStream_t st) {
             return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, st) == cudaSuccess ? MOCA_OK : MOCA_E_CUDA;
-        });
+        }, "tap", 0);
     }
 
     Act res_block(const LayerW& L, const Act& x, const Act* skip, const float* embout);
@@ -170,6 +181,7 @@ struct Builder {
 // ResBlock._forward (openaimodel3d.py:208-234) followed by its TemporalConvBlock (:269-276)
 Act Builder::res_block(const LayerW& L, const Act& x, const Act* skip, const float* embout) {
     const ResW& r = L.res;
+    scope = L.name;
     const int H = x.H, W = x.W, HW = H * W;
     const int64_t rows = (int64_t)NF * HW;
     const int C2 = skip ? skip->C : 0;
@@ -213,6 +225,7 @@ Act Builder::res_block(const LayerW& L, const Act& x, const Act* skip, const flo
 // BasicTransformerBlock (:216-220): x += attn1(LN1 x); x += attn2(LN2 x, ctx); x += ff(LN3 x).  Runs in place on x.
 void Builder::transformer(const LayerW& L, const Act& x, const __nv_bfloat16* kv) {
     const TfW& t = L.tf;
+    scope = L.name;
     const int H = x.H, W = x.W, HW = H * W;
     const int64_t rows = (int64_t)NF * HW;
     const int C = t.C, I = t.inner;
@@ -244,7 +257,7 @@ void Builder::transformer(const LayerW& L, const Act& x, const __nv_bfloat16* kv
     // attn1: self-attention
     lnorm(y, t.ln1, rows, I, lin);
     linear(lin, rows, I, t.qkv1, EPI_BF16, qkv, 3 * I, nullptr);
-    push(run_self); plan->flops += attn_flops;
+    push(run_self, 1, "attn_self", attn_flops); plan->flops += attn_flops;
     linear(att, rows, I, t.out1, EPI_F32, y, I, y);
     // attn2: cross-attention on the text context (spatial) or a second self-attention (temporal_selfatt_only, attention.py:313-314)
     lnorm(y, t.ln2, rows, I, lin);
@@ -256,11 +269,11 @@ void Builder::transformer(const LayerW& L, const Act& x, const __nv_bfloat16* kv
         ca.kvmap.div = T; ca.kvmap.mul_a = Lmax; ca.kvmap.mul_b = 0; ca.kvmap.step = 1;     // frame o uses the context of sample o / T
         ca.out = att; ca.ldo = I; ca.n_outer = NF; ca.heads = t.heads; ca.Lq = HW; ca.Lk = Lmax;
         ca.kv_len = plan->d_ctxlen; ca.kv_len_div = T; ca.scale = 0.125f;
-        push([=](cudaStream_t st) { return attention_flash(ca, st); });
+        push([=](cudaStream_t st) { return attention_flash(ca, st); }, 1, "attn_cross", 4.0 * (double)NF * t.heads * HW * Lmax * 64.0);
         plan->flops += 4.0 * (double)NF * t.heads * HW * Lmax * 64.0;
     } else {
         linear(lin, rows, I, t.qkv2, EPI_BF16, qkv, 3 * I, nullptr);
-        push(run_self); plan->flops += attn_flops;
+        push(run_self, 1, "attn_self", attn_flops); plan->flops += attn_flops;
     }
     linear(att, rows, I, t.out2, EPI_F32, y, I, y);
     // feed-forward: Linear(C -> 8C) with the GEGLU gate fused into the GEMM epilogue, Linear(4C -> C) + residual
@@ -308,10 +321,11 @@ void Builder::build() {
     float* embout = (float*)palloc((size_t)NF * n->n_emb * 4);
     __nv_bfloat16* ctx_bf = (__nv_bfloat16*)palloc((size_t)B * Lmax * n->ctx_dim * 2);
     __nv_bfloat16* kv = (__nv_bfloat16*)palloc((size_t)B * Lmax * (n->n_kv > 0 ? n->n_kv : 16) * 2);
+    scope = "embed";
     if (!dry) {
         double* stats = plan->stats;
         const size_t sb = plan->stats_bytes;
-        plan->ops.push_back([=](cudaStream_t st) { return cudaMemsetAsync(stats, 0, sb, st) == cudaSuccess ? MOCA_OK : MOCA_E_CUDA; });
+        raw_push([=](cudaStream_t st) { return cudaMemsetAsync(stats, 0, sb, st) == cudaSuccess ? MOCA_OK : MOCA_E_CUDA; }, "memset stats", 0);
     }
     plan->launches += 1;
     // ---- time / fps embeddings (openaimodel3d.py:536-543) and all 22 emb_layers in one GEMM (:166-172, 221-226)
@@ -357,6 +371,7 @@ void Builder::build() {
             } else if (L.kind == "st" || L.kind == "tt") {
                 transformer(L, cur, kv);
             } else if (L.kind == "down") {
+                scope = L.name;
                 const int64_t rows = (int64_t)NF * cur.H * cur.W;
                 __nv_bfloat16* pad = scratch<__nv_bfloat16>(S_PAD, (size_t)NF * (cur.H + 2) * (cur.W + 2) * cur.C);
                 convert(cur.p, cur.C, rows, DST_SPATIAL_PAD, cur.H, cur.W, pad);
@@ -365,6 +380,7 @@ void Builder::build() {
                 conv3x3(pad, cur.H, cur.W, cur.C, L.conv, 2, o.p, nullptr, 0, nullptr);
                 cur = o;
             } else if (L.kind == "up") {
+                scope = L.name;
                 const int64_t rows = (int64_t)NF * cur.H * cur.W;
                 const int H2 = cur.H * 2, W2 = cur.W * 2;
                 __nv_bfloat16* pad = scratch<__nv_bfloat16>(S_PAD, (size_t)NF * (H2 + 2) * (W2 + 2) * cur.C);
@@ -391,6 +407,7 @@ void Builder::build() {
         run_layers(n->outb[i], &skip);                        // h = cat([h, hs.pop()], 1) is virtual: two-source GroupNorm
     }
     // ---- out: GN -> SiLU -> conv3x3 (openaimodel3d.py:528-532, 574)
+    scope = "out";
     {
         const int64_t rows = rows0;
         __nv_bfloat16* pad = scratch<__nv_bfloat16>(S_PAD, (size_t)NF * (H0 + 2) * (W0 + 2) * cur.C);
@@ -520,3 +537,31 @@ extern "C" int32_t moca_unet_launches(moca_unet* n) { return (n && n->last) ? n-
 extern "C" double moca_unet_flops(moca_unet* n) { return (n && n->last) ? n->last->flops : 0.0; }
 extern "C" int64_t moca_unet_workspace_bytes(moca_unet* n) { return (n && n->last) ? (int64_t)n->last->workspace_bytes : 0; }
 extern "C" int64_t moca_unet_weight_bytes(moca_unet* n) { return n ? (int64_t)n->weight_bytes : 0; }
+
+// Per-op device timing of the last planned forward (inputs must have been staged by a moca_unet_forward call).
+// Writes CSV "idx,us,gflop,label" lines into buf; returns the number of bytes needed.
+extern "C" int64_t moca_unet_profile(moca_unet* n, int32_t iters, char* buf, int64_t cap, void* stream) {
+    if (!n || !n->last || iters < 1) return -1;
+    Plan* plan = n->last;
+    cudaStream_t st = (cudaStream_t)stream;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    std::string out;
+    for (size_t i = 0; i < plan->ops.size(); ++i) {
+        plan->ops[i](st);                                 // warm
+        cudaEventRecord(e0, st);
+        for (int k = 0; k < iters; ++k) plan->ops[i](st);
+        cudaEventRecord(e1, st);
+        cudaEventSynchronize(e1);
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        char line[512];
+        snprintf(line, sizeof(line), "%zu,%.3f,%.3f,%s\n", i, ms * 1e3 / iters, plan->op_flops[i] / 1e9, plan->labels[i].c_str());
+        out += line;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (buf && cap > 0) {
+        snprintf(buf, (size_t)cap, "%s", out.c_str());
+    }
+    return (int64_t)out.size() + 1;
+}

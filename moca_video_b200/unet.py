@@ -132,6 +132,17 @@ class UNet3D:
             out[buf.value.decode()] = t
         return out
 
+    def profile(self, iters=5):
+        """Per-op device times of the last planned forward: list of (us, gflop, label)."""
+        need = lib().moca_unet_profile(self._h, 1, None, 0, stream_ptr())
+        buf = C.create_string_buffer(int(need) + 4096)
+        lib().moca_unet_profile(self._h, int(iters), buf, len(buf), stream_ptr())
+        rows = []
+        for line in buf.value.decode().splitlines():
+            i, us, gf, label = line.split(",", 3)
+            rows.append((float(us), float(gf), label))
+        return rows
+
     def launches(self):
         return int(lib().moca_unet_launches(self._h))
 

@@ -115,7 +115,7 @@ def test_unet_full_cfg_batch_equals_separate_forwards(full):
     ctx = torch.zeros(2, 154, 1024, device=DEV)
     ctx[0] = c[0]; ctx[1, :77] = u[0]; ctx[1, 77:] = 1e4          # poison the padding
     e2 = net(torch.cat([x, x]), ts + ts, ctx, fps=10, ctx_len=[154, 77])
-    assert rel(e2[0:1], e_c) < 2e-3 and rel(e2[1:2], e_u) < 2e-3     # same kernels, different tile schedule / atomics order
+    assert rel(e2[0:1], e_c) < 1e-3 and rel(e2[1:2], e_u) < 1e-3     # same kernels and statistics chunks; only fp64 atomics order differs
 
 
 def test_fifo_onestep_vs_oracle(small):
@@ -145,7 +145,9 @@ def test_fifo_onestep_vs_oracle(small):
         e = R.cfg_combine(unet_forward(sd, cfg, x, tt, c, fps=10).cpu().numpy(), unet_forward(sd, cfg, x, tt, u, fps=10).cpu().numpy(), 12.0)
         xo, po = R.moca_ddim_step(x.cpu().numpy(), e, noise.cpu().numpy(), R.coef_rows(R.make_tables(64, 1.0), idx), t,
                                   mask.cpu().numpy(), R.parity_mask_index(16, 8), cimg.cpu().numpy(), 0.5)
-        assert rel(xp.cpu(), torch.from_numpy(xo)) < TOL and rel(p0.cpu(), torch.from_numpy(po)) < TOL
+        # x_prev is the per-step latent the FIFO consumes (bar 2e-2).  pred_x0 = (x - sqrt(1-a) e)/sqrt(a) with e = e_u + 12 (e_c - e_u)
+        # multiplies the bf16 error of the small difference e_c - e_u by the guidance scale and 1/sqrt(a): looser bar.
+        assert rel(xp.cpu(), torch.from_numpy(xo)) < TOL and rel(p0.cpu(), torch.from_numpy(po)) < 6e-2
 
 
 def test_fifo_iterations_vs_oracle(small):
