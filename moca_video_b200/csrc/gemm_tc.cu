@@ -5,7 +5,7 @@ namespace moca {
 
 using namespace ptx;
 
-constexpr int kGemmThreads = 192;
+constexpr int kGemmThreads = 320;        // 2 control warps + 8 epilogue warps
 constexpr int kBM = 128;
 constexpr int kBK = 64;
 constexpr int kABytes = kBM * kBK * 2;        // 16 KB, 128 rows of 128 B
@@ -16,10 +16,26 @@ struct GemmCfg {
     static constexpr int STAGE_BYTES = kABytes + B_BYTES;
     static constexpr int STAGES = (BN == 256) ? 4 : (BN == 160 ? 5 : 6);
     static constexpr int TMEM_COLS = (2 * BN <= 256) ? 256 : 512;
-    static constexpr size_t SMEM = (size_t)STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+    static constexpr size_t SMEM = (size_t)STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ + 8 * 4096 /*epilogue staging*/;
 };
 
 __device__ __forceinline__ float gelu_erf(float g) { return 0.5f * g * (1.0f + erff(g * 0.70710678118654752f)); }
+
+// Exact-erf GELU (attention.py:383 uses F.gelu's default) through erfc(|z|) = poly(t) e^{-z^2}, t = 1/(1 + p|z|)
+// (Abramowitz-Stegun 7.1.26, |error| <= 1.5e-7 — far below the bf16 rounding of the output); 1 + erf(z) is formed
+// without cancellation: erfc(|z|) for z < 0, 2 - erfc(z) for z >= 0.
+__device__ __forceinline__ float gelu_fast(float g) {
+    const float z = g * 0.70710678118654752f;
+    const float az = fabsf(z);
+    const float t = __fdividef(1.0f, fmaf(0.3275911f, az, 1.0f));
+    float p = fmaf(1.061405429f, t, -1.453152027f);
+    p = fmaf(p, t, 1.421413741f);
+    p = fmaf(p, t, -0.284496736f);
+    p = fmaf(p, t, 0.254829592f);
+    const float e = p * t * __expf(-az * az);
+    const float one_plus_erf = z < 0.f ? e : 2.0f - e;
+    return 0.5f * g * one_plus_erf;
+}
 
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
     __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
@@ -54,7 +70,7 @@ __device__ __forceinline__ bool map_row(const GemmParams& P, int row, int& out_r
     return true;
 }
 
-template <int BN>
+template <int BN, int EPI>
 __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_constant__ GemmParams P) {
     using Cfg = GemmCfg<BN>;
     constexpr int STAGES = Cfg::STAGES;
@@ -80,7 +96,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&tfull[i], 1);
-            mbar_init(&tempty[i], 4);
+            mbar_init(&tempty[i], 8);
         }
         fence_mbar_init();
     }
@@ -145,105 +161,187 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
             }
         }
     } else {
-        // ===== epilogue warps 2..5: TMEM lane quarter = warp % 4 =====
+        // ===== epilogue warps 2..9: TMEM lane quarter q = warp % 4, two warps per quarter take alternate 32-column chunks.
+        // Each chunk goes TMEM -> registers (thread = row) -> XOR-swizzled smem staging -> registers (8 lanes = one row's
+        // 128 bytes) so that residual reads and output stores are full 128-byte segments per row.  The residual (+ per-frame
+        // embedding bias) of the NEXT chunk is loaded before the current one is processed, across tile boundaries, so a
+        // warp always has a DRAM round trip in flight behind its TMEM / staging work.
         const int q = warp & 3;
+        const int half = (warp - 2) >> 2;
+        float* stg = reinterpret_cast<float*>(base + (size_t)STAGES * Cfg::STAGE_BYTES + 256) + (size_t)(warp - 2) * 1024;
+        constexpr bool kGeglu = EPI == EPI_GEGLU;
+        constexpr int kChunks = kGeglu ? BN / 64 : BN / 32;
+        const int ncols_total = kGeglu ? (P.N >> 1) : P.N;
         int as = 0;
         uint32_t aphase = 0;
-        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-            const int mt = tile / P.num_n_tiles, nt = tile - mt * P.num_n_tiles;
-            mbar_wait(&tfull[as], aphase);
-            tc_fence_after();
+
+        auto tile_rows = [&](int tile, int& out_row, uint32_t& vmask) {
+            const int mt = tile / P.num_n_tiles;
             const int row = mt * kBM + q * 32 + lane;
-            int out_row = 0;
+            out_row = 0;
             const bool valid = map_row(P, row, out_row);
-            const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN);
-            if (P.epi == EPI_GEGLU) {
-                constexpr int HALF = BN / 2;
-                const int nout = P.N >> 1;
-                for (int c = 0; c < HALF / 32; ++c) {
-                    const int n0 = nt * HALF + c * 32;          // output column
-                    if (n0 >= nout) break;
-                    __syncwarp();
-                    uint32_t rv[32], rg[32];
-                    tmem_ld32(t_row + (uint32_t)(c * 32), rv);
-                    tmem_ld32(t_row + (uint32_t)(HALF + c * 32), rg);
-                    tmem_ld_wait();
-                    if (valid) {
-                        const float* bv = P.bias + (size_t)nt * BN + c * 32;
-                        const float* bg = bv + HALF;
-                        __nv_bfloat16* o = P.outb + (size_t)out_row * P.ldo + n0;
+            vmask = __ballot_sync(0xffffffffu, valid);
+        };
+        auto col0_of = [&](int tile) {
+            const int nt = tile % P.num_n_tiles;
+            return kGeglu ? nt * (BN / 2) : nt * BN;
+        };
+        // fp32 path: lane covers columns cc*4..cc*4+3 of rows rr = i*4 + lane/8
+        auto prefetch = [&](float4 (&pre)[8], int out_row, uint32_t vmask, int n0) {
+            const int col = n0 + (lane & 7) * 4;
+            const bool full = col + 4 <= P.N;
 #pragma unroll
-                        for (int j = 0; j < 32; j += 8) {
-                            uint32_t w[4];
-#pragma unroll
-                            for (int u = 0; u < 4; ++u) {
-                                const int jj = j + 2 * u;
-                                const float v0 = __uint_as_float(rv[jj]) + bv[jj], v1 = __uint_as_float(rv[jj + 1]) + bv[jj + 1];
-                                const float g0 = __uint_as_float(rg[jj]) + bg[jj], g1 = __uint_as_float(rg[jj + 1]) + bg[jj + 1];
-                                w[u] = pack_bf16(v0 * gelu_erf(g0), v1 * gelu_erf(g1));
-                            }
-                            *reinterpret_cast<uint4*>(o + j) = make_uint4(w[0], w[1], w[2], w[3]);
-                        }
+            for (int i = 0; i < 8; ++i) {
+                const int rr = i * 4 + (lane >> 3);
+                const int orow = __shfl_sync(0xffffffffu, out_row, rr);
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (full && ((vmask >> rr) & 1u)) {
+                    if (P.residual) v = __ldg(reinterpret_cast<const float4*>(P.residual + (size_t)orow * P.ldo + col));
+                    if (P.rowbias) {
+                        const float4 t = __ldg(reinterpret_cast<const float4*>(P.rowbias + (size_t)(orow / P.rows_per_frame) * P.rb_ld + col));
+                        v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
                     }
                 }
-            } else {
-                for (int c = 0; c < BN / 32; ++c) {
-                    const int n0 = nt * BN + c * 32;
-                    if (n0 >= P.N) break;
-                    __syncwarp();
-                    uint32_t r[32];
-                    tmem_ld32(t_row + (uint32_t)(c * 32), r);
+                pre[i] = v;
+            }
+        };
+
+        int tile = blockIdx.x;
+        int out_row = 0, nxt_row = 0;
+        uint32_t vmask = 0, nxt_mask = 0;
+        float4 pre[8];
+        bool have_pre = false;
+        if (tile < ntiles) {
+            tile_rows(tile, out_row, vmask);
+            if (EPI == EPI_F32 && col0_of(tile) + half * 32 < ncols_total) {
+                prefetch(pre, out_row, vmask, col0_of(tile) + half * 32);
+                have_pre = true;
+            }
+        }
+        for (; tile < ntiles; tile += gridDim.x) {
+            const int nt = tile % P.num_n_tiles;
+            const int col_tile0 = col0_of(tile);
+            const int ntile = tile + gridDim.x;
+            bool nxt_ready = false;
+            mbar_wait(&tfull[as], aphase);
+            tc_fence_after();
+            const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN);
+            for (int c = half; c < kChunks; c += 2) {
+                const int n0 = col_tile0 + c * 32;                 // first output column of this chunk
+                if (n0 >= ncols_total) break;
+                uint32_t r[32];
+                tmem_ld32(t_row + (uint32_t)(c * 32), r);
+                if constexpr (EPI == EPI_F32) {
+                    // issue the next chunk's residual loads before touching this chunk's data
+                    float4 nxt[8];
+                    bool have_nxt = false;
+                    if (c + 2 < kChunks && n0 + 64 < ncols_total) {
+                        prefetch(nxt, out_row, vmask, n0 + 64);
+                        have_nxt = true;
+                    } else if (ntile < ntiles) {
+                        if (!nxt_ready) { tile_rows(ntile, nxt_row, nxt_mask); nxt_ready = true; }
+                        if (col0_of(ntile) + half * 32 < ncols_total) {
+                            prefetch(nxt, nxt_row, nxt_mask, col0_of(ntile) + half * 32);
+                            have_nxt = true;
+                        }
+                    }
                     tmem_ld_wait();
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        *reinterpret_cast<uint4*>(stg + lane * 32 + ((j ^ (lane & 7)) << 2)) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
                     __syncwarp();
-                    if (!valid) continue;
-                    const int ncols = min(32, P.N - n0);
-                    float v[32];
+                    const int cc = lane & 7;
+                    const int col = n0 + cc * 4;
+                    const int nvalid = min(4, P.N - col);          // <= 0: nothing to store for this lane
+                    float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (P.bias && nvalid >= 4) b4 = __ldg(reinterpret_cast<const float4*>(P.bias + col));
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-                    if (P.bias) {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            if (j < ncols) v[j] += P.bias[n0 + j];
-                    }
-                    if (P.rowbias) {
-                        const float* rb = P.rowbias + (size_t)(out_row / P.rows_per_frame) * P.rb_ld + n0;
-#pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            if (j < ncols) v[j] += rb[j];
-                    }
-                    if (P.epi == EPI_F32) {
-                        float* o = P.outf + (size_t)out_row * P.ldo + n0;
-                        if (ncols == 32) {
-                            if (P.residual) {
-                                const float4* rs = reinterpret_cast<const float4*>(P.residual + (size_t)out_row * P.ldo + n0);
-#pragma unroll
-                                for (int j = 0; j < 8; ++j) {
-                                    const float4 t = rs[j];
-                                    v[4 * j] += t.x; v[4 * j + 1] += t.y; v[4 * j + 2] += t.z; v[4 * j + 3] += t.w;
-                                }
+                    for (int i = 0; i < 8; ++i) {
+                        const int rr = i * 4 + (lane >> 3);
+                        const int orow = __shfl_sync(0xffffffffu, out_row, rr);
+                        if (!((vmask >> rr) & 1u) || nvalid <= 0) continue;
+                        float4 v = *reinterpret_cast<const float4*>(stg + rr * 32 + ((cc ^ (rr & 7)) << 2));
+                        const size_t o = (size_t)orow * P.ldo + col;
+                        if (nvalid >= 4) {
+                            v.x += b4.x; v.y += b4.y; v.z += b4.z; v.w += b4.w;
+                            if (have_pre) { v.x += pre[i].x; v.y += pre[i].y; v.z += pre[i].z; v.w += pre[i].w; }
+                            *reinterpret_cast<float4*>(P.outf + o) = v;
+                        } else {                                     // ragged last columns (N % 4 != 0): scalar path
+                            const float vv[4] = {v.x, v.y, v.z, v.w};
+                            for (int e = 0; e < nvalid; ++e) {
+                                float t = vv[e] + (P.bias ? P.bias[col + e] : 0.f);
+                                if (P.rowbias) t += P.rowbias[(size_t)(orow / P.rows_per_frame) * P.rb_ld + col + e];
+                                if (P.residual) t += P.residual[o + e];
+                                P.outf[o + e] = t;
                             }
-#pragma unroll
-                            for (int j = 0; j < 8; ++j)
-                                reinterpret_cast<float4*>(o)[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-                        } else {
-                            const float* rs = P.residual ? P.residual + (size_t)out_row * P.ldo + n0 : nullptr;
-#pragma unroll
-                            for (int j = 0; j < 32; ++j)
-                                if (j < ncols) o[j] = v[j] + (rs ? rs[j] : 0.0f);
-                        }
-                    } else {
-                        __nv_bfloat16* o = P.outb + (size_t)out_row * P.ldo + n0;
-                        if (ncols == 32) {
-#pragma unroll
-                            for (int j = 0; j < 32; j += 8)
-                                *reinterpret_cast<uint4*>(o + j) = make_uint4(pack_bf16(v[j], v[j + 1]), pack_bf16(v[j + 2], v[j + 3]),
-                                                                              pack_bf16(v[j + 4], v[j + 5]), pack_bf16(v[j + 6], v[j + 7]));
-                        } else {
-#pragma unroll
-                            for (int j = 0; j < 32; ++j)
-                                if (j < ncols) o[j] = __float2bfloat16_rn(v[j]);
                         }
                     }
+                    __syncwarp();
+                    have_pre = have_nxt;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) pre[i] = nxt[i];
+                } else {
+                    // bf16 output: 4 lanes cover one row's 32 columns (64 bytes), 8 rows per pass
+                    const int cc = lane & 3;
+                    const int col = n0 + cc * 8;
+                    const int nvalid = min(8, ncols_total - col);
+                    float va[4][8];
+                    float bb[8], bg[8];
+                    if constexpr (kGeglu) {
+                        uint32_t rg[32];
+                        tmem_ld32(t_row + (uint32_t)(BN / 2 + c * 32), rg);
+                        tmem_ld_wait();
+                        // values first: stage, read back in the store layout, then the gates through the same buffer
+#pragma unroll
+                        for (int j = 0; j < 8; ++j)
+                            *reinterpret_cast<uint4*>(stg + lane * 32 + ((j ^ (lane & 7)) << 2)) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+                        __syncwarp();
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const int rr = i * 8 + (lane >> 2);
+                            const float4 a = *reinterpret_cast<const float4*>(stg + rr * 32 + (((2 * cc) ^ (rr & 7)) << 2));
+                            const float4 b = *reinterpret_cast<const float4*>(stg + rr * 32 + (((2 * cc + 1) ^ (rr & 7)) << 2));
+                            va[i][0] = a.x; va[i][1] = a.y; va[i][2] = a.z; va[i][3] = a.w;
+                            va[i][4] = b.x; va[i][5] = b.y; va[i][6] = b.z; va[i][7] = b.w;
+                        }
+                        __syncwarp();
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) r[j] = rg[j];
+                        const float* bvp = P.bias + (size_t)nt * BN + c * 32 + cc * 8;
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) { bb[e] = __ldg(bvp + e); bg[e] = __ldg(bvp + BN / 2 + e); }
+                    } else {
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) bb[e] = (P.bias && e < nvalid) ? P.bias[col + e] : 0.f;
+                    }
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        *reinterpret_cast<uint4*>(stg + lane * 32 + ((j ^ (lane & 7)) << 2)) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+                    __syncwarp();
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const int rr = i * 8 + (lane >> 2);
+                        const int orow = __shfl_sync(0xffffffffu, out_row, rr);
+                        if (!((vmask >> rr) & 1u) || nvalid <= 0) continue;
+                        const float4 a = *reinterpret_cast<const float4*>(stg + rr * 32 + (((2 * cc) ^ (rr & 7)) << 2));
+                        const float4 b = *reinterpret_cast<const float4*>(stg + rr * 32 + (((2 * cc + 1) ^ (rr & 7)) << 2));
+                        float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+                        if constexpr (kGeglu) {
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) v[e] = (va[i][e] + bb[e]) * gelu_fast(v[e] + bg[e]);
+                        } else {
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) v[e] += bb[e];
+                        }
+                        __nv_bfloat16* o = P.outb + (size_t)orow * P.ldo + col;
+                        if (nvalid >= 8) {
+                            *reinterpret_cast<uint4*>(o) = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+                        } else {
+                            for (int e = 0; e < nvalid; ++e) o[e] = __float2bfloat16_rn(v[e]);
+                        }
+                    }
+                    __syncwarp();
                 }
             }
             tc_fence_before();
@@ -251,6 +349,12 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
             if (lane == 0) mbar_arrive(&tempty[as]);
             as ^= 1;
             if (as == 0) aphase ^= 1;
+            if (EPI == EPI_F32) {
+                if (!nxt_ready && ntile < ntiles) tile_rows(ntile, nxt_row, nxt_mask);
+                out_row = nxt_row; vmask = nxt_mask;
+            } else if (ntile < ntiles) {
+                tile_rows(ntile, out_row, vmask);
+            }
         }
     }
     tc_fence_before();
@@ -304,22 +408,47 @@ int make_tmap_bf16(CUtensorMap* tm, const void* ptr, int64_t rows, int64_t cols,
     return MOCA_OK;
 }
 
-static int pick_bn(const GemmDesc& d) {
+// Tile width: minimise (waves over the SMs) x (columns computed per tile), with a small penalty for the narrower tiles
+// (a 128-wide B tile keeps the MMA shared-memory-bandwidth bound).  GEGLU weights are packed for 256-wide tiles.
+static int pick_bn(const GemmDesc& d, int num_sms) {
     if (d.epi == EPI_GEGLU) return 256;
-    if (d.N % 256 == 0) return 256;
-    if (d.N % 160 == 0) return 160;
-    if (d.N > 128 && d.N % 128 != 0 && d.N <= 160) return 160;
-    return 128;
+    const int cand[3] = {256, 160, 128};
+    const double pen[3] = {1.0, 1.06, 1.15};
+    const int64_t mt = (d.M + kBM - 1) / kBM;
+    int best = 128;
+    double best_cost = 1e30;
+    for (int i = 0; i < 3; ++i) {
+        const int bn = cand[i];
+        const int64_t tiles = mt * ((d.N + bn - 1) / bn);
+        const double waves = (double)((tiles + num_sms - 1) / num_sms);
+        const double cost = waves * bn * pen[i];
+        if (cost < best_cost - 1e-9) { best_cost = cost; best = bn; }
+    }
+    return best;
 }
 
-template <int BN>
+template <int BN, int EPI>
 static int set_attr() {
     static bool done = false;
     if (!done) {
-        MOCA_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GemmCfg<BN>::SMEM));
+        MOCA_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GemmCfg<BN>::SMEM));
         done = true;
     }
     return MOCA_OK;
+}
+
+template <int BN>
+static int set_attr_bn(int epi) {
+    if (epi == EPI_F32) return set_attr<BN, EPI_F32>();
+    if (epi == EPI_BF16) return set_attr<BN, EPI_BF16>();
+    return set_attr<BN, EPI_GEGLU>();
+}
+
+template <int BN>
+static void launch_bn(const GemmLaunch& l, cudaStream_t st) {
+    if (l.p.epi == EPI_F32) gemm_tc_kernel<BN, EPI_F32><<<l.grid, kGemmThreads, l.smem, st>>>(l.p);
+    else if (l.p.epi == EPI_BF16) gemm_tc_kernel<BN, EPI_BF16><<<l.grid, kGemmThreads, l.smem, st>>>(l.p);
+    else gemm_tc_kernel<BN, EPI_GEGLU><<<l.grid, kGemmThreads, l.smem, st>>>(l.p);
 }
 
 int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
@@ -332,7 +461,7 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
                  MOCA_E_ALIGN, "gemm_plan: output pitch %d not vector aligned", d.ldo);
     GemmLaunch L;
     memset(&L.p, 0, sizeof(L.p));
-    L.BN = pick_bn(d);
+    L.BN = pick_bn(d, ctx.num_sms);
     int rc = make_tmap_bf16(&L.p.tmA, d.A, d.a_rows, d.a_cols, d.a_pitch, kBM);
     if (rc) return rc;
     rc = make_tmap_bf16(&L.p.tmB, d.Wt, d.N, (int64_t)d.ntaps * d.Kp, (int64_t)d.ntaps * d.Kp, L.BN);
@@ -350,16 +479,16 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
     L.grid = ntiles < ctx.num_sms ? ntiles : ctx.num_sms;
     L.smem = L.BN == 256 ? GemmCfg<256>::SMEM : (L.BN == 160 ? GemmCfg<160>::SMEM : GemmCfg<128>::SMEM);
     L.flops = 2.0 * (double)d.M * d.N * d.ntaps * d.a_cols;
-    rc = L.BN == 256 ? set_attr<256>() : (L.BN == 160 ? set_attr<160>() : set_attr<128>());
+    rc = L.BN == 256 ? set_attr_bn<256>(d.epi) : (L.BN == 160 ? set_attr_bn<160>(d.epi) : set_attr_bn<128>(d.epi));
     if (rc) return rc;
     *out = L;
     return MOCA_OK;
 }
 
 int gemm_run(const GemmLaunch& l, cudaStream_t st) {
-    if (l.BN == 256) gemm_tc_kernel<256><<<l.grid, kGemmThreads, l.smem, st>>>(l.p);
-    else if (l.BN == 160) gemm_tc_kernel<160><<<l.grid, kGemmThreads, l.smem, st>>>(l.p);
-    else gemm_tc_kernel<128><<<l.grid, kGemmThreads, l.smem, st>>>(l.p);
+    if (l.BN == 256) launch_bn<256>(l, st);
+    else if (l.BN == 160) launch_bn<160>(l, st);
+    else launch_bn<128>(l, st);
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
 }

@@ -35,74 +35,94 @@ int pack_weight(const float* src, int N, int K, int taps, int Kp, __nv_bfloat16*
 
 // ---------------------------------------------------------------------------------------------------------------
 // GroupNorm statistics
-constexpr int kStatThreads = 256;
+// Block = TPR x RP threads: thread (x, y) owns the float4 channel vectors x, x+TPR, .. of rows y, y+RP, .. of its 32-row
+// chunk, so its channels (and groups) are fixed and partial sums stay in registers.
 constexpr int kStatSlots = 3;      // float4 slots per thread: supports C <= 256*3*4 = 3072
+constexpr int kStatChunk = 32;     // rows per block; fixed so that statistics do not depend on the batch size
 
-__global__ void __launch_bounds__(kStatThreads) gn_stats_kernel(const float* __restrict__ x1, int C1, const float* __restrict__ x2,
-                                                                int C2, int rows_per_stat, int chunk, int Cg,
-                                                                double* __restrict__ acc) {
-    __shared__ double sh[64];
-    if (threadIdx.x < 64) sh[threadIdx.x] = 0.0;
-    __syncthreads();
+__global__ void __launch_bounds__(256) gn_stats_kernel(const float* __restrict__ x1, int C1, const float* __restrict__ x2,
+                                                       int C2, int rows_per_stat, int Cg, int tpr, int rp,
+                                                       double* __restrict__ acc) {
+    // per-(row lane, channel) partial sums; a thread owns its channels so plain stores suffice
+    __shared__ float s_sum[256 * kStatSlots * 4];
+    __shared__ float s_sq[256 * kStatSlots * 4];
     const int stat = blockIdx.y;
-    const int r0 = blockIdx.x * chunk;
-    const int r1 = min(rows_per_stat, r0 + chunk);
+    const int r0 = blockIdx.x * kStatChunk;
+    const int r1 = min(rows_per_stat, r0 + kStatChunk);
     const int C = C1 + C2;
     const int nvec = C >> 2;
+    const int tx = threadIdx.x % tpr, ty = threadIdx.x / tpr;
     float s[kStatSlots][4], ss[kStatSlots][4];
 #pragma unroll
     for (int u = 0; u < kStatSlots; ++u)
 #pragma unroll
         for (int e = 0; e < 4; ++e) s[u][e] = ss[u][e] = 0.0f;
-    for (int r = r0; r < r1; ++r) {
-        const int64_t row = (int64_t)stat * rows_per_stat + r;
+    if (ty < rp) {
+#pragma unroll 4
+        for (int r = r0 + ty; r < r1; r += rp) {
+            const size_t row = (size_t)stat * rows_per_stat + r;
 #pragma unroll
-        for (int u = 0; u < kStatSlots; ++u) {
-            const int v = threadIdx.x + u * kStatThreads;
-            if (v < nvec) {
-                const int c = v << 2;
-                const float4 t = c < C1 ? *reinterpret_cast<const float4*>(x1 + row * C1 + c)
-                                        : *reinterpret_cast<const float4*>(x2 + row * C2 + (c - C1));
-                s[u][0] += t.x; ss[u][0] += t.x * t.x;
-                s[u][1] += t.y; ss[u][1] += t.y * t.y;
-                s[u][2] += t.z; ss[u][2] += t.z * t.z;
-                s[u][3] += t.w; ss[u][3] += t.w * t.w;
+            for (int u = 0; u < kStatSlots; ++u) {
+                const int v = tx + u * tpr;
+                if (v < nvec) {
+                    const int c = v << 2;
+                    const float4 t = c < C1 ? __ldg(reinterpret_cast<const float4*>(x1 + row * C1 + c))
+                                            : __ldg(reinterpret_cast<const float4*>(x2 + row * C2 + (c - C1)));
+                    s[u][0] += t.x; ss[u][0] += t.x * t.x;
+                    s[u][1] += t.y; ss[u][1] += t.y * t.y;
+                    s[u][2] += t.z; ss[u][2] += t.z * t.z;
+                    s[u][3] += t.w; ss[u][3] += t.w * t.w;
+                }
             }
         }
-    }
 #pragma unroll
-    for (int u = 0; u < kStatSlots; ++u) {
-        const int v = threadIdx.x + u * kStatThreads;
-        if (v < nvec) {
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                const int g = ((v << 2) + e) / Cg;
-                atomicAdd(&sh[2 * g], (double)s[u][e]);
-                atomicAdd(&sh[2 * g + 1], (double)ss[u][e]);
+        for (int u = 0; u < kStatSlots; ++u) {
+            const int v = tx + u * tpr;
+            if (v < nvec) {
+                *reinterpret_cast<float4*>(&s_sum[ty * C + (v << 2)]) = make_float4(s[u][0], s[u][1], s[u][2], s[u][3]);
+                *reinterpret_cast<float4*>(&s_sq[ty * C + (v << 2)]) = make_float4(ss[u][0], ss[u][1], ss[u][2], ss[u][3]);
             }
         }
     }
     __syncthreads();
-    if (threadIdx.x < 64) atomicAdd(&acc[(int64_t)stat * 64 + threadIdx.x], sh[threadIdx.x]);
+    // 64 threads: (group, sum|sumsq) -> fixed-order double sum over the group's channels and row lanes, one atomic each
+    if (threadIdx.x < 64) {
+        const int g = threadIdx.x >> 1;
+        const float* src = (threadIdx.x & 1) ? s_sq : s_sum;
+        double a = 0.0;
+        for (int y = 0; y < rp; ++y)
+            for (int c = g * Cg; c < (g + 1) * Cg; ++c) a += (double)src[y * C + c];
+        atomicAdd(&acc[(size_t)stat * 64 + threadIdx.x], a);
+    }
+}
+
+static void stat_geometry(int nvec, int& slots, int& tpr, int& rp) {
+    slots = (nvec + 255) / 256;
+    tpr = (((nvec + slots - 1) / slots) + 31) / 32 * 32;
+    if (tpr > 256) tpr = 256;
+    rp = 256 / tpr;
+    if (rp < 1) rp = 1;
 }
 
 int gn_stats(const float* x1, int C1, const float* x2, int C2, int64_t rows, int rows_per_stat, int groups, double* acc,
              cudaStream_t st) {
     const int C = C1 + C2;
-    MOCA_REQUIRE(groups == 32 && C % 32 == 0 && C % 4 == 0 && C1 % 4 == 0 && C <= kStatThreads * kStatSlots * 4, MOCA_E_SHAPE,
+    MOCA_REQUIRE(groups == 32 && C % 32 == 0 && C % 4 == 0 && C1 % 4 == 0 && C <= 256 * kStatSlots * 4, MOCA_E_SHAPE,
                  "gn_stats: unsupported channels C1=%d C2=%d groups=%d", C1, C2, groups);
     MOCA_REQUIRE(rows % rows_per_stat == 0, MOCA_E_SHAPE, "gn_stats: rows %lld not a multiple of %d", (long long)rows, rows_per_stat);
     const int nstat = (int)(rows / rows_per_stat);
-    // fixed chunk: the fp32 partial sums (and so the statistics, bit for bit up to the order of the fp64 atomics) do not
-    // depend on how many frames are batched — a b=2 CFG launch reproduces two b=1 launches
-    const int chunk = 32;
-    dim3 grid(cdiv(rows_per_stat, chunk), nstat);
-    gn_stats_kernel<<<grid, kStatThreads, 0, st>>>(x1, C1, x2, C2, rows_per_stat, chunk, C / 32, acc);
+    int slots, tpr, rp;
+    stat_geometry(C / 4, slots, tpr, rp);
+    dim3 grid(cdiv(rows_per_stat, kStatChunk), nstat);
+    gn_stats_kernel<<<grid, 256, 0, st>>>(x1, C1, x2, C2, rows_per_stat, C / 32, tpr, rp, acc);
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
 }
 
 // ---------------------------------------------------------------------------------------------------------------
+// GroupNorm apply (+SiLU) with layout scatter.  Block = TPR x RP threads as above; each block walks kApplyRows destination
+// rows.  A thread's channels are fixed: gamma / beta / group ids live in registers; mean / rstd of the (at most two)
+// statistics groups a block touches are derived once per block into shared memory.
 struct ApplyP {
     const float* x1; int C1;
     const float* x2; int C2;
@@ -111,106 +131,155 @@ struct ApplyP {
     float eps; int silu; int mode;
     int NF, H, W;        // source geometry
     int T, HW;
-    int64_t dst_rows;    // rows of the destination layout
+    int dst_rows;        // rows of the destination layout
+    int nstat;
+    int tpr, rp;
     __nv_bfloat16* dst; __nv_bfloat16* raw;
 };
 
-__device__ __forceinline__ float silu_f(float v) { return v / (1.0f + __expf(-v)); }
+constexpr int kApplyRows = 16;
+
+__device__ __forceinline__ float silu_f(float v) { return __fdividef(v, 1.0f + __expf(-v)); }
+
+// destination row -> source row (or -1 for a zero border / padding row)
+__device__ __forceinline__ int apply_src_row(const ApplyP& P, int drow) {
+    if (P.mode == DST_LINEAR) return drow;
+    if (P.mode == DST_TIME_PAD) {
+        const int per = P.HW * (P.T + 2);
+        const int b = drow / per, r = drow - b * per;
+        const int tp = r / P.HW, hw = r - tp * P.HW;
+        return (tp < 1 || tp > P.T) ? -1 : (b * P.T + (tp - 1)) * P.HW + hw;
+    }
+    const int up = P.mode == DST_SPATIAL_PAD_UP2 ? 1 : 0;
+    const int Hd = P.H << up, Wd = P.W << up, Wp = Wd + 2, Hp = Hd + 2;
+    const int f = drow / (Wp * Hp), r = drow - f * (Wp * Hp);
+    const int hp = r / Wp, wp = r - hp * Wp;
+    if (hp < 1 || hp > Hd || wp < 1 || wp > Wd) return -1;
+    return (f * P.H + ((hp - 1) >> up)) * P.W + ((wp - 1) >> up);
+}
 
 __global__ void __launch_bounds__(256) gn_apply_kernel(const __grid_constant__ ApplyP P) {
+    __shared__ float2 s_mr[kApplyRows + 1][32];   // (mean, rstd) of statistics groups s_first, s_first + 1, ..
+    __shared__ int s_first;
     const int C = P.C1 + P.C2;
     const int nvec = C >> 2;
-    const int64_t total = P.dst_rows * nvec;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int v = (int)(i % nvec);
-        const int64_t drow = i / nvec;
-        const int c = v << 2;
-        int64_t srow = drow;
-        bool zero = false;
-        if (P.mode == DST_SPATIAL_PAD || P.mode == DST_SPATIAL_PAD_UP2) {
-            const int up = P.mode == DST_SPATIAL_PAD_UP2 ? 1 : 0;
-            const int Hd = P.H << up, Wd = P.W << up;
-            const int Wp = Wd + 2, Hp = Hd + 2;
-            const int wp = (int)(drow % Wp);
-            const int hp = (int)((drow / Wp) % Hp);
-            const int f = (int)(drow / ((int64_t)Wp * Hp));
-            if (hp < 1 || hp > Hd || wp < 1 || wp > Wd) zero = true;
-            else srow = ((int64_t)f * P.H + ((hp - 1) >> up)) * P.W + ((wp - 1) >> up);
-        } else if (P.mode == DST_TIME_PAD) {
-            const int hw = (int)(drow % P.HW);
-            const int tp = (int)((drow / P.HW) % (P.T + 2));
-            const int b = (int)(drow / ((int64_t)P.HW * (P.T + 2)));
-            if (tp < 1 || tp > P.T) zero = true;
-            else srow = ((int64_t)b * P.T + (tp - 1)) * P.HW + hw;
-        }
-        uint2 o = make_uint2(0u, 0u);
-        if (!zero) {
-            const float4 t = c < P.C1 ? *reinterpret_cast<const float4*>(P.x1 + srow * P.C1 + c)
-                                      : *reinterpret_cast<const float4*>(P.x2 + srow * P.C2 + (c - P.C1));
-            float x[4] = {t.x, t.y, t.z, t.w};
-            if (P.raw) {
-                __nv_bfloat162 a = __floats2bfloat162_rn(x[0], x[1]), b = __floats2bfloat162_rn(x[2], x[3]);
-                *reinterpret_cast<uint2*>(P.raw + srow * C + c) = make_uint2(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&b));
+    const int tx = threadIdx.x % P.tpr, ty = threadIdx.x / P.tpr;
+    const int d0 = blockIdx.x * kApplyRows;
+    const int d1 = min(P.dst_rows, d0 + kApplyRows);
+    if (P.rows_per_stat > 0) {
+        if (threadIdx.x == 0) {
+            int first = -1;
+            for (int d = d0; d < d1 && first < 0; ++d) {
+                const int sr = apply_src_row(P, d);
+                if (sr >= 0) first = sr / P.rows_per_stat;
             }
-            if (P.rows_per_stat > 0) {
-                const int64_t stat = srow / P.rows_per_stat;
-                const double n = (double)P.rows_per_stat * P.Cg;
-                int gprev = -1;
-                float mean = 0.f, rstd = 0.f;
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    const int g = (c + e) / P.Cg;
-                    if (g != gprev) {
-                        const double s = P.acc[stat * 64 + 2 * g], q = P.acc[stat * 64 + 2 * g + 1];
-                        const double m = s / n;
-                        double var = q / n - m * m;
-                        var = var < 0.0 ? 0.0 : var;
-                        mean = (float)m;
-                        rstd = rsqrtf((float)var + P.eps);
-                        gprev = g;
-                    }
-                    float y = (x[e] - mean) * rstd * P.gamma[c + e] + P.beta[c + e];
-                    if (P.silu) y = silu_f(y);
-                    x[e] = y;
+            s_first = first;
+        }
+        __syncthreads();
+        const int first = s_first;
+        if (first >= 0) {
+            // a block's kApplyRows destination rows map to at most kApplyRows consecutive statistics groups
+            const int nwhich = min(kApplyRows + 1, (kApplyRows + P.rows_per_stat - 1) / P.rows_per_stat + 1);
+            for (int i = threadIdx.x; i < nwhich * 32; i += blockDim.x) {
+                const int which = i >> 5, g = i & 31;
+                const int stat = first + which;
+                if (stat < P.nstat) {
+                    const double n = (double)P.rows_per_stat * P.Cg;
+                    const double sum = P.acc[(size_t)stat * 64 + 2 * g], sq = P.acc[(size_t)stat * 64 + 2 * g + 1];
+                    const double m = sum / n;
+                    double var = sq / n - m * m;
+                    var = var < 0.0 ? 0.0 : var;
+                    s_mr[which][g] = make_float2((float)m, rsqrtf((float)var + P.eps));
                 }
-            } else if (P.silu) {
-#pragma unroll
-                for (int e = 0; e < 4; ++e) x[e] = silu_f(x[e]);
             }
-            __nv_bfloat162 a = __floats2bfloat162_rn(x[0], x[1]), b = __floats2bfloat162_rn(x[2], x[3]);
-            o = make_uint2(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&b));
         }
-        *reinterpret_cast<uint2*>(P.dst + drow * C + c) = o;
+        __syncthreads();
+    }
+    if (ty >= P.rp) return;
+    float4 ga[kStatSlots], be[kStatSlots];
+    int grp[kStatSlots][4];
+#pragma unroll
+    for (int u = 0; u < kStatSlots; ++u) {
+        const int v = tx + u * P.tpr;
+        if (v < nvec && P.rows_per_stat > 0) {
+            ga[u] = *reinterpret_cast<const float4*>(P.gamma + (v << 2));
+            be[u] = *reinterpret_cast<const float4*>(P.beta + (v << 2));
+#pragma unroll
+            for (int e = 0; e < 4; ++e) grp[u][e] = ((v << 2) + e) / P.Cg;
+        }
+    }
+    const int first = P.rows_per_stat > 0 ? s_first : 0;
+    for (int d = d0 + ty; d < d1; d += P.rp) {
+        const int sr = apply_src_row(P, d);
+        const int which = (sr >= 0 && P.rows_per_stat > 0) ? sr / P.rows_per_stat - first : 0;
+#pragma unroll
+        for (int u = 0; u < kStatSlots; ++u) {
+            const int v = tx + u * P.tpr;
+            if (v >= nvec) continue;
+            const int c = v << 2;
+            uint2 o = make_uint2(0u, 0u);
+            if (sr >= 0) {
+                const float4 t = c < P.C1 ? __ldg(reinterpret_cast<const float4*>(P.x1 + (size_t)sr * P.C1 + c))
+                                          : __ldg(reinterpret_cast<const float4*>(P.x2 + (size_t)sr * P.C2 + (c - P.C1)));
+                float x[4] = {t.x, t.y, t.z, t.w};
+                if (P.raw) {
+                    __nv_bfloat162 a = __floats2bfloat162_rn(x[0], x[1]), b = __floats2bfloat162_rn(x[2], x[3]);
+                    *reinterpret_cast<uint2*>(P.raw + (size_t)sr * C + c) = make_uint2(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&b));
+                }
+                if (P.rows_per_stat > 0) {
+                    const float g4[4] = {ga[u].x, ga[u].y, ga[u].z, ga[u].w};
+                    const float b4[4] = {be[u].x, be[u].y, be[u].z, be[u].w};
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const float2 mr = s_mr[which][grp[u][e]];
+                        float y = (x[e] - mr.x) * mr.y * g4[e] + b4[e];
+                        if (P.silu) y = silu_f(y);
+                        x[e] = y;
+                    }
+                } else if (P.silu) {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) x[e] = silu_f(x[e]);
+                }
+                __nv_bfloat162 a = __floats2bfloat162_rn(x[0], x[1]), b = __floats2bfloat162_rn(x[2], x[3]);
+                o = make_uint2(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&b));
+            }
+            *reinterpret_cast<uint2*>(P.dst + (size_t)d * C + c) = o;
+        }
     }
 }
 
 int gn_apply(const ApplyArgs& a, cudaStream_t st) {
     const int C = a.C1 + a.C2;
-    MOCA_REQUIRE(C % 4 == 0 && a.C1 % 4 == 0, MOCA_E_SHAPE, "gn_apply: channels C1=%d C2=%d must be multiples of 4", a.C1, a.C2);
+    MOCA_REQUIRE(C % 4 == 0 && a.C1 % 4 == 0 && C <= 256 * kStatSlots * 4, MOCA_E_SHAPE, "gn_apply: channels C1=%d C2=%d unsupported", a.C1, a.C2);
     MOCA_REQUIRE(a.rows_per_stat == 0 || (a.groups == 32 && C % 32 == 0 && a.acc && a.gamma && a.beta), MOCA_E_ARG,
                  "gn_apply: bad normalisation arguments");
+    MOCA_REQUIRE(a.rows_per_stat == 0 || a.rows % a.rows_per_stat == 0, MOCA_E_SHAPE, "gn_apply: bad statistics span");
     ApplyP P;
     P.x1 = a.x1; P.C1 = a.C1; P.x2 = a.x2; P.C2 = a.C2;
     P.rows_per_stat = a.rows_per_stat; P.Cg = C / 32 > 0 ? C / 32 : 1;
     P.acc = a.acc; P.gamma = a.gamma; P.beta = a.beta; P.eps = a.eps; P.silu = a.silu; P.mode = a.dst_mode;
     P.NF = a.NF; P.H = a.H; P.W = a.W; P.T = a.T; P.HW = a.HW;
     P.dst = a.dst; P.raw = a.raw;
+    int64_t dst_rows = 0;
     switch (a.dst_mode) {
-        case DST_LINEAR: P.dst_rows = a.rows; break;
+        case DST_LINEAR: dst_rows = a.rows; break;
         case DST_SPATIAL_PAD:
             MOCA_REQUIRE((int64_t)a.NF * a.H * a.W == a.rows, MOCA_E_SHAPE, "gn_apply: spatial geometry does not match rows");
-            P.dst_rows = (int64_t)a.NF * (a.H + 2) * (a.W + 2); break;
+            dst_rows = (int64_t)a.NF * (a.H + 2) * (a.W + 2); break;
         case DST_SPATIAL_PAD_UP2:
             MOCA_REQUIRE((int64_t)a.NF * a.H * a.W == a.rows, MOCA_E_SHAPE, "gn_apply: spatial geometry does not match rows");
-            P.dst_rows = (int64_t)a.NF * (2 * a.H + 2) * (2 * a.W + 2); break;
+            dst_rows = (int64_t)a.NF * (2 * a.H + 2) * (2 * a.W + 2); break;
         case DST_TIME_PAD:
             MOCA_REQUIRE((int64_t)a.B * a.T * a.HW == a.rows, MOCA_E_SHAPE, "gn_apply: time geometry does not match rows");
-            P.dst_rows = (int64_t)a.B * (a.T + 2) * a.HW; break;
+            dst_rows = (int64_t)a.B * (a.T + 2) * a.HW; break;
         default: MOCA_REQUIRE(false, MOCA_E_ARG, "gn_apply: unknown dst mode %d", a.dst_mode);
     }
-    const int64_t total = P.dst_rows * (C / 4);
-    const int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
-    gn_apply_kernel<<<blocks, 256, 0, st>>>(P);
+    MOCA_REQUIRE(dst_rows < (1ll << 31) && a.rows < (1ll << 31), MOCA_E_SHAPE, "gn_apply: too many rows");
+    P.dst_rows = (int)dst_rows;
+    P.nstat = a.rows_per_stat > 0 ? (int)(a.rows / a.rows_per_stat) : 0;
+    int slots;
+    stat_geometry(C / 4, slots, P.tpr, P.rp);
+    gn_apply_kernel<<<cdiv(dst_rows, kApplyRows), 256, 0, st>>>(P);
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
 }
