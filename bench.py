@@ -146,10 +146,15 @@ def run_ddim(args, dev):
     torch.cuda.synchronize()
     clocks = ClockSampler(torch.cuda.current_device()); clocks.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    prof = os.environ.get("MOCA_CUDA_PROFILER") == "1"      # ncu --profile-from-start off captures the timed region only
+    if prof:
+        torch.cuda.profiler.start()
     e0.record()
     for i in range(args.warmup, total):
         x = step(i, x0, noise)
     e1.record(); torch.cuda.synchronize()
+    if prof:
+        torch.cuda.profiler.stop()
     clocks.stop_flag = True; clocks.join()
     ms = e0.elapsed_time(e1) / args.steps
     assert torch.isfinite(x).all()

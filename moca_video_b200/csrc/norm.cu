@@ -38,11 +38,12 @@ int pack_weight(const float* src, int N, int K, int taps, int Kp, __nv_bfloat16*
 // Block = TPR x RP threads: thread (x, y) owns the float4 channel vectors x, x+TPR, .. of rows y, y+RP, .. of its 32-row
 // chunk, so its channels (and groups) are fixed and partial sums stay in registers.
 constexpr int kStatSlots = 3;      // float4 slots per thread: supports C <= 256*3*4 = 3072
-constexpr int kStatChunk = 32;     // rows per block; fixed so that statistics do not depend on the batch size
+constexpr int kStatChunk = 128;    // rows per block; fixed so that statistics do not depend on the batch size
 
 __global__ void __launch_bounds__(256) gn_stats_kernel(const float* __restrict__ x1, int C1, const float* __restrict__ x2,
                                                        int C2, int rows_per_stat, int Cg, int tpr, int rp,
-                                                       double* __restrict__ acc) {
+                                                       double* __restrict__ acc, float eps, float2* __restrict__ table,
+                                                       unsigned* __restrict__ counter) {
     // per-(row lane, channel) partial sums; a thread owns its channels so plain stores suffice
     __shared__ float s_sum[256 * kStatSlots * 4];
     __shared__ float s_sq[256 * kStatSlots * 4];
@@ -58,22 +59,32 @@ __global__ void __launch_bounds__(256) gn_stats_kernel(const float* __restrict__
 #pragma unroll
         for (int e = 0; e < 4; ++e) s[u][e] = ss[u][e] = 0.0f;
     if (ty < rp) {
-#pragma unroll 4
-        for (int r = r0 + ty; r < r1; r += rp) {
-            const size_t row = (size_t)stat * rows_per_stat + r;
+        for (int r = r0 + ty; r < r1; r += 4 * rp) {
+            float4 t[4][kStatSlots];
 #pragma unroll
-            for (int u = 0; u < kStatSlots; ++u) {
-                const int v = tx + u * tpr;
-                if (v < nvec) {
-                    const int c = v << 2;
-                    const float4 t = c < C1 ? __ldg(reinterpret_cast<const float4*>(x1 + row * C1 + c))
-                                            : __ldg(reinterpret_cast<const float4*>(x2 + row * C2 + (c - C1)));
-                    s[u][0] += t.x; ss[u][0] += t.x * t.x;
-                    s[u][1] += t.y; ss[u][1] += t.y * t.y;
-                    s[u][2] += t.z; ss[u][2] += t.z * t.z;
-                    s[u][3] += t.w; ss[u][3] += t.w * t.w;
+            for (int k = 0; k < 4; ++k) {
+                const int rk = r + k * rp;
+                const size_t row = (size_t)stat * rows_per_stat + rk;
+#pragma unroll
+                for (int u = 0; u < kStatSlots; ++u) {
+                    const int v = tx + u * tpr;
+                    t[k][u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (rk < r1 && v < nvec) {
+                        const int c = v << 2;
+                        t[k][u] = c < C1 ? __ldg(reinterpret_cast<const float4*>(x1 + row * C1 + c))
+                                         : __ldg(reinterpret_cast<const float4*>(x2 + row * C2 + (c - C1)));
+                    }
                 }
             }
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+#pragma unroll
+                for (int u = 0; u < kStatSlots; ++u) {
+                    s[u][0] += t[k][u].x; ss[u][0] += t[k][u].x * t[k][u].x;
+                    s[u][1] += t[k][u].y; ss[u][1] += t[k][u].y * t[k][u].y;
+                    s[u][2] += t[k][u].z; ss[u][2] += t[k][u].z * t[k][u].z;
+                    s[u][3] += t[k][u].w; ss[u][3] += t[k][u].w * t[k][u].w;
+                }
         }
 #pragma unroll
         for (int u = 0; u < kStatSlots; ++u) {
@@ -94,6 +105,25 @@ __global__ void __launch_bounds__(256) gn_stats_kernel(const float* __restrict__
             for (int c = g * Cg; c < (g + 1) * Cg; ++c) a += (double)src[y * C + c];
         atomicAdd(&acc[(size_t)stat * 64 + threadIdx.x], a);
     }
+    // last block of this statistics group: sums -> (mean, rstd)
+    __shared__ unsigned s_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(&counter[stat], 1u) == gridDim.x - 1 ? 1u : 0u;
+    __syncthreads();
+    if (s_last) {
+        __threadfence();
+        if (threadIdx.x < 32) {
+            const int g = threadIdx.x;
+            const double n = (double)rows_per_stat * Cg;
+            const double sum = __ldcg(&acc[(size_t)stat * 64 + 2 * g]), sq = __ldcg(&acc[(size_t)stat * 64 + 2 * g + 1]);
+            const double m = sum / n;
+            double var = sq / n - m * m;
+            var = var < 0.0 ? 0.0 : var;
+            table[(size_t)stat * 32 + g] = make_float2((float)m, rsqrtf((float)var + eps));
+        }
+        if (threadIdx.x == 0) counter[stat] = 0u;
+    }
 }
 
 static void stat_geometry(int nvec, int& slots, int& tpr, int& rp) {
@@ -105,7 +135,7 @@ static void stat_geometry(int nvec, int& slots, int& tpr, int& rp) {
 }
 
 int gn_stats(const float* x1, int C1, const float* x2, int C2, int64_t rows, int rows_per_stat, int groups, double* acc,
-             cudaStream_t st) {
+             float eps, float2* table, unsigned* counter, cudaStream_t st) {
     const int C = C1 + C2;
     MOCA_REQUIRE(groups == 32 && C % 32 == 0 && C % 4 == 0 && C1 % 4 == 0 && C <= 256 * kStatSlots * 4, MOCA_E_SHAPE,
                  "gn_stats: unsupported channels C1=%d C2=%d groups=%d", C1, C2, groups);
@@ -114,30 +144,25 @@ int gn_stats(const float* x1, int C1, const float* x2, int C2, int64_t rows, int
     int slots, tpr, rp;
     stat_geometry(C / 4, slots, tpr, rp);
     dim3 grid(cdiv(rows_per_stat, kStatChunk), nstat);
-    gn_stats_kernel<<<grid, 256, 0, st>>>(x1, C1, x2, C2, rows_per_stat, C / 32, tpr, rp, acc);
+    gn_stats_kernel<<<grid, 256, 0, st>>>(x1, C1, x2, C2, rows_per_stat, C / 32, tpr, rp, acc, eps, table, counter);
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// GroupNorm apply (+SiLU) with layout scatter.  Block = TPR x RP threads as above; each block walks kApplyRows destination
-// rows.  A thread's channels are fixed: gamma / beta / group ids live in registers; mean / rstd of the (at most two)
-// statistics groups a block touches are derived once per block into shared memory.
+// GroupNorm apply (+SiLU) with layout scatter: one warp per destination row, lanes stride over the row's float4 channel
+// vectors with up to 4 loads in flight each; no block-level synchronisation.
 struct ApplyP {
     const float* x1; int C1;
     const float* x2; int C2;
     int rows_per_stat; int Cg;
-    const double* acc; const float* gamma; const float* beta;
-    float eps; int silu; int mode;
+    const float2* table; const float* gamma; const float* beta;
+    int silu; int mode;
     int NF, H, W;        // source geometry
     int T, HW;
     int dst_rows;        // rows of the destination layout
-    int nstat;
-    int tpr, rp;
     __nv_bfloat16* dst; __nv_bfloat16* raw;
 };
-
-constexpr int kApplyRows = 16;
 
 __device__ __forceinline__ float silu_f(float v) { return __fdividef(v, 1.0f + __expf(-v)); }
 
@@ -158,92 +183,61 @@ __device__ __forceinline__ int apply_src_row(const ApplyP& P, int drow) {
     return (f * P.H + ((hp - 1) >> up)) * P.W + ((wp - 1) >> up);
 }
 
+__device__ __forceinline__ uint2 pack4(const float* x) {
+    __nv_bfloat162 a = __floats2bfloat162_rn(x[0], x[1]), b = __floats2bfloat162_rn(x[2], x[3]);
+    return make_uint2(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&b));
+}
+
 __global__ void __launch_bounds__(256) gn_apply_kernel(const __grid_constant__ ApplyP P) {
-    __shared__ float2 s_mr[kApplyRows + 1][32];   // (mean, rstd) of statistics groups s_first, s_first + 1, ..
-    __shared__ int s_first;
+    const int lane = threadIdx.x & 31;
+    const int drow = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (drow >= P.dst_rows) return;
     const int C = P.C1 + P.C2;
     const int nvec = C >> 2;
-    const int tx = threadIdx.x % P.tpr, ty = threadIdx.x / P.tpr;
-    const int d0 = blockIdx.x * kApplyRows;
-    const int d1 = min(P.dst_rows, d0 + kApplyRows);
-    if (P.rows_per_stat > 0) {
-        if (threadIdx.x == 0) {
-            int first = -1;
-            for (int d = d0; d < d1 && first < 0; ++d) {
-                const int sr = apply_src_row(P, d);
-                if (sr >= 0) first = sr / P.rows_per_stat;
-            }
-            s_first = first;
-        }
-        __syncthreads();
-        const int first = s_first;
-        if (first >= 0) {
-            // a block's kApplyRows destination rows map to at most kApplyRows consecutive statistics groups
-            const int nwhich = min(kApplyRows + 1, (kApplyRows + P.rows_per_stat - 1) / P.rows_per_stat + 1);
-            for (int i = threadIdx.x; i < nwhich * 32; i += blockDim.x) {
-                const int which = i >> 5, g = i & 31;
-                const int stat = first + which;
-                if (stat < P.nstat) {
-                    const double n = (double)P.rows_per_stat * P.Cg;
-                    const double sum = P.acc[(size_t)stat * 64 + 2 * g], sq = P.acc[(size_t)stat * 64 + 2 * g + 1];
-                    const double m = sum / n;
-                    double var = sq / n - m * m;
-                    var = var < 0.0 ? 0.0 : var;
-                    s_mr[which][g] = make_float2((float)m, rsqrtf((float)var + P.eps));
-                }
-            }
-        }
-        __syncthreads();
+    const int sr = apply_src_row(P, drow);
+    uint2* drow_p = reinterpret_cast<uint2*>(P.dst + (size_t)drow * C);
+    if (sr < 0) {
+        for (int v = lane; v < nvec; v += 32) drow_p[v] = make_uint2(0u, 0u);
+        return;
     }
-    if (ty >= P.rp) return;
-    float4 ga[kStatSlots], be[kStatSlots];
-    int grp[kStatSlots][4];
+    const float2* tab = P.rows_per_stat > 0 ? P.table + (size_t)(sr / P.rows_per_stat) * 32 : nullptr;
+    const float4* s1 = reinterpret_cast<const float4*>(P.x1 + (size_t)sr * P.C1);
+    const float4* s2 = P.x2 ? reinterpret_cast<const float4*>(P.x2 + (size_t)sr * P.C2) : nullptr;
+    const int nv1 = P.C1 >> 2;
+    for (int v0 = lane; v0 < nvec; v0 += 128) {
+        float4 t[4];
 #pragma unroll
-    for (int u = 0; u < kStatSlots; ++u) {
-        const int v = tx + u * P.tpr;
-        if (v < nvec && P.rows_per_stat > 0) {
-            ga[u] = *reinterpret_cast<const float4*>(P.gamma + (v << 2));
-            be[u] = *reinterpret_cast<const float4*>(P.beta + (v << 2));
-#pragma unroll
-            for (int e = 0; e < 4; ++e) grp[u][e] = ((v << 2) + e) / P.Cg;
+        for (int k = 0; k < 4; ++k) {
+            const int v = v0 + 32 * k;
+            if (v < nvec) t[k] = v < nv1 ? __ldg(s1 + v) : __ldg(s2 + (v - nv1));
         }
-    }
-    const int first = P.rows_per_stat > 0 ? s_first : 0;
-    for (int d = d0 + ty; d < d1; d += P.rp) {
-        const int sr = apply_src_row(P, d);
-        const int which = (sr >= 0 && P.rows_per_stat > 0) ? sr / P.rows_per_stat - first : 0;
 #pragma unroll
-        for (int u = 0; u < kStatSlots; ++u) {
-            const int v = tx + u * P.tpr;
+        for (int k = 0; k < 4; ++k) {
+            const int v = v0 + 32 * k;
             if (v >= nvec) continue;
             const int c = v << 2;
-            uint2 o = make_uint2(0u, 0u);
-            if (sr >= 0) {
-                const float4 t = c < P.C1 ? __ldg(reinterpret_cast<const float4*>(P.x1 + (size_t)sr * P.C1 + c))
-                                          : __ldg(reinterpret_cast<const float4*>(P.x2 + (size_t)sr * P.C2 + (c - P.C1)));
-                float x[4] = {t.x, t.y, t.z, t.w};
-                if (P.raw) {
-                    __nv_bfloat162 a = __floats2bfloat162_rn(x[0], x[1]), b = __floats2bfloat162_rn(x[2], x[3]);
-                    *reinterpret_cast<uint2*>(P.raw + (size_t)sr * C + c) = make_uint2(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&b));
-                }
-                if (P.rows_per_stat > 0) {
-                    const float g4[4] = {ga[u].x, ga[u].y, ga[u].z, ga[u].w};
-                    const float b4[4] = {be[u].x, be[u].y, be[u].z, be[u].w};
+            float x[4] = {t[k].x, t[k].y, t[k].z, t[k].w};
+            if (P.raw) *reinterpret_cast<uint2*>(P.raw + (size_t)sr * C + c) = pack4(x);
+            if (tab) {
+                const float4 g4 = __ldg(reinterpret_cast<const float4*>(P.gamma + c));
+                const float4 b4 = __ldg(reinterpret_cast<const float4*>(P.beta + c));
+                const float gg[4] = {g4.x, g4.y, g4.z, g4.w}, bb[4] = {b4.x, b4.y, b4.z, b4.w};
+                const int g0 = c / P.Cg, g1 = (c + 3) / P.Cg;
+                const float2 m0 = __ldg(tab + g0);
+                const float2 m1 = g1 != g0 ? __ldg(tab + g1) : m0;
+                const int split = (g0 + 1) * P.Cg - c;           // first element index that belongs to g1
 #pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                        const float2 mr = s_mr[which][grp[u][e]];
-                        float y = (x[e] - mr.x) * mr.y * g4[e] + b4[e];
-                        if (P.silu) y = silu_f(y);
-                        x[e] = y;
-                    }
-                } else if (P.silu) {
-#pragma unroll
-                    for (int e = 0; e < 4; ++e) x[e] = silu_f(x[e]);
+                for (int e = 0; e < 4; ++e) {
+                    const float2 mr = e < split ? m0 : m1;
+                    float y = (x[e] - mr.x) * mr.y * gg[e] + bb[e];
+                    if (P.silu) y = silu_f(y);
+                    x[e] = y;
                 }
-                __nv_bfloat162 a = __floats2bfloat162_rn(x[0], x[1]), b = __floats2bfloat162_rn(x[2], x[3]);
-                o = make_uint2(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&b));
+            } else if (P.silu) {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) x[e] = silu_f(x[e]);
             }
-            *reinterpret_cast<uint2*>(P.dst + (size_t)d * C + c) = o;
+            drow_p[v] = pack4(x);
         }
     }
 }
@@ -251,13 +245,13 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const __grid_constant__ A
 int gn_apply(const ApplyArgs& a, cudaStream_t st) {
     const int C = a.C1 + a.C2;
     MOCA_REQUIRE(C % 4 == 0 && a.C1 % 4 == 0 && C <= 256 * kStatSlots * 4, MOCA_E_SHAPE, "gn_apply: channels C1=%d C2=%d unsupported", a.C1, a.C2);
-    MOCA_REQUIRE(a.rows_per_stat == 0 || (a.groups == 32 && C % 32 == 0 && a.acc && a.gamma && a.beta), MOCA_E_ARG,
+    MOCA_REQUIRE(a.rows_per_stat == 0 || (a.groups == 32 && C % 32 == 0 && C / 32 >= 2 && a.table && a.gamma && a.beta), MOCA_E_ARG,
                  "gn_apply: bad normalisation arguments");
     MOCA_REQUIRE(a.rows_per_stat == 0 || a.rows % a.rows_per_stat == 0, MOCA_E_SHAPE, "gn_apply: bad statistics span");
     ApplyP P;
     P.x1 = a.x1; P.C1 = a.C1; P.x2 = a.x2; P.C2 = a.C2;
     P.rows_per_stat = a.rows_per_stat; P.Cg = C / 32 > 0 ? C / 32 : 1;
-    P.acc = a.acc; P.gamma = a.gamma; P.beta = a.beta; P.eps = a.eps; P.silu = a.silu; P.mode = a.dst_mode;
+    P.table = a.table; P.gamma = a.gamma; P.beta = a.beta; P.silu = a.silu; P.mode = a.dst_mode;
     P.NF = a.NF; P.H = a.H; P.W = a.W; P.T = a.T; P.HW = a.HW;
     P.dst = a.dst; P.raw = a.raw;
     int64_t dst_rows = 0;
@@ -276,10 +270,7 @@ int gn_apply(const ApplyArgs& a, cudaStream_t st) {
     }
     MOCA_REQUIRE(dst_rows < (1ll << 31) && a.rows < (1ll << 31), MOCA_E_SHAPE, "gn_apply: too many rows");
     P.dst_rows = (int)dst_rows;
-    P.nstat = a.rows_per_stat > 0 ? (int)(a.rows / a.rows_per_stat) : 0;
-    int slots;
-    stat_geometry(C / 4, slots, P.tpr, P.rp);
-    gn_apply_kernel<<<cdiv(dst_rows, kApplyRows), 256, 0, st>>>(P);
+    gn_apply_kernel<<<cdiv(dst_rows, 8), 256, 0, st>>>(P);
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
 }

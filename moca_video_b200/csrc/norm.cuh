@@ -16,8 +16,10 @@ int pack_weight(const float* src, int N, int K, int taps, int Kp, __nv_bfloat16*
 // Sum / sum of squares per (stat group, channel group) in double.  Tokens are channels-last fp32 [rows, C1] (+ optional
 // second source [rows, C2] = virtual channel concat, openaimodel3d.py:571).  rows_per_stat = H*W (per-frame GroupNorm)
 // or T*H*W (GroupNorm on 5-D input: TemporalConvBlock / TemporalTransformer).  acc: [nstat, 32, 2] doubles, zeroed.
+// The last block of each statistics group to finish turns the sums into (mean, rstd) pairs: table [nstat, 32] float2.
+// counter: [nstat] unsigned, zero before the first launch, reset by the kernel itself.
 int gn_stats(const float* x1, int C1, const float* x2, int C2, int64_t rows, int rows_per_stat, int groups, double* acc,
-             cudaStream_t st);
+             float eps, float2* table, unsigned* counter, cudaStream_t st);
 
 struct ApplyArgs {
     const float* x1 = nullptr; int C1 = 0;
@@ -25,7 +27,7 @@ struct ApplyArgs {
     int64_t rows = 0;
     int rows_per_stat = 0;          // 0: no normalisation (plain convert)
     int groups = 32;
-    const double* acc = nullptr;
+    const float2* table = nullptr;  // (mean, rstd) per (statistics group, channel group), written by gn_stats
     const float* gamma = nullptr; const float* beta = nullptr;
     float eps = 1e-5f;
     int silu = 0;

@@ -124,15 +124,18 @@ extern "C" int32_t moca_groupnorm_bf16(moca_ctx* ctx, const float* x, const floa
     cudaStream_t st = (cudaStream_t)stream;
     const int nstat = (int)(rows / rows_per_stat);
     double* acc = dmalloc<double>((size_t)nstat * 64);
-    MOCA_REQUIRE(acc, MOCA_E_CUDA, "moca_groupnorm_bf16: allocation failed");
+    float2* table = dmalloc<float2>((size_t)nstat * 32);
+    unsigned* counter = dmalloc<unsigned>((size_t)nstat);
+    MOCA_REQUIRE(acc && table && counter, MOCA_E_CUDA, "moca_groupnorm_bf16: allocation failed");
     cudaMemsetAsync(acc, 0, (size_t)nstat * 64 * sizeof(double), st);
-    int rc = gn_stats(x, C, nullptr, 0, rows, rows_per_stat, 32, acc, st);
+    cudaMemsetAsync(counter, 0, (size_t)nstat * sizeof(unsigned), st);
+    int rc = gn_stats(x, C, nullptr, 0, rows, rows_per_stat, 32, acc, eps, table, counter, st);
     ApplyArgs a;
-    a.x1 = x; a.C1 = C; a.rows = rows; a.rows_per_stat = rows_per_stat; a.acc = acc; a.gamma = gamma; a.beta = beta; a.eps = eps;
+    a.x1 = x; a.C1 = C; a.rows = rows; a.rows_per_stat = rows_per_stat; a.table = table; a.gamma = gamma; a.beta = beta; a.eps = eps;
     a.silu = silu; a.dst_mode = DST_LINEAR; a.dst = (__nv_bfloat16*)out_bf16;
     if (!rc) rc = gn_apply(a, st);
     cudaStreamSynchronize(st);
-    cudaFree(acc);
+    cudaFree(acc); cudaFree(table); cudaFree(counter);
     return rc;
 }
 

@@ -34,6 +34,8 @@ struct Plan {
     float* out_tok = nullptr;
     double* stats = nullptr;
     size_t stats_bytes = 0;
+    float2* mr_table = nullptr;       // (mean, rstd) tables written by gn_stats, one slot per GroupNorm
+    unsigned* stat_counters = nullptr;
     cudaGraphExec_t gexec = nullptr;
     std::vector<Tap> taps;
     bool with_taps = false;
@@ -86,10 +88,7 @@ struct Builder {
         plan->launches += nlaunch;
         if (!dry) raw_push(std::move(op), label, flops);
     }
-    double* stat_slot() {
-        const int s = stat_slots++;
-        return dry ? nullptr : plan->stats + (size_t)s * NF * 64;
-    }
+    int stat_slot() { return stat_slots++; }
 
     // ---- GEMM flavours -------------------------------------------------------------------------------------
     void gemm(GemmDesc d, double useful_flops) {
@@ -138,15 +137,17 @@ struct Builder {
     // ---- normalisation flavours ----------------------------------------------------------------------------
     void gnorm(const float* x1, int C1, const float* x2, int C2, int64_t rows, int rows_per_stat, const NormW& w, float eps, int silu,
                int dst_mode, int H, int W, __nv_bfloat16* dst, __nv_bfloat16* raw) {
-        double* acc = stat_slot();
+        const int slot = stat_slot();
+        double* acc = dry ? nullptr : plan->stats + (size_t)slot * NF * 64;
+        float2* table = dry ? nullptr : plan->mr_table + (size_t)slot * NF * 32;
+        unsigned* counter = dry ? nullptr : plan->stat_counters + (size_t)slot * NF;
         ApplyArgs a;
-        a.x1 = x1; a.C1 = C1; a.x2 = x2; a.C2 = C2; a.rows = rows; a.rows_per_stat = rows_per_stat; a.acc = acc;
+        a.x1 = x1; a.C1 = C1; a.x2 = x2; a.C2 = C2; a.rows = rows; a.rows_per_stat = rows_per_stat; a.table = table;
         a.gamma = w.g; a.beta = w.b; a.eps = eps; a.silu = silu; a.dst_mode = dst_mode;
         a.NF = NF; a.H = H; a.W = W; a.B = B; a.T = T; a.HW = H * W; a.dst = dst; a.raw = raw;
-        push([=](cudaStream_t st) {
-            int r = gn_stats(x1, C1, x2, C2, rows, rows_per_stat, 32, acc, st);
-            return r ? r : gn_apply(a, st);
-        }, 2, "gnorm rows=" + std::to_string(rows) + " C=" + std::to_string(C1 + C2) + " dst=" + std::to_string(dst_mode));
+        const std::string dims = " rows=" + std::to_string(rows) + " C=" + std::to_string(C1 + C2) + " dst=" + std::to_string(dst_mode);
+        push([=](cudaStream_t st) { return gn_stats(x1, C1, x2, C2, rows, rows_per_stat, 32, acc, eps, table, counter, st); }, 1, "gn_stats" + dims);
+        push([=](cudaStream_t st) { return gn_apply(a, st); }, 1, "gn_apply" + dims);
     }
     void convert(const float* x, int C, int64_t rows, int dst_mode, int H, int W, __nv_bfloat16* dst) {
         ApplyArgs a;
@@ -439,6 +440,9 @@ static int get_plan(moca_unet* n, int B, int T, int H, int W, int Lmax, Plan** o
     plan->launches = 0; plan->flops = 0;
     plan->stats_bytes = (size_t)dry.stat_slots * B * T * 64 * sizeof(double);
     plan->stats = (double*)real.palloc(plan->stats_bytes);
+    plan->mr_table = (float2*)real.palloc((size_t)dry.stat_slots * B * T * 32 * sizeof(float2));
+    plan->stat_counters = (unsigned*)real.palloc((size_t)dry.stat_slots * B * T * sizeof(unsigned));
+    if (plan->stat_counters) cudaMemset(plan->stat_counters, 0, (size_t)dry.stat_slots * B * T * sizeof(unsigned));
     for (int i = 0; i < S_COUNT; ++i) {
         real.sptr[i] = real.palloc(dry.need[i] + 256);
         plan->workspace_bytes += dry.need[i];
