@@ -9,3 +9,4 @@ python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/bench_short.
 ncu --metrics gpu__time_duration.sum --clock-control none -s 3000 -c 2000 --csv --log-file gpurun_out/launches.csv \
     python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_bench.log 2>&1
 echo "ncu rc=$?"; tail -n 3 gpurun_out/ncu_bench.log; wc -l gpurun_out/launches.csv
+timeout 600 python tools/profile_forward.py 2 gpurun_out/profile_ops_b2.csv 2>&1 | tail -16
