@@ -70,7 +70,7 @@ __device__ __forceinline__ bool map_row(const GemmParams& P, int row, int& out_r
     return true;
 }
 
-template <int BN, int EPI>
+template <int BN, int EPI, bool STATS>
 __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_constant__ GemmParams P) {
     using Cfg = GemmCfg<BN>;
     constexpr int STAGES = Cfg::STAGES;
@@ -175,12 +175,20 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
         int as = 0;
         uint32_t aphase = 0;
 
-        auto tile_rows = [&](int tile, int& out_row, uint32_t& vmask) {
+        // frame_u: the frame all valid rows of this warp's 32-row slice belong to, or -1 when they straddle frames
+        auto tile_rows = [&](int tile, int& out_row, uint32_t& vmask, int& frame_u) {
             const int mt = tile / P.num_n_tiles;
             const int row = mt * kBM + q * 32 + lane;
             out_row = 0;
             const bool valid = map_row(P, row, out_row);
             vmask = __ballot_sync(0xffffffffu, valid);
+            frame_u = -1;
+            if constexpr (STATS) {
+                const int fr = out_row / P.stat_rpf;
+                const int lo = __reduce_min_sync(0xffffffffu, valid ? fr : 0x7fffffff);
+                const int hi = __reduce_max_sync(0xffffffffu, valid ? fr : -1);
+                if (lo == hi && (P.stat_fast || P.spart)) frame_u = lo;
+            }
         };
         auto col0_of = [&](int tile) {
             const int nt = tile % P.num_n_tiles;
@@ -208,11 +216,12 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
 
         int tile = blockIdx.x;
         int out_row = 0, nxt_row = 0;
+        int frame_u = -1, nxt_frame = -1;
         uint32_t vmask = 0, nxt_mask = 0;
         float4 pre[8];
         bool have_pre = false;
         if (tile < ntiles) {
-            tile_rows(tile, out_row, vmask);
+            tile_rows(tile, out_row, vmask, frame_u);
             if (EPI == EPI_F32 && col0_of(tile) + half * 32 < ncols_total) {
                 prefetch(pre, out_row, vmask, col0_of(tile) + half * 32);
                 have_pre = true;
@@ -239,7 +248,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
                         prefetch(nxt, out_row, vmask, n0 + 64);
                         have_nxt = true;
                     } else if (ntile < ntiles) {
-                        if (!nxt_ready) { tile_rows(ntile, nxt_row, nxt_mask); nxt_ready = true; }
+                        if (!nxt_ready) { tile_rows(ntile, nxt_row, nxt_mask, nxt_frame); nxt_ready = true; }
                         if (col0_of(ntile) + half * 32 < ncols_total) {
                             prefetch(nxt, nxt_row, nxt_mask, col0_of(ntile) + half * 32);
                             have_nxt = true;
@@ -255,10 +264,12 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
                     const int nvalid = min(4, P.N - col);          // <= 0: nothing to store for this lane
                     float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
                     if (P.bias && nvalid >= 4) b4 = __ldg(reinterpret_cast<const float4*>(P.bias + col));
+                    float4 vv[8];                                    // stored values (zero for rows / columns not stored)
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
                         const int rr = i * 4 + (lane >> 3);
                         const int orow = __shfl_sync(0xffffffffu, out_row, rr);
+                        vv[i] = make_float4(0.f, 0.f, 0.f, 0.f);
                         if (!((vmask >> rr) & 1u) || nvalid <= 0) continue;
                         float4 v = *reinterpret_cast<const float4*>(stg + rr * 32 + ((cc ^ (rr & 7)) << 2));
                         const size_t o = (size_t)orow * P.ldo + col;
@@ -266,13 +277,81 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
                             v.x += b4.x; v.y += b4.y; v.z += b4.z; v.w += b4.w;
                             if (have_pre) { v.x += pre[i].x; v.y += pre[i].y; v.z += pre[i].z; v.w += pre[i].w; }
                             *reinterpret_cast<float4*>(P.outf + o) = v;
+                            vv[i] = v;
                         } else {                                     // ragged last columns (N % 4 != 0): scalar path
-                            const float vv[4] = {v.x, v.y, v.z, v.w};
+                            const float sv[4] = {v.x, v.y, v.z, v.w};
                             for (int e = 0; e < nvalid; ++e) {
-                                float t = vv[e] + (P.bias ? P.bias[col + e] : 0.f);
+                                float t = sv[e] + (P.bias ? P.bias[col + e] : 0.f);
                                 if (P.rowbias) t += P.rowbias[(size_t)(orow / P.rows_per_frame) * P.rb_ld + col + e];
                                 if (P.residual) t += P.residual[o + e];
                                 P.outf[o + e] = t;
+                            }
+                        }
+                    }
+                    if constexpr (STATS) {
+                        if (frame_u >= 0) {
+                            // all valid rows of the slice are one frame: fp32 partials, 8 rows per lane -> 32 rows
+                            // (lanes with equal (lane & 7) hold the same 4 columns)
+                            float4 cs = make_float4(0.f, 0.f, 0.f, 0.f), cq = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) {
+                                cs.x += vv[i].x; cs.y += vv[i].y; cs.z += vv[i].z; cs.w += vv[i].w;
+                                cq.x = fmaf(vv[i].x, vv[i].x, cq.x); cq.y = fmaf(vv[i].y, vv[i].y, cq.y);
+                                cq.z = fmaf(vv[i].z, vv[i].z, cq.z); cq.w = fmaf(vv[i].w, vv[i].w, cq.w);
+                            }
+#pragma unroll
+                            for (int o = 8; o <= 16; o <<= 1) {
+                                cs.x += __shfl_xor_sync(0xffffffffu, cs.x, o); cs.y += __shfl_xor_sync(0xffffffffu, cs.y, o);
+                                cs.z += __shfl_xor_sync(0xffffffffu, cs.z, o); cs.w += __shfl_xor_sync(0xffffffffu, cs.w, o);
+                                cq.x += __shfl_xor_sync(0xffffffffu, cq.x, o); cq.y += __shfl_xor_sync(0xffffffffu, cq.y, o);
+                                cq.z += __shfl_xor_sync(0xffffffffu, cq.z, o); cq.w += __shfl_xor_sync(0xffffffffu, cq.w, o);
+                            }
+                            const int e = lane >> 3;                   // lane group e publishes column col + e
+                            const float s1 = e == 0 ? cs.x : (e == 1 ? cs.y : (e == 2 ? cs.z : cs.w));
+                            const float s2 = e == 0 ? cq.x : (e == 1 ? cq.y : (e == 2 ? cq.z : cq.w));
+                            if (P.spart) {
+                                // partial-sum mode: one {sum, sumsq} per (32-row slice, column), plain coalesced stores;
+                                // gn_finalize adds the slices of a frame in a fixed order
+                                if (nvalid >= 4)
+                                    P.spart[(size_t)((tile / P.num_n_tiles) * (kBM / 32) + q) * P.N + col + e] = make_float2(s1, s2);
+                            } else if (nvalid >= 4) {
+                                double* d = P.cstat + ((size_t)frame_u * P.N + col + e) * 2;
+                                atomicAdd(d, (double)s1);
+                                atomicAdd(d + 1, (double)s2);
+                            }
+                        } else if (vmask != 0u && P.cstat) {
+                            // slice straddles frames (or samples are not 32-row aligned): exact double partials per lane,
+                            // flushed when the frame changes — the result does not depend on the row grouping
+                            double ds[4] = {0.0, 0.0, 0.0, 0.0}, dq[4] = {0.0, 0.0, 0.0, 0.0};
+                            int dfr = -1;
+#pragma unroll 1
+                            for (int i = 0; i <= 8; ++i) {
+                                const int rr = (i & 7) * 4 + (lane >> 3);
+                                const int orow = __shfl_sync(0xffffffffu, out_row, rr);
+                                const bool ok = i < 8 && ((vmask >> rr) & 1u) && nvalid >= 4;
+                                const int fr = ok ? orow / P.stat_rpf : -1;
+                                if ((fr != dfr || i == 8) && dfr >= 0) {
+                                    double* d = P.cstat + ((size_t)dfr * P.N + col) * 2;
+#pragma unroll
+                                    for (int e = 0; e < 4; ++e) {
+                                        atomicAdd(d + 2 * e, ds[e]);
+                                        atomicAdd(d + 2 * e + 1, dq[e]);
+                                        ds[e] = 0.0; dq[e] = 0.0;
+                                    }
+                                }
+                                dfr = fr;
+                                if (ok) {
+                                    float4 t = vv[0];
+#pragma unroll
+                                    for (int k = 1; k < 8; ++k)
+                                        if (i == k) t = vv[k];
+                                    const float sv[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+                                    for (int e = 0; e < 4; ++e) {
+                                        ds[e] += (double)sv[e];
+                                        dq[e] = fma((double)sv[e], (double)sv[e], dq[e]);
+                                    }
+                                }
                             }
                         }
                     }
@@ -350,10 +429,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
             as ^= 1;
             if (as == 0) aphase ^= 1;
             if (EPI == EPI_F32) {
-                if (!nxt_ready && ntile < ntiles) tile_rows(ntile, nxt_row, nxt_mask);
-                out_row = nxt_row; vmask = nxt_mask;
+                if (!nxt_ready && ntile < ntiles) tile_rows(ntile, nxt_row, nxt_mask, nxt_frame);
+                out_row = nxt_row; vmask = nxt_mask; frame_u = nxt_frame;
             } else if (ntile < ntiles) {
-                tile_rows(ntile, out_row, vmask);
+                tile_rows(ntile, out_row, vmask, frame_u);
             }
         }
     }
@@ -427,11 +506,11 @@ static int pick_bn(const GemmDesc& d, int num_sms) {
     return best;
 }
 
-template <int BN, int EPI>
+template <int BN, int EPI, bool STATS = false>
 static int set_attr() {
     static bool done = false;
     if (!done) {
-        MOCA_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GemmCfg<BN>::SMEM));
+        MOCA_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI, STATS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GemmCfg<BN>::SMEM));
         done = true;
     }
     return MOCA_OK;
@@ -439,16 +518,17 @@ static int set_attr() {
 
 template <int BN>
 static int set_attr_bn(int epi) {
-    if (epi == EPI_F32) return set_attr<BN, EPI_F32>();
+    if (epi == EPI_F32) { int rc = set_attr<BN, EPI_F32, true>(); return rc ? rc : set_attr<BN, EPI_F32>(); }
     if (epi == EPI_BF16) return set_attr<BN, EPI_BF16>();
     return set_attr<BN, EPI_GEGLU>();
 }
 
 template <int BN>
 static void launch_bn(const GemmLaunch& l, cudaStream_t st) {
-    if (l.p.epi == EPI_F32) gemm_tc_kernel<BN, EPI_F32><<<l.grid, kGemmThreads, l.smem, st>>>(l.p);
-    else if (l.p.epi == EPI_BF16) gemm_tc_kernel<BN, EPI_BF16><<<l.grid, kGemmThreads, l.smem, st>>>(l.p);
-    else gemm_tc_kernel<BN, EPI_GEGLU><<<l.grid, kGemmThreads, l.smem, st>>>(l.p);
+    if (l.p.epi == EPI_F32 && (l.p.cstat || l.p.spart)) gemm_tc_kernel<BN, EPI_F32, true><<<l.grid, kGemmThreads, l.smem, st>>>(l.p);
+    else if (l.p.epi == EPI_F32) gemm_tc_kernel<BN, EPI_F32, false><<<l.grid, kGemmThreads, l.smem, st>>>(l.p);
+    else if (l.p.epi == EPI_BF16) gemm_tc_kernel<BN, EPI_BF16, false><<<l.grid, kGemmThreads, l.smem, st>>>(l.p);
+    else gemm_tc_kernel<BN, EPI_GEGLU, false><<<l.grid, kGemmThreads, l.smem, st>>>(l.p);
 }
 
 int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
@@ -473,6 +553,16 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
     p.outf = (float*)d.out; p.outb = (__nv_bfloat16*)d.out; p.ldo = d.ldo;
     p.bias = d.bias; p.rowbias = d.rowbias; p.rb_ld = d.rb_ld; p.rows_per_frame = d.rows_per_frame > 0 ? d.rows_per_frame : 1;
     p.residual = d.residual; p.epi = d.epi;
+    p.cstat = d.chan_stats; p.stat_rpf = d.stat_rows_per_frame > 0 ? d.stat_rows_per_frame : 1;
+    // fp32 warp-slice partial sums only when every sample starts on a 32-row slice boundary, so that the grouping (and
+    // with it every rounding) is the same whatever the batch size; otherwise exact double partials
+    p.stat_fast = d.stat_sample_rows > 0 && d.stat_sample_rows % 32 == 0;
+    p.spart = d.stat_partials;
+    MOCA_REQUIRE(!d.stat_partials || (!d.chan_stats && d.epi == EPI_F32 && d.N % 4 == 0 && d.stat_rows_per_frame % 32 == 0 &&
+                                      (d.mode == GEMM_LINEAR || (d.mode == GEMM_TIME_PAD && d.g_w % 32 == 0))),
+                 MOCA_E_ARG, "gemm_plan: slice partial statistics need 32-row aligned frames (linear / time-padded rows)");
+    MOCA_REQUIRE(!d.chan_stats || (d.epi == EPI_F32 && d.N % 4 == 0 && d.stat_rows_per_frame > 0), MOCA_E_ARG,
+                 "gemm_plan: channel statistics need the fp32 epilogue, N %% 4 == 0 and rows per frame");
     p.num_m_tiles = cdiv(d.M, kBM);
     p.num_n_tiles = cdiv(d.N, L.BN);
     const int ntiles = p.num_m_tiles * p.num_n_tiles;

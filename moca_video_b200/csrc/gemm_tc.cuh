@@ -43,6 +43,10 @@ struct GemmParams {
     const float* residual;    // fp32 [out_rows, ldo] or null
     int epi;
     int num_m_tiles, num_n_tiles;
+    double* cstat;            // optional per-(frame, output channel) {sum, sum of squares} of the stored fp32 values
+    int stat_rpf;             // output rows per frame (frame = out_row / stat_rpf)
+    int stat_fast;
+    float2* spart;            // optional {sum, sumsq} per (32-row slice of the input-row space, column): [ceil(M/32)][N]
 };
 
 struct GemmDesc {
@@ -62,6 +66,12 @@ struct GemmDesc {
     const float* rowbias = nullptr;
     int rb_ld = 0, rows_per_frame = 1;
     const float* residual = nullptr;
+    // EPI_F32 only: accumulate {sum, sumsq} of the stored values into chan_stats[frame][N][2] (doubles, zeroed by the
+    // caller) — the GroupNorm that consumes this tensor needs no statistics pass of its own.
+    double* chan_stats = nullptr;
+    int stat_rows_per_frame = 0;
+    float2* stat_partials = nullptr;  // alternative to chan_stats for 32-row aligned frames: [ceil(M/32)][N] float2, no atomics
+    int stat_sample_rows = 0;         // rows of one sample in the GEMM's input-row space (0: unknown -> exact double partials)
 };
 
 struct GemmLaunch {

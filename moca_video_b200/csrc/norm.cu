@@ -150,6 +150,67 @@ int gn_stats(const float* x1, int C1, const float* x2, int C2, int64_t rows, int
 }
 
 // ---------------------------------------------------------------------------------------------------------------
+// GroupNorm statistics from what the GEMM epilogues left behind (gemm_tc.cuh): per-(frame, channel) {sum, sumsq} doubles
+// (atomic mode) or per-(32-row slice, channel) float2 partials (slice mode).  One block per (channel group, statistics
+// group); every thread adds a fixed strided subset in double, then a fixed-order block reduction -> (mean, rstd).
+__device__ __forceinline__ void stat_accumulate(const StatSrc& S, int c0, int c1, int stat, int fps, int T, double& s, double& q) {
+    const int nch = c1 - c0;
+    if (nch <= 0) return;
+    if (S.part) {
+        const int per_f = S.spf * nch, n = fps * per_f;
+        for (int i = threadIdx.x; i < n; i += blockDim.x) {
+            const int fl = i / per_f, r = i - fl * per_f;
+            const int k = r / nch, ch = c0 + r - k * nch;
+            const int f = stat * fps + fl;
+            const size_t slice = (size_t)((f / T) * S.tpad + (f % T) + S.toff) * S.spf + k;
+            const float2 v = __ldcg(S.part + slice * S.C + ch);
+            s += (double)v.x; q += (double)v.y;
+        }
+    } else {
+        const int n = fps * nch;
+        for (int i = threadIdx.x; i < n; i += blockDim.x) {
+            const int fl = i / nch, ch = c0 + i - fl * nch;
+            const double2 v = __ldcg(reinterpret_cast<const double2*>(S.cs) + (size_t)(stat * fps + fl) * S.C + ch);
+            s += v.x; q += v.y;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) gn_finalize_kernel(const StatSrc S1, const StatSrc S2, int frames_per_stat, int T,
+                                                          int rows_per_frame, float eps, float2* __restrict__ table) {
+    __shared__ double red[2][8];
+    const int g = blockIdx.x, stat = blockIdx.y;
+    const int Cg = (S1.C + S2.C) >> 5;
+    const int lo = g * Cg, hi = lo + Cg;                 // channel range of the group in the (virtual) concat
+    double s = 0.0, q = 0.0;
+    stat_accumulate(S1, min(lo, S1.C), min(hi, S1.C), stat, frames_per_stat, T, s, q);
+    if (S2.C > 0) stat_accumulate(S2, max(lo, S1.C) - S1.C, max(hi, S1.C) - S1.C, stat, frames_per_stat, T, s, q);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { s += __shfl_xor_sync(0xffffffffu, s, o); q += __shfl_xor_sync(0xffffffffu, q, o); }
+    if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = s; red[1][threadIdx.x >> 5] = q; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double ts = 0.0, tq = 0.0;
+        for (int w = 0; w < 8; ++w) { ts += red[0][w]; tq += red[1][w]; }
+        const double cnt = (double)frames_per_stat * Cg * rows_per_frame;
+        const double m = ts / cnt;
+        double var = tq / cnt - m * m;
+        var = var < 0.0 ? 0.0 : var;
+        table[(size_t)stat * 32 + g] = make_float2((float)m, rsqrtf((float)var + eps));
+    }
+}
+
+int gn_finalize(const StatSrc& s1, const StatSrc& s2, int nstat, int frames_per_stat, int T, int rows_per_frame, float eps,
+                float2* table, cudaStream_t st) {
+    MOCA_REQUIRE((s1.cs || s1.part) && table && (s2.C == 0 || s2.cs || s2.part), MOCA_E_ARG, "gn_finalize: NULL argument");
+    MOCA_REQUIRE((s1.C + s2.C) % 32 == 0 && nstat > 0 && frames_per_stat > 0 && rows_per_frame > 0 && T > 0, MOCA_E_SHAPE,
+                 "gn_finalize: unsupported geometry C=%d nstat=%d", s1.C + s2.C, nstat);
+    gn_finalize_kernel<<<dim3(32, nstat), 256, 0, st>>>(s1, s2, frames_per_stat, T, rows_per_frame, eps, table);
+    MOCA_LAUNCH_CHECK();
+    return MOCA_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
 // GroupNorm apply (+SiLU) with layout scatter: one warp per destination row, lanes stride over the row's float4 channel
 // vectors with up to 4 loads in flight each; no block-level synchronisation.
 struct ApplyP {

@@ -21,6 +21,19 @@ int pack_weight(const float* src, int N, int K, int taps, int Kp, __nv_bfloat16*
 int gn_stats(const float* x1, int C1, const float* x2, int C2, int64_t rows, int rows_per_stat, int groups, double* acc,
              float eps, float2* table, unsigned* counter, cudaStream_t st);
 
+// Statistics a GEMM epilogue left behind for the tensor it wrote (gemm_tc.cuh): either per-(frame, channel) {sum, sumsq}
+// doubles cs [frames, C, 2] (atomic mode) or float2 partials part [slices, C] per 32-row slice of the GEMM's input-row space
+// (slice mode; frame f owns slices ((f / T) * tpad + f % T + toff) * spf .. + spf).
+struct StatSrc {
+    const double* cs = nullptr;
+    const float2* part = nullptr;
+    int C = 0;
+    int spf = 0, tpad = 0, toff = 0;
+};
+// (mean, rstd) table [nstat, 32] of GroupNorm(32) over the virtual channel concat of s1 and s2 (s2.C == 0: single source)
+int gn_finalize(const StatSrc& s1, const StatSrc& s2, int nstat, int frames_per_stat, int T, int rows_per_frame, float eps,
+                float2* table, cudaStream_t st);
+
 struct ApplyArgs {
     const float* x1 = nullptr; int C1 = 0;
     const float* x2 = nullptr; int C2 = 0;

@@ -34,6 +34,7 @@ struct Plan {
     float* out_tok = nullptr;
     double* stats = nullptr;
     size_t stats_bytes = 0;
+    float2* parts = nullptr;          // slice-partial statistics (bump allocated; fully rewritten by every forward)
     float2* mr_table = nullptr;       // (mean, rstd) tables written by gn_stats, one slot per GroupNorm
     unsigned* stat_counters = nullptr;
     cudaGraphExec_t gexec = nullptr;
@@ -49,6 +50,7 @@ struct Plan {
 struct Act {
     float* p = nullptr;
     int C = 0, H = 0, W = 0;
+    StatSrc st;               // GroupNorm statistics material left by the GEMM epilogue that wrote p
 };
 
 enum ScratchId { S_PAD = 0, S_RAW, S_LIN, S_QKV, S_ATT, S_FFH, S_F32A, S_F32B, S_Y, S_COUNT };
@@ -61,6 +63,8 @@ struct Builder {
     size_t need[S_COUNT] = {0};
     void* sptr[S_COUNT] = {nullptr};
     int stat_slots = 0;
+    size_t cs_doubles = 0;    // bump allocator over plan->stats (atomic mode, zeroed at the start of every forward)
+    size_t part_elems = 0;    // bump allocator over plan->parts (slice mode)
     int B, T, H0, W0, NF, Lmax;
     std::string scope;
 
@@ -89,6 +93,22 @@ struct Builder {
         if (!dry) raw_push(std::move(op), label, flops);
     }
     int stat_slot() { return stat_slots++; }
+    // producer: 0 = linear GEMM over tokens, 1 = Conv3d (3,1,1) over time-padded rows, 2 = 3x3 conv over bordered rows
+    StatSrc stat_alloc(int C, int HW, int producer) {
+        StatSrc r;
+        r.C = C;
+        if (producer != 2 && HW % 32 == 0) {
+            r.spf = HW / 32; r.tpad = producer == 1 ? T + 2 : T; r.toff = producer == 1 ? 1 : 0;
+            const size_t off = part_elems;
+            part_elems += (size_t)B * r.tpad * r.spf * C;
+            r.part = dry ? (const float2*)16 : plan->parts + off;
+        } else {
+            const size_t off = cs_doubles;
+            cs_doubles += (size_t)NF * C * 2;
+            r.cs = dry ? (const double*)16 : plan->stats + off;
+        }
+        return r;
+    }
 
     // ---- GEMM flavours -------------------------------------------------------------------------------------
     void gemm(GemmDesc d, double useful_flops) {
@@ -104,15 +124,17 @@ struct Builder {
         raw_push([L](cudaStream_t st) { return gemm_run(L, st); }, buf, useful_flops);
     }
     void linear(const __nv_bfloat16* A, int64_t rows, int K, const PackedW& w, int epi, void* out, int ldo, const float* residual,
-                int n_override = 0) {
+                int n_override = 0, const StatSrc* ss = nullptr, int rpf = 0) {
         GemmDesc d;
         d.A = A; d.a_rows = rows; d.a_cols = K; d.a_pitch = K;
         d.Wt = w.w; d.N = n_override ? n_override : w.N; d.ntaps = 1; d.Kp = w.Kp;
         d.mode = GEMM_LINEAR; d.M = (int)rows; d.epi = epi; d.out = out; d.ldo = ldo; d.bias = w.b; d.residual = residual;
+        if (ss) { d.chan_stats = (double*)ss->cs; d.stat_partials = (float2*)ss->part; }
+        d.stat_rows_per_frame = rpf; d.stat_sample_rows = T * rpf;
         gemm(d, 2.0 * rows * d.N * K);
     }
     void conv3x3(const __nv_bfloat16* pad, int H, int W, int Cin, const PackedW& w, int stride, float* out, const float* rowbias,
-                 int rb_ld, const float* residual) {
+                 int rb_ld, const float* residual, const StatSrc* ss) {
         GemmDesc d;
         const int Hp = H + 2, Wp = W + 2;
         d.A = pad; d.a_rows = (int64_t)NF * Hp * Wp; d.a_cols = Cin; d.a_pitch = Cin;
@@ -122,31 +144,37 @@ struct Builder {
         d.mode = GEMM_SPATIAL_PAD; d.g_rows = Hp * Wp; d.g_w = Wp; d.g_H = H; d.g_W = W; d.stride = stride;
         d.M = (int)d.a_rows; d.epi = EPI_F32; d.out = out; d.ldo = w.N; d.bias = w.b;
         d.rowbias = rowbias; d.rb_ld = rb_ld; d.rows_per_frame = (H / stride) * (W / stride); d.residual = residual;
+        if (ss) d.chan_stats = (double*)ss->cs;
+        d.stat_rows_per_frame = d.rows_per_frame; d.stat_sample_rows = T * Hp * Wp;
         gemm(d, 2.0 * NF * (H / stride) * (W / stride) * w.N * 9.0 * w.K);
     }
-    void tconv(const __nv_bfloat16* padT, int HW, int C, const PackedW& w, float* out, const float* residual) {
+    void tconv(const __nv_bfloat16* padT, int HW, int C, const PackedW& w, float* out, const float* residual, const StatSrc* ss) {
         GemmDesc d;
         d.A = padT; d.a_rows = (int64_t)B * (T + 2) * HW; d.a_cols = C; d.a_pitch = C;
         d.Wt = w.w; d.N = w.N; d.ntaps = 3; d.Kp = w.Kp;
         for (int dt = 0; dt < 3; ++dt) d.tap_shift[dt] = (dt - 1) * HW;
         d.mode = GEMM_TIME_PAD; d.g_rows = (T + 2) * HW; d.g_w = HW; d.g_H = T;
         d.M = (int)d.a_rows; d.epi = EPI_F32; d.out = out; d.ldo = w.N; d.bias = w.b; d.residual = residual;
+        if (ss) { d.chan_stats = (double*)ss->cs; d.stat_partials = (float2*)ss->part; }
+        d.stat_rows_per_frame = HW; d.stat_sample_rows = (T + 2) * HW;
         gemm(d, 2.0 * NF * HW * w.N * 3.0 * C);
     }
 
     // ---- normalisation flavours ----------------------------------------------------------------------------
-    void gnorm(const float* x1, int C1, const float* x2, int C2, int64_t rows, int rows_per_stat, const NormW& w, float eps, int silu,
-               int dst_mode, int H, int W, __nv_bfloat16* dst, __nv_bfloat16* raw) {
+    void gnorm(const float* x1, const StatSrc& s1, int C1, const float* x2, const StatSrc& s2in, int C2, int64_t rows, int rows_per_stat,
+               const NormW& w, float eps, int silu, int dst_mode, int H, int W, __nv_bfloat16* dst, __nv_bfloat16* raw) {
         const int slot = stat_slot();
-        double* acc = dry ? nullptr : plan->stats + (size_t)slot * NF * 64;
         float2* table = dry ? nullptr : plan->mr_table + (size_t)slot * NF * 32;
-        unsigned* counter = dry ? nullptr : plan->stat_counters + (size_t)slot * NF;
+        const int nstat = (int)(rows / rows_per_stat), fps = rows_per_stat / (H * W), rpf = H * W, Tn = T;
+        StatSrc s2 = s2in;
+        if (!x2) s2 = StatSrc();
+        if (!dry && (s1.C != C1 || s2.C != C2)) { set_error("plan: statistics source does not match the GroupNorm input (%d/%d vs %d/%d)", s1.C, s2.C, C1, C2); fail(MOCA_E_STATE); }
         ApplyArgs a;
         a.x1 = x1; a.C1 = C1; a.x2 = x2; a.C2 = C2; a.rows = rows; a.rows_per_stat = rows_per_stat; a.table = table;
         a.gamma = w.g; a.beta = w.b; a.eps = eps; a.silu = silu; a.dst_mode = dst_mode;
         a.NF = NF; a.H = H; a.W = W; a.B = B; a.T = T; a.HW = H * W; a.dst = dst; a.raw = raw;
         const std::string dims = " rows=" + std::to_string(rows) + " C=" + std::to_string(C1 + C2) + " dst=" + std::to_string(dst_mode);
-        push([=](cudaStream_t st) { return gn_stats(x1, C1, x2, C2, rows, rows_per_stat, 32, acc, eps, table, counter, st); }, 1, "gn_stats" + dims);
+        push([=](cudaStream_t st) { return gn_finalize(s1, s2, nstat, fps, Tn, rpf, eps, table, st); }, 1, "gn_finalize" + dims);
         push([=](cudaStream_t st) { return gn_apply(a, st); }, 1, "gn_apply" + dims);
     }
     void convert(const float* x, int C, int64_t rows, int dst_mode, int H, int W, __nv_bfloat16* dst) {
@@ -175,7 +203,7 @@ struct Builder {
     }
 
     Act res_block(const LayerW& L, const Act& x, const Act* skip, const float* embout);
-    void transformer(const LayerW& L, const Act& x, const __nv_bfloat16* kv);
+    void transformer(const LayerW& L, Act& x, const __nv_bfloat16* kv);
     void build();
 };
 
@@ -198,15 +226,17 @@ Act Builder::res_block(const LayerW& L, const Act& x, const Act* skip, const flo
     out.C = r.cout; out.H = H; out.W = W;
     out.p = (float*)palloc((size_t)rows * r.cout * sizeof(float));
     // in_layers: GN(fp32, eps 1e-5) -> SiLU -> conv3x3 ; + emb_layers(emb)[:, :, None, None]
-    gnorm(x.p, x.C, skip ? skip->p : nullptr, C2, rows, HW, r.gn1, 1e-5f, 1, DST_SPATIAL_PAD, H, W, pad, raw);
-    conv3x3(pad, H, W, Cin, r.conv1, 1, t1, embout + r.emb_off, net->n_emb, nullptr);
+    gnorm(x.p, x.st, x.C, skip ? skip->p : nullptr, skip ? skip->st : StatSrc(), C2, rows, HW, r.gn1, 1e-5f, 1, DST_SPATIAL_PAD, H, W, pad, raw);
+    const StatSrc st_t1 = stat_alloc(r.cout, HW, 2);
+    conv3x3(pad, H, W, Cin, r.conv1, 1, t1, embout + r.emb_off, net->n_emb, nullptr, &st_t1);
     // out_layers: GN -> SiLU -> (dropout) -> conv3x3 ; + skip_connection(x)
-    gnorm(t1, r.cout, nullptr, 0, rows, HW, r.gn2, 1e-5f, 1, DST_SPATIAL_PAD, H, W, pad, nullptr);
+    gnorm(t1, st_t1, r.cout, nullptr, StatSrc(), 0, rows, HW, r.gn2, 1e-5f, 1, DST_SPATIAL_PAD, H, W, pad, nullptr);
+    StatSrc st_cur = stat_alloc(r.cout, HW, 2);
     if (r.has_skip) {
         linear(raw, rows, Cin, r.skip, EPI_F32, out.p, r.cout, nullptr);
-        conv3x3(pad, H, W, r.cout, r.conv2, 1, out.p, nullptr, 0, out.p);
+        conv3x3(pad, H, W, r.cout, r.conv2, 1, out.p, nullptr, 0, out.p, &st_cur);
     } else {
-        conv3x3(pad, H, W, r.cout, r.conv2, 1, out.p, nullptr, 0, x.p);
+        conv3x3(pad, H, W, r.cout, r.conv2, 1, out.p, nullptr, 0, x.p, &st_cur);
     }
     // TemporalConvBlock: 4 x [GN over (C/32, T, H, W) -> SiLU -> Conv3d (3,1,1)] + identity
     const size_t padt_elems = (size_t)B * (T + 2) * HW * r.cout;
@@ -214,17 +244,19 @@ Act Builder::res_block(const LayerW& L, const Act& x, const Act* skip, const flo
     const float* src = out.p;
     float* dsts[4] = {t1, t2, t1, out.p};
     for (int i = 0; i < 4; ++i) {
-        gnorm(src, r.cout, nullptr, 0, rows, T * HW, r.tgn[i], 1e-5f, 1, DST_TIME_PAD, H, W, padT, nullptr);
-        tconv(padT, HW, r.cout, r.tconv[i], dsts[i], i == 3 ? out.p : nullptr);
+        gnorm(src, st_cur, r.cout, nullptr, StatSrc(), 0, rows, T * HW, r.tgn[i], 1e-5f, 1, DST_TIME_PAD, H, W, padT, nullptr);
+        st_cur = stat_alloc(r.cout, HW, 1);
+        tconv(padT, HW, r.cout, r.tconv[i], dsts[i], i == 3 ? out.p : nullptr, &st_cur);
         src = dsts[i];
     }
+    out.st = st_cur;
     return out;
 }
 
 
 // SpatialTransformer.forward (attention.py:262-278) / TemporalTransformer.forward (:331-373) with one
 // BasicTransformerBlock (:216-220): x += attn1(LN1 x); x += attn2(LN2 x, ctx); x += ff(LN3 x).  Runs in place on x.
-void Builder::transformer(const LayerW& L, const Act& x, const __nv_bfloat16* kv) {
+void Builder::transformer(const LayerW& L, Act& x, const __nv_bfloat16* kv) {
     const TfW& t = L.tf;
     scope = L.name;
     const int H = x.H, W = x.W, HW = H * W;
@@ -237,7 +269,7 @@ void Builder::transformer(const LayerW& L, const Act& x, const __nv_bfloat16* kv
     __nv_bfloat16* ffh = scratch<__nv_bfloat16>(S_FFH, (size_t)rows * 4 * I);
     float* y = scratch<float>(S_Y, (size_t)rows * I);
     // norm (GroupNorm eps 1e-6; spatial: per frame, temporal: 5-D input so statistics span all T frames)
-    gnorm(x.p, C, nullptr, 0, rows, t.spatial ? HW : T * HW, t.gn, 1e-6f, 0, DST_LINEAR, H, W, lin, nullptr);
+    gnorm(x.p, x.st, C, nullptr, StatSrc(), 0, rows, t.spatial ? HW : T * HW, t.gn, 1e-6f, 0, DST_LINEAR, H, W, lin, nullptr);
     linear(lin, rows, C, t.proj_in, EPI_F32, y, I, nullptr);
 
     AttnArgs self;
@@ -283,7 +315,8 @@ void Builder::transformer(const LayerW& L, const Act& x, const __nv_bfloat16* kv
     linear(ffh, rows, 4 * I, t.ff2, EPI_F32, y, I, y);
     // proj_out + x_in
     convert(y, I, rows, DST_LINEAR, H, W, lin);
-    linear(lin, rows, I, t.proj_out, EPI_F32, x.p, C, x.p);
+    x.st = stat_alloc(C, HW, 0);
+    linear(lin, rows, I, t.proj_out, EPI_F32, x.p, C, x.p, 0, &x.st, HW);
 }
 
 
@@ -360,7 +393,8 @@ void Builder::build() {
         const int b = B, c = n->in_ch, t = T, h = H0, w = W0;
         push([=](cudaStream_t st) { return ncthw_to_pad(x_in, b, c, t, h, w, 64, pad, st); });
         cur.p = (float*)palloc((size_t)rows0 * mc * 4);
-        conv3x3(pad, H0, W0, 64, n->inp[0].layers[0].conv, 1, cur.p, nullptr, 0, nullptr);
+        cur.st = stat_alloc(mc, H0 * W0, 2);
+        conv3x3(pad, H0, W0, 64, n->inp[0].layers[0].conv, 1, cur.p, nullptr, 0, nullptr, &cur.st);
         tap("input_blocks.0.0", cur);
     }
     auto run_layers = [&](const BlockW& blk, const Act* skip) {
@@ -378,7 +412,8 @@ void Builder::build() {
                 convert(cur.p, cur.C, rows, DST_SPATIAL_PAD, cur.H, cur.W, pad);
                 Act o; o.C = L.cout; o.H = cur.H / 2; o.W = cur.W / 2;
                 o.p = (float*)palloc((size_t)NF * o.H * o.W * o.C * 4);
-                conv3x3(pad, cur.H, cur.W, cur.C, L.conv, 2, o.p, nullptr, 0, nullptr);
+                o.st = stat_alloc(o.C, o.H * o.W, 2);
+                conv3x3(pad, cur.H, cur.W, cur.C, L.conv, 2, o.p, nullptr, 0, nullptr, &o.st);
                 cur = o;
             } else if (L.kind == "up") {
                 scope = L.name;
@@ -388,7 +423,8 @@ void Builder::build() {
                 convert(cur.p, cur.C, rows, DST_SPATIAL_PAD_UP2, cur.H, cur.W, pad);
                 Act o; o.C = L.cout; o.H = H2; o.W = W2;
                 o.p = (float*)palloc((size_t)NF * H2 * W2 * o.C * 4);
-                conv3x3(pad, H2, W2, cur.C, L.conv, 1, o.p, nullptr, 0, nullptr);
+                o.st = stat_alloc(o.C, H2 * W2, 2);
+                conv3x3(pad, H2, W2, cur.C, L.conv, 1, o.p, nullptr, 0, nullptr, &o.st);
                 cur = o;
             }
             tap(L.name, cur);
@@ -412,8 +448,8 @@ void Builder::build() {
     {
         const int64_t rows = rows0;
         __nv_bfloat16* pad = scratch<__nv_bfloat16>(S_PAD, (size_t)NF * (H0 + 2) * (W0 + 2) * cur.C);
-        gnorm(cur.p, cur.C, nullptr, 0, rows, H0 * W0, n->gn_out, 1e-5f, 1, DST_SPATIAL_PAD, H0, W0, pad, nullptr);
-        conv3x3(pad, H0, W0, cur.C, n->conv_out, 1, plan->out_tok, nullptr, 0, nullptr);
+        gnorm(cur.p, cur.st, cur.C, nullptr, StatSrc(), 0, rows, H0 * W0, n->gn_out, 1e-5f, 1, DST_SPATIAL_PAD, H0, W0, pad, nullptr);
+        conv3x3(pad, H0, W0, cur.C, n->conv_out, 1, plan->out_tok, nullptr, 0, nullptr, nullptr);
     }
 }
 
@@ -436,13 +472,12 @@ static int get_plan(moca_unet* n, int B, int T, int H, int W, int Lmax, Plan** o
     dry.build();
     if (dry.rc) return dry.rc;
     Builder real = dry;
-    real.dry = false; real.stat_slots = 0;
+    real.dry = false; real.stat_slots = 0; real.cs_doubles = 0; real.part_elems = 0;
     plan->launches = 0; plan->flops = 0;
-    plan->stats_bytes = (size_t)dry.stat_slots * B * T * 64 * sizeof(double);
+    plan->stats_bytes = dry.cs_doubles * sizeof(double);
     plan->stats = (double*)real.palloc(plan->stats_bytes);
+    plan->parts = (float2*)real.palloc(dry.part_elems * sizeof(float2));
     plan->mr_table = (float2*)real.palloc((size_t)dry.stat_slots * B * T * 32 * sizeof(float2));
-    plan->stat_counters = (unsigned*)real.palloc((size_t)dry.stat_slots * B * T * sizeof(unsigned));
-    if (plan->stat_counters) cudaMemset(plan->stat_counters, 0, (size_t)dry.stat_slots * B * T * sizeof(unsigned));
     for (int i = 0; i < S_COUNT; ++i) {
         real.sptr[i] = real.palloc(dry.need[i] + 256);
         plan->workspace_bytes += dry.need[i];
