@@ -16,6 +16,7 @@ struct AttnArgs {
     const __nv_bfloat16* k = nullptr; const __nv_bfloat16* v = nullptr; int ldkv = 0; SeqMap kvmap;
     __nv_bfloat16* out = nullptr; int ldo = 0;                       // addressed with qmap
     int n_outer = 0, heads = 0, Lq = 0, Lk = 0;
+    int64_t q_rows = 0, kv_rows = 0;   // rows of the q / kv buffers (TMA bounds of the tcgen05 kernel; 0: unknown -> mma.sync kernel)
     const int* kv_len = nullptr;   // optional device int[n_outer / kv_len_div]: valid keys (cross-attention)
     int kv_len_div = 1;
     float scale = 0.125f;
@@ -23,6 +24,14 @@ struct AttnArgs {
 
 // Flash-style kernel: 64 query rows per CTA, 64-key tiles, online softmax (spatial self- and cross-attention).
 int attention_flash(const AttnArgs& a, cudaStream_t st);
+// tcgen05 / TMEM / TMA flash kernel (attn_tc.cu): 128 query rows per CTA, 128-key tiles, S and P.V accumulated in TMEM.
+// Needs contiguous sequences (step == 1), q_rows / kv_rows, Lq >= 64.  Planned once (tensor maps), run many times.
+struct AttnTcLaunch {
+    alignas(64) unsigned char storage[640];
+};
+bool attention_tc_supported(const AttnArgs& a);
+int attention_tc_plan(const AttnArgs& a, AttnTcLaunch* out);
+int attention_tc_run(const AttnTcLaunch& l, cudaStream_t st);
 // One warp per sequence, Lq = Lk <= 16 (temporal attention over frames).
 int attention_short(const AttnArgs& a, cudaStream_t st);
 

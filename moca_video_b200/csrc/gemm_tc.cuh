@@ -82,6 +82,8 @@ struct GemmLaunch {
     double flops = 0;
 };
 
+// 2-D bf16 tensor map, box = 64 columns x box_rows rows, SWIZZLE_128B, out-of-bounds rows/columns read as zero
+int make_tmap_bf16(CUtensorMap* tm, const void* ptr, int64_t rows, int64_t cols, int64_t pitch, int box_rows);
 int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out);
 int gemm_run(const GemmLaunch& l, cudaStream_t st);
 

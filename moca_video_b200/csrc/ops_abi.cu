@@ -162,5 +162,12 @@ extern "C" int32_t moca_attention_bf16(moca_ctx* ctx, const void* q, const void*
     }
     a.qmap.div = 1; a.qmap.mul_a = Lq; a.qmap.step = 1;
     a.kvmap.div = 1; a.kvmap.mul_a = Lk; a.kvmap.step = 1;
+    a.q_rows = (int64_t)batch * Lq; a.kv_rows = (int64_t)batch * Lk;
+    if (attention_tc_supported(a)) {
+        AttnTcLaunch l;
+        int rc = attention_tc_plan(a, &l);
+        if (rc) return rc;
+        return attention_tc_run(l, (cudaStream_t)stream);
+    }
     return attention_flash(a, (cudaStream_t)stream);
 }

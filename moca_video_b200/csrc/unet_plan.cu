@@ -283,9 +283,16 @@ void Builder::transformer(const LayerW& L, Act& x, const __nv_bfloat16* kv) {
         self.qmap.div = HW; self.qmap.mul_a = T * HW; self.qmap.mul_b = 1; self.qmap.step = HW;
     }
     self.kvmap = self.qmap;
+    self.q_rows = rows; self.kv_rows = rows;
     const double attn_flops = 4.0 * (double)self.n_outer * t.heads * self.Lq * self.Lk * 64.0;
     const bool spatial = t.spatial;
-    auto run_self = [=](cudaStream_t st) { return spatial ? attention_flash(self, st) : attention_short(self, st); };
+    // spatial sequences of >= 64 tokens run on the tcgen05 kernel (tensor maps built here, once per plan)
+    const bool self_tc = spatial && attention_tc_supported(self);
+    AttnTcLaunch self_l;
+    if (self_tc && !dry && !rc) { int r = attention_tc_plan(self, &self_l); if (r) fail(r); }
+    auto run_self = [=](cudaStream_t st) {
+        return self_tc ? attention_tc_run(self_l, st) : spatial ? attention_flash(self, st) : attention_short(self, st);
+    };
 
     // attn1: self-attention
     lnorm(y, t.ln1, rows, I, lin);
@@ -302,7 +309,11 @@ void Builder::transformer(const LayerW& L, Act& x, const __nv_bfloat16* kv) {
         ca.kvmap.div = T; ca.kvmap.mul_a = Lmax; ca.kvmap.mul_b = 0; ca.kvmap.step = 1;     // frame o uses the context of sample o / T
         ca.out = att; ca.ldo = I; ca.n_outer = NF; ca.heads = t.heads; ca.Lq = HW; ca.Lk = Lmax;
         ca.kv_len = plan->d_ctxlen; ca.kv_len_div = T; ca.scale = 0.125f;
-        push([=](cudaStream_t st) { return attention_flash(ca, st); }, 1, "attn_cross", 4.0 * (double)NF * t.heads * HW * Lmax * 64.0);
+        ca.q_rows = rows; ca.kv_rows = (int64_t)B * Lmax;
+        const bool ca_tc = attention_tc_supported(ca);
+        AttnTcLaunch ca_l;
+        if (ca_tc && !dry && !rc) { int r = attention_tc_plan(ca, &ca_l); if (r) fail(r); }
+        push([=](cudaStream_t st) { return ca_tc ? attention_tc_run(ca_l, st) : attention_flash(ca, st); }, 1, "attn_cross", 4.0 * (double)NF * t.heads * HW * Lmax * 64.0);
         plan->flops += 4.0 * (double)NF * t.heads * HW * Lmax * 64.0;
     } else {
         linear(lin, rows, I, t.qkv2, EPI_BF16, qkv, 3 * I, nullptr);
