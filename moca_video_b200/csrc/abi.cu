@@ -1,8 +1,14 @@
 // Context object and error plumbing of the C-ABI (include/moca_b200.h).
+#include <stdlib.h>
 #include "common.cuh"
 
 namespace moca {
 static thread_local char g_err[1024] = "";
+bool pdl_enabled() {
+    static const int on = [] { const char* e = getenv("MOCA_PDL"); return (e && e[0] == '0') ? 0 : 1; }();
+    return on != 0;
+}
+
 void set_error(const char* fmt, ...) {
     va_list ap;
     va_start(ap, fmt);

@@ -71,6 +71,8 @@ __global__ void __launch_bounds__(128) attn_flash_kernel(const __grid_constant__
     __shared__ __align__(128) __nv_bfloat16 sQ[64 * D];
     __shared__ __align__(128) __nv_bfloat16 sK[2][64 * D];
     __shared__ __align__(128) __nv_bfloat16 sV[2][64 * D];
+    pdl_wait();
+    pdl_launch_dependents();
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int g = lane >> 2, t = lane & 3;
     const int o = blockIdx.y / P.heads, h = blockIdx.y - o * P.heads;
@@ -200,6 +202,8 @@ __global__ void __launch_bounds__(128) attn_flash_kernel(const __grid_constant__
 // spatial position, rows `step` = H*W apart in the channels-last token matrix — no rearrange copy is ever made).
 __global__ void __launch_bounds__(128) attn_short_kernel(const __grid_constant__ AttnP P) {
     __shared__ __align__(128) __nv_bfloat16 sm[4][3][16 * D];
+    pdl_wait();
+    pdl_launch_dependents();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int g = lane >> 2, t = lane & 3;
     const int item = blockIdx.x * 4 + warp;
@@ -295,7 +299,7 @@ int attention_flash(const AttnArgs& a, cudaStream_t st) {
     MOCA_REQUIRE((int64_t)a.n_outer * a.heads <= 65535, MOCA_E_SHAPE, "attention_flash: outer*heads = %lld exceeds grid.y",
                  (long long)a.n_outer * a.heads);
     dim3 grid(cdiv(a.Lq, 64), a.n_outer * a.heads);
-    attn_flash_kernel<<<grid, 128, 0, st>>>(P);
+    launch_pdl(attn_flash_kernel, grid, dim3(128), 0, st, P);
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
 }
@@ -306,7 +310,7 @@ int attention_short(const AttnArgs& a, cudaStream_t st) {
     if (rc) return rc;
     MOCA_REQUIRE(a.Lq == a.Lk && a.Lq <= 16 && a.kv_len == nullptr, MOCA_E_SHAPE, "attention_short: needs Lq == Lk <= 16 (got %d, %d)", a.Lq, a.Lk);
     const int64_t items = (int64_t)a.n_outer * a.heads;
-    attn_short_kernel<<<cdiv(items, 4), 128, 0, st>>>(P);
+    launch_pdl(attn_short_kernel, dim3(cdiv(items, 4)), dim3(128), 0, st, P);
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
 }

@@ -66,8 +66,6 @@ __global__ void __launch_bounds__(kThreads, 2) attn_tc_kernel(const __grid_const
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int o = blockIdx.y / P.heads, h = blockIdx.y - o * P.heads;
     const int q0 = blockIdx.x * kTileQ;
-    const int Lk = P.kv_len ? P.kv_len[o / P.kv_len_div] : P.Lk;
-    const int ntiles = (Lk + kTileK - 1) / kTileK;
     const int qrow0 = (int)first_row(P.qmap, o), kvrow0 = (int)first_row(P.kvmap, o);
 
     if (threadIdx.x == 0) {
@@ -89,6 +87,10 @@ __global__ void __launch_bounds__(kThreads, 2) attn_tc_kernel(const __grid_const
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();                  // PDL (common.cuh): the prologue above overlaps the previous kernel's tail
+    pdl_launch_dependents();
+    const int Lk = P.kv_len ? P.kv_len[o / P.kv_len_div] : P.Lk;
+    const int ntiles = (Lk + kTileK - 1) / kTileK;
 
     if (warp == 4) {
         if (lane == 0) {
@@ -288,7 +290,7 @@ int attention_tc_plan(const AttnArgs& a, AttnTcLaunch* out) {
 
 int attention_tc_run(const AttnTcLaunch& l, cudaStream_t st) {
     const AttnTcLaunchImpl* L = reinterpret_cast<const AttnTcLaunchImpl*>(l.storage);
-    attn_tc_kernel<<<L->grid, kThreads, kSmem, st>>>(L->p);
+    launch_pdl(attn_tc_kernel, L->grid, dim3(kThreads), kSmem, st, L->p);
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
 }

@@ -49,6 +49,31 @@ struct Ctx {
 
 static inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 
+// ---- programmatic dependent launch (PDL) ------------------------------------------------------------------------
+// Every kernel of the UNet forward is launched with cudaLaunchAttributeProgrammaticStreamSerialization (kept as
+// programmatic edges by the CUDA-graph capture): its CTAs may become resident, and run their prologue (barrier init,
+// TMEM allocation, tensor-map prefetch), while the previous kernel drains.  Contract: pdl_wait() is the first statement of
+// the kernel, before any early return and before any global-memory access; it returns when all earlier kernels have
+// completed and their writes are visible.  MOCA_PDL=0 in the environment turns the attribute off (the instructions are
+// then no-ops).
+bool pdl_enabled();
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#endif
+
 }  // namespace moca
 
 struct moca_ctx {

@@ -108,6 +108,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // everything above overlaps the tail of the previous kernel (PDL, common.cuh); global memory is touched only below
+    pdl_wait();
+    pdl_launch_dependents();
 
     if (warp == 0) {
         if (lane == 0) {
@@ -525,10 +528,10 @@ static int set_attr_bn(int epi) {
 
 template <int BN>
 static void launch_bn(const GemmLaunch& l, cudaStream_t st) {
-    if (l.p.epi == EPI_F32 && (l.p.cstat || l.p.spart)) gemm_tc_kernel<BN, EPI_F32, true><<<l.grid, kGemmThreads, l.smem, st>>>(l.p);
-    else if (l.p.epi == EPI_F32) gemm_tc_kernel<BN, EPI_F32, false><<<l.grid, kGemmThreads, l.smem, st>>>(l.p);
-    else if (l.p.epi == EPI_BF16) gemm_tc_kernel<BN, EPI_BF16, false><<<l.grid, kGemmThreads, l.smem, st>>>(l.p);
-    else gemm_tc_kernel<BN, EPI_GEGLU, false><<<l.grid, kGemmThreads, l.smem, st>>>(l.p);
+    if (l.p.epi == EPI_F32 && (l.p.cstat || l.p.spart)) launch_pdl(gemm_tc_kernel<BN, EPI_F32, true>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
+    else if (l.p.epi == EPI_F32) launch_pdl(gemm_tc_kernel<BN, EPI_F32, false>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
+    else if (l.p.epi == EPI_BF16) launch_pdl(gemm_tc_kernel<BN, EPI_BF16, false>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
+    else launch_pdl(gemm_tc_kernel<BN, EPI_GEGLU, false>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
 }
 
 int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {

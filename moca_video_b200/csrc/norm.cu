@@ -44,6 +44,8 @@ __global__ void __launch_bounds__(256) gn_stats_kernel(const float* __restrict__
                                                        int C2, int rows_per_stat, int Cg, int tpr, int rp,
                                                        double* __restrict__ acc, float eps, float2* __restrict__ table,
                                                        unsigned* __restrict__ counter) {
+    pdl_wait();
+    pdl_launch_dependents();
     // per-(row lane, channel) partial sums; a thread owns its channels so plain stores suffice
     __shared__ float s_sum[256 * kStatSlots * 4];
     __shared__ float s_sq[256 * kStatSlots * 4];
@@ -144,7 +146,7 @@ int gn_stats(const float* x1, int C1, const float* x2, int C2, int64_t rows, int
     int slots, tpr, rp;
     stat_geometry(C / 4, slots, tpr, rp);
     dim3 grid(cdiv(rows_per_stat, kStatChunk), nstat);
-    gn_stats_kernel<<<grid, 256, 0, st>>>(x1, C1, x2, C2, rows_per_stat, C / 32, tpr, rp, acc, eps, table, counter);
+    launch_pdl(gn_stats_kernel, grid, dim3(256), 0, st, x1, C1, x2, C2, rows_per_stat, C / 32, tpr, rp, acc, eps, table, counter);
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
 }
@@ -178,6 +180,8 @@ __device__ __forceinline__ void stat_accumulate(const StatSrc& S, int c0, int c1
 
 __global__ void __launch_bounds__(256) gn_finalize_kernel(const StatSrc S1, const StatSrc S2, int frames_per_stat, int T,
                                                           int rows_per_frame, float eps, float2* __restrict__ table) {
+    pdl_wait();
+    pdl_launch_dependents();
     __shared__ double red[2][8];
     const int g = blockIdx.x, stat = blockIdx.y;
     const int Cg = (S1.C + S2.C) >> 5;
@@ -205,7 +209,7 @@ int gn_finalize(const StatSrc& s1, const StatSrc& s2, int nstat, int frames_per_
     MOCA_REQUIRE((s1.cs || s1.part) && table && (s2.C == 0 || s2.cs || s2.part), MOCA_E_ARG, "gn_finalize: NULL argument");
     MOCA_REQUIRE((s1.C + s2.C) % 32 == 0 && nstat > 0 && frames_per_stat > 0 && rows_per_frame > 0 && T > 0, MOCA_E_SHAPE,
                  "gn_finalize: unsupported geometry C=%d nstat=%d", s1.C + s2.C, nstat);
-    gn_finalize_kernel<<<dim3(32, nstat), 256, 0, st>>>(s1, s2, frames_per_stat, T, rows_per_frame, eps, table);
+    launch_pdl(gn_finalize_kernel, dim3(32, nstat), dim3(256), 0, st, s1, s2, frames_per_stat, T, rows_per_frame, eps, table);
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
 }
@@ -250,6 +254,8 @@ __device__ __forceinline__ uint2 pack4(const float* x) {
 }
 
 __global__ void __launch_bounds__(256) gn_apply_kernel(const __grid_constant__ ApplyP P) {
+    pdl_wait();
+    pdl_launch_dependents();
     const int lane = threadIdx.x & 31;
     const int drow = blockIdx.x * 8 + (threadIdx.x >> 5);
     if (drow >= P.dst_rows) return;
@@ -331,69 +337,92 @@ int gn_apply(const ApplyArgs& a, cudaStream_t st) {
     }
     MOCA_REQUIRE(dst_rows < (1ll << 31) && a.rows < (1ll << 31), MOCA_E_SHAPE, "gn_apply: too many rows");
     P.dst_rows = (int)dst_rows;
-    gn_apply_kernel<<<cdiv(dst_rows, 8), 256, 0, st>>>(P);
+    launch_pdl(gn_apply_kernel, dim3(cdiv(dst_rows, 8)), dim3(256), 0, st, P);
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-constexpr int kLnSlots = 10;   // C <= 32*4*10 = 1280
-
+// One warp normalises R consecutive rows; all R * SLOTS float4 loads of a lane are issued before the first use so that a
+// warp keeps R rows of HBM traffic in flight (C = 320: 4 rows = 5 KB per warp).  C <= 128 * SLOTS.
+template <int SLOTS, int R>
 __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
                                                         const float* __restrict__ beta, int64_t rows, int C,
                                                         __nv_bfloat16* __restrict__ out) {
+    pdl_wait();
+    pdl_launch_dependents();
     const int lane = threadIdx.x & 31;
-    const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (row >= rows) return;
+    const int64_t row0 = ((int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * R;
+    if (row0 >= rows) return;
     const int nvec = C >> 2;
-    const float4* xr = reinterpret_cast<const float4*>(x + row * C);
-    float4 v[kLnSlots];
-    float s = 0.f;
+    float4 v[R][SLOTS];
 #pragma unroll
-    for (int u = 0; u < kLnSlots; ++u) {
-        const int i = lane + 32 * u;
-        if (i < nvec) {
-            v[u] = xr[i];
-            s += (v[u].x + v[u].y) + (v[u].z + v[u].w);
+    for (int r = 0; r < R; ++r) {
+        const float4* xr = reinterpret_cast<const float4*>(x + (row0 + r) * C);
+#pragma unroll
+        for (int u = 0; u < SLOTS; ++u) {
+            const int i = lane + 32 * u;
+            v[r][u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (i < nvec && row0 + r < rows) v[r][u] = __ldg(xr + i);
         }
     }
-    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    const float mean = s / (float)C;
-    float q = 0.f;
-#pragma unroll
-    for (int u = 0; u < kLnSlots; ++u) {
-        const int i = lane + 32 * u;
-        if (i < nvec) {
-            const float a = v[u].x - mean, b = v[u].y - mean, c = v[u].z - mean, d = v[u].w - mean;
-            q += (a * a + b * b) + (c * c + d * d);
-        }
-    }
-    for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
-    const float rstd = rsqrtf(q / (float)C + 1e-5f);
-    uint2* orow = reinterpret_cast<uint2*>(out + row * C);
     const float4* g4 = reinterpret_cast<const float4*>(gamma);
     const float4* b4 = reinterpret_cast<const float4*>(beta);
+    float4 g[R > 1 ? SLOTS : 1], b[R > 1 ? SLOTS : 1];     // shared by the R rows; a single-row warp reads them at the point of use
+    if constexpr (R > 1) {
 #pragma unroll
-    for (int u = 0; u < kLnSlots; ++u) {
-        const int i = lane + 32 * u;
-        if (i < nvec) {
-            const float4 g = g4[i], b = b4[i];
-            __nv_bfloat162 lo = __floats2bfloat162_rn((v[u].x - mean) * rstd * g.x + b.x, (v[u].y - mean) * rstd * g.y + b.y);
-            __nv_bfloat162 hi = __floats2bfloat162_rn((v[u].z - mean) * rstd * g.z + b.z, (v[u].w - mean) * rstd * g.w + b.w);
-            orow[i] = make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
+        for (int u = 0; u < SLOTS; ++u) {
+            const int i = lane + 32 * u;
+            if (i < nvec) { g[u] = __ldg(g4 + i); b[u] = __ldg(b4 + i); }
+        }
+    }
+    const float inv_c = 1.0f / (float)C;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        if (row0 + r >= rows) break;
+        float s = 0.f;
+#pragma unroll
+        for (int u = 0; u < SLOTS; ++u) s += (v[r][u].x + v[r][u].y) + (v[r][u].z + v[r][u].w);      // absent vectors are zero
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        const float mean = s * inv_c;
+        float q = 0.f;
+#pragma unroll
+        for (int u = 0; u < SLOTS; ++u) {
+            if (lane + 32 * u < nvec) {
+                const float a = v[r][u].x - mean, bb = v[r][u].y - mean, c = v[r][u].z - mean, d = v[r][u].w - mean;
+                q += (a * a + bb * bb) + (c * c + d * d);
+            }
+        }
+        for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+        const float rstd = rsqrtf(q * inv_c + 1e-5f);
+        uint2* orow = reinterpret_cast<uint2*>(out + (row0 + r) * C);
+#pragma unroll
+        for (int u = 0; u < SLOTS; ++u) {
+            const int i = lane + 32 * u;
+            if (i < nvec) {
+                float4 gu, bu;
+                if constexpr (R > 1) { gu = g[u]; bu = b[u]; } else { gu = __ldg(g4 + i); bu = __ldg(b4 + i); }
+                __nv_bfloat162 lo = __floats2bfloat162_rn((v[r][u].x - mean) * rstd * gu.x + bu.x, (v[r][u].y - mean) * rstd * gu.y + bu.y);
+                __nv_bfloat162 hi = __floats2bfloat162_rn((v[r][u].z - mean) * rstd * gu.z + bu.z, (v[r][u].w - mean) * rstd * gu.w + bu.w);
+                orow[i] = make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
+            }
         }
     }
 }
 
 int layernorm_bf16(const float* x, const float* gamma, const float* beta, int64_t rows, int C, __nv_bfloat16* out, cudaStream_t st) {
-    MOCA_REQUIRE(C % 4 == 0 && C <= 128 * kLnSlots, MOCA_E_SHAPE, "layernorm: C=%d unsupported (multiple of 4, <= %d)", C, 128 * kLnSlots);
-    layernorm_kernel<<<cdiv(rows, 8), 256, 0, st>>>(x, gamma, beta, rows, C, out);
+    MOCA_REQUIRE(C % 4 == 0 && C <= 1280, MOCA_E_SHAPE, "layernorm: C=%d unsupported (multiple of 4, <= 1280)", C);
+    if (C <= 384) launch_pdl(layernorm_kernel<3, 4>, dim3(cdiv(rows, 32)), dim3(256), 0, st, x, gamma, beta, rows, C, out);
+    else if (C <= 640) launch_pdl(layernorm_kernel<5, 2>, dim3(cdiv(rows, 16)), dim3(256), 0, st, x, gamma, beta, rows, C, out);
+    else launch_pdl(layernorm_kernel<10, 1>, dim3(cdiv(rows, 8)), dim3(256), 0, st, x, gamma, beta, rows, C, out);
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
 }
 
 // ---------------------------------------------------------------------------------------------------------------
 __global__ void timestep_embedding_kernel(const int* __restrict__ t, int n, int dim, __nv_bfloat16* __restrict__ out) {
+    pdl_wait();
+    pdl_launch_dependents();
     const int half = dim / 2;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n * half) return;
@@ -406,13 +435,15 @@ __global__ void timestep_embedding_kernel(const int* __restrict__ t, int n, int 
 
 int timestep_embedding_bf16(const int* t_dev, int n, int dim, __nv_bfloat16* out, cudaStream_t st) {
     MOCA_REQUIRE(dim % 2 == 0, MOCA_E_SHAPE, "timestep_embedding: odd dim %d", dim);
-    timestep_embedding_kernel<<<cdiv((int64_t)n * dim / 2, 256), 256, 0, st>>>(t_dev, n, dim, out);
+    launch_pdl(timestep_embedding_kernel, dim3(cdiv((int64_t)n * dim / 2, 256)), dim3(256), 0, st, t_dev, n, dim, out);
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
 }
 
 __global__ void silu_add_kernel(const float* __restrict__ a, const float* __restrict__ b, int64_t n, int do_silu,
                                 __nv_bfloat16* __restrict__ out) {
+    pdl_wait();
+    pdl_launch_dependents();
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
         float v = a[i];
         if (b) v += b[i];
@@ -423,14 +454,14 @@ __global__ void silu_add_kernel(const float* __restrict__ a, const float* __rest
 
 int silu_add_bf16(const float* a, const float* b, int64_t n, __nv_bfloat16* out, cudaStream_t st) {
     const int blocks = (int)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
-    silu_add_kernel<<<blocks, 256, 0, st>>>(a, b, n, 1, out);
+    launch_pdl(silu_add_kernel, dim3(blocks), dim3(256), 0, st, a, b, n, 1, out);
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
 }
 
 int f32_to_bf16(const float* a, int64_t n, __nv_bfloat16* out, cudaStream_t st) {
     const int blocks = (int)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
-    silu_add_kernel<<<blocks, 256, 0, st>>>(a, nullptr, n, 0, out);
+    launch_pdl(silu_add_kernel, dim3(blocks), dim3(256), 0, st, a, (const float*)nullptr, n, 0, out);
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
 }
@@ -438,6 +469,8 @@ int f32_to_bf16(const float* a, int64_t n, __nv_bfloat16* out, cudaStream_t st) 
 // ---------------------------------------------------------------------------------------------------------------
 __global__ void ncthw_to_pad_kernel(const float* __restrict__ x, int B, int C, int T, int H, int W, int Cp,
                                     __nv_bfloat16* __restrict__ dst) {
+    pdl_wait();
+    pdl_launch_dependents();
     const int Hp = H + 2, Wp = W + 2;
     const int64_t total = (int64_t)B * T * Hp * Wp * Cp;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -457,12 +490,14 @@ __global__ void ncthw_to_pad_kernel(const float* __restrict__ x, int B, int C, i
 int ncthw_to_pad(const float* x, int B, int C, int T, int H, int W, int Cp, __nv_bfloat16* dst, cudaStream_t st) {
     const int64_t total = (int64_t)B * T * (H + 2) * (W + 2) * Cp;
     const int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
-    ncthw_to_pad_kernel<<<blocks, 256, 0, st>>>(x, B, C, T, H, W, Cp, dst);
+    launch_pdl(ncthw_to_pad_kernel, dim3(blocks), dim3(256), 0, st, x, B, C, T, H, W, Cp, dst);
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
 }
 
 __global__ void tokens_to_ncthw_kernel(const float* __restrict__ tok, int ld, int B, int C, int T, int H, int W, float* __restrict__ y) {
+    pdl_wait();
+    pdl_launch_dependents();
     const int64_t total = (int64_t)B * C * T * H * W;
     const int HW = H * W;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -477,7 +512,7 @@ __global__ void tokens_to_ncthw_kernel(const float* __restrict__ tok, int ld, in
 int tokens_to_ncthw(const float* tok, int ld, int B, int C, int T, int H, int W, float* y, cudaStream_t st) {
     const int64_t total = (int64_t)B * C * T * H * W;
     const int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
-    tokens_to_ncthw_kernel<<<blocks, 256, 0, st>>>(tok, ld, B, C, T, H, W, y);
+    launch_pdl(tokens_to_ncthw_kernel, dim3(blocks), dim3(256), 0, st, tok, ld, B, C, T, H, W, y);
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
 }
