@@ -4,9 +4,9 @@
 
 namespace moca {
 static thread_local char g_err[1024] = "";
-bool pdl_enabled() {
-    static const int on = [] { const char* e = getenv("MOCA_PDL"); return (e && e[0] == '0') ? 0 : 1; }();
-    return on != 0;
+int pdl_level() {
+    static const int lvl = [] { const char* e = getenv("MOCA_PDL"); return e ? atoi(e) : 0; }();
+    return lvl;
 }
 
 void set_error(const char* fmt, ...) {

@@ -290,7 +290,7 @@ int attention_tc_plan(const AttnArgs& a, AttnTcLaunch* out) {
 
 int attention_tc_run(const AttnTcLaunch& l, cudaStream_t st) {
     const AttnTcLaunchImpl* L = reinterpret_cast<const AttnTcLaunchImpl*>(l.storage);
-    launch_pdl(attn_tc_kernel, L->grid, dim3(kThreads), kSmem, st, L->p);
+    launch_pdl_tc(attn_tc_kernel, L->grid, dim3(kThreads), kSmem, st, L->p);
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
 }

@@ -56,22 +56,24 @@ static inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 // the kernel, before any early return and before any global-memory access; it returns when all earlier kernels have
 // completed and their writes are visible.  MOCA_PDL=0 in the environment turns the attribute off (the instructions are
 // then no-ops).
-bool pdl_enabled();
+int pdl_level();      // MOCA_PDL: 0 off, 1 tensor-core kernels only, 2 every kernel
 #ifdef __CUDACC__
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 template <typename... KArgs, typename... Args>
-static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+static inline cudaError_t launch_pdl_lvl(int level, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    cfg.numAttrs = pdl_level() >= level ? 1 : 0;
     return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
+#define launch_pdl(...) launch_pdl_lvl(2, __VA_ARGS__)
+#define launch_pdl_tc(...) launch_pdl_lvl(1, __VA_ARGS__)
 #endif
 
 }  // namespace moca

@@ -528,10 +528,10 @@ static int set_attr_bn(int epi) {
 
 template <int BN>
 static void launch_bn(const GemmLaunch& l, cudaStream_t st) {
-    if (l.p.epi == EPI_F32 && (l.p.cstat || l.p.spart)) launch_pdl(gemm_tc_kernel<BN, EPI_F32, true>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
-    else if (l.p.epi == EPI_F32) launch_pdl(gemm_tc_kernel<BN, EPI_F32, false>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
-    else if (l.p.epi == EPI_BF16) launch_pdl(gemm_tc_kernel<BN, EPI_BF16, false>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
-    else launch_pdl(gemm_tc_kernel<BN, EPI_GEGLU, false>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
+    if (l.p.epi == EPI_F32 && (l.p.cstat || l.p.spart)) launch_pdl_tc(gemm_tc_kernel<BN, EPI_F32, true>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
+    else if (l.p.epi == EPI_F32) launch_pdl_tc(gemm_tc_kernel<BN, EPI_F32, false>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
+    else if (l.p.epi == EPI_BF16) launch_pdl_tc(gemm_tc_kernel<BN, EPI_BF16, false>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
+    else launch_pdl_tc(gemm_tc_kernel<BN, EPI_GEGLU, false>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
 }
 
 int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {

@@ -179,10 +179,13 @@ __device__ __forceinline__ void stat_accumulate(const StatSrc& S, int c0, int c1
 }
 
 __global__ void __launch_bounds__(256) gn_finalize_kernel(const StatSrc S1, const StatSrc S2, int frames_per_stat, int T,
-                                                          int rows_per_frame, float eps, float2* __restrict__ table) {
+                                                          int rows_per_frame, float eps, float2* __restrict__ table,
+                                                          const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                          float2* __restrict__ ab) {
     pdl_wait();
     pdl_launch_dependents();
     __shared__ double red[2][8];
+    __shared__ float s_mr[2];
     const int g = blockIdx.x, stat = blockIdx.y;
     const int Cg = (S1.C + S2.C) >> 5;
     const int lo = g * Cg, hi = lo + Cg;                 // channel range of the group in the (virtual) concat
@@ -200,16 +203,27 @@ __global__ void __launch_bounds__(256) gn_finalize_kernel(const StatSrc S1, cons
         const double m = ts / cnt;
         double var = tq / cnt - m * m;
         var = var < 0.0 ? 0.0 : var;
-        table[(size_t)stat * 32 + g] = make_float2((float)m, rsqrtf((float)var + eps));
+        const float rstd = rsqrtf((float)var + eps);
+        table[(size_t)stat * 32 + g] = make_float2((float)m, rstd);
+        s_mr[0] = (float)m; s_mr[1] = rstd;
+    }
+    if (ab) {
+        __syncthreads();
+        const int C = S1.C + S2.C;
+        for (int c = lo + threadIdx.x; c < hi; c += blockDim.x) {
+            const float a = s_mr[1] * gamma[c];
+            ab[(size_t)stat * C + c] = make_float2(a, beta[c] - s_mr[0] * a);
+        }
     }
 }
 
 int gn_finalize(const StatSrc& s1, const StatSrc& s2, int nstat, int frames_per_stat, int T, int rows_per_frame, float eps,
-                float2* table, cudaStream_t st) {
+                float2* table, cudaStream_t st, const float* gamma, const float* beta, float2* ab) {
+    MOCA_REQUIRE(!ab || (gamma && beta), MOCA_E_ARG, "gn_finalize: the affine table needs gamma and beta");
     MOCA_REQUIRE((s1.cs || s1.part) && table && (s2.C == 0 || s2.cs || s2.part), MOCA_E_ARG, "gn_finalize: NULL argument");
     MOCA_REQUIRE((s1.C + s2.C) % 32 == 0 && nstat > 0 && frames_per_stat > 0 && rows_per_frame > 0 && T > 0, MOCA_E_SHAPE,
                  "gn_finalize: unsupported geometry C=%d nstat=%d", s1.C + s2.C, nstat);
-    launch_pdl(gn_finalize_kernel, dim3(32, nstat), dim3(256), 0, st, s1, s2, frames_per_stat, T, rows_per_frame, eps, table);
+    launch_pdl(gn_finalize_kernel, dim3(32, nstat), dim3(256), 0, st, s1, s2, frames_per_stat, T, rows_per_frame, eps, table, gamma, beta, ab);
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
 }
@@ -222,6 +236,7 @@ struct ApplyP {
     const float* x2; int C2;
     int rows_per_stat; int Cg;
     const float2* table; const float* gamma; const float* beta;
+    const float2* ab;
     int silu; int mode;
     int NF, H, W;        // source geometry
     int T, HW;
@@ -267,7 +282,8 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const __grid_constant__ A
         for (int v = lane; v < nvec; v += 32) drow_p[v] = make_uint2(0u, 0u);
         return;
     }
-    const float2* tab = P.rows_per_stat > 0 ? P.table + (size_t)(sr / P.rows_per_stat) * 32 : nullptr;
+    const float2* tab = (P.rows_per_stat > 0 && !P.ab) ? P.table + (size_t)(sr / P.rows_per_stat) * 32 : nullptr;
+    const float4* ab4 = P.ab ? reinterpret_cast<const float4*>(P.ab + (size_t)(sr / P.rows_per_stat) * C) : nullptr;
     const float4* s1 = reinterpret_cast<const float4*>(P.x1 + (size_t)sr * P.C1);
     const float4* s2 = P.x2 ? reinterpret_cast<const float4*>(P.x2 + (size_t)sr * P.C2) : nullptr;
     const int nv1 = P.C1 >> 2;
@@ -285,7 +301,15 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const __grid_constant__ A
             const int c = v << 2;
             float x[4] = {t[k].x, t[k].y, t[k].z, t[k].w};
             if (P.raw) *reinterpret_cast<uint2*>(P.raw + (size_t)sr * C + c) = pack4(x);
-            if (tab) {
+            if (ab4) {
+                const float4 p0 = __ldg(ab4 + 2 * v), p1 = __ldg(ab4 + 2 * v + 1);      // (a, b) of channels c, c+1 | c+2, c+3
+                x[0] = fmaf(x[0], p0.x, p0.y); x[1] = fmaf(x[1], p0.z, p0.w);
+                x[2] = fmaf(x[2], p1.x, p1.y); x[3] = fmaf(x[3], p1.z, p1.w);
+                if (P.silu) {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) x[e] = silu_f(x[e]);
+                }
+            } else if (tab) {
                 const float4 g4 = __ldg(reinterpret_cast<const float4*>(P.gamma + c));
                 const float4 b4 = __ldg(reinterpret_cast<const float4*>(P.beta + c));
                 const float gg[4] = {g4.x, g4.y, g4.z, g4.w}, bb[4] = {b4.x, b4.y, b4.z, b4.w};
@@ -312,13 +336,13 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const __grid_constant__ A
 int gn_apply(const ApplyArgs& a, cudaStream_t st) {
     const int C = a.C1 + a.C2;
     MOCA_REQUIRE(C % 4 == 0 && a.C1 % 4 == 0 && C <= 256 * kStatSlots * 4, MOCA_E_SHAPE, "gn_apply: channels C1=%d C2=%d unsupported", a.C1, a.C2);
-    MOCA_REQUIRE(a.rows_per_stat == 0 || (a.groups == 32 && C % 32 == 0 && C / 32 >= 2 && a.table && a.gamma && a.beta), MOCA_E_ARG,
+    MOCA_REQUIRE(a.rows_per_stat == 0 || a.ab || (a.groups == 32 && C % 32 == 0 && C / 32 >= 2 && a.table && a.gamma && a.beta), MOCA_E_ARG,
                  "gn_apply: bad normalisation arguments");
     MOCA_REQUIRE(a.rows_per_stat == 0 || a.rows % a.rows_per_stat == 0, MOCA_E_SHAPE, "gn_apply: bad statistics span");
     ApplyP P;
     P.x1 = a.x1; P.C1 = a.C1; P.x2 = a.x2; P.C2 = a.C2;
     P.rows_per_stat = a.rows_per_stat; P.Cg = C / 32 > 0 ? C / 32 : 1;
-    P.table = a.table; P.gamma = a.gamma; P.beta = a.beta; P.silu = a.silu; P.mode = a.dst_mode;
+    P.table = a.table; P.gamma = a.gamma; P.beta = a.beta; P.ab = a.rows_per_stat > 0 ? a.ab : nullptr; P.silu = a.silu; P.mode = a.dst_mode;
     P.NF = a.NF; P.H = a.H; P.W = a.W; P.T = a.T; P.HW = a.HW;
     P.dst = a.dst; P.raw = a.raw;
     int64_t dst_rows = 0;

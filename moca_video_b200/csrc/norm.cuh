@@ -31,8 +31,10 @@ struct StatSrc {
     int spf = 0, tpad = 0, toff = 0;
 };
 // (mean, rstd) table [nstat, 32] of GroupNorm(32) over the virtual channel concat of s1 and s2 (s2.C == 0: single source)
+// ab (optional, with gamma / beta): per-(statistics group, channel) affine form of the normalisation, [nstat, C] float2
+// (rstd * gamma, beta - mean * rstd * gamma), so that gn_apply is one FMA per element with no group arithmetic.
 int gn_finalize(const StatSrc& s1, const StatSrc& s2, int nstat, int frames_per_stat, int T, int rows_per_frame, float eps,
-                float2* table, cudaStream_t st);
+                float2* table, cudaStream_t st, const float* gamma = nullptr, const float* beta = nullptr, float2* ab = nullptr);
 
 struct ApplyArgs {
     const float* x1 = nullptr; int C1 = 0;
@@ -42,6 +44,7 @@ struct ApplyArgs {
     int groups = 32;
     const float2* table = nullptr;  // (mean, rstd) per (statistics group, channel group), written by gn_stats
     const float* gamma = nullptr; const float* beta = nullptr;
+    const float2* ab = nullptr;     // optional [nstat, C1+C2] (scale, shift) written by gn_finalize; replaces table/gamma/beta
     float eps = 1e-5f;
     int silu = 0;
     int dst_mode = DST_LINEAR;

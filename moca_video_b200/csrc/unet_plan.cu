@@ -36,6 +36,7 @@ struct Plan {
     size_t stats_bytes = 0;
     float2* parts = nullptr;          // slice-partial statistics (bump allocated; fully rewritten by every forward)
     float2* mr_table = nullptr;       // (mean, rstd) tables written by gn_stats, one slot per GroupNorm
+    float2* ab_table = nullptr;       // (scale, shift) per (statistics group, channel) of the GroupNorm being applied (shared)
     unsigned* stat_counters = nullptr;
     cudaGraphExec_t gexec = nullptr;
     std::vector<Tap> taps;
@@ -173,8 +174,12 @@ struct Builder {
         a.x1 = x1; a.C1 = C1; a.x2 = x2; a.C2 = C2; a.rows = rows; a.rows_per_stat = rows_per_stat; a.table = table;
         a.gamma = w.g; a.beta = w.b; a.eps = eps; a.silu = silu; a.dst_mode = dst_mode;
         a.NF = NF; a.H = H; a.W = W; a.B = B; a.T = T; a.HW = H * W; a.dst = dst; a.raw = raw;
+        // (scale, shift) per (statistics group, channel): one buffer for all GroupNorms, finalize -> apply are adjacent in the stream
+        float2* ab = dry ? nullptr : plan->ab_table;
+        a.ab = ab;
+        const float* gam = w.g; const float* bet = w.b;
         const std::string dims = " rows=" + std::to_string(rows) + " C=" + std::to_string(C1 + C2) + " dst=" + std::to_string(dst_mode);
-        push([=](cudaStream_t st) { return gn_finalize(s1, s2, nstat, fps, Tn, rpf, eps, table, st); }, 1, "gn_finalize" + dims);
+        push([=](cudaStream_t st) { return gn_finalize(s1, s2, nstat, fps, Tn, rpf, eps, table, st, gam, bet, ab); }, 1, "gn_finalize" + dims);
         push([=](cudaStream_t st) { return gn_apply(a, st); }, 1, "gn_apply" + dims);
     }
     void convert(const float* x, int C, int64_t rows, int dst_mode, int H, int W, __nv_bfloat16* dst) {
@@ -489,6 +494,7 @@ static int get_plan(moca_unet* n, int B, int T, int H, int W, int Lmax, Plan** o
     plan->stats = (double*)real.palloc(plan->stats_bytes);
     plan->parts = (float2*)real.palloc(dry.part_elems * sizeof(float2));
     plan->mr_table = (float2*)real.palloc((size_t)dry.stat_slots * B * T * 32 * sizeof(float2));
+    plan->ab_table = (float2*)real.palloc((size_t)B * T * 3072 * sizeof(float2));      // gn_apply supports C <= 3072
     for (int i = 0; i < S_COUNT; ++i) {
         real.sptr[i] = real.palloc(dry.need[i] + 256);
         plan->workspace_bytes += dry.need[i];
