@@ -252,8 +252,18 @@ def main():
     if world > 1:
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        # NCCL prints its version banner on stdout; keep stdout for the one JSON line
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=dev)
         r = run_fifo(args, dev, rank, world)
+        r["net"] = None
+        dist.barrier()
+        dist.destroy_process_group()
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
+        os.close(saved_stdout)
     else:
         r = run_ddim(args, dev)
     if rank != 0:

@@ -10,6 +10,7 @@
 //                      bf16 P written into a 128-byte-swizzled K-major smem tile), running (max, sum) and the 64 fp32 output
 //                      accumulators stay in registers; PV of every key tile is read back from TMEM and added.
 // Scores never leave the SM; keys >= Lk (sequence tail, cross-attention padding) get P = 0.
+#include <stdlib.h>
 #include "attn.cuh"
 #include "gemm_tc.cuh"
 
@@ -250,9 +251,258 @@ __global__ void __launch_bounds__(kThreads, 2) attn_tc_kernel(const __grid_const
 }
 
 // ---------------------------------------------------------------------------------------------------------------
+// Second kernel shape, for sequences of >= 256 queries and keys: one CTA = 256 query rows (tiles A and B) of one (frame, head),
+// one CTA per SM, 320 threads:
+//   warps 0-3 / 4-7   softmax warpgroups of tile A / B (thread = query row = TMEM lane)
+//   warp 8 (one lane) TMA producer: Q_A, Q_B once, then K and V tiles of 128 keys through 3-stage rings
+//   warp 9 (one lane) MMA issuer: S_X = Q_X K^T into TMEM columns [128 X, 128 X + 128); O_X (+)= P_X V into [256 + 64 X, ..+64)
+// The output accumulator stays in TMEM: a softmax thread reads its 128 scores once, releases S (the next QK^T starts while
+// it computes the exponentials), and rescales O only when the running row maximum has grown by more than 2^8 since the
+// reference maximum was fixed (warp-uniform decision; exact: the reference maximum cancels in the final division), so the
+// per-tile work of a thread is 128 exp2 + one swizzled bf16 row of P.  While warpgroup A is in its exponentials the tensor
+// pipe runs the MMAs of tile B and vice versa.
+namespace {
+constexpr int kThreads2 = 320;
+constexpr int kStages2 = 3;
+// smem: Q_A | Q_B | K[3] | V[3] | P_A (2 halves) | P_B (2 halves) | barriers
+constexpr int kOff2Q = 0, kOff2K = 2 * kTileBytes, kOff2V = kOff2K + kStages2 * kTileBytes, kOff2P = kOff2V + kStages2 * kTileBytes,
+              kOff2Bar = kOff2P + 4 * kTileBytes;
+constexpr size_t kSmem2 = (size_t)kOff2Bar + 256 + 1024;
+constexpr float kRescaleLog2 = 8.0f;
+}  // namespace
+
+__global__ void __launch_bounds__(kThreads2, 1) attn_tc2_kernel(const __grid_constant__ AttnTcP P) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(base + kOff2Bar);
+    uint64_t* q_full = bars + 0;
+    uint64_t* k_full = bars + 1;      // [3]
+    uint64_t* k_empty = bars + 4;     // [3]
+    uint64_t* v_full = bars + 7;      // [3]
+    uint64_t* v_empty = bars + 10;    // [3]
+    uint64_t* s_full = bars + 13;     // [2] S_X(j) is in TMEM
+    uint64_t* s_free = bars + 15;     // [2] S_X(j) has been read into registers
+    uint64_t* p_full = bars + 17;     // [2] P_X(j) is in smem (and O_X rescaled if needed)
+    uint64_t* o_done = bars + 19;     // [2] P_X(j) V_j has been accumulated
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 21);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int o = blockIdx.y / P.heads, h = blockIdx.y - o * P.heads;
+    const int q0 = blockIdx.x * 2 * kTileQ;
+    const bool hasB = q0 + kTileQ < P.Lq;
+    const int qrow0 = (int)first_row(P.qmap, o), kvrow0 = (int)first_row(P.kvmap, o);
+
+    if (threadIdx.x == 0) {
+        prefetch_tmap(&P.tmQ); prefetch_tmap(&P.tmK); prefetch_tmap(&P.tmV);
+        mbar_init(q_full, 1);
+        for (int i = 0; i < kStages2; ++i) {
+            mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1);
+            mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1);
+        }
+        for (int x = 0; x < 2; ++x) {
+            mbar_init(&s_full[x], 1); mbar_init(&s_free[x], 4);
+            mbar_init(&p_full[x], 4); mbar_init(&o_done[x], 1);
+        }
+        fence_mbar_init();
+    }
+    if (warp == 9) {
+        tmem_alloc(tmem_slot, 512);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
+    pdl_launch_dependents();
+    const int Lk = P.kv_len ? P.kv_len[o / P.kv_len_div] : P.Lk;
+    const int ntiles = (Lk + kTileK - 1) / kTileK;
+
+    if (warp == 8) {
+        if (lane == 0) {
+            // ===== TMA producer =====
+            mbar_expect_tx(q_full, hasB ? 2 * kTileBytes : kTileBytes);
+            tma_load_2d(base + kOff2Q, &P.tmQ, q_full, h * kD, qrow0 + q0);
+            if (hasB) tma_load_2d(base + kOff2Q + kTileBytes, &P.tmQ, q_full, h * kD, qrow0 + q0 + kTileQ);
+            for (int j = 0; j < ntiles; ++j) {
+                const int s = j % kStages2;
+                const uint32_t ph = (uint32_t)(((j / kStages2) & 1) ^ 1);
+                mbar_wait(&k_empty[s], ph);
+                mbar_expect_tx(&k_full[s], kTileBytes);
+                tma_load_2d(base + kOff2K + s * kTileBytes, &P.tmK, &k_full[s], h * kD, kvrow0 + j * kTileK);
+                mbar_wait(&v_empty[s], ph);
+                mbar_expect_tx(&v_full[s], kTileBytes);
+                tma_load_2d(base + kOff2V + s * kTileBytes, &P.tmV, &v_full[s], h * kD, kvrow0 + j * kTileK);
+            }
+        }
+    } else if (warp == 9) {
+        if (lane == 0) {
+            // ===== MMA issuer =====
+            constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128);
+            constexpr uint32_t idesc_pv = umma_idesc_bf16(128, 64) | (1u << 16);      // B (= V) is MN-major
+            const int nx = hasB ? 2 : 1;
+            mbar_wait(q_full, 0);
+            auto issue_s = [&](int x, int j) {
+                const uint64_t dq = umma_desc_sw128(smem_u32(base + kOff2Q + x * kTileBytes));
+                const uint64_t dk = umma_desc_sw128(smem_u32(base + kOff2K + (j % kStages2) * kTileBytes));
+#pragma unroll
+                for (int k = 0; k < kD / 16; ++k)
+                    umma_bf16(tmem_base + (uint32_t)(x * 128), dq + (uint64_t)(2 * k), dk + (uint64_t)(2 * k), idesc_s, (uint32_t)(k != 0));
+                umma_commit(&s_full[x]);
+            };
+            mbar_wait(&k_full[0], 0);
+            tc_fence_after();
+            for (int x = 0; x < nx; ++x) issue_s(x, 0);
+            umma_commit(&k_empty[0]);
+            for (int j = 0; j < ntiles; ++j) {
+                const uint32_t ph = (uint32_t)(j & 1);
+                const bool more = j + 1 < ntiles;
+                if (more) { mbar_wait(&k_full[(j + 1) % kStages2], (uint32_t)(((j + 1) / kStages2) & 1)); }
+                if (more) {
+                    for (int x = 0; x < nx; ++x) {
+                        mbar_wait(&s_free[x], ph);            // S_X(j) is in registers: QK^T of the next key tile may overwrite it
+                        tc_fence_after();
+                        issue_s(x, j + 1);
+                    }
+                    umma_commit(&k_empty[(j + 1) % kStages2]);
+                }
+                mbar_wait(&v_full[j % kStages2], (uint32_t)((j / kStages2) & 1));
+                for (int x = 0; x < nx; ++x) {
+                    mbar_wait(&p_full[x], ph);
+                    tc_fence_after();
+                    const uint32_t t_o = tmem_base + (uint32_t)(256 + x * 64);
+                    const uint32_t pb = smem_u32(base + kOff2P + x * 2 * kTileBytes);
+                    const uint32_t vb = smem_u32(base + kOff2V + (j % kStages2) * kTileBytes);
+#pragma unroll
+                    for (int k = 0; k < kTileK / 16; ++k) {
+                        const uint64_t dp = umma_desc_sw128(pb + (k >> 2) * kTileBytes) + (uint64_t)(2 * (k & 3));
+                        const uint64_t dv = umma_desc_sw128(vb + k * 2048);
+                        umma_bf16(t_o, dp, dv, idesc_pv, (uint32_t)((j | k) != 0));
+                    }
+                    umma_commit(&o_done[x]);
+                }
+                umma_commit(&v_empty[j % kStages2]);
+            }
+        }
+    } else {
+        // ===== softmax warpgroups: x = tile (A / B), thread = query row =====
+        const int x = warp >> 2, wq = warp & 3;
+        if (x == 0 || hasB) {
+            const int row = wq * 32 + lane;
+            const uint32_t t_lane = tmem_base + ((uint32_t)(wq * 32) << 16);
+            const uint32_t t_s = t_lane + (uint32_t)(x * 128), t_o = t_lane + (uint32_t)(256 + x * 64);
+            uint8_t* prow = base + kOff2P + x * 2 * kTileBytes + row * 128;        // this row inside either 64-key half of P_X
+            float m_ref = -INFINITY, l = 0.f;
+            for (int j = 0; j < ntiles; ++j) {
+                const uint32_t ph = (uint32_t)(j & 1);
+                const int nvalid = min(kTileK, Lk - j * kTileK);
+                mbar_wait(&s_full[x], ph);
+                tc_fence_after();
+                uint32_t r[128];
+                tmem_ld32(t_s, r); tmem_ld32(t_s + 32, r + 32); tmem_ld32(t_s + 64, r + 64); tmem_ld32(t_s + 96, r + 96);
+                tmem_ld_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&s_free[x]);
+                if (nvalid < kTileK) {
+#pragma unroll
+                    for (int i = 0; i < 128; ++i)
+                        if (i >= nvalid) r[i] = 0xff800000u;             // -inf: exp2 gives exactly 0
+                }
+                float mxp[8];                                             // 8 independent chains instead of one of 128
+#pragma unroll
+                for (int i = 0; i < 8; ++i) mxp[i] = __uint_as_float(r[i]);
+#pragma unroll
+                for (int i = 8; i < 128; ++i) mxp[i & 7] = fmaxf(mxp[i & 7], __uint_as_float(r[i]));
+                const float mx = fmaxf(fmaxf(fmaxf(mxp[0], mxp[1]), fmaxf(mxp[2], mxp[3])), fmaxf(fmaxf(mxp[4], mxp[5]), fmaxf(mxp[6], mxp[7])));
+                // the reference maximum moves only when some row of the warp outgrew it by 2^8 (first tile: always)
+                const bool grow = (mx - m_ref) * P.scale_log2 > kRescaleLog2;
+                if (j > 0) {
+                    mbar_wait(&o_done[x], ph ^ 1u);                        // P_X(j-1) V has been accumulated: P_X smem and O_X are ours
+                    tc_fence_after();
+                }
+                if (__any_sync(0xffffffffu, grow)) {
+                    const float m_new = fmaxf(m_ref, mx);
+                    const float alpha = ex2((m_ref - m_new) * P.scale_log2);       // first tile: exp2(-inf) = 0, l = 0 anyway
+                    m_ref = m_new;
+                    l *= alpha;
+                    if (j > 0) {
+#pragma unroll 1
+                        for (int c = 0; c < 8; ++c) {                      // rare path: 8 columns at a time keeps the 128 scores in registers
+                            uint32_t ov[8];
+                            tmem_ld8(t_o + (uint32_t)(c * 8), ov);
+                            tmem_ld_wait();
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) ov[i] = __float_as_uint(__uint_as_float(ov[i]) * alpha);
+                            tmem_st8(t_o + (uint32_t)(c * 8), ov);
+                        }
+                        tmem_st_wait();
+                    }
+                }
+                const float ms = m_ref * P.scale_log2;
+                float rsp[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    uint32_t pk[16];
+#pragma unroll
+                    for (int i = 0; i < 32; i += 2) {
+                        const float p0 = ex2(fmaf(__uint_as_float(r[c * 32 + i]), P.scale_log2, -ms));
+                        const float p1 = ex2(fmaf(__uint_as_float(r[c * 32 + i + 1]), P.scale_log2, -ms));
+                        rsp[(i >> 1) & 3] += p0 + p1;
+                        pk[i >> 1] = pack2(p0, p1);
+                    }
+                    uint8_t* dst = prow + (c >> 1) * kTileBytes;
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const int chunk = ((c & 1) * 4 + u) ^ (row & 7);
+                        *reinterpret_cast<uint4*>(dst + chunk * 16) = make_uint4(pk[4 * u], pk[4 * u + 1], pk[4 * u + 2], pk[4 * u + 3]);
+                    }
+                }
+                l += (rsp[0] + rsp[1]) + (rsp[2] + rsp[3]);
+                tc_fence_before();
+                fence_async_smem();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&p_full[x]);
+            }
+            // epilogue: O_X / l -> bf16
+            mbar_wait(&o_done[x], (uint32_t)((ntiles - 1) & 1));
+            tc_fence_after();
+            const int qr = q0 + x * kTileQ + row;
+            const float inv = 1.0f / l;
+            __nv_bfloat16* op = P.out + ((int64_t)qrow0 + qr) * P.ldo + h * kD;
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                uint32_t ov[32];
+                tmem_ld32(t_o + (uint32_t)(c * 32), ov);
+                tmem_ld_wait();
+                if (qr < P.Lq) {
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        float f[8];
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(ov[8 * u + e]) * inv;
+                        *reinterpret_cast<uint4*>(op + c * 32 + u * 8) =
+                            make_uint4(pack2(f[0], f[1]), pack2(f[2], f[3]), pack2(f[4], f[5]), pack2(f[6], f[7]));
+                    }
+                }
+            }
+            tc_fence_before();
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 9) {
+        __syncwarp();
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
 struct AttnTcLaunchImpl {
     AttnTcP p;
     dim3 grid;
+    int version;      // 1: 128 query rows per CTA, two CTAs per SM; 2: 256 query rows per CTA, accumulator in TMEM
 };
 
 bool attention_tc_supported(const AttnArgs& a) {
@@ -278,10 +528,13 @@ int attention_tc_plan(const AttnArgs& a, AttnTcLaunch* out) {
     L.p.heads = a.heads; L.p.Lq = a.Lq; L.p.Lk = a.Lk;
     L.p.kv_len = a.kv_len; L.p.kv_len_div = a.kv_len_div > 0 ? a.kv_len_div : 1;
     L.p.scale_log2 = a.scale * 1.4426950408889634f;
-    L.grid = dim3(cdiv(a.Lq, kTileQ), a.n_outer * a.heads);
+    static const int forced = [] { const char* e = getenv("MOCA_ATTN_TC"); return e ? atoi(e) : 0; }();      // 1 / 2 pins the kernel shape
+    L.version = forced == 1 || forced == 2 ? forced : (a.Lq >= 256 && a.Lk >= 256 ? 2 : 1);
+    L.grid = dim3(cdiv(a.Lq, L.version == 2 ? 2 * kTileQ : kTileQ), a.n_outer * a.heads);
     static bool attr_done = false;
     if (!attr_done) {
         MOCA_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
+        MOCA_CHECK_CUDA(cudaFuncSetAttribute(attn_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem2));
         attr_done = true;
     }
     memcpy(out->storage, &L, sizeof(L));
@@ -290,7 +543,8 @@ int attention_tc_plan(const AttnArgs& a, AttnTcLaunch* out) {
 
 int attention_tc_run(const AttnTcLaunch& l, cudaStream_t st) {
     const AttnTcLaunchImpl* L = reinterpret_cast<const AttnTcLaunchImpl*>(l.storage);
-    launch_pdl_tc(attn_tc_kernel, L->grid, dim3(kThreads), kSmem, st, L->p);
+    if (L->version == 2) launch_pdl_tc(attn_tc2_kernel, L->grid, dim3(kThreads2), kSmem2, st, L->p);
+    else launch_pdl_tc(attn_tc_kernel, L->grid, dim3(kThreads), kSmem, st, L->p);
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
 }
