@@ -271,6 +271,13 @@ def main():
     tf_peak, hbm_peak, peak_src = peaks()
     value = r["units_per_step"] / (r["ms"] * 1e-3)
     achieved = value * r["flop_per_unit"] / 1e12 / max(world, 1)           # per GPU
+    # DRAM bytes of one step (all kernels, ncu dram__bytes_read + write per launch, cold L2 per launch = upper bound); committed
+    # capture of the N=1 workload, see profiles/README.md
+    traffic = None
+    tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_traffic.json")
+    if world == 1 and os.path.exists(tpath):
+        with open(tpath) as f:
+            traffic = json.load(f).get("dram_bytes_per_step")
     out = {"metric": "UNet denoise steps/s (16f 320x512)", "value": value, "unit": "steps/s", "n_gpus": world, "steps": args.steps,
            "warmup": args.warmup, "ms_per_step": r["ms"], "higher_is_better": True, "scaling": "weak" if world == 1 else "strong",
            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
@@ -280,7 +287,7 @@ def main():
                    "d2h_bytes_per_step": r["d2h"]},
            "gpu_launches": r["launches"], "clocks": r["clocks"],
            "roofline": {"bound": "tensor", "achieved": achieved, "peak": tf_peak, "unit": "TFLOP/s", "frac": achieved / tf_peak,
-                        "traffic": None, "peak_source": peak_src,
+                        "traffic": traffic, "peak_source": peak_src,
                         "note": "whole UNet step: algorithmic 2*MAC of the reference forward (SURVEY 8d) x forwards per step / step time, per GPU; "
                                 f"executed useful FLOPs per forward {r['executed_flops'] / 1e12:.3f} T"}}
     if world == 1 and not args.no_cpu_baseline:
