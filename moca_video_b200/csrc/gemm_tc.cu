@@ -1,4 +1,5 @@
 // See gemm_tc.cuh for the contract.  sm_100a only: tcgen05.mma (UTCHMMA), tcgen05.ld (LDTM), TMA (UTMALDG).
+#include <stdlib.h>
 #include "gemm_tc.cuh"
 
 namespace moca {
@@ -10,13 +11,17 @@ constexpr int kBM = 128;
 constexpr int kBK = 64;
 constexpr int kABytes = kBM * kBK * 2;        // 16 KB, 128 rows of 128 B
 
-template <int BN>
+// TEPI: TMA-store epilogue variant (3 stages; per epilogue warp 4 KB output staging + two 4 KB residual buffers)
+template <int BN, bool TEPI = false>
 struct GemmCfg {
     static constexpr int B_BYTES = BN * kBK * 2;
-    static constexpr int STAGE_BYTES = kABytes + B_BYTES;
-    static constexpr int STAGES = (BN == 256) ? 4 : (BN == 160 ? 5 : 6);
+    static constexpr int STAGE_BYTES = kABytes + B_BYTES;                   // multiple of 1024 for BN in {128, 160, 256}
+    static constexpr int STAGES = TEPI ? 3 : ((BN == 256) ? 4 : (BN == 160 ? 5 : 6));
     static constexpr int TMEM_COLS = (2 * BN <= 256) ? 256 : 512;
-    static constexpr size_t SMEM = (size_t)STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ + 8 * 4096 /*epilogue staging*/;
+    static constexpr int WARP_STG = TEPI ? 12288 : 4096;                    // epilogue staging per warp
+    static constexpr int OFF_STG = STAGES * STAGE_BYTES;                    // 1024-byte aligned
+    static constexpr int OFF_BAR = OFF_STG + 8 * WARP_STG;
+    static constexpr size_t SMEM = (size_t)OFF_BAR + 512 /*barriers*/ + 1024 /*align slack*/;
 };
 
 __device__ __forceinline__ float gelu_erf(float g) { return 0.5f * g * (1.0f + erff(g * 0.70710678118654752f)); }
@@ -70,17 +75,19 @@ __device__ __forceinline__ bool map_row(const GemmParams& P, int row, int& out_r
     return true;
 }
 
-template <int BN, int EPI, bool STATS>
+template <int BN, int EPI, bool STATS, bool TEPI = false>
 __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_constant__ GemmParams P) {
-    using Cfg = GemmCfg<BN>;
+    using Cfg = GemmCfg<BN, TEPI>;
+    static_assert(!TEPI || EPI == EPI_F32, "the TMA-store epilogue is an fp32 epilogue");
     constexpr int STAGES = Cfg::STAGES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    uint64_t* full = reinterpret_cast<uint64_t*>(base + (size_t)STAGES * Cfg::STAGE_BYTES);
+    uint64_t* full = reinterpret_cast<uint64_t*>(base + Cfg::OFF_BAR);
     uint64_t* empty = full + STAGES;
     uint64_t* tfull = empty + STAGES;
     uint64_t* tempty = tfull + 2;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+    uint64_t* rfull = tempty + 2;                          // [8 warps][2] residual chunk landed (TEPI)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(rfull + 16);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -97,6 +104,11 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
         for (int i = 0; i < 2; ++i) {
             mbar_init(&tfull[i], 1);
             mbar_init(&tempty[i], 8);
+        }
+        if constexpr (TEPI) {
+            prefetch_tmap(&P.tmOut);
+            prefetch_tmap(&P.tmRes);
+            for (int i = 0; i < 16; ++i) mbar_init(&rfull[i], 1);
         }
         fence_mbar_init();
     }
@@ -163,6 +175,118 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
                 if (as == 0) aphase ^= 1;
             }
         }
+    } else if constexpr (TEPI) {
+        // ===== TMA-store epilogue (linear / time-padded rows, 32-row slices that map to 32 consecutive output rows) =====
+        // Warp = (lane quarter q, half): alternate 32-column chunks of the tile.  Everything stays in the thread = row layout
+        // of tcgen05.ld: the residual chunk arrives by TMA in a 128-byte-swizzled 32 x 32 fp32 box (two buffers per warp, the
+        // load for chunk k + 2 is issued as soon as chunk k has been read), the thread adds bias + residual to its row and
+        // writes it into a swizzled staging box that one lane hands to a TMA store.  GroupNorm partial sums are column sums
+        // of the staging box (lane = column).  ~10x fewer instructions per chunk than the staged-and-coalesced epilogue below.
+        const int w = warp - 2, q = warp & 3, half = w >> 2;
+        uint8_t* wbuf = base + Cfg::OFF_STG + (size_t)w * Cfg::WARP_STG;          // [out 4 KB][res0 4 KB][res1 4 KB]
+        uint64_t* rbar = rfull + 2 * w;
+        constexpr int kChunks = BN / 32;
+        const bool has_res = P.residual != nullptr;
+        // slice of 32 input-space rows -> first output row (or -1: padding frame / beyond M)
+        auto slice_row = [&](int tile) -> int {
+            const int row0 = (tile / P.num_n_tiles) * kBM + q * 32;
+            if (row0 >= P.M) return -1;
+            if (P.mode == GEMM_LINEAR) return row0;
+            const int f = row0 / P.g_rows, r = row0 - f * P.g_rows;
+            const int a = r / P.g_w, b = r - a * P.g_w;
+            return (a < 1 || a > P.g_H) ? -1 : (f * P.g_H + (a - 1)) * P.g_w + b;
+        };
+        // chunk cursor: (tile, c) with c = half, half + 2, ..; normalised so that the chunk exists
+        auto norm = [&](int& t, int& c) {
+            while (t < ntiles && !(c < kChunks && (t % P.num_n_tiles) * BN + c * 32 < P.N)) { t += gridDim.x; c = half; }
+        };
+        auto next = [&](int& t, int& c) { c += 2; norm(t, c); };
+        // producer cursor runs two loaded chunks ahead
+        int pt = blockIdx.x, pc = half;
+        uint32_t n_issued = 0, n_waited = 0;
+        norm(pt, pc);
+        auto issue_res = [&]() {                               // lane 0 only
+            while (pt < ntiles) {
+                const int orow = slice_row(pt);
+                const int n0 = (pt % P.num_n_tiles) * BN + pc * 32;
+                next(pt, pc);
+                if (orow < 0) continue;
+                const uint32_t slot = n_issued & 1u;
+                mbar_expect_tx(&rbar[slot], 4096);
+                tma_load_2d(wbuf + 4096 + slot * 4096, &P.tmRes, &rbar[slot], n0, orow);
+                ++n_issued;
+                return;
+            }
+        };
+        if (has_res && lane == 0) { issue_res(); issue_res(); }
+        int as = 0;
+        uint32_t aphase = 0;
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+            const int orow0 = slice_row(tile);
+            const int col_tile0 = (tile % P.num_n_tiles) * BN;
+            mbar_wait(&tfull[as], aphase);
+            tc_fence_after();
+            const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN);
+            if (orow0 >= 0) {
+                for (int c = half; c < kChunks; c += 2) {
+                    const int n0 = col_tile0 + c * 32;
+                    if (n0 >= P.N) break;
+                    uint32_t r[32];
+                    tmem_ld32(t_row + (uint32_t)(c * 32), r);
+                    const uint8_t* rsrc = wbuf + 4096 + (n_waited & 1u) * 4096 + lane * 128;
+                    if (has_res) mbar_wait(&rbar[n_waited & 1u], (n_waited >> 1) & 1u);
+                    // the previous store of this warp must have finished reading the staging box
+                    if (lane == 0) bulk_wait_read0();
+                    __syncwarp();
+                    tmem_ld_wait();
+                    uint8_t* dst = wbuf + lane * 128;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        float4 v = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]),
+                                               __uint_as_float(r[4 * j + 3]));
+                        if (P.bias) {
+                            const float4 b4 = __ldg(reinterpret_cast<const float4*>(P.bias + n0) + j);
+                            v.x += b4.x; v.y += b4.y; v.z += b4.z; v.w += b4.w;
+                        }
+                        const int sw = (j ^ (lane & 7)) << 4;
+                        if (has_res) {
+                            const float4 t4 = *reinterpret_cast<const float4*>(rsrc + sw);
+                            v.x += t4.x; v.y += t4.y; v.z += t4.z; v.w += t4.w;
+                        }
+                        *reinterpret_cast<float4*>(dst + sw) = v;
+                    }
+                    fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0) {
+                        tma_store_2d(&P.tmOut, wbuf, n0, orow0);
+                        bulk_commit_group();
+                        if (has_res) issue_res();              // the buffer just read is free again
+                    }
+                    if (has_res) ++n_waited;
+                    if constexpr (STATS) {
+                        // lane = column: sum / sum of squares over the 32 rows of the staging box (conflict-free: one row per step)
+                        // (same association as the staged epilogue: rows 4i + g summed over i for g = 0..3, then (p0 + p1) + (p2 + p3),
+                        // so both epilogues give bit-identical statistics and the result does not depend on the tile width)
+                        float ps[4] = {0.f, 0.f, 0.f, 0.f}, pq[4] = {0.f, 0.f, 0.f, 0.f};
+                        const int cj = lane >> 2, ce = (lane & 3) << 2;
+#pragma unroll
+                        for (int rr = 0; rr < 32; ++rr) {
+                            const float x = *reinterpret_cast<const float*>(wbuf + rr * 128 + ((cj ^ (rr & 7)) << 4) + ce);
+                            ps[rr & 3] += x;
+                            pq[rr & 3] = fmaf(x, x, pq[rr & 3]);
+                        }
+                        P.spart[(size_t)((tile / P.num_n_tiles) * (kBM / 32) + q) * P.N + n0 + lane] =
+                            make_float2((ps[0] + ps[1]) + (ps[2] + ps[3]), (pq[0] + pq[1]) + (pq[2] + pq[3]));
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty[as]);
+            as ^= 1;
+            if (as == 0) aphase ^= 1;
+        }
+        if (lane == 0) bulk_wait0();
     } else {
         // ===== epilogue warps 2..9: TMEM lane quarter q = warp % 4, two warps per quarter take alternate 32-column chunks.
         // Each chunk goes TMEM -> registers (thread = row) -> XOR-swizzled smem staging -> registers (8 lanes = one row's
@@ -171,7 +295,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
         // warp always has a DRAM round trip in flight behind its TMEM / staging work.
         const int q = warp & 3;
         const int half = (warp - 2) >> 2;
-        float* stg = reinterpret_cast<float*>(base + (size_t)STAGES * Cfg::STAGE_BYTES + 256) + (size_t)(warp - 2) * 1024;
+        float* stg = reinterpret_cast<float*>(base + Cfg::OFF_STG) + (size_t)(warp - 2) * 1024;
         constexpr bool kGeglu = EPI == EPI_GEGLU;
         constexpr int kChunks = kGeglu ? BN / 64 : BN / 32;
         const int ncols_total = kGeglu ? (P.N >> 1) : P.N;
@@ -490,6 +614,23 @@ int make_tmap_bf16(CUtensorMap* tm, const void* ptr, int64_t rows, int64_t cols,
     return MOCA_OK;
 }
 
+// fp32 row-major [rows, cols] (pitch elements) -> box of 32 columns (128 bytes) x 32 rows, 128-byte swizzle: the per-warp
+// epilogue chunk of the TMA-store epilogue (residual load and output store)
+int make_tmap_f32_chunk(CUtensorMap* tm, const void* ptr, int64_t rows, int64_t cols, int64_t pitch) {
+    EncodeTiledFn enc = get_encode();
+    MOCA_REQUIRE(enc != nullptr, MOCA_E_CUDA, "cuTensorMapEncodeTiled entry point not available");
+    MOCA_REQUIRE(((uintptr_t)ptr & 15) == 0 && (pitch * 4) % 16 == 0, MOCA_E_ALIGN, "TMA fp32 tensor %p pitch %lld not 16-byte aligned", ptr,
+                 (long long)pitch);
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)pitch * 4};
+    cuuint32_t box[2] = {32, 32};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    MOCA_REQUIRE(r == CUDA_SUCCESS, MOCA_E_CUDA, "cuTensorMapEncodeTiled (fp32 chunk) failed with CUresult %d", (int)r);
+    return MOCA_OK;
+}
+
 // Tile width: minimise (waves over the SMs) x (columns computed per tile), with a small penalty for the narrower tiles
 // (a 128-wide B tile keeps the MMA shared-memory-bandwidth bound).  GEGLU weights are packed for 256-wide tiles.
 static int pick_bn(const GemmDesc& d, int num_sms) {
@@ -509,26 +650,39 @@ static int pick_bn(const GemmDesc& d, int num_sms) {
     return best;
 }
 
-template <int BN, int EPI, bool STATS = false>
+template <int BN, int EPI, bool STATS = false, bool TEPI = false>
 static int set_attr() {
     static bool done = false;
     if (!done) {
-        MOCA_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI, STATS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GemmCfg<BN>::SMEM));
+        MOCA_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI, STATS, TEPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)GemmCfg<BN, TEPI>::SMEM));
         done = true;
     }
     return MOCA_OK;
 }
 
 template <int BN>
-static int set_attr_bn(int epi) {
-    if (epi == EPI_F32) { int rc = set_attr<BN, EPI_F32, true>(); return rc ? rc : set_attr<BN, EPI_F32>(); }
+static int set_attr_bn(int epi, int tepi) {
+    if (epi == EPI_F32) {
+        if (tepi) {
+            if constexpr (BN != 256) { int rc = set_attr<BN, EPI_F32, true, true>(); return rc ? rc : set_attr<BN, EPI_F32, false, true>(); }
+        }
+        int rc = set_attr<BN, EPI_F32, true>();
+        return rc ? rc : set_attr<BN, EPI_F32>();
+    }
     if (epi == EPI_BF16) return set_attr<BN, EPI_BF16>();
     return set_attr<BN, EPI_GEGLU>();
 }
 
 template <int BN>
 static void launch_bn(const GemmLaunch& l, cudaStream_t st) {
-    if (l.p.epi == EPI_F32 && (l.p.cstat || l.p.spart)) launch_pdl_tc(gemm_tc_kernel<BN, EPI_F32, true>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
+    const bool stats = l.p.cstat || l.p.spart;
+    if (l.p.epi == EPI_F32 && l.p.tepi) {
+        if constexpr (BN != 256) {
+            if (stats) launch_pdl_tc(gemm_tc_kernel<BN, EPI_F32, true, true>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
+            else launch_pdl_tc(gemm_tc_kernel<BN, EPI_F32, false, true>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
+        }
+    } else if (l.p.epi == EPI_F32 && stats) launch_pdl_tc(gemm_tc_kernel<BN, EPI_F32, true>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
     else if (l.p.epi == EPI_F32) launch_pdl_tc(gemm_tc_kernel<BN, EPI_F32, false>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
     else if (l.p.epi == EPI_BF16) launch_pdl_tc(gemm_tc_kernel<BN, EPI_BF16, false>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
     else launch_pdl_tc(gemm_tc_kernel<BN, EPI_GEGLU, false>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
@@ -570,9 +724,25 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
     p.num_n_tiles = cdiv(d.N, L.BN);
     const int ntiles = p.num_m_tiles * p.num_n_tiles;
     L.grid = ntiles < ctx.num_sms ? ntiles : ctx.num_sms;
-    L.smem = L.BN == 256 ? GemmCfg<256>::SMEM : (L.BN == 160 ? GemmCfg<160>::SMEM : GemmCfg<128>::SMEM);
+    // TMA-store epilogue: fp32 output whose 32-row slices map to 32 consecutive output rows, short K (the epilogue, not the
+    // main loop, bounds these), slice-mode statistics only.  MOCA_GEMM_TEPI=0 pins the staged-and-coalesced epilogue.
+    static const int tepi_on = [] { const char* e = getenv("MOCA_GEMM_TEPI"); return e ? atoi(e) : 1; }();
+    static const int tepi_maxk = [] { const char* e = getenv("MOCA_GEMM_TEPI_MAXK"); return e ? atoi(e) : 20; }();
+    const bool rows_ok = (d.mode == GEMM_LINEAR && d.M % 32 == 0) || (d.mode == GEMM_TIME_PAD && d.g_w % 32 == 0 && d.g_rows % 32 == 0);
+    p.tepi = tepi_on && d.epi == EPI_F32 && L.BN != 256 && rows_ok && d.N % 32 == 0 && d.ldo % 4 == 0 && !d.rowbias && !d.chan_stats &&
+             d.ntaps * p.kblocks <= tepi_maxk && (((uintptr_t)d.out | (uintptr_t)d.residual | (uintptr_t)d.bias) & 15) == 0;
+    if (p.tepi) {
+        const int64_t out_rows = d.mode == GEMM_LINEAR ? d.M : (int64_t)(d.M / d.g_rows) * d.g_H * d.g_w;
+        rc = make_tmap_f32_chunk(&p.tmOut, d.out, out_rows, d.N, d.ldo);
+        if (rc) return rc;
+        rc = make_tmap_f32_chunk(&p.tmRes, d.residual ? (const void*)d.residual : d.out, out_rows, d.N, d.ldo);
+        if (rc) return rc;
+        L.smem = L.BN == 160 ? GemmCfg<160, true>::SMEM : GemmCfg<128, true>::SMEM;
+    } else {
+        L.smem = L.BN == 256 ? GemmCfg<256>::SMEM : (L.BN == 160 ? GemmCfg<160>::SMEM : GemmCfg<128>::SMEM);
+    }
     L.flops = 2.0 * (double)d.M * d.N * d.ntaps * d.a_cols;
-    rc = L.BN == 256 ? set_attr_bn<256>(d.epi) : (L.BN == 160 ? set_attr_bn<160>(d.epi) : set_attr_bn<128>(d.epi));
+    rc = L.BN == 256 ? set_attr_bn<256>(d.epi, p.tepi) : (L.BN == 160 ? set_attr_bn<160>(d.epi, p.tepi) : set_attr_bn<128>(d.epi, p.tepi));
     if (rc) return rc;
     *out = L;
     return MOCA_OK;

@@ -26,6 +26,8 @@ enum GemmEpi { EPI_F32 = 0, EPI_BF16 = 1, EPI_GEGLU = 2 };
 
 struct GemmParams {
     CUtensorMap tmA, tmB;
+    CUtensorMap tmOut, tmRes;  // TMA-store epilogue only: fp32 [out_rows, N] output / residual, 32 x 32 boxes
+    int tepi;                 // 1: TMA-store epilogue (gemm_tc.cu)
     int M, N;                 // rows computed (input-row space), accumulator columns
     int ntaps, kblocks, Kp;   // kblocks = Kp / 64 per tap
     int tap_shift[9];
