@@ -11,16 +11,21 @@ constexpr int kBM = 128;
 constexpr int kBK = 64;
 constexpr int kABytes = kBM * kBK * 2;        // 16 KB, 128 rows of 128 B
 
-// TEPI: TMA-store epilogue variant (3 stages; per epilogue warp 4 KB output staging + two 4 KB residual buffers)
-template <int BN, bool TEPI = false>
+// TEPI: TMA-store epilogue variants.  fp32: 3 stages, per epilogue warp 4 KB output staging + two 4 KB residual buffers.
+// GEGLU: 16 epilogue warps (one 32-column output chunk each, the GELU arithmetic needs the extra warps to hide its
+// latencies), 2 KB bf16 staging per warp.
+template <int BN, bool TEPI = false, int EPI = EPI_F32>
 struct GemmCfg {
+    static constexpr bool GT = TEPI && EPI == EPI_GEGLU;
     static constexpr int B_BYTES = BN * kBK * 2;
     static constexpr int STAGE_BYTES = kABytes + B_BYTES;                   // multiple of 1024 for BN in {128, 160, 256}
-    static constexpr int STAGES = TEPI ? 3 : ((BN == 256) ? 4 : (BN == 160 ? 5 : 6));
+    static constexpr int STAGES = GT ? 4 : (TEPI ? 3 : ((BN == 256) ? 4 : (BN == 160 ? 5 : 6)));
     static constexpr int TMEM_COLS = (2 * BN <= 256) ? 256 : 512;
-    static constexpr int WARP_STG = TEPI ? 12288 : 4096;                    // epilogue staging per warp
+    static constexpr int EPI_WARPS = GT ? 16 : 8;
+    static constexpr int THREADS = 64 + 32 * EPI_WARPS;
+    static constexpr int WARP_STG = GT ? 2048 : (TEPI ? 12288 : 4096);      // epilogue staging per warp
     static constexpr int OFF_STG = STAGES * STAGE_BYTES;                    // 1024-byte aligned
-    static constexpr int OFF_BAR = OFF_STG + 8 * WARP_STG;
+    static constexpr int OFF_BAR = OFF_STG + EPI_WARPS * WARP_STG;
     static constexpr size_t SMEM = (size_t)OFF_BAR + 512 /*barriers*/ + 1024 /*align slack*/;
 };
 
@@ -76,9 +81,9 @@ __device__ __forceinline__ bool map_row(const GemmParams& P, int row, int& out_r
 }
 
 template <int BN, int EPI, bool STATS, bool TEPI = false>
-__global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_constant__ GemmParams P) {
-    using Cfg = GemmCfg<BN, TEPI>;
-    static_assert(!TEPI || EPI == EPI_F32, "the TMA-store epilogue is an fp32 epilogue");
+__global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI>::THREADS), 1) gemm_tc_kernel(const __grid_constant__ GemmParams P) {
+    using Cfg = GemmCfg<BN, TEPI, EPI>;
+    static_assert(!TEPI || EPI == EPI_F32 || EPI == EPI_GEGLU, "TMA-store epilogues exist for fp32 and GEGLU output");
     constexpr int STAGES = Cfg::STAGES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -103,7 +108,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&tfull[i], 1);
-            mbar_init(&tempty[i], 8);
+            mbar_init(&tempty[i], Cfg::EPI_WARPS);
         }
         if constexpr (TEPI) {
             prefetch_tmap(&P.tmOut);
@@ -175,6 +180,62 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
                 if (as == 0) aphase ^= 1;
             }
         }
+    } else if constexpr (TEPI && EPI == EPI_GEGLU) {
+        // ===== GEGLU, thread = row, 16 warps: warp (q, c) owns output columns c*32 .. +31 of the tile's 128 for the rows of
+        // TMEM lane quarter q: value and gate straight from TMEM (16 columns at a time), x * gelu(gate) in registers, bf16 row
+        // segment into a 32 x 64-byte staging box, one TMA store per tile and warp.
+        const int w = warp - 2, q = warp & 3, c = w >> 2;
+        uint8_t* stgb = base + Cfg::OFF_STG + (size_t)w * Cfg::WARP_STG;
+        const int ncols_total = P.N >> 1;
+        int as = 0;
+        uint32_t aphase = 0;
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+            const int mt = tile / P.num_n_tiles, nt = tile - mt * P.num_n_tiles;
+            const int row0 = mt * kBM + q * 32;
+            const int n0 = nt * (BN / 2) + c * 32;
+            mbar_wait(&tfull[as], aphase);
+            tc_fence_after();
+            const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN);
+            if (row0 < P.M && n0 < ncols_total) {
+                if (lane == 0) bulk_wait_read0();
+                __syncwarp();
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    uint32_t rv[16], rg[16];
+                    tmem_ld16(t_row + (uint32_t)(c * 32 + h * 16), rv);
+                    tmem_ld16(t_row + (uint32_t)(BN / 2 + c * 32 + h * 16), rg);
+                    const float4* bv = reinterpret_cast<const float4*>(P.bias + (size_t)nt * BN + c * 32 + h * 16);
+                    const float4* bg = reinterpret_cast<const float4*>(P.bias + (size_t)nt * BN + BN / 2 + c * 32 + h * 16);
+                    tmem_ld_wait();
+                    uint32_t pk[8];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const float4 b1 = __ldg(bv + u), b2 = __ldg(bg + u);
+                        const float o0 = (__uint_as_float(rv[4 * u]) + b1.x) * gelu_fast(__uint_as_float(rg[4 * u]) + b2.x);
+                        const float o1 = (__uint_as_float(rv[4 * u + 1]) + b1.y) * gelu_fast(__uint_as_float(rg[4 * u + 1]) + b2.y);
+                        const float o2 = (__uint_as_float(rv[4 * u + 2]) + b1.z) * gelu_fast(__uint_as_float(rg[4 * u + 2]) + b2.z);
+                        const float o3 = (__uint_as_float(rv[4 * u + 3]) + b1.w) * gelu_fast(__uint_as_float(rg[4 * u + 3]) + b2.w);
+                        pk[2 * u] = pack_bf16(o0, o1);
+                        pk[2 * u + 1] = pack_bf16(o2, o3);
+                    }
+                    uint4* dst = reinterpret_cast<uint4*>(stgb + lane * 64 + h * 32);
+                    dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                    dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                }
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) {
+                    tma_store_2d(&P.tmOut, stgb, n0, row0);
+                    bulk_commit_group();
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty[as]);
+            as ^= 1;
+            if (as == 0) aphase ^= 1;
+        }
+        if (lane == 0) bulk_wait0();
     } else if constexpr (TEPI) {
         // ===== TMA-store epilogue (linear / time-padded rows, 32-row slices that map to 32 consecutive output rows) =====
         // Warp = (lane quarter q, half): alternate 32-column chunks of the tile.  Everything stays in the thread = row layout
@@ -631,6 +692,22 @@ int make_tmap_f32_chunk(CUtensorMap* tm, const void* ptr, int64_t rows, int64_t 
     return MOCA_OK;
 }
 
+// bf16 row-major [rows, cols] -> box of 32 columns (64 bytes) x 32 rows, no swizzle (GEGLU TMA-store epilogue)
+int make_tmap_bf16_chunk(CUtensorMap* tm, const void* ptr, int64_t rows, int64_t cols, int64_t pitch) {
+    EncodeTiledFn enc = get_encode();
+    MOCA_REQUIRE(enc != nullptr, MOCA_E_CUDA, "cuTensorMapEncodeTiled entry point not available");
+    MOCA_REQUIRE(((uintptr_t)ptr & 15) == 0 && (pitch * 2) % 16 == 0, MOCA_E_ALIGN, "TMA bf16 tensor %p pitch %lld not 16-byte aligned", ptr,
+                 (long long)pitch);
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)pitch * 2};
+    cuuint32_t box[2] = {32, 32};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    MOCA_REQUIRE(r == CUDA_SUCCESS, MOCA_E_CUDA, "cuTensorMapEncodeTiled (bf16 chunk) failed with CUresult %d", (int)r);
+    return MOCA_OK;
+}
+
 // Tile width: minimise (waves over the SMs) x (columns computed per tile), with a small penalty for the narrower tiles
 // (a 128-wide B tile keeps the MMA shared-memory-bandwidth bound).  GEGLU weights are packed for 256-wide tiles.
 static int pick_bn(const GemmDesc& d, int num_sms) {
@@ -655,7 +732,7 @@ static int set_attr() {
     static bool done = false;
     if (!done) {
         MOCA_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI, STATS, TEPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)GemmCfg<BN, TEPI>::SMEM));
+                                             (int)GemmCfg<BN, TEPI, EPI>::SMEM));
         done = true;
     }
     return MOCA_OK;
@@ -671,6 +748,9 @@ static int set_attr_bn(int epi, int tepi) {
         return rc ? rc : set_attr<BN, EPI_F32>();
     }
     if (epi == EPI_BF16) return set_attr<BN, EPI_BF16>();
+    if (tepi) {
+        if constexpr (BN == 256) return set_attr<BN, EPI_GEGLU, false, true>();
+    }
     return set_attr<BN, EPI_GEGLU>();
 }
 
@@ -685,7 +765,10 @@ static void launch_bn(const GemmLaunch& l, cudaStream_t st) {
     } else if (l.p.epi == EPI_F32 && stats) launch_pdl_tc(gemm_tc_kernel<BN, EPI_F32, true>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
     else if (l.p.epi == EPI_F32) launch_pdl_tc(gemm_tc_kernel<BN, EPI_F32, false>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
     else if (l.p.epi == EPI_BF16) launch_pdl_tc(gemm_tc_kernel<BN, EPI_BF16, false>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
-    else launch_pdl_tc(gemm_tc_kernel<BN, EPI_GEGLU, false>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
+    else if (l.p.tepi) {
+        if constexpr (BN == 256)
+            launch_pdl_tc(gemm_tc_kernel<BN, EPI_GEGLU, false, true>, dim3(l.grid), dim3(GemmCfg<BN, true, EPI_GEGLU>::THREADS), l.smem, st, l.p);
+    } else launch_pdl_tc(gemm_tc_kernel<BN, EPI_GEGLU, false>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
 }
 
 int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
@@ -727,11 +810,18 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
     // TMA-store epilogue: fp32 output whose 32-row slices map to 32 consecutive output rows, short K (the epilogue, not the
     // main loop, bounds these), slice-mode statistics only.  MOCA_GEMM_TEPI=0 pins the staged-and-coalesced epilogue.
     static const int tepi_on = [] { const char* e = getenv("MOCA_GEMM_TEPI"); return e ? atoi(e) : 1; }();
-    static const int tepi_maxk = [] { const char* e = getenv("MOCA_GEMM_TEPI_MAXK"); return e ? atoi(e) : 20; }();
+    static const int tepi_maxk = [] { const char* e = getenv("MOCA_GEMM_TEPI_MAXK"); return e ? atoi(e) : 15; }();
     const bool rows_ok = (d.mode == GEMM_LINEAR && d.M % 32 == 0) || (d.mode == GEMM_TIME_PAD && d.g_w % 32 == 0 && d.g_rows % 32 == 0);
     p.tepi = tepi_on && d.epi == EPI_F32 && L.BN != 256 && rows_ok && d.N % 32 == 0 && d.ldo % 4 == 0 && !d.rowbias && !d.chan_stats &&
              d.ntaps * p.kblocks <= tepi_maxk && (((uintptr_t)d.out | (uintptr_t)d.residual | (uintptr_t)d.bias) & 15) == 0;
-    if (p.tepi) {
+    const bool gt = tepi_on && d.epi == EPI_GEGLU && L.BN == 256 && d.mode == GEMM_LINEAR && d.M % 32 == 0 && (d.N / 2) % 32 == 0 &&
+                    d.ldo % 8 == 0 && (((uintptr_t)d.out | (uintptr_t)d.bias) & 15) == 0;
+    if (gt) {
+        p.tepi = 1;
+        rc = make_tmap_bf16_chunk(&p.tmOut, d.out, d.M, d.N / 2, d.ldo);
+        if (rc) return rc;
+        L.smem = GemmCfg<256, true, EPI_GEGLU>::SMEM;
+    } else if (p.tepi) {
         const int64_t out_rows = d.mode == GEMM_LINEAR ? d.M : (int64_t)(d.M / d.g_rows) * d.g_H * d.g_w;
         rc = make_tmap_f32_chunk(&p.tmOut, d.out, out_rows, d.N, d.ldo);
         if (rc) return rc;
