@@ -19,11 +19,12 @@ struct GemmCfg {
     static constexpr bool GT = TEPI && EPI == EPI_GEGLU;
     static constexpr int B_BYTES = BN * kBK * 2;
     static constexpr int STAGE_BYTES = kABytes + B_BYTES;                   // multiple of 1024 for BN in {128, 160, 256}
-    static constexpr int STAGES = GT ? 4 : (TEPI ? 3 : ((BN == 256) ? 4 : (BN == 160 ? 5 : 6)));
+    static constexpr bool BT = TEPI && EPI == EPI_BF16;      // bf16 thread = row epilogue: classic ring, two 2 KB staging boxes per warp
+    static constexpr int STAGES = GT ? 4 : ((TEPI && !BT) ? 3 : ((BN == 256) ? 4 : (BN == 160 ? 5 : 6)));
     static constexpr int TMEM_COLS = (2 * BN <= 256) ? 256 : 512;
     static constexpr int EPI_WARPS = GT ? 16 : 8;
     static constexpr int THREADS = 64 + 32 * EPI_WARPS;
-    static constexpr int WARP_STG = GT ? 2048 : (TEPI ? 12288 : 4096);      // epilogue staging per warp
+    static constexpr int WARP_STG = GT ? 2048 : ((TEPI && !BT) ? 12288 : 4096);      // epilogue staging per warp
     static constexpr int OFF_STG = STAGES * STAGE_BYTES;                    // 1024-byte aligned
     static constexpr int OFF_BAR = OFF_STG + EPI_WARPS * WARP_STG;
     static constexpr size_t SMEM = (size_t)OFF_BAR + 512 /*barriers*/ + 1024 /*align slack*/;
@@ -83,7 +84,7 @@ __device__ __forceinline__ bool map_row(const GemmParams& P, int row, int& out_r
 template <int BN, int EPI, bool STATS, bool TEPI = false>
 __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI>::THREADS), 1) gemm_tc_kernel(const __grid_constant__ GemmParams P) {
     using Cfg = GemmCfg<BN, TEPI, EPI>;
-    static_assert(!TEPI || EPI == EPI_F32 || EPI == EPI_GEGLU, "TMA-store epilogues exist for fp32 and GEGLU output");
+    static_assert(EPI == EPI_F32 || EPI == EPI_GEGLU || EPI == EPI_BF16, "unknown epilogue");
     constexpr int STAGES = Cfg::STAGES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -227,6 +228,58 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI>::THREADS), 1) gemm_tc_
                 if (lane == 0) {
                     tma_store_2d(&P.tmOut, stgb, n0, row0);
                     bulk_commit_group();
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty[as]);
+            as ^= 1;
+            if (as == 0) aphase ^= 1;
+        }
+        if (lane == 0) bulk_wait0();
+    } else if constexpr (TEPI && EPI == EPI_BF16) {
+        // ===== bf16 output, thread = row: TMEM -> (+ bias) -> bf16 row segment in one of two 32 x 64-byte staging boxes -> TMA store
+        const int w = warp - 2, q = warp & 3, half = w >> 2;
+        uint8_t* stgb = base + Cfg::OFF_STG + (size_t)w * Cfg::WARP_STG;
+        constexpr int kChunks = BN / 32;
+        int as = 0;
+        uint32_t aphase = 0, nst = 0;
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+            const int mt = tile / P.num_n_tiles, nt = tile - mt * P.num_n_tiles;
+            const int row0 = mt * kBM + q * 32;
+            mbar_wait(&tfull[as], aphase);
+            tc_fence_after();
+            const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN);
+            if (row0 < P.M) {
+                for (int c = half; c < kChunks; c += 2) {
+                    const int n0 = nt * BN + c * 32;
+                    if (n0 >= P.N) break;
+                    uint32_t r[32];
+                    tmem_ld32(t_row + (uint32_t)(c * 32), r);
+                    if (lane == 0) bulk_wait_read1();          // the store issued two chunks ago has released this box
+                    __syncwarp();
+                    tmem_ld_wait();
+                    uint4* dst = reinterpret_cast<uint4*>(stgb + (nst & 1u) * 2048 + lane * 64);
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        float v[8];
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[8 * u + e]);
+                        if (P.bias) {
+                            const float4 b1 = __ldg(reinterpret_cast<const float4*>(P.bias + n0) + 2 * u);
+                            const float4 b2 = __ldg(reinterpret_cast<const float4*>(P.bias + n0) + 2 * u + 1);
+                            v[0] += b1.x; v[1] += b1.y; v[2] += b1.z; v[3] += b1.w;
+                            v[4] += b2.x; v[5] += b2.y; v[6] += b2.z; v[7] += b2.w;
+                        }
+                        dst[u] = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+                    }
+                    fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0) {
+                        tma_store_2d(&P.tmOut, stgb + (nst & 1u) * 2048, n0, row0);
+                        bulk_commit_group();
+                    }
+                    ++nst;
                 }
             }
             tc_fence_before();
@@ -747,7 +800,7 @@ static int set_attr_bn(int epi, int tepi) {
         int rc = set_attr<BN, EPI_F32, true>();
         return rc ? rc : set_attr<BN, EPI_F32>();
     }
-    if (epi == EPI_BF16) return set_attr<BN, EPI_BF16>();
+    if (epi == EPI_BF16) return tepi ? set_attr<BN, EPI_BF16, false, true>() : set_attr<BN, EPI_BF16>();
     if (tepi) {
         if constexpr (BN == 256) return set_attr<BN, EPI_GEGLU, false, true>();
     }
@@ -764,6 +817,7 @@ static void launch_bn(const GemmLaunch& l, cudaStream_t st) {
         }
     } else if (l.p.epi == EPI_F32 && stats) launch_pdl_tc(gemm_tc_kernel<BN, EPI_F32, true>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
     else if (l.p.epi == EPI_F32) launch_pdl_tc(gemm_tc_kernel<BN, EPI_F32, false>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
+    else if (l.p.epi == EPI_BF16 && l.p.tepi) launch_pdl_tc(gemm_tc_kernel<BN, EPI_BF16, false, true>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
     else if (l.p.epi == EPI_BF16) launch_pdl_tc(gemm_tc_kernel<BN, EPI_BF16, false>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
     else if (l.p.tepi) {
         if constexpr (BN == 256)
@@ -816,7 +870,14 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
              d.ntaps * p.kblocks <= tepi_maxk && (((uintptr_t)d.out | (uintptr_t)d.residual | (uintptr_t)d.bias) & 15) == 0;
     const bool gt = tepi_on && d.epi == EPI_GEGLU && L.BN == 256 && d.mode == GEMM_LINEAR && d.M % 32 == 0 && (d.N / 2) % 32 == 0 &&
                     d.ldo % 8 == 0 && (((uintptr_t)d.out | (uintptr_t)d.bias) & 15) == 0;
-    if (gt) {
+    const bool bt = tepi_on && d.epi == EPI_BF16 && d.mode == GEMM_LINEAR && d.M % 32 == 0 && d.N % 32 == 0 && d.ldo % 8 == 0 &&
+                    (((uintptr_t)d.out | (uintptr_t)d.bias) & 15) == 0;
+    if (bt) {
+        p.tepi = 1;
+        rc = make_tmap_bf16_chunk(&p.tmOut, d.out, d.M, d.N, d.ldo);
+        if (rc) return rc;
+        L.smem = L.BN == 256 ? GemmCfg<256, true, EPI_BF16>::SMEM : (L.BN == 160 ? GemmCfg<160, true, EPI_BF16>::SMEM : GemmCfg<128, true, EPI_BF16>::SMEM);
+    } else if (gt) {
         p.tepi = 1;
         rc = make_tmap_bf16_chunk(&p.tmOut, d.out, d.M, d.N / 2, d.ldo);
         if (rc) return rc;
