@@ -231,6 +231,23 @@ int gn_finalize(const StatSrc& s1, const StatSrc& s2, int nstat, int frames_per_
 // ---------------------------------------------------------------------------------------------------------------
 // GroupNorm apply (+SiLU) with layout scatter: one warp per destination row, lanes stride over the row's float4 channel
 // vectors with up to 4 loads in flight each; no block-level synchronisation.
+// Division of a non-negative int (< 2^31) by a launch constant: q = umulhi(n, mul) >> shr (round-up magic number), d == 1 passes through.
+struct FastDiv {
+    uint32_t mul = 0, shr = 0;
+    int d = 1;
+    FastDiv() = default;
+    explicit FastDiv(int div) : d(div > 0 ? div : 1) {
+        if (d > 1) {
+            uint32_t lg = 0;
+            while ((1ull << lg) < (uint64_t)d) ++lg;
+            const uint64_t p = 31 + lg;
+            mul = (uint32_t)(((1ull << p) + (uint64_t)d - 1) / (uint64_t)d);
+            shr = (uint32_t)(p - 32);
+        }
+    }
+    __device__ __forceinline__ int div(int n) const { return d == 1 ? n : (int)(__umulhi((uint32_t)n, mul) >> shr); }
+};
+
 struct ApplyP {
     const float* x1; int C1;
     const float* x2; int C2;
@@ -242,6 +259,9 @@ struct ApplyP {
     int T, HW;
     int dst_rows;        // rows of the destination layout
     __nv_bfloat16* dst; __nv_bfloat16* raw;
+    FastDiv d_stat;      // rows_per_stat
+    FastDiv d_outer;     // TIME_PAD: HW * (T + 2)      SPATIAL: (Hd + 2) * (Wd + 2)
+    FastDiv d_inner;     // TIME_PAD: HW                SPATIAL: Wd + 2
 };
 
 __device__ __forceinline__ float silu_f(float v) { return __fdividef(v, 1.0f + __expf(-v)); }
@@ -250,15 +270,14 @@ __device__ __forceinline__ float silu_f(float v) { return __fdividef(v, 1.0f + _
 __device__ __forceinline__ int apply_src_row(const ApplyP& P, int drow) {
     if (P.mode == DST_LINEAR) return drow;
     if (P.mode == DST_TIME_PAD) {
-        const int per = P.HW * (P.T + 2);
-        const int b = drow / per, r = drow - b * per;
-        const int tp = r / P.HW, hw = r - tp * P.HW;
+        const int b = P.d_outer.div(drow), r = drow - b * P.d_outer.d;
+        const int tp = P.d_inner.div(r), hw = r - tp * P.HW;
         return (tp < 1 || tp > P.T) ? -1 : (b * P.T + (tp - 1)) * P.HW + hw;
     }
     const int up = P.mode == DST_SPATIAL_PAD_UP2 ? 1 : 0;
-    const int Hd = P.H << up, Wd = P.W << up, Wp = Wd + 2, Hp = Hd + 2;
-    const int f = drow / (Wp * Hp), r = drow - f * (Wp * Hp);
-    const int hp = r / Wp, wp = r - hp * Wp;
+    const int Hd = P.H << up, Wd = P.W << up, Wp = Wd + 2;
+    const int f = P.d_outer.div(drow), r = drow - f * P.d_outer.d;
+    const int hp = P.d_inner.div(r), wp = r - hp * Wp;
     if (hp < 1 || hp > Hd || wp < 1 || wp > Wd) return -1;
     return (f * P.H + ((hp - 1) >> up)) * P.W + ((wp - 1) >> up);
 }
@@ -282,8 +301,8 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const __grid_constant__ A
         for (int v = lane; v < nvec; v += 32) drow_p[v] = make_uint2(0u, 0u);
         return;
     }
-    const float2* tab = (P.rows_per_stat > 0 && !P.ab) ? P.table + (size_t)(sr / P.rows_per_stat) * 32 : nullptr;
-    const float4* ab4 = P.ab ? reinterpret_cast<const float4*>(P.ab + (size_t)(sr / P.rows_per_stat) * C) : nullptr;
+    const float2* tab = (P.rows_per_stat > 0 && !P.ab) ? P.table + (size_t)P.d_stat.div(sr) * 32 : nullptr;
+    const float4* ab4 = P.ab ? reinterpret_cast<const float4*>(P.ab + (size_t)P.d_stat.div(sr) * C) : nullptr;
     const float4* s1 = reinterpret_cast<const float4*>(P.x1 + (size_t)sr * P.C1);
     const float4* s2 = P.x2 ? reinterpret_cast<const float4*>(P.x2 + (size_t)sr * P.C2) : nullptr;
     const int nv1 = P.C1 >> 2;
@@ -361,6 +380,12 @@ int gn_apply(const ApplyArgs& a, cudaStream_t st) {
     }
     MOCA_REQUIRE(dst_rows < (1ll << 31) && a.rows < (1ll << 31), MOCA_E_SHAPE, "gn_apply: too many rows");
     P.dst_rows = (int)dst_rows;
+    P.d_stat = FastDiv(a.rows_per_stat);
+    if (a.dst_mode == DST_TIME_PAD) { P.d_outer = FastDiv(a.HW * (a.T + 2)); P.d_inner = FastDiv(a.HW); }
+    else if (a.dst_mode != DST_LINEAR) {
+        const int up = a.dst_mode == DST_SPATIAL_PAD_UP2 ? 1 : 0;
+        P.d_outer = FastDiv(((a.H << up) + 2) * ((a.W << up) + 2)); P.d_inner = FastDiv((a.W << up) + 2);
+    }
     launch_pdl(gn_apply_kernel, dim3(cdiv(dst_rows, 8)), dim3(256), 0, st, P);
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
