@@ -20,7 +20,7 @@ struct GemmCfg {
     static constexpr int B_BYTES = BN * kBK * 2;
     static constexpr int STAGE_BYTES = kABytes + B_BYTES;                   // multiple of 1024 for BN in {128, 160, 256}
     static constexpr bool BT = TEPI && EPI == EPI_BF16;      // bf16 thread = row epilogue: classic ring, two 2 KB staging boxes per warp
-    static constexpr int STAGES = GT ? 4 : ((TEPI && !BT) ? 3 : ((BN == 256) ? 4 : (BN == 160 ? 5 : 6)));
+    static constexpr int STAGES = GT ? 4 : ((TEPI && !BT) ? (BN == 128 ? 4 : 3) : ((BN == 256) ? 4 : (BN == 160 ? 5 : 6)));
     static constexpr int TMEM_COLS = (2 * BN <= 256) ? 256 : 512;
     static constexpr int EPI_WARPS = GT ? 16 : 8;
     static constexpr int THREADS = 64 + 32 * EPI_WARPS;

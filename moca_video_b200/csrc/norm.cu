@@ -178,13 +178,13 @@ __device__ __forceinline__ void stat_accumulate(const StatSrc& S, int c0, int c1
     }
 }
 
-__global__ void __launch_bounds__(256) gn_finalize_kernel(const StatSrc S1, const StatSrc S2, int frames_per_stat, int T,
+__global__ void __launch_bounds__(1024) gn_finalize_kernel(const StatSrc S1, const StatSrc S2, int frames_per_stat, int T,
                                                           int rows_per_frame, float eps, float2* __restrict__ table,
                                                           const float* __restrict__ gamma, const float* __restrict__ beta,
                                                           float2* __restrict__ ab) {
     pdl_wait();
     pdl_launch_dependents();
-    __shared__ double red[2][8];
+    __shared__ double red[2][32];
     __shared__ float s_mr[2];
     const int g = blockIdx.x, stat = blockIdx.y;
     const int Cg = (S1.C + S2.C) >> 5;
@@ -198,7 +198,7 @@ __global__ void __launch_bounds__(256) gn_finalize_kernel(const StatSrc S1, cons
     __syncthreads();
     if (threadIdx.x == 0) {
         double ts = 0.0, tq = 0.0;
-        for (int w = 0; w < 8; ++w) { ts += red[0][w]; tq += red[1][w]; }
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) { ts += red[0][w]; tq += red[1][w]; }
         const double cnt = (double)frames_per_stat * Cg * rows_per_frame;
         const double m = ts / cnt;
         double var = tq / cnt - m * m;
@@ -223,7 +223,8 @@ int gn_finalize(const StatSrc& s1, const StatSrc& s2, int nstat, int frames_per_
     MOCA_REQUIRE((s1.cs || s1.part) && table && (s2.C == 0 || s2.cs || s2.part), MOCA_E_ARG, "gn_finalize: NULL argument");
     MOCA_REQUIRE((s1.C + s2.C) % 32 == 0 && nstat > 0 && frames_per_stat > 0 && rows_per_frame > 0 && T > 0, MOCA_E_SHAPE,
                  "gn_finalize: unsupported geometry C=%d nstat=%d", s1.C + s2.C, nstat);
-    launch_pdl(gn_finalize_kernel, dim3(32, nstat), dim3(256), 0, st, s1, s2, frames_per_stat, T, rows_per_frame, eps, table, gamma, beta, ab);
+    // statistics that span the frames of a sample have few (group, sample) blocks with long sums: 1024 threads each
+    launch_pdl(gn_finalize_kernel, dim3(32, nstat), dim3(frames_per_stat > 1 ? 1024 : 256), 0, st, s1, s2, frames_per_stat, T, rows_per_frame, eps, table, gamma, beta, ab);
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
 }
