@@ -864,7 +864,9 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
     // TMA-store epilogue: fp32 output whose 32-row slices map to 32 consecutive output rows, short K (the epilogue, not the
     // main loop, bounds these), slice-mode statistics only.  MOCA_GEMM_TEPI=0 pins the staged-and-coalesced epilogue.
     static const int tepi_on = [] { const char* e = getenv("MOCA_GEMM_TEPI"); return e ? atoi(e) : 1; }();
-    static const int tepi_maxk = [] { const char* e = getenv("MOCA_GEMM_TEPI_MAXK"); return e ? atoi(e) : 15; }();
+    static const int tepi_maxk160 = [] { const char* e = getenv("MOCA_GEMM_TEPI_MAXK"); return e ? atoi(e) : 15; }();       // 3-stage ring
+    static const int tepi_maxk128 = [] { const char* e = getenv("MOCA_GEMM_TEPI_MAXK128"); return e ? atoi(e) : 15; }();    // 4-stage ring
+    const int tepi_maxk = L.BN == 128 ? tepi_maxk128 : tepi_maxk160;
     const bool rows_ok = (d.mode == GEMM_LINEAR && d.M % 32 == 0) || (d.mode == GEMM_TIME_PAD && d.g_w % 32 == 0 && d.g_rows % 32 == 0);
     p.tepi = tepi_on && d.epi == EPI_F32 && L.BN != 256 && rows_ok && d.N % 32 == 0 && d.ldo % 4 == 0 && !d.rowbias && !d.chan_stats &&
              d.ntaps * p.kblocks <= tepi_maxk && (((uintptr_t)d.out | (uintptr_t)d.residual | (uintptr_t)d.bias) & 15) == 0;
