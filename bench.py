@@ -95,7 +95,8 @@ def run_reference(args, rank):
         return
     cb, t = cpu_reference_sample(args.steps, args.warmup)
     out = {"impl": "reference", "metric": "UNet denoise steps/s (16f 320x512)", "value": cb["value"], "unit": "steps/s",
-           "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True,
+           "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / cb["value"], "ms_per_sample": t * 1e3,
+           "higher_is_better": True,
            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
            "config": {"workload": "configs[1]: VideoCrafter2 UNet DDIM step, 16x320x512 (latent [1,4,16,40,64]), CFG, random-init; "
                                   "bounded CPU sample scaled to a full step"},
