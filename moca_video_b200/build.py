@@ -19,6 +19,8 @@ ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default"]
 # per-file extra flags: the sampler kernels must not contract mul+add (bit parity with torch eager, see step_kernels.cu)
 EXTRA = {"step_kernels.cu": ["-fmad=false"]}
+if os.environ.get("MOCA_DEBUG_HANG") == "1":
+    COMMON = COMMON + ["-DMOCA_DEBUG_HANG"]
 SOURCES = ["abi.cu", "step_kernels.cu", "freeinit.cu", "gemm_tc.cu", "norm.cu", "attn.cu", "attn_tc.cu", "unet.cu", "unet_plan.cu", "ops_abi.cu"]
 
 

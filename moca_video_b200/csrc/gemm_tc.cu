@@ -14,13 +14,13 @@ constexpr int kABytes = kBM * kBK * 2;        // 16 KB, 128 rows of 128 B
 // TEPI: TMA-store epilogue variants.  fp32: 3 stages, per epilogue warp 4 KB output staging + two 4 KB residual buffers.
 // GEGLU: 16 epilogue warps (one 32-column output chunk each, the GELU arithmetic needs the extra warps to hide its
 // latencies), 2 KB bf16 staging per warp.
-template <int BN, bool TEPI = false, int EPI = EPI_F32>
+template <int BN, bool TEPI = false, int EPI = EPI_F32, int NCTA = 1>
 struct GemmCfg {
     static constexpr bool GT = TEPI && EPI == EPI_GEGLU;
-    static constexpr int B_BYTES = BN * kBK * 2;
+    static constexpr int B_BYTES = (BN / NCTA) * kBK * 2;                   // CTA pair: each CTA holds half of the B rows
     static constexpr int STAGE_BYTES = kABytes + B_BYTES;                   // multiple of 1024 for BN in {128, 160, 256}
     static constexpr bool BT = TEPI && EPI == EPI_BF16;      // bf16 thread = row epilogue: classic ring, two 2 KB staging boxes per warp
-    static constexpr int STAGES = GT ? 4 : ((TEPI && !BT) ? (BN == 128 ? 4 : 3) : ((BN == 256) ? 4 : (BN == 160 ? 5 : 6)));
+    static constexpr int STAGES = NCTA == 2 ? 6 : (GT ? 4 : ((TEPI && !BT) ? (BN == 128 ? 4 : 3) : ((BN == 256) ? 4 : (BN == 160 ? 5 : 6))));
     static constexpr int TMEM_COLS = (2 * BN <= 256) ? 256 : 512;
     static constexpr int EPI_WARPS = GT ? 16 : 8;
     static constexpr int THREADS = 64 + 32 * EPI_WARPS;
@@ -81,10 +81,11 @@ __device__ __forceinline__ bool map_row(const GemmParams& P, int row, int& out_r
     return true;
 }
 
-template <int BN, int EPI, bool STATS, bool TEPI = false>
-__global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI>::THREADS), 1) gemm_tc_kernel(const __grid_constant__ GemmParams P) {
-    using Cfg = GemmCfg<BN, TEPI, EPI>;
+template <int BN, int EPI, bool STATS, bool TEPI = false, int NCTA = 1>
+__global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA>::THREADS), 1) gemm_tc_kernel(const __grid_constant__ GemmParams P) {
+    using Cfg = GemmCfg<BN, TEPI, EPI, NCTA>;
     static_assert(EPI == EPI_F32 || EPI == EPI_GEGLU || EPI == EPI_BF16, "unknown epilogue");
+    static_assert(NCTA == 1 || (NCTA == 2 && !TEPI && EPI == EPI_F32), "the CTA-pair shape exists for the staged fp32 epilogue");
     constexpr int STAGES = Cfg::STAGES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -97,7 +98,14 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI>::THREADS), 1) gemm_tc_
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    const int ntiles = P.num_m_tiles * P.num_n_tiles;
+    // Tile sequence of this CTA.  NCTA == 2 (launched as clusters of 2): a tile index names a PAIR tile of 256 rows, pair
+    // pm = tile / num_n_tiles; this CTA computes m-tile 2 pm + rank of it (rank 1 may fall off the end of an odd M: its rows are
+    // >= M, TMA zero-fills them and the epilogue stores nothing, but it still takes part in every barrier).
+    const int cta_rank = NCTA == 2 ? (int)cluster_ctarank() : 0;
+    const int tile0 = NCTA == 2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+    const int tstep = NCTA == 2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+    const int ntiles = NCTA == 2 ? ((P.num_m_tiles + 1) >> 1) * P.num_n_tiles : P.num_m_tiles * P.num_n_tiles;
+    auto MT = [&](int tile) { return NCTA == 2 ? 2 * (tile / P.num_n_tiles) + cta_rank : tile / P.num_n_tiles; };
     const int kiters = P.ntaps * P.kblocks;
 
     if (threadIdx.x == 0) {
@@ -109,7 +117,7 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI>::THREADS), 1) gemm_tc_
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&tfull[i], 1);
-            mbar_init(&tempty[i], Cfg::EPI_WARPS);
+            mbar_init(&tempty[i], Cfg::EPI_WARPS * NCTA);       // pair: the leader's barrier collects the epilogue warps of both CTAs
         }
         if constexpr (TEPI) {
             prefetch_tmap(&P.tmOut);
@@ -119,11 +127,12 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI>::THREADS), 1) gemm_tc_
         fence_mbar_init();
     }
     if (warp == 1) {
-        tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
-        tmem_relinquish();
+        if constexpr (NCTA == 2) { tmem_alloc2(tmem_slot, Cfg::TMEM_COLS); tmem_relinquish2(); }
+        else { tmem_alloc(tmem_slot, Cfg::TMEM_COLS); tmem_relinquish(); }
     }
     tc_fence_before();
-    __syncthreads();
+    if constexpr (NCTA == 2) cluster_sync_all();             // the peer's barriers exist before anything arrives on them
+    else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     // everything above overlaps the tail of the previous kernel (PDL, common.cuh); global memory is touched only below
@@ -135,30 +144,37 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI>::THREADS), 1) gemm_tc_
             // ===== TMA producer =====
             int stage = 0;
             uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-                const int mt = tile / P.num_n_tiles, nt = tile - mt * P.num_n_tiles;
+            for (int tile = tile0; tile < ntiles; tile += tstep) {
+                const int mt = MT(tile), nt = tile % P.num_n_tiles;
                 for (int tap = 0; tap < P.ntaps; ++tap) {
                     const int arow = mt * kBM + P.tap_shift[tap];
                     for (int kb = 0; kb < P.kblocks; ++kb) {
                         mbar_wait(&empty[stage], phase ^ 1);
                         uint8_t* sa = base + (size_t)stage * Cfg::STAGE_BYTES;
-                        mbar_expect_tx(&full[stage], Cfg::STAGE_BYTES);
-                        tma_load_2d(sa, &P.tmA, &full[stage], kb * kBK, arow);
-                        tma_load_2d(sa + kABytes, &P.tmB, &full[stage], tap * P.Kp + kb * kBK, nt * BN);
+                        if constexpr (NCTA == 2) {
+                            // both CTAs load their A rows and their half of the B rows; all bytes are counted on the leader's barrier
+                            if (cta_rank == 0) mbar_expect_tx(&full[stage], 2 * Cfg::STAGE_BYTES);
+                            tma_load_2d_pair(sa, &P.tmA, &full[stage], kb * kBK, arow);
+                            tma_load_2d_pair(sa + kABytes, &P.tmB, &full[stage], tap * P.Kp + kb * kBK, nt * BN + cta_rank * (BN / 2));
+                        } else {
+                            mbar_expect_tx(&full[stage], Cfg::STAGE_BYTES);
+                            tma_load_2d(sa, &P.tmA, &full[stage], kb * kBK, arow);
+                            tma_load_2d(sa + kABytes, &P.tmB, &full[stage], tap * P.Kp + kb * kBK, nt * BN);
+                        }
                         if (++stage == STAGES) { stage = 0; phase ^= 1; }
                     }
                 }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // ===== MMA issuer =====
-            constexpr uint32_t idesc = umma_idesc_bf16(kBM, BN);
+        if (lane == 0 && cta_rank == 0) {
+            // ===== MMA issuer (pair: the leader CTA issues 256 x BN x 16 MMAs that read A / B halves from both CTAs' smem) =====
+            constexpr uint32_t idesc = umma_idesc_bf16(kBM * NCTA, BN);
             int stage = 0;
             uint32_t phase = 0;
             int as = 0;
             uint32_t aphase = 0;
-            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+            for (int tile = tile0; tile < ntiles; tile += tstep) {
                 mbar_wait(&tempty[as], aphase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + (uint32_t)(as * BN);
@@ -171,12 +187,15 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI>::THREADS), 1) gemm_tc_
 #pragma unroll
                     for (int k = 0; k < kBK / 16; ++k) {
                         // advance 16 bf16 = 32 bytes inside the 128-byte swizzle atom: +2 in the (addr >> 4) field
-                        umma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((it | k) != 0));
+                        if constexpr (NCTA == 2) umma_bf16_pair(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((it | k) != 0));
+                        else umma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((it | k) != 0));
                     }
-                    umma_commit(&empty[stage]);
+                    if constexpr (NCTA == 2) umma_commit_pair(&empty[stage], 3);
+                    else umma_commit(&empty[stage]);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
-                umma_commit(&tfull[as]);
+                if constexpr (NCTA == 2) umma_commit_pair(&tfull[as], 3);
+                else umma_commit(&tfull[as]);
                 as ^= 1;
                 if (as == 0) aphase ^= 1;
             }
@@ -190,8 +209,8 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI>::THREADS), 1) gemm_tc_
         const int ncols_total = P.N >> 1;
         int as = 0;
         uint32_t aphase = 0;
-        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-            const int mt = tile / P.num_n_tiles, nt = tile - mt * P.num_n_tiles;
+        for (int tile = tile0; tile < ntiles; tile += tstep) {
+            const int mt = MT(tile), nt = tile % P.num_n_tiles;
             const int row0 = mt * kBM + q * 32;
             const int n0 = nt * (BN / 2) + c * 32;
             mbar_wait(&tfull[as], aphase);
@@ -244,8 +263,8 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI>::THREADS), 1) gemm_tc_
         constexpr int kChunks = BN / 32;
         int as = 0;
         uint32_t aphase = 0, nst = 0;
-        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-            const int mt = tile / P.num_n_tiles, nt = tile - mt * P.num_n_tiles;
+        for (int tile = tile0; tile < ntiles; tile += tstep) {
+            const int mt = MT(tile), nt = tile % P.num_n_tiles;
             const int row0 = mt * kBM + q * 32;
             mbar_wait(&tfull[as], aphase);
             tc_fence_after();
@@ -303,7 +322,7 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI>::THREADS), 1) gemm_tc_
         const bool has_res = P.residual != nullptr;
         // slice of 32 input-space rows -> first output row (or -1: padding frame / beyond M)
         auto slice_row = [&](int tile) -> int {
-            const int row0 = (tile / P.num_n_tiles) * kBM + q * 32;
+            const int row0 = MT(tile) * kBM + q * 32;
             if (row0 >= P.M) return -1;
             if (P.mode == GEMM_LINEAR) return row0;
             const int f = row0 / P.g_rows, r = row0 - f * P.g_rows;
@@ -312,11 +331,11 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI>::THREADS), 1) gemm_tc_
         };
         // chunk cursor: (tile, c) with c = half, half + 2, ..; normalised so that the chunk exists
         auto norm = [&](int& t, int& c) {
-            while (t < ntiles && !(c < kChunks && (t % P.num_n_tiles) * BN + c * 32 < P.N)) { t += gridDim.x; c = half; }
+            while (t < ntiles && !(c < kChunks && (t % P.num_n_tiles) * BN + c * 32 < P.N)) { t += tstep; c = half; }
         };
         auto next = [&](int& t, int& c) { c += 2; norm(t, c); };
         // producer cursor runs two loaded chunks ahead
-        int pt = blockIdx.x, pc = half;
+        int pt = tile0, pc = half;
         uint32_t n_issued = 0, n_waited = 0;
         norm(pt, pc);
         auto issue_res = [&]() {                               // lane 0 only
@@ -335,7 +354,7 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI>::THREADS), 1) gemm_tc_
         if (has_res && lane == 0) { issue_res(); issue_res(); }
         int as = 0;
         uint32_t aphase = 0;
-        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        for (int tile = tile0; tile < ntiles; tile += tstep) {
             const int orow0 = slice_row(tile);
             const int col_tile0 = (tile % P.num_n_tiles) * BN;
             mbar_wait(&tfull[as], aphase);
@@ -389,7 +408,7 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI>::THREADS), 1) gemm_tc_
                             ps[rr & 3] += x;
                             pq[rr & 3] = fmaf(x, x, pq[rr & 3]);
                         }
-                        P.spart[(size_t)((tile / P.num_n_tiles) * (kBM / 32) + q) * P.N + n0 + lane] =
+                        P.spart[(size_t)(MT(tile) * (kBM / 32) + q) * P.N + n0 + lane] =
                             make_float2((ps[0] + ps[1]) + (ps[2] + ps[3]), (pq[0] + pq[1]) + (pq[2] + pq[3]));
                     }
                 }
@@ -418,7 +437,7 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI>::THREADS), 1) gemm_tc_
 
         // frame_u: the frame all valid rows of this warp's 32-row slice belong to, or -1 when they straddle frames
         auto tile_rows = [&](int tile, int& out_row, uint32_t& vmask, int& frame_u) {
-            const int mt = tile / P.num_n_tiles;
+            const int mt = MT(tile);
             const int row = mt * kBM + q * 32 + lane;
             out_row = 0;
             const bool valid = map_row(P, row, out_row);
@@ -455,7 +474,7 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI>::THREADS), 1) gemm_tc_
             }
         };
 
-        int tile = blockIdx.x;
+        int tile = tile0;
         int out_row = 0, nxt_row = 0;
         int frame_u = -1, nxt_frame = -1;
         uint32_t vmask = 0, nxt_mask = 0;
@@ -468,10 +487,10 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI>::THREADS), 1) gemm_tc_
                 have_pre = true;
             }
         }
-        for (; tile < ntiles; tile += gridDim.x) {
+        for (; tile < ntiles; tile += tstep) {
             const int nt = tile % P.num_n_tiles;
             const int col_tile0 = col0_of(tile);
-            const int ntile = tile + gridDim.x;
+            const int ntile = tile + tstep;
             bool nxt_ready = false;
             mbar_wait(&tfull[as], aphase);
             tc_fence_after();
@@ -554,7 +573,7 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI>::THREADS), 1) gemm_tc_
                                 // partial-sum mode: one {sum, sumsq} per (32-row slice, column), plain coalesced stores;
                                 // gn_finalize adds the slices of a frame in a fixed order
                                 if (nvalid >= 4)
-                                    P.spart[(size_t)((tile / P.num_n_tiles) * (kBM / 32) + q) * P.N + col + e] = make_float2(s1, s2);
+                                    P.spart[(size_t)(MT(tile) * (kBM / 32) + q) * P.N + col + e] = make_float2(s1, s2);
                             } else if (nvalid >= 4) {
                                 double* d = P.cstat + ((size_t)frame_u * P.N + col + e) * 2;
                                 atomicAdd(d, (double)s1);
@@ -666,7 +685,10 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI>::THREADS), 1) gemm_tc_
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tempty[as]);
+            if (lane == 0) {
+                if constexpr (NCTA == 2) mbar_arrive_cluster(&tempty[as], 0);       // the leader's MMA thread owns the accumulator ring
+                else mbar_arrive(&tempty[as]);
+            }
             as ^= 1;
             if (as == 0) aphase ^= 1;
             if (EPI == EPI_F32) {
@@ -678,11 +700,13 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI>::THREADS), 1) gemm_tc_
         }
     }
     tc_fence_before();
-    __syncthreads();
+    if constexpr (NCTA == 2) cluster_sync_all();             // no CTA of the pair exits while its peer can still reach its smem / TMEM
+    else __syncthreads();
     if (warp == 1) {
         __syncwarp();
         tc_fence_after();
-        tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+        if constexpr (NCTA == 2) tmem_dealloc2(tmem_base, Cfg::TMEM_COLS);
+        else tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
     }
 }
 
@@ -791,6 +815,33 @@ static int set_attr() {
     return MOCA_OK;
 }
 
+template <int BN, bool STATS>
+static int set_attr_pair() {
+    static bool done = false;
+    if (!done) {
+        MOCA_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI_F32, STATS, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)GemmCfg<BN, false, EPI_F32, 2>::SMEM));
+        MOCA_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI_F32, STATS, false, 2>, cudaFuncAttributeNonPortableClusterSizeAllowed, 0));
+        done = true;
+    }
+    return MOCA_OK;
+}
+
+// clusters of 2 CTAs (the pair is co-scheduled on one TPC)
+template <typename K>
+static cudaError_t launch_pair(K kernel, int grid, int threads, size_t smem, cudaStream_t st, const GemmParams& p) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(threads); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_level() >= 1 ? 2 : 1;
+    return cudaLaunchKernelEx(&cfg, kernel, p);
+}
+
 template <int BN>
 static int set_attr_bn(int epi, int tepi) {
     if (epi == EPI_F32) {
@@ -810,7 +861,12 @@ static int set_attr_bn(int epi, int tepi) {
 template <int BN>
 static void launch_bn(const GemmLaunch& l, cudaStream_t st) {
     const bool stats = l.p.cstat || l.p.spart;
-    if (l.p.epi == EPI_F32 && l.p.tepi) {
+    if (l.p.ncta == 2) {
+        if constexpr (BN != 128) {
+            if (stats) launch_pair(gemm_tc_kernel<BN, EPI_F32, true, false, 2>, l.grid, kGemmThreads, l.smem, st, l.p);
+            else launch_pair(gemm_tc_kernel<BN, EPI_F32, false, false, 2>, l.grid, kGemmThreads, l.smem, st, l.p);
+        }
+    } else if (l.p.epi == EPI_F32 && l.p.tepi) {
         if constexpr (BN != 256) {
             if (stats) launch_pdl_tc(gemm_tc_kernel<BN, EPI_F32, true, true>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
             else launch_pdl_tc(gemm_tc_kernel<BN, EPI_F32, false, true>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
@@ -838,8 +894,13 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
     L.BN = pick_bn(d, ctx.num_sms);
     int rc = make_tmap_bf16(&L.p.tmA, d.A, d.a_rows, d.a_cols, d.a_pitch, kBM);
     if (rc) return rc;
-    rc = make_tmap_bf16(&L.p.tmB, d.Wt, d.N, (int64_t)d.ntaps * d.Kp, (int64_t)d.ntaps * d.Kp, L.BN);
+    // CTA-pair shape (MOCA_GEMM_2CTA=1): staged fp32 epilogue, 160- / 256-wide tiles, long main loops
+    static const int pair_on = [] { const char* e = getenv("MOCA_GEMM_2CTA"); return e ? atoi(e) : 0; }();
+    static const int pair_mink = [] { const char* e = getenv("MOCA_GEMM_2CTA_MINK"); return e ? atoi(e) : 16; }();
+    const int ncta = (pair_on && d.epi == EPI_F32 && L.BN != 128 && d.ntaps * (d.Kp / 64) >= pair_mink && ctx.num_sms >= 2) ? 2 : 1;
+    rc = make_tmap_bf16(&L.p.tmB, d.Wt, d.N, (int64_t)d.ntaps * d.Kp, (int64_t)d.ntaps * d.Kp, L.BN / ncta);
     if (rc) return rc;
+    L.p.ncta = ncta;
     GemmParams& p = L.p;
     p.M = d.M; p.N = d.N; p.ntaps = d.ntaps; p.Kp = d.Kp; p.kblocks = d.Kp / 64;
     for (int i = 0; i < 9; ++i) p.tap_shift[i] = d.tap_shift[i];
@@ -861,6 +922,10 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
     p.num_n_tiles = cdiv(d.N, L.BN);
     const int ntiles = p.num_m_tiles * p.num_n_tiles;
     L.grid = ntiles < ctx.num_sms ? ntiles : ctx.num_sms;
+    if (ncta == 2) {
+        const int npair = ((p.num_m_tiles + 1) / 2) * p.num_n_tiles, maxpair = ctx.num_sms / 2;
+        L.grid = 2 * (npair < maxpair ? npair : maxpair);
+    }
     // TMA-store epilogue: fp32 output whose 32-row slices map to 32 consecutive output rows, short K (the epilogue, not the
     // main loop, bounds these), slice-mode statistics only.  MOCA_GEMM_TEPI=0 pins the staged-and-coalesced epilogue.
     static const int tepi_on = [] { const char* e = getenv("MOCA_GEMM_TEPI"); return e ? atoi(e) : 1; }();
@@ -868,7 +933,7 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
     static const int tepi_maxk128 = [] { const char* e = getenv("MOCA_GEMM_TEPI_MAXK128"); return e ? atoi(e) : 15; }();    // 4-stage ring
     const int tepi_maxk = L.BN == 128 ? tepi_maxk128 : tepi_maxk160;
     const bool rows_ok = (d.mode == GEMM_LINEAR && d.M % 32 == 0) || (d.mode == GEMM_TIME_PAD && d.g_w % 32 == 0 && d.g_rows % 32 == 0);
-    p.tepi = tepi_on && d.epi == EPI_F32 && L.BN != 256 && rows_ok && d.N % 32 == 0 && d.ldo % 4 == 0 && !d.rowbias && !d.chan_stats &&
+    p.tepi = tepi_on && ncta == 1 && d.epi == EPI_F32 && L.BN != 256 && rows_ok && d.N % 32 == 0 && d.ldo % 4 == 0 && !d.rowbias && !d.chan_stats &&
              d.ntaps * p.kblocks <= tepi_maxk && (((uintptr_t)d.out | (uintptr_t)d.residual | (uintptr_t)d.bias) & 15) == 0;
     const bool gt = tepi_on && d.epi == EPI_GEGLU && L.BN == 256 && d.mode == GEMM_LINEAR && d.M % 32 == 0 && (d.N / 2) % 32 == 0 &&
                     d.ldo % 8 == 0 && (((uintptr_t)d.out | (uintptr_t)d.bias) & 15) == 0;
@@ -895,6 +960,12 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
         L.smem = L.BN == 256 ? GemmCfg<256>::SMEM : (L.BN == 160 ? GemmCfg<160>::SMEM : GemmCfg<128>::SMEM);
     }
     L.flops = 2.0 * (double)d.M * d.N * d.ntaps * d.a_cols;
+    if (ncta == 2) {
+        L.smem = L.BN == 256 ? GemmCfg<256, false, EPI_F32, 2>::SMEM : GemmCfg<160, false, EPI_F32, 2>::SMEM;
+        rc = L.BN == 256 ? set_attr_pair<256, true>() : set_attr_pair<160, true>();
+        if (!rc) rc = L.BN == 256 ? set_attr_pair<256, false>() : set_attr_pair<160, false>();
+        if (rc) return rc;
+    }
     rc = L.BN == 256 ? set_attr_bn<256>(d.epi, p.tepi) : (L.BN == 160 ? set_attr_bn<160>(d.epi, p.tepi) : set_attr_bn<128>(d.epi, p.tepi));
     if (rc) return rc;
     *out = L;

@@ -28,6 +28,7 @@ struct GemmParams {
     CUtensorMap tmA, tmB;
     CUtensorMap tmOut, tmRes;  // TMA-store epilogue only: fp32 [out_rows, N] output / residual, 32 x 32 boxes
     int tepi;                 // 1: TMA-store epilogue (gemm_tc.cu)
+    int ncta;                 // 2: CTA-pair shape (cluster of 2, tcgen05 cta_group::2, 256-row tiles)
     int M, N;                 // rows computed (input-row space), accumulator columns
     int ntaps, kblocks, Kp;   // kblocks = Kp / 64 per tap
     int tap_shift[9];

@@ -142,3 +142,29 @@ def test_attention_temporal(B, T, HW, heads):
     perm = lambda t: t.float().reshape(B, T, HW, C).permute(0, 2, 1, 3).reshape(B * HW * T, C)
     r = _ref_attn(perm(q), perm(k), perm(v), B * HW, heads, T, T, T).reshape(B, HW, T, C).permute(0, 2, 1, 3).reshape(B * T * HW, C)
     assert rel(y, r) < 5e-3
+
+
+@pytest.mark.parametrize("M,N,K", [(77, 320, 1024), (256, 256, 1024), (20480, 320, 1024), (40960, 512, 1024), (2560, 3840, 1280), (3000, 640, 1920)])
+def test_gemm_cta_pair(M, N, K):
+    """The CTA-pair shape of the GEMM (cluster of 2, tcgen05 cta_group::2), pinned by MOCA_GEMM_2CTA=1 in a subprocess: odd and
+    even numbers of 128-row tiles, one and several tiles per pair, 160- and 256-wide tiles."""
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    script = f"""
+import sys, torch
+sys.path.insert(0, {root!r})
+from moca_video_b200 import ops
+torch.backends.cuda.matmul.allow_tf32 = False
+g = torch.Generator(device="cuda").manual_seed(1)
+a = torch.randn({M}, {K}, device="cuda", generator=g).bfloat16()
+w = (torch.randn({N}, {K}, device="cuda", generator=g) / {K} ** 0.5).bfloat16()
+b = torch.randn({N}, device="cuda", generator=g)
+y = ops.gemm_bf16(a, w, b, False)
+ref = a.float() @ w.float().t() + b
+print("REL", float((y - ref).norm() / ref.norm()))
+"""
+    env = dict(os.environ); env["MOCA_GEMM_2CTA"] = "1"
+    out = subprocess.run([sys.executable, "-c", script], env=env, capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stderr[-2000:]
+    r = float([l for l in out.stdout.splitlines() if l.startswith("REL")][0].split()[1])
+    assert r < 2e-5

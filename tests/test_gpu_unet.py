@@ -243,3 +243,11 @@ def test_programmatic_dependent_launch_same_result(tmp_path):
     y0 = _variant_output({"MOCA_PDL": "0"}, tmp_path, "pdl0")
     y2 = _variant_output({"MOCA_PDL": "2"}, tmp_path, "pdl2")
     assert rel(y0, y2) < 1e-4
+
+
+def test_cta_pair_gemm_same_result(tmp_path):
+    """MOCA_GEMM_2CTA=1: long-K fp32 GEMMs / convs as clusters of two CTAs (tcgen05 cta_group::2, 256-row tiles, B split
+    between the two CTAs).  Same accumulation order per output element, same epilogue."""
+    y0 = _variant_output({"MOCA_GEMM_2CTA": "0"}, tmp_path, "pair0")
+    y1 = _variant_output({"MOCA_GEMM_2CTA": "1", "MOCA_GEMM_2CTA_MINK": "1"}, tmp_path, "pair1")
+    assert rel(y1, y0) < 1e-4
