@@ -462,132 +462,7 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict_
     }
 }
 
-// Streaming variant for long inputs (C <= 640): persistent CTAs, one producer thread keeps a 3-stage ring of R-row blocks in
-// flight with 1-D bulk copies (cp.async.bulk, ~20 KB each, completion on an mbarrier), 8 consumer warps normalise the rows
-// out of shared memory into a bf16 staging block that leaves through a bulk store (two staging blocks).  The loads no longer
-// live in registers, so a CTA sustains 60 KB of reads in flight independent of where its warps are in their arithmetic.
-constexpr int kLnStages = 3;
-template <int SLOTS, int R>
-__global__ void __launch_bounds__(288, 2) layernorm_stream_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
-                                                               const float* __restrict__ beta, int64_t rows, int C,
-                                                               __nv_bfloat16* __restrict__ out) {
-    using namespace ptx;
-    extern __shared__ uint8_t ln_smem_raw[];
-    uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(ln_smem_raw) + 127) & ~(uintptr_t)127);
-    const int in_bytes = R * C * 4, out_bytes = R * C * 2;
-    uint8_t* s_in = base;
-    uint8_t* s_out = base + kLnStages * in_bytes;
-    uint64_t* full = reinterpret_cast<uint64_t*>(s_out + 2 * out_bytes);
-    uint64_t* empty = full + kLnStages;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (threadIdx.x == 0) {
-        for (int i = 0; i < kLnStages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 8); }
-        fence_mbar_init();
-    }
-    __syncthreads();
-    pdl_wait();
-    pdl_launch_dependents();
-    const int64_t nblocks = (rows + R - 1) / R;
-    if (warp == 8) {
-        if (lane == 0) {
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int64_t blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
-                const int nr = (int)min((int64_t)R, rows - blk * R);
-                mbar_wait(&empty[stage], phase ^ 1);
-                mbar_expect_tx(&full[stage], (uint32_t)(nr * C * 4));
-                bulk_load_1d(s_in + stage * in_bytes, x + blk * R * C, (uint32_t)(nr * C * 4), &full[stage]);
-                if (++stage == kLnStages) { stage = 0; phase ^= 1; }
-            }
-        }
-        return;
-    }
-    const int nvec = C >> 2;
-    float4 g[SLOTS], b[SLOTS];
-#pragma unroll
-    for (int u = 0; u < SLOTS; ++u) {
-        const int i = lane + 32 * u;
-        if (i < nvec) { g[u] = __ldg(reinterpret_cast<const float4*>(gamma) + i); b[u] = __ldg(reinterpret_cast<const float4*>(beta) + i); }
-    }
-    const float inv_c = 1.0f / (float)C;
-    int stage = 0;
-    uint32_t phase = 0, ob = 0;
-    for (int64_t blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
-        const int nr = (int)min((int64_t)R, rows - blk * R);
-        // the staging block about to be written was handed to a bulk store two blocks ago
-        if (threadIdx.x == 0) bulk_wait_read1();
-        asm volatile("bar.sync 1, 256;" ::: "memory");
-        mbar_wait(&full[stage], phase);
-        uint8_t* so = s_out + ob * out_bytes;
-        for (int r = warp; r < nr; r += 8) {
-            const float4* xr = reinterpret_cast<const float4*>(s_in + stage * in_bytes + (size_t)r * C * 4);
-            float4 v[SLOTS];
-            float s = 0.f;
-#pragma unroll
-            for (int u = 0; u < SLOTS; ++u) {
-                const int i = lane + 32 * u;
-                v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (i < nvec) v[u] = xr[i];
-                s += (v[u].x + v[u].y) + (v[u].z + v[u].w);
-            }
-            for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-            const float mean = s * inv_c;
-            float q = 0.f;
-#pragma unroll
-            for (int u = 0; u < SLOTS; ++u) {
-                if (lane + 32 * u < nvec) {
-                    const float a = v[u].x - mean, bb = v[u].y - mean, c = v[u].z - mean, d = v[u].w - mean;
-                    q += (a * a + bb * bb) + (c * c + d * d);
-                }
-            }
-            for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
-            const float rstd = rsqrtf(q * inv_c + 1e-5f);
-            uint2* orow = reinterpret_cast<uint2*>(so + (size_t)r * C * 2);
-#pragma unroll
-            for (int u = 0; u < SLOTS; ++u) {
-                const int i = lane + 32 * u;
-                if (i < nvec) {
-                    __nv_bfloat162 lo = __floats2bfloat162_rn((v[u].x - mean) * rstd * g[u].x + b[u].x, (v[u].y - mean) * rstd * g[u].y + b[u].y);
-                    __nv_bfloat162 hi = __floats2bfloat162_rn((v[u].z - mean) * rstd * g[u].z + b[u].z, (v[u].w - mean) * rstd * g[u].w + b[u].w);
-                    orow[i] = make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
-                }
-            }
-        }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&empty[stage]);            // this warp has read its rows of the input block
-        fence_proxy_async_smem();
-        asm volatile("bar.sync 1, 256;" ::: "memory");
-        if (threadIdx.x == 0) {
-            bulk_store_1d(out + blk * R * C, so, (uint32_t)(nr * C * 2));
-            bulk_commit_group();
-        }
-        ob ^= 1u;
-        if (++stage == kLnStages) { stage = 0; phase ^= 1; }
-    }
-    if (threadIdx.x == 0) bulk_wait0();
-}
-
-template <int SLOTS, int R>
-static int layernorm_stream_launch(const float* x, const float* gamma, const float* beta, int64_t rows, int C, __nv_bfloat16* out, cudaStream_t st) {
-    const size_t smem = (size_t)kLnStages * R * C * 4 + 2 * (size_t)R * C * 2 + 64 + 128;
-    static bool done = false;
-    if (!done) {
-        MOCA_CHECK_CUDA(cudaFuncSetAttribute(layernorm_stream_kernel<SLOTS, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-        done = true;
-    }
-    const int64_t nblocks = (rows + R - 1) / R;
-    const int grid = (int)(nblocks < 296 ? nblocks : 296);          // two CTAs per SM
-    launch_pdl(layernorm_stream_kernel<SLOTS, R>, dim3(grid), dim3(288), smem, st, x, gamma, beta, rows, C, out);
-    MOCA_LAUNCH_CHECK();
-    return MOCA_OK;
-}
-
 int layernorm_bf16(const float* x, const float* gamma, const float* beta, int64_t rows, int C, __nv_bfloat16* out, cudaStream_t st) {
-    static const int stream_on = [] { const char* e = getenv("MOCA_LN_STREAM"); return e ? atoi(e) : 1; }();
-    if (stream_on && C % 4 == 0 && C <= 640 && rows >= 4096 && (((uintptr_t)x | (uintptr_t)out) & 15) == 0) {
-        if (C <= 384) return layernorm_stream_launch<3, 16>(x, gamma, beta, rows, C, out, st);
-        return layernorm_stream_launch<5, 8>(x, gamma, beta, rows, C, out, st);
-    }
     MOCA_REQUIRE(C % 4 == 0 && C <= 1280, MOCA_E_SHAPE, "layernorm: C=%d unsupported (multiple of 4, <= 1280)", C);
     if (C <= 384) launch_pdl(layernorm_kernel<3, 4>, dim3(cdiv(rows, 32)), dim3(256), 0, st, x, gamma, beta, rows, C, out);
     else if (C <= 640) launch_pdl(layernorm_kernel<5, 2>, dim3(cdiv(rows, 16)), dim3(256), 0, st, x, gamma, beta, rows, C, out);
