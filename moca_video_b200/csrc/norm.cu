@@ -267,7 +267,15 @@ struct ApplyP {
     FastDiv d_inner;     // TIME_PAD: HW                SPATIAL: Wd + 2
 };
 
-__device__ __forceinline__ float silu_f(float v) { return __fdividef(v, 1.0f + __expf(-v)); }
+// SiLU with one MUFU op: x * sigmoid(x) = h + h * tanh(h), h = x / 2 (tanh.approx.f32: max relative error 2^-11, i.e. below the
+// bf16 rounding of the stored result); the exp + reciprocal form needs two MUFU ops per element, which at 16 per clock and SM
+// costs as much as the HBM traffic of the 320-channel GroupNorms.
+__device__ __forceinline__ float silu_f(float v) {
+    const float h = 0.5f * v;
+    float th;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(th) : "f"(h));
+    return fmaf(h, th, h);
+}
 
 // destination row -> source row (or -1 for a zero border / padding row)
 __device__ __forceinline__ int apply_src_row(const ApplyP& P, int drow) {
@@ -355,6 +363,74 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const __grid_constant__ A
     }
 }
 
+// Affine-table path for narrow rows (C <= 128 * SLOTS): a warp handles R consecutive destination rows, issues all of their
+// loads first and keeps the (scale, shift) pairs of its channels in registers while the rows stay in one statistics group
+// (they do except at frame boundaries), so a row costs its own 16-byte loads only.
+template <int SLOTS, int R>
+__global__ void __launch_bounds__(256) gn_apply_ab_kernel(const __grid_constant__ ApplyP P) {
+    pdl_wait();
+    pdl_launch_dependents();
+    const int lane = threadIdx.x & 31;
+    const int drow0 = (blockIdx.x * 8 + (threadIdx.x >> 5)) * R;
+    if (drow0 >= P.dst_rows) return;
+    const int C = P.C1 + P.C2;
+    const int nvec = C >> 2, nv1 = P.C1 >> 2;
+    int sr[R];
+    float4 t[R][SLOTS];
+    int st0 = -1;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        sr[r] = drow0 + r < P.dst_rows ? apply_src_row(P, drow0 + r) : -2;
+        if (sr[r] >= 0) {
+            if (st0 < 0) st0 = P.d_stat.div(sr[r]);
+            const float4* s1 = reinterpret_cast<const float4*>(P.x1 + (size_t)sr[r] * P.C1);
+            const float4* s2 = P.x2 ? reinterpret_cast<const float4*>(P.x2 + (size_t)sr[r] * P.C2) : nullptr;
+#pragma unroll
+            for (int u = 0; u < SLOTS; ++u) {
+                const int v = lane + 32 * u;
+                if (v < nvec) t[r][u] = v < nv1 ? __ldg(s1 + v) : __ldg(s2 + (v - nv1));
+            }
+        }
+    }
+    float4 a0[SLOTS], a1[SLOTS];
+    auto load_ab = [&](int stat) {
+        const float4* ab4 = reinterpret_cast<const float4*>(P.ab + (size_t)stat * C);
+#pragma unroll
+        for (int u = 0; u < SLOTS; ++u) {
+            const int v = lane + 32 * u;
+            if (v < nvec) { a0[u] = __ldg(ab4 + 2 * v); a1[u] = __ldg(ab4 + 2 * v + 1); }
+        }
+    };
+    if (st0 >= 0) load_ab(st0);
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        if (sr[r] == -2) break;
+        uint2* drow_p = reinterpret_cast<uint2*>(P.dst + (size_t)(drow0 + r) * C);
+        if (sr[r] < 0) {
+#pragma unroll
+            for (int u = 0; u < SLOTS; ++u)
+                if (lane + 32 * u < nvec) drow_p[lane + 32 * u] = make_uint2(0u, 0u);
+            continue;
+        }
+        const int stat = P.d_stat.div(sr[r]);
+        if (stat != st0) { load_ab(stat); st0 = stat; }
+#pragma unroll
+        for (int u = 0; u < SLOTS; ++u) {
+            const int v = lane + 32 * u;
+            if (v >= nvec) continue;
+            float x[4] = {t[r][u].x, t[r][u].y, t[r][u].z, t[r][u].w};
+            if (P.raw) *reinterpret_cast<uint2*>(P.raw + (size_t)sr[r] * C + (v << 2)) = pack4(x);
+            x[0] = fmaf(x[0], a0[u].x, a0[u].y); x[1] = fmaf(x[1], a0[u].z, a0[u].w);
+            x[2] = fmaf(x[2], a1[u].x, a1[u].y); x[3] = fmaf(x[3], a1[u].z, a1[u].w);
+            if (P.silu) {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) x[e] = silu_f(x[e]);
+            }
+            drow_p[v] = pack4(x);
+        }
+    }
+}
+
 int gn_apply(const ApplyArgs& a, cudaStream_t st) {
     const int C = a.C1 + a.C2;
     MOCA_REQUIRE(C % 4 == 0 && a.C1 % 4 == 0 && C <= 256 * kStatSlots * 4, MOCA_E_SHAPE, "gn_apply: channels C1=%d C2=%d unsupported", a.C1, a.C2);
@@ -389,7 +465,10 @@ int gn_apply(const ApplyArgs& a, cudaStream_t st) {
         const int up = a.dst_mode == DST_SPATIAL_PAD_UP2 ? 1 : 0;
         P.d_outer = FastDiv(((a.H << up) + 2) * ((a.W << up) + 2)); P.d_inner = FastDiv((a.W << up) + 2);
     }
-    launch_pdl(gn_apply_kernel, dim3(cdiv(dst_rows, 8)), dim3(256), 0, st, P);
+    static const int rows_on = [] { const char* e = getenv("MOCA_GN_ROWS"); return e ? atoi(e) : 1; }();
+    if (rows_on && P.ab && C <= 384) launch_pdl(gn_apply_ab_kernel<3, 4>, dim3(cdiv(dst_rows, 32)), dim3(256), 0, st, P);
+    else if (rows_on && P.ab && C <= 768) launch_pdl(gn_apply_ab_kernel<6, 2>, dim3(cdiv(dst_rows, 16)), dim3(256), 0, st, P);
+    else launch_pdl(gn_apply_kernel, dim3(cdiv(dst_rows, 8)), dim3(256), 0, st, P);
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
 }
