@@ -38,12 +38,17 @@ __device__ __forceinline__ float gelu_erf(float g) { return 0.5f * g * (1.0f + e
 __device__ __forceinline__ float gelu_fast(float g) {
     const float z = g * 0.70710678118654752f;
     const float az = fabsf(z);
-    const float t = __fdividef(1.0f, fmaf(0.3275911f, az, 1.0f));
+    // rcp / ex2 in their flush-to-zero forms: the non-ftz intrinsics wrap each MUFU op in denormal range checks and rescaling
+    // (3 FSETP + ~6 FMUL per GEGLU output in the ncu source view), which this epilogue-bound kernel cannot afford
+    float t;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, az, 1.0f)));
     float p = fmaf(1.061405429f, t, -1.453152027f);
     p = fmaf(p, t, 1.421413741f);
     p = fmaf(p, t, -0.284496736f);
     p = fmaf(p, t, 0.254829592f);
-    const float e = p * t * __expf(-az * az);
+    float ex;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(ex) : "f"(az * az * -1.4426950408889634f));
+    const float e = p * t * ex;
     const float one_plus_erf = z < 0.f ? e : 2.0f - e;
     return 0.5f * g * one_plus_erf;
 }
