@@ -803,12 +803,17 @@ int make_tmap_bf16_chunk(CUtensorMap* tm, const void* ptr, int64_t rows, int64_t
     return MOCA_OK;
 }
 
-// Tile width: minimise (waves over the SMs) x (columns computed per tile), with a small penalty for the narrower tiles
-// (a 128-wide B tile keeps the MMA shared-memory-bandwidth bound).  GEGLU weights are packed for 256-wide tiles.
+// Tile width: minimise (waves over the SMs) x (columns computed per tile) x (cost per column of that width).  The cost per
+// column is the measured main-loop rate: 1412 TFLOP/s marginal with 128x256 tiles, ~1240 with 128x160, less with 128x128
+// (the A tile is re-read from shared memory for fewer columns).  A sweep over the b=2 forward (per-op times, same box)
+// put the ratios at 1.20 / 1.40: with the earlier 1.06 / 1.15 the 20x32 and 10x16 convolutions ran 748 / 432 tiles of
+// 160 columns where 561 / 270 tiles of 256 are 15-20 % faster (1.35 ms per forward).  GEGLU weights are packed for 256.
 static int pick_bn(const GemmDesc& d, int num_sms) {
     if (d.epi == EPI_GEGLU) return 256;
     const int cand[3] = {256, 160, 128};
-    const double pen[3] = {1.0, 1.06, 1.15};
+    static const double pen160 = [] { const char* e = getenv("MOCA_GEMM_PEN160"); return e ? atof(e) : 1.20; }();
+    static const double pen128 = [] { const char* e = getenv("MOCA_GEMM_PEN128"); return e ? atof(e) : 1.40; }();
+    const double pen[3] = {1.0, pen160, pen128};
     const int64_t mt = (d.M + kBM - 1) / kBM;
     int best = 128;
     double best_cost = 1e30;
