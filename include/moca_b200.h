@@ -35,6 +35,7 @@ extern "C" {
 #define MOCA_E_STATE (-8)
 
 #define MOCA_MAX_FRAMES 64
+#define MOCA_MAX_MASKS 1024    /* F * masks-per-frame of the SAM branch; also the scratch size of the mask pre-passes */
 
 typedef struct moca_ctx moca_ctx;       /* one per process / GPU; not thread-safe */
 typedef struct moca_unet moca_unet;     /* packed bf16 weights + execution plan of one UNet */
@@ -55,13 +56,37 @@ int32_t moca_ctx_destroy(moca_ctx* ctx);
  *       (the reference's clobbered loop index, SURVEY Q3, is expressed by the caller through this table).
  * cond_img: [B,C,1,H,W] fp32 (ignored when mask is NULL).
  * enh_lo / enh_hi: blend gain for t <= t_thresh / t > t_thresh (ddim.py:584: 1.5 / 1.0; SAM branch :845: 2 / 0=off).
- * cover_max: masks whose sum exceeds cover_max*H*W*B are skipped (ddim.py:826); >= 1 disables the test.
+ * cover_max: masks whose sum exceeds cover_max*H*W*B are skipped; <= 0 = no coverage test (the DAVIS branch has none,
+ *       ddim.py:587; the SAM branch's 80 % rule lives in moca_sam_blend).
  * F <= MOCA_MAX_FRAMES. */
 int32_t moca_cfg_ddim_step(moca_ctx* ctx, const float* x, const float* e_c, const float* e_u, const float* noise,
                            float cfg_scale, const float* coef, const int32_t* ts, const float* mask, int32_t Fm,
                            const int32_t* mask_idx, const float* cond_img, double gamma, float enh_lo, float enh_hi,
                            int32_t t_thresh, float cover_max, int32_t B, int32_t C, int32_t F, int32_t H, int32_t W,
                            float* x_prev, float* pred_x0, void* stream);
+
+/* ---- SAM branch of ddim_step (no DAVIS masks): DDIMSampler.apply_cond_img -> _apply_segmentation
+ *      (ddim.py:591-606, 739-903) and calculate_iou (:905-943) ------------------------------------------------
+ * Grounding-DINO / SAM-2 themselves are third-party networks: their masks are inputs.  The flow of one step is
+ *   1. moca_cfg_ddim_step(gamma = 0, no mask)  -> x_prev and the momentum-corrected x0 prediction p' (pred_x0 slot)
+ *   2. per frame with t <= 300, in frame order: moca_latent_to_u8(p', frame) -> image for the segmenter (:745-761);
+ *      no box -> previous frame's masks (:787-793); else moca_mask_iou(new, previous) < 0.5 -> previous (:809-813)
+ *   3. moca_sam_blend: masks applied in order, a mask covering more than cover_max (0.8) of the frame RESETS the frame
+ *      to p' (:826-828), otherwise where(mask > 0.5, cond_img * gain (2), cur) (:845, :897-901); then
+ *      pred_x0 = (1 - gamma) * cur + gamma * sigma * noise (:609).
+ * moca_latent_to_u8: pred_x0 = sample 0 of [B,C,F,H,W] (the reference squeezes b = 1); image: DEVICE uint8 [H,W,3].
+ * moca_mask_iou:     masks fp32 [n,H,W]; pairs = zip(a, b); *iou_mean is a HOST float; synchronises the stream
+ *                    (the caller branches on it, as the reference does with .item()).
+ * moca_sam_blend:    p_corr, noise, pred_x0 [B,C,F,H,W]; sigma HOST float[F]; cond_img [B,C,1,H,W];
+ *                    masks fp32 [F,Nmax,H,W]; n_masks HOST int32[F] (0 = frame untouched; F*Nmax <= MOCA_MAX_MASKS). */
+int32_t moca_latent_to_u8(moca_ctx* ctx, const float* pred_x0, int32_t C, int32_t F, int32_t H, int32_t W, int32_t frame,
+                          uint8_t* image, void* stream);
+int32_t moca_mask_iou(moca_ctx* ctx, const float* masks_a, int32_t n_a, const float* masks_b, int32_t n_b, int32_t H,
+                      int32_t W, float* iou_mean, void* stream);
+int32_t moca_sam_blend(moca_ctx* ctx, const float* p_corr, const float* noise, const float* sigma, const float* cond_img,
+                       const float* masks, const int32_t* n_masks, int32_t Nmax, double gamma, float gain,
+                       float cover_max, int32_t B, int32_t C, int32_t F, int32_t H, int32_t W, float* pred_x0,
+                       void* stream);
 
 /* ---- DDIMSampler.p_sample_ddim (ddim.py:274-359): CFG + plain DDIM update, scalar table index -------------
  * n = B*C*F*H*W elements.  coef: A, A_prev, sigma, sqrt(1-A).  use_scale selects ddim.py:349-355. */
@@ -119,6 +144,10 @@ int32_t moca_unet_create(moca_ctx* ctx, int32_t in_channels, int32_t out_channel
                          int32_t context_dim, int32_t init_attn_heads, moca_unet** out);
 int32_t moca_unet_destroy(moca_unet* net);
 int32_t moca_unet_load(moca_unet* net, const char* name, const float* data, int64_t numel, void* stream);
+/* The whole state_dict in one kernel launch (SURVEY §8b `moca_weights_pack`): names / data (fp32 DEVICE pointers) / numel
+ * arrays of `count` entries; synchronises the stream before returning, so the tensors may be freed afterwards. */
+int32_t moca_unet_load_many(moca_unet* net, int32_t count, const char* const* names, const float* const* data,
+                            const int64_t* numel, void* stream);
 int32_t moca_unet_finalize(moca_unet* net);
 int32_t moca_unet_forward(moca_unet* net, const float* x, const int32_t* timesteps, const float* context,
                           const int32_t* ctx_len, int32_t Lmax, const int32_t* fps, int32_t B, int32_t T, int32_t H,

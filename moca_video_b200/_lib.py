@@ -19,6 +19,9 @@ SIGNATURES = {
     "moca_ctx_destroy": (i32, [vp]),
     "moca_cfg_ddim_step": (i32, [vp, vp, vp, vp, vp, f32, vp, vp, vp, i32, vp, vp, f64, f32, f32, i32, f32,
                                  i32, i32, i32, i32, i32, vp, vp, vp]),
+    "moca_latent_to_u8": (i32, [vp, vp, i32, i32, i32, i32, i32, vp, vp]),
+    "moca_mask_iou": (i32, [vp, vp, i32, vp, i32, i32, i32, C.POINTER(C.c_float), vp]),
+    "moca_sam_blend": (i32, [vp, vp, vp, vp, vp, vp, vp, i32, f64, f32, f32, i32, i32, i32, i32, i32, vp, vp]),
     "moca_p_sample_ddim": (i32, [vp, vp, vp, vp, vp, f32, f32, f32, f32, f32, i32, f32, f32, i64, vp, vp, vp]),
     "moca_renoise": (i32, [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, vp]),
     "moca_queue_shift": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, vp, vp]),
@@ -30,6 +33,7 @@ SIGNATURES = {
     "moca_unet_create": (i32, [vp, i32, i32, i32, i32, vp, i32, vp, i32, i32, i32, i32, C.POINTER(vp)]),
     "moca_unet_destroy": (i32, [vp]),
     "moca_unet_load": (i32, [vp, cp, vp, i64, vp]),
+    "moca_unet_load_many": (i32, [vp, i32, C.POINTER(cp), C.POINTER(vp), pi64, vp]),
     "moca_unet_finalize": (i32, [vp]),
     "moca_unet_forward": (i32, [vp, vp, vp, vp, vp, i32, vp, i32, i32, i32, i32, vp, vp]),
     "moca_unet_set_taps": (i32, [vp, i32]),

@@ -39,8 +39,8 @@ extern "C" int32_t moca_ctx_create(int32_t device, moca_ctx** out) {
     c->c.num_sms = prop.multiProcessorCount;
     c->c.cc_major = prop.major;
     c->c.cc_minor = prop.minor;
-    MOCA_CHECK_CUDA(cudaMalloc(&c->c.d_mask_sums, sizeof(double) * MOCA_MAX_FRAMES));
-    MOCA_CHECK_CUDA(cudaMemset(c->c.d_mask_sums, 0, sizeof(double) * MOCA_MAX_FRAMES));
+    MOCA_CHECK_CUDA(cudaMalloc(&c->c.d_mask_sums, sizeof(double) * MOCA_MAX_MASKS));
+    MOCA_CHECK_CUDA(cudaMemset(c->c.d_mask_sums, 0, sizeof(double) * MOCA_MAX_MASKS));
     *out = c;
     return MOCA_OK;
 }

@@ -69,7 +69,7 @@ __global__ void __launch_bounds__(128) cfg_ddim_step_kernel(
         if (mask != nullptr && j >= 0 && j < P.Fm) {
             k = P.ts[i] <= P.t_thresh ? P.enh_lo : P.enh_hi;          // :584 / :592,:845
             const double s = mask_sums[j];
-            if (!(s != 0.0 && s <= P.cover_limit)) k = 0.0f;          // :587 / :826
+            if (!(s != 0.0 && (P.cover_limit <= 0.0 || s <= P.cover_limit))) k = 0.0f;     // :587 / :826 (limit <= 0: no coverage test)
         }
         s_k[i] = k;
     }
@@ -142,6 +142,100 @@ __global__ void p_sample_kernel(const float* __restrict__ x, const float* __rest
         if (use_scale) p = p / scale;                    // :353
         x_prev[i] = (xcoef * p + d) + nz;                // :355 / :357
         pred_x0[i] = p;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// SAM branch of ddim_step (no DAVIS masks; lvdm/models/samplers/ddim.py:591-606 -> _apply_segmentation :739-903)
+//
+//   latent_to_u8_kernel   :745-761  x0 prediction of one frame -> the uint8 RGB image shown to Grounding-DINO / SAM-2
+//   mask_iou_kernel       :905-943  intersection / union counts of mask pairs (the `iou < 0.5` fallback gate, :809-813)
+//   sam_blend_kernel      :818-901 + :609  per frame: masks in order, a mask covering > cover_max of the frame RESETS the
+//                         result to the unblended prediction, otherwise where(mask > 0.5, cond * gain, cur); then the
+//                         gamma noise blend.  (As shipped the reference's torch.where returns C identical copies of the
+//                         frame along dim 2; one copy is produced here.)
+// One block; the frame is 3*H*W <= a few 10k values.
+__global__ void __launch_bounds__(1024) latent_to_u8_kernel(const float* __restrict__ p, int C, int F, int HW, int frame,
+                                                            uint8_t* __restrict__ img) {
+    __shared__ float red[32];
+    __shared__ float s_max;
+    const int nch = C == 1 ? 1 : 3;
+    float mx = -INFINITY;
+    for (int i = threadIdx.x; i < nch * HW; i += blockDim.x) {
+        const int c = i / HW, hw = i - c * HW;
+        mx = fmaxf(mx, p[((size_t)c * F + frame) * HW + hw]);
+    }
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = mx;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float m = red[0];
+        for (int w = 1; w < (int)(blockDim.x >> 5); ++w) m = fmaxf(m, red[w]);
+        s_max = m;
+    }
+    __syncthreads();
+    const bool scale = floorf(s_max) <= 1.0f;                               // :757 `np.floor(frame.max()) <= 1.0`
+    for (int i = threadIdx.x; i < 3 * HW; i += blockDim.x) {
+        const int hw = i / 3, c = i - hw * 3;
+        float v = p[((size_t)(C == 1 ? 0 : c) * F + frame) * HW + hw];
+        if (scale) v = v * 255.0f;                                          // :758
+        // ndarray.astype(np.uint8) of a float: truncate toward zero, keep the low 8 bits (x86-64 numpy; pinned by the golden)
+        const long long t = (long long)truncf(v);
+        img[i] = (uint8_t)(t & 255);
+    }
+}
+
+// pair j: masks a[j], b[j] (fp32 [HW]) binarised at 0.5 -> counts[2j] = |a & b|, counts[2j+1] = |a | b|
+__global__ void __launch_bounds__(256) mask_iou_kernel(const float* __restrict__ a, const float* __restrict__ b, int HW,
+                                                       int* __restrict__ counts) {
+    const int j = blockIdx.x;
+    int inter = 0, uni = 0;
+    for (int i = threadIdx.x; i < HW; i += blockDim.x) {
+        const bool x = a[(size_t)j * HW + i] > 0.5f, y = b[(size_t)j * HW + i] > 0.5f;
+        inter += (x && y) ? 1 : 0;
+        uni += (x || y) ? 1 : 0;
+    }
+    __shared__ int sh[2][8];
+    for (int o = 16; o > 0; o >>= 1) { inter += __shfl_xor_sync(0xffffffffu, inter, o); uni += __shfl_xor_sync(0xffffffffu, uni, o); }
+    if ((threadIdx.x & 31) == 0) { sh[0][threadIdx.x >> 5] = inter; sh[1][threadIdx.x >> 5] = uni; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int ti = 0, tu = 0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) { ti += sh[0][w]; tu += sh[1][w]; }
+        counts[2 * j] = ti; counts[2 * j + 1] = tu;
+    }
+}
+
+struct SamParams {
+    float Sg[MOCA_MAX_FRAMES];
+    int nmask[MOCA_MAX_FRAMES];       // masks to apply for the frame (0: none, also for t > t_thresh)
+    float omg, g, gain;
+    double cover_limit;               // cover_max * H * W
+    int B, C, F, HW, Nmax;
+};
+
+__global__ void __launch_bounds__(128) sam_blend_kernel(const float* __restrict__ p_corr, const float* __restrict__ noise,
+                                                        const float* __restrict__ cond, const float* __restrict__ masks,
+                                                        const double* __restrict__ mask_sums, float* __restrict__ pred_x0,
+                                                        const __grid_constant__ SamParams P) {
+    const int total = P.B * P.C * P.HW;
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid >= total) return;
+    const int hw = tid % P.HW;
+    const int bc = tid / P.HW;
+    const size_t base = (size_t)bc * P.F * P.HW + hw;
+    const float cg = cond[(size_t)bc * P.HW + hw] * P.gain;                 // :851 `cond_image * enhancement_factor`
+    for (int i = 0; i < P.F; ++i) {
+        const size_t o = base + (size_t)i * P.HW;
+        const float p = p_corr[o];
+        float cur = p;
+        for (int m = 0; m < P.nmask[i]; ++m) {
+            const int j = i * P.Nmax + m;
+            if (mask_sums[j] > P.cover_limit) { cur = p; continue; }        // :826-828
+            if (masks[(size_t)j * P.HW + hw] > 0.5f) cur = cg;             // :897-901
+        }
+        const float n = P.Sg[i] * noise[o];                                 // :561
+        pred_x0[o] = P.omg * cur + P.g * n;                                 // :609
     }
 }
 
@@ -335,5 +429,71 @@ extern "C" int32_t moca_halfwin_unpack(moca_ctx* ctx, const float* packed, int32
         int rc = copy_frames(packed + per * i, half, 0, queue, Q, dst0, half, B * C, H * W, (cudaStream_t)stream);
         if (rc) return rc;
     }
+    return MOCA_OK;
+}
+
+// ---- SAM branch glue (ddim.py:739-761, 787-822, 905-943) ----------------------------------------------
+extern "C" int32_t moca_latent_to_u8(moca_ctx* ctx, const float* pred_x0, int32_t C, int32_t F, int32_t H, int32_t W,
+                                     int32_t frame, uint8_t* image, void* stream) {
+    MOCA_REQUIRE(ctx != nullptr && pred_x0 && image, MOCA_E_ARG, "moca_latent_to_u8: NULL argument");
+    MOCA_REQUIRE((C == 1 || C >= 3) && F > 0 && H > 0 && W > 0 && frame >= 0 && frame < F, MOCA_E_SHAPE,
+                 "moca_latent_to_u8: C=%d (1 or >= 3) F=%d frame=%d", C, F, frame);
+    latent_to_u8_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(pred_x0, C, F, H * W, frame, image);
+    MOCA_LAUNCH_CHECK();
+    return MOCA_OK;
+}
+
+extern "C" int32_t moca_mask_iou(moca_ctx* ctx, const float* masks_a, int32_t n_a, const float* masks_b, int32_t n_b,
+                                 int32_t H, int32_t W, float* iou_mean, void* stream) {
+    MOCA_REQUIRE(ctx != nullptr && masks_a && masks_b && iou_mean, MOCA_E_ARG, "moca_mask_iou: NULL argument");
+    const int n = n_a < n_b ? n_a : n_b;                                   // zip(masks1, masks2), ddim.py:925
+    MOCA_REQUIRE(n >= 0 && n <= MOCA_MAX_MASKS && H > 0 && W > 0, MOCA_E_SHAPE, "moca_mask_iou: %d pairs (max %d)", n, MOCA_MAX_MASKS);
+    if (n == 0) { *iou_mean = nanf(""); return MOCA_OK; }                  // torch.tensor([]).mean()
+    cudaStream_t st = (cudaStream_t)stream;
+    int* d_counts = reinterpret_cast<int*>(ctx->c.d_mask_sums);
+    mask_iou_kernel<<<n, 256, 0, st>>>(masks_a, masks_b, H * W, d_counts);
+    MOCA_LAUNCH_CHECK();
+    int h[2 * MOCA_MAX_MASKS];
+    MOCA_CHECK_CUDA(cudaMemcpyAsync(h, d_counts, sizeof(int) * 2 * n, cudaMemcpyDeviceToHost, st));
+    MOCA_CHECK_CUDA(cudaStreamSynchronize(st));       // the caller branches on the value (ddim.py:811)
+    volatile float acc = 0.0f;
+    for (int j = 0; j < n; ++j) {
+        volatile float inter = (float)h[2 * j], uni = (float)h[2 * j + 1];
+        volatile float iou = h[2 * j + 1] == 0 ? 1.0f : inter / uni;        // :931-938
+        acc = acc + iou;
+    }
+    *iou_mean = acc / (float)n;                                            // :943
+    return MOCA_OK;
+}
+
+extern "C" int32_t moca_sam_blend(moca_ctx* ctx, const float* p_corr, const float* noise, const float* sigma,
+                                  const float* cond_img, const float* masks, const int32_t* n_masks, int32_t Nmax,
+                                  double gamma, float gain, float cover_max, int32_t B, int32_t C, int32_t F, int32_t H,
+                                  int32_t W, float* pred_x0, void* stream) {
+    MOCA_REQUIRE(ctx != nullptr && p_corr && noise && sigma && n_masks && pred_x0, MOCA_E_ARG, "moca_sam_blend: NULL argument");
+    MOCA_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0 && F > 0 && F <= MOCA_MAX_FRAMES, MOCA_E_SHAPE, "moca_sam_blend: bad shape");
+    MOCA_REQUIRE(Nmax >= 0 && (int64_t)F * Nmax <= MOCA_MAX_MASKS, MOCA_E_SHAPE, "moca_sam_blend: F*Nmax=%lld > %d", (long long)F * Nmax,
+                 MOCA_MAX_MASKS);
+    cudaStream_t st = (cudaStream_t)stream;
+    SamParams P;
+    memset(&P, 0, sizeof(P));
+    bool any = false;
+    for (int i = 0; i < F; ++i) {
+        MOCA_REQUIRE(n_masks[i] >= 0 && n_masks[i] <= Nmax, MOCA_E_ARG, "moca_sam_blend: n_masks[%d]=%d outside 0..%d", i, n_masks[i], Nmax);
+        P.Sg[i] = sigma[i];
+        P.nmask[i] = n_masks[i];
+        any = any || n_masks[i] > 0;
+    }
+    MOCA_REQUIRE(!any || (masks && cond_img), MOCA_E_ARG, "moca_sam_blend: masks listed without mask / cond_img tensors");
+    P.omg = (float)(1.0 - gamma); P.g = (float)gamma; P.gain = gain;
+    P.cover_limit = (double)cover_max * (double)H * W;
+    P.B = B; P.C = C; P.F = F; P.HW = H * W; P.Nmax = Nmax;
+    if (any) {
+        mask_sum_kernel<<<F * Nmax, 256, 0, st>>>(masks, 1, F * Nmax, H * W, ctx->c.d_mask_sums);
+        MOCA_LAUNCH_CHECK();
+    }
+    const int total = B * C * H * W;
+    sam_blend_kernel<<<cdiv(total, 128), 128, 0, st>>>(p_corr, noise, any ? cond_img : p_corr, masks, ctx->c.d_mask_sums, pred_x0, P);
+    MOCA_LAUNCH_CHECK();
     return MOCA_OK;
 }

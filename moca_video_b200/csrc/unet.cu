@@ -250,6 +250,58 @@ __global__ void copy_bias_kernel(const float* __restrict__ src, float* __restric
     dst[r] = src[i];
 }
 
+// One launch for a whole state_dict (moca_unet_load_many): job j covers work elements [start[j], start[j+1]) of the
+// concatenated work list; a block takes 1024-element chunks and finds its job by bisection.
+struct LoadJob {
+    const float* src;
+    float* dst_f32;
+    __nv_bfloat16* dst;
+    long long pitch, start;
+    int kind, N, K, taps, Kp, row0, geglu_bn, pad;
+};
+
+__device__ __forceinline__ int geglu_row(int n, int N, int geglu_bn) {
+    if (geglu_bn <= 0) return n;
+    const int half = N / 2, hb = geglu_bn / 2;
+    const int j = n < half ? n : n - half;
+    return (j / hb) * geglu_bn + (n < half ? 0 : hb) + (j % hb);
+}
+
+__global__ void __launch_bounds__(256) load_many_kernel(const LoadJob* __restrict__ jobs, int njobs, long long total) {
+    __shared__ int s_job;
+    const long long nchunks = (total + 1023) / 1024;
+    for (long long c = blockIdx.x; c < nchunks; c += gridDim.x) {
+        const long long w0 = c * 1024;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            int lo = 0, hi = njobs - 1;                 // last job with start <= w0
+            while (lo < hi) {
+                const int mid = (lo + hi + 1) >> 1;
+                if (jobs[mid].start <= w0) lo = mid; else hi = mid - 1;
+            }
+            s_job = lo;
+        }
+        __syncthreads();
+        int j = s_job;
+        for (int e = threadIdx.x; e < 1024; e += 256) {
+            const long long w = w0 + e;
+            if (w >= total) break;
+            while (j + 1 < njobs && jobs[j + 1].start <= w) ++j;
+            const LoadJob J = jobs[j];
+            const long long i = w - J.start;
+            if (J.kind == 0) {
+                J.dst_f32[geglu_row((int)i, J.N, J.geglu_bn)] = J.src[i];
+            } else {
+                const int k = (int)(i % J.Kp);
+                const int tap = (int)((i / J.Kp) % J.taps);
+                const int n = (int)(i / ((long long)J.Kp * J.taps));
+                const float v = k < J.K ? J.src[((long long)n * J.K + k) * J.taps + tap] : 0.0f;
+                J.dst[(long long)(J.row0 + geglu_row(n, J.N, J.geglu_bn)) * J.pitch + (long long)tap * J.Kp + k] = __float2bfloat16_rn(v);
+            }
+        }
+    }
+}
+
 }  // namespace moca
 
 extern "C" int32_t moca_unet_create(moca_ctx* ctx, int32_t in_channels, int32_t out_channels, int32_t model_channels,
@@ -306,6 +358,50 @@ extern "C" int32_t moca_unet_load(moca_unet* n, const char* name, const float* d
         if (rc) return rc;
     }
     s.loaded = true;
+    n->finalized = false;
+    return MOCA_OK;
+}
+
+// The whole state_dict in ONE kernel launch: names[i] / data[i] (fp32 DEVICE pointers, all valid until the stream has run
+// the kernel) / numel[i].  Same conversion as moca_unet_load.
+extern "C" int32_t moca_unet_load_many(moca_unet* n, int32_t count, const char* const* names, const float* const* data,
+                                       const int64_t* numel, void* stream) {
+    MOCA_REQUIRE(n && names && data && numel && count > 0, MOCA_E_ARG, "moca_unet_load_many: NULL argument");
+    MOCA_REQUIRE(!n->dry, MOCA_E_STATE, "moca_unet_load_many: network was created without a context (listing only)");
+    std::vector<LoadJob> jobs((size_t)count);
+    long long total = 0;
+    for (int i = 0; i < count; ++i) {
+        MOCA_REQUIRE(names[i] && data[i], MOCA_E_ARG, "moca_unet_load_many: NULL entry %d", i);
+        auto it = n->slots.find(names[i]);
+        MOCA_REQUIRE(it != n->slots.end(), MOCA_E_ARG, "moca_unet_load_many: unknown parameter '%s'", names[i]);
+        const LoadSlot& s = it->second;
+        MOCA_REQUIRE(s.numel == numel[i], MOCA_E_SHAPE, "moca_unet_load_many: '%s' has %lld elements, expected %lld", names[i],
+                     (long long)numel[i], (long long)s.numel);
+        LoadJob& J = jobs[i];
+        memset(&J, 0, sizeof(J));
+        J.src = data[i]; J.start = total; J.geglu_bn = s.geglu_bn;
+        if (s.kind == LoadSlot::COPY_F32) {
+            J.kind = 0; J.dst_f32 = s.dst_f32; J.N = (int)s.numel;
+            total += s.numel;
+        } else {
+            J.kind = 1; J.dst = s.dst; J.N = s.N; J.K = s.K; J.taps = s.taps; J.Kp = s.Kp; J.row0 = s.row0; J.pitch = s.pitch;
+            total += (long long)s.N * s.taps * s.Kp;
+        }
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    LoadJob* d_jobs = nullptr;
+    MOCA_CHECK_CUDA(cudaMalloc(&d_jobs, sizeof(LoadJob) * (size_t)count));
+    cudaError_t ce = cudaMemcpyAsync(d_jobs, jobs.data(), sizeof(LoadJob) * (size_t)count, cudaMemcpyHostToDevice, st);
+    if (ce == cudaSuccess) {
+        const long long nchunks = (total + 1023) / 1024;
+        const int blocks = (int)(nchunks < (long long)n->ctx->c.num_sms * 16 ? nchunks : (long long)n->ctx->c.num_sms * 16);
+        load_many_kernel<<<blocks, 256, 0, st>>>(d_jobs, count, total);
+        ce = cudaGetLastError();
+    }
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(st);       // jobs (host vector) and d_jobs are released below
+    cudaFree(d_jobs);
+    MOCA_REQUIRE(ce == cudaSuccess, MOCA_E_CUDA, "moca_unet_load_many: %s", cudaGetErrorString(ce));
+    for (int i = 0; i < count; ++i) n->slots[names[i]].loaded = true;
     n->finalized = false;
     return MOCA_OK;
 }

@@ -7,9 +7,9 @@
                                           are sharded over the ranks of a torch.distributed group: window r runs on rank
                                           r mod G, the updated half-windows are exchanged with ONE all_gather per
                                           iteration (NCCL over NVLink), every rank then applies the same shift.
-RNG parity: every rank draws the noise of ALL windows from an identically seeded generator in the reference's order
-(window 2n-1 .. 0, one draw per frame, then the shift's tail draw) and uses its own share, so 1-GPU and G-GPU runs
-produce the same queue.  VAE decode of the popped frame and PNG writing are out of scope: popped
+RNG parity: the noise stream is the reference's (window 2n-1 .. 0, one draw per frame, then the shift's tail draw) from
+an identically seeded generator on every rank; a rank draws only the windows it owns and advances the generator's
+Philox offset past the others (``_NoiseStream``), so 1-GPU and G-GPU runs produce the same queue without 8x the launches.  VAE decode of the popped frame and PNG writing are out of scope: popped
 latent frames are returned (or handed to ``on_frame``).
 """
 import numpy as np
@@ -57,6 +57,53 @@ def shift_latents(latents, davis_data=None, model=None, new_noise=None, generato
     return ops.queue_shift(latents, tail)
 
 
+class _NoiseStream:
+    """The reference's per-frame N(0,1) draws (ddim.py:561 through lvdm/common.py:31-34; funcs.py:93) as a stream that can
+    be skipped: ``block(n, keep)`` returns n frames drawn one randn call each, or advances the generator past n such calls.
+    CUDA generators are advanced through their Philox offset (measured from one real call); CPU generators (the gloo
+    tests) draw and discard."""
+
+    def __init__(self, generator, device, frame_shape):
+        self.dev = torch.device(device)
+        self.shape = tuple(frame_shape)
+        self.gen = generator
+        if generator is None and self.dev.type == "cuda":
+            self.gen = torch.cuda.default_generators[self.dev.index if self.dev.index is not None else torch.cuda.current_device()]
+        self.delta = None
+
+    def _one(self):
+        if self.dev.type == "cuda" and self.delta is None:
+            o0 = self.gen.get_offset()
+            t = torch.randn(self.shape, device=self.dev, generator=self.gen)
+            self.delta = self.gen.get_offset() - o0
+            return t
+        return torch.randn(self.shape, device=self.dev, generator=self.gen)
+
+    def block(self, n, keep=True):
+        if keep:
+            return torch.cat([self._one() for _ in range(n)], dim=2)
+        if self.dev.type != "cuda":
+            for _ in range(n):
+                self._one()
+            return None
+        if self.delta is None:
+            self._one()
+            n -= 1
+        self.gen.set_offset(self.gen.get_offset() + n * self.delta)
+        return None
+
+
+_xchg_cache = {}
+
+
+def _xchg_buffers(key, per, world, shape, dev):
+    """Hand-off staging, allocated once per geometry (no allocator traffic between the graph replays of an iteration)."""
+    if key not in _xchg_cache:
+        _xchg_cache[key] = (torch.zeros((per,) + shape, device=dev, dtype=torch.float32),
+                            torch.empty((world, per) + shape, device=dev, dtype=torch.float32))
+    return _xchg_cache[key]
+
+
 def window_plan(args):
     """[(start, mid, end)] for rank = 2n-1 .. 0 in the reference's (reversed) order, funcs.py:306-310."""
     f = args.video_length
@@ -71,14 +118,16 @@ def window_plan(args):
 def fifo_ddim_sampling(args, model, conditioning, noise_shape, ddim_sampler, cfg_scale=1.0, output_dir=None, latents_dir=None,
                        save_frames=False, conditioned_image=None, targets=None, gamma=0.5, use_self_attention=False,
                        davis_data=None, anchor_frame=None, unconditional_conditioning=None, masks=None, latents=None,
-                       generator=None, group=None, on_frame=None, num_iterations=None, queue_out=None, **kwargs):
+                       generator=None, group=None, on_frame=None, num_iterations=None, queue_out=None, shard=True,
+                       **kwargs):
     """funcs.py:243-371.  Returns the list of popped latent frames [B,C,1,H,W] (one per iteration).
 
     ``unconditional_conditioning``: the reference encodes "" with CLIP here (funcs.py:267-276); CLIP is out of scope, so
     the embedding is an input (or ``model.get_learned_conditioning`` is used when the model has it).
     ``masks`` [B,1,Q,H,W]: per-queue-slot masks (the reference's DAVIS masks).  ``group``: torch.distributed group to
     shard windows over (None = the default group if initialised, else single GPU).  ``queue_out``: dict that receives the
-    final queue (``latents``, ``masks``) so a caller can continue the run."""
+    final queue (``latents``, ``masks``) so a caller can continue the run.  ``shard=False`` runs every window on the calling
+    rank even when a process group exists (the 1-GPU replay the multi-GPU equality checks compare with)."""
     import torch.distributed as dist
     kwargs.update({"clean_cond": True})
     cond = conditioning
@@ -96,56 +145,56 @@ def fifo_ddim_sampling(args, model, conditioning, noise_shape, ddim_sampler, cfg
     half = f // 2
     ts_q, idx_q = fifo_queue_tables(args.num_inference_steps, f, args.lookahead_denoising)
     wins = window_plan(args)
-    world = dist.get_world_size(group) if (group is not None or (dist.is_available() and dist.is_initialized())) else 1
+    world = dist.get_world_size(group) if shard and (group is not None or (dist.is_available() and dist.is_initialized())) else 1
     rank = dist.get_rank(group) if world > 1 else 0
     n_iter = num_iterations if num_iterations is not None else args.new_video_length + args.num_inference_steps - f
     popped = []
     dev = latents.device
+    stream = _NoiseStream(generator, dev, (B, C, 1, H, W))
+    keep = half if args.lookahead_denoising else f
+    per = (len(wins) + world - 1) // world
+
+    def onestep(start, end, nz):
+        x_in = ops.window_gather(latents, start, f)
+        m_in = ops.window_gather(masks, start, f) if masks is not None else None
+        return ddim_sampler.fifo_onestep(cond=cond, shape=noise_shape, latents=x_in, timesteps=ts_q[start:end],
+                                         indices=idx_q[start:end], unconditional_guidance_scale=cfg_scale,
+                                         unconditional_conditioning=uc, cond_image=conditioned_image, target=targets,
+                                         gamma=gamma, use_self_attention=use_self_attention, davis_masks=m_in, noise=nz,
+                                         **kwargs)[0]
+
     for it in range(n_iter):
-        # noise of every window in the reference's draw order (identical on all ranks)
-        noises = [torch.cat([torch.randn((B, C, 1, H, W), device=dev, generator=generator) for _ in range(f)], dim=2)
-                  for _ in wins]
         if world == 1:
-            for (w, start, mid, end), nz in zip(wins, noises):
-                x_in = ops.window_gather(latents, start, f)
-                m_in = ops.window_gather(masks, start, f) if masks is not None else None
-                x_prev, _ = ddim_sampler.fifo_onestep(cond=cond, shape=noise_shape, latents=x_in, timesteps=ts_q[start:end],
-                                                      indices=idx_q[start:end], unconditional_guidance_scale=cfg_scale,
-                                                      unconditional_conditioning=uc, cond_image=conditioned_image,
-                                                      target=targets, gamma=gamma, use_self_attention=use_self_attention,
-                                                      davis_masks=m_in, noise=nz, **kwargs)
+            for (w, start, mid, end) in wins:
+                x_prev = onestep(start, end, stream.block(f))
                 if args.lookahead_denoising:
                     ops.window_scatter(latents, x_prev, half, mid, half)
                 else:
                     ops.window_scatter(latents, x_prev, 0, start, f)
         else:
-            # snapshot semantics (funcs_mp.py:207): all windows read the iteration-start queue
-            keep = half if args.lookahead_denoising else f
-            mine = [(w, start, mid, end, nz) for (w, start, mid, end), nz in zip(wins, noises) if w % world == rank]
-            per = (len(wins) + world - 1) // world
-            packed = torch.zeros((per, B, C, keep, H, W), device=dev, dtype=torch.float32)
-            for j, (w, start, mid, end, nz) in enumerate(mine):
-                x_in = ops.window_gather(latents, start, f)
-                m_in = ops.window_gather(masks, start, f) if masks is not None else None
-                x_prev, _ = ddim_sampler.fifo_onestep(cond=cond, shape=noise_shape, latents=x_in, timesteps=ts_q[start:end],
-                                                      indices=idx_q[start:end], unconditional_guidance_scale=cfg_scale,
-                                                      unconditional_conditioning=uc, cond_image=conditioned_image,
-                                                      target=targets, gamma=gamma, use_self_attention=use_self_attention,
-                                                      davis_masks=m_in, noise=nz, **kwargs)
-                packed[j] = ops.window_gather(x_prev, f - keep, keep)
-            gathered = torch.empty((world, per, B, C, keep, H, W), device=dev, dtype=torch.float32)
+            # snapshot semantics (funcs_mp.py:207): all windows read the iteration-start queue, so the owned windows run
+            # first and the queue is only written after the exchange
+            packed, gathered = _xchg_buffers((world, per, B, C, keep, H, W, dev.index), per, world, (B, C, keep, H, W), dev)
+            j = 0
+            for (w, start, mid, end) in wins:
+                nz = stream.block(f, keep=(w % world == rank))
+                if nz is None:
+                    continue
+                x_prev = onestep(start, end, nz)
+                ops.window_scatter(packed[j], x_prev, f - keep, 0, keep)
+                j += 1
             dist.all_gather_into_tensor(gathered.view(-1), packed.view(-1), group=group)   # the queue hand-off
             for (w, start, mid, end) in wins:
                 owner = w % world
-                slot = [x[0] for x in wins if x[0] % world == owner].index(w)       # same order as `mine` on the owner
+                slot = [x[0] for x in wins if x[0] % world == owner].index(w)       # same order as on the owner
                 ops.window_scatter(latents, gathered[owner, slot], 0, mid if args.lookahead_denoising else start, keep)
         first = half if args.lookahead_denoising else 0
         frame = ops.window_gather(latents, first, 1)
         if on_frame is not None:
             on_frame(it, frame)
         popped.append(frame)
-        tail_noise = torch.randn((B, C, H, W), device=dev, generator=generator).unsqueeze(2)
-        latents = shift_latents(latents, new_noise=tail_noise)
+        # funcs.py:93 draws randn_like(latents[:, :, -1]) = [B,C,H,W]; same element count and Philox consumption as one frame
+        latents = shift_latents(latents, new_noise=stream.block(1))
         if masks is not None:
             masks = ops.queue_shift(masks, ops.window_gather(masks, Q - 1, 1))
     if queue_out is not None:

@@ -21,7 +21,7 @@ def _f32c(t, name):
 
 
 def cfg_ddim_step(x, e_c, e_u, noise, cfg_scale, coef, ts, mask=None, mask_idx=None, cond_img=None, gamma=0.5,
-                  enh_lo=1.5, enh_hi=1.0, t_thresh=300, cover_max=2.0):
+                  enh_lo=1.5, enh_hi=1.0, t_thresh=300, cover_max=0.0):
     """DDIMSampler.unet CFG combine + DDIMSampler.ddim_step (lvdm/models/samplers/ddim.py:372, 377-649).
 
     x, e_c, e_u, noise: [B,C,F,H,W]; coef: float32 [4,F] (A, A_prev, sigma, sqrt(1-A)); ts: int [F].
@@ -41,12 +41,57 @@ def cfg_ddim_step(x, e_c, e_u, noise, cfg_scale, coef, ts, mask=None, mask_idx=N
     else:
         midx = None
     ts_h = host_i32(ts)
-    check(lib().moca_cfg_ddim_step(ctx(x.device.index), ptr(x), ptr(e_c), ptr(e_u), ptr(noise), float(cfg_scale),
-                                   coef.ctypes.data_as(C.c_void_p), C.cast(ts_h, C.c_void_p), ptr(mask), Fm,
-                                   C.cast(midx, C.c_void_p) if midx is not None else None, ptr(cond_img), float(gamma),
-                                   float(enh_lo), float(enh_hi), int(t_thresh), float(cover_max), B, Cc, F, H, W,
-                                   ptr(xp), ptr(p0), stream_ptr()))
+    with torch.cuda.device(x.device):
+        check(lib().moca_cfg_ddim_step(ctx(x.device.index), ptr(x), ptr(e_c), ptr(e_u), ptr(noise), float(cfg_scale),
+                                       coef.ctypes.data_as(C.c_void_p), C.cast(ts_h, C.c_void_p), ptr(mask), Fm,
+                                       C.cast(midx, C.c_void_p) if midx is not None else None, ptr(cond_img), float(gamma),
+                                       float(enh_lo), float(enh_hi), int(t_thresh), float(cover_max), B, Cc, F, H, W,
+                                       ptr(xp), ptr(p0), stream_ptr()))
     return xp, p0
+
+
+def latent_to_u8(pred_x0, frame):
+    """_apply_segmentation's image conversion (ddim.py:745-761): frame ``frame`` of sample 0 of pred_x0 [B,C,F,H,W] ->
+    uint8 [H,W,3] (device tensor) for Grounding-DINO / SAM-2."""
+    pred_x0 = _f32c(pred_x0, "pred_x0")
+    B, Cc, F, H, W = pred_x0.shape
+    img = torch.empty((H, W, 3), device=pred_x0.device, dtype=torch.uint8)
+    with torch.cuda.device(pred_x0.device):
+        check(lib().moca_latent_to_u8(ctx(pred_x0.device.index), ptr(pred_x0), Cc, F, H, W, int(frame), ptr(img), stream_ptr()))
+    return img
+
+
+def mask_iou(masks_a, masks_b):
+    """DDIMSampler.calculate_iou (ddim.py:905-943): mean IoU over zip(masks_a, masks_b) binarised at 0.5 -> python float."""
+    if masks_a.numel() == 0 or masks_b.numel() == 0:
+        return float("nan")                                  # torch.tensor([]).mean(): never below the 0.5 gate
+    a = _f32c(masks_a, "masks_a"); b = _f32c(masks_b, "masks_b")
+    H, W = a.shape[-2:]
+    assert b.shape[-2:] == (H, W)
+    out = C.c_float()
+    with torch.cuda.device(a.device):
+        check(lib().moca_mask_iou(ctx(a.device.index), ptr(a), a.reshape(-1, H, W).shape[0], ptr(b), b.reshape(-1, H, W).shape[0],
+                                  H, W, C.byref(out), stream_ptr()))
+    return float(out.value)
+
+
+def sam_blend(p_corr, noise, sigma, cond_img, masks, n_masks, gamma=0.5, gain=2.0, cover_max=0.8):
+    """The blend loop of _apply_segmentation (ddim.py:818-901) for all frames + the gamma noise blend (:609).
+    p_corr, noise [B,C,F,H,W]; sigma float [F]; masks [F,Nmax,H,W] or None; n_masks int [F]."""
+    p_corr = _f32c(p_corr, "p_corr"); noise = _f32c(noise, "noise")
+    B, Cc, F, H, W = p_corr.shape
+    Nmax = 0
+    if masks is not None:
+        masks = _f32c(masks, "masks"); cond_img = _f32c(cond_img, "cond_img")
+        assert masks.shape[0] == F and masks.shape[-2:] == (H, W) and cond_img.shape == (B, Cc, 1, H, W)
+        Nmax = masks.shape[1]
+    out = torch.empty_like(p_corr)
+    sg, nm = host_f32(sigma), host_i32(n_masks)
+    with torch.cuda.device(p_corr.device):
+        check(lib().moca_sam_blend(ctx(p_corr.device.index), ptr(p_corr), ptr(noise), C.cast(sg, C.c_void_p), ptr(cond_img),
+                                   ptr(masks), C.cast(nm, C.c_void_p), Nmax, float(gamma), float(gain), float(cover_max), B, Cc, F,
+                                   H, W, ptr(out), stream_ptr()))
+    return out
 
 
 def p_sample_ddim(x, e_c, e_u, noise, cfg_scale, A, A_prev, sigma, sqrt_one_minus_A, scale=None, scale_prev=None):
@@ -55,10 +100,11 @@ def p_sample_ddim(x, e_c, e_u, noise, cfg_scale, A, A_prev, sigma, sqrt_one_minu
     e_u = _f32c(e_u, "e_u") if e_u is not None else None
     xp = torch.empty_like(x); p0 = torch.empty_like(x)
     use_scale = scale is not None
-    check(lib().moca_p_sample_ddim(ctx(x.device.index), ptr(x), ptr(e_c), ptr(e_u), ptr(noise), float(cfg_scale), float(A),
-                                   float(A_prev), float(sigma), float(sqrt_one_minus_A), int(use_scale),
-                                   float(scale if use_scale else 1.0), float(scale_prev if use_scale else 1.0), x.numel(),
-                                   ptr(xp), ptr(p0), stream_ptr()))
+    with torch.cuda.device(x.device):
+        check(lib().moca_p_sample_ddim(ctx(x.device.index), ptr(x), ptr(e_c), ptr(e_u), ptr(noise), float(cfg_scale), float(A),
+                                       float(A_prev), float(sigma), float(sqrt_one_minus_A), int(use_scale),
+                                       float(scale if use_scale else 1.0), float(scale_prev if use_scale else 1.0), x.numel(),
+                                       ptr(xp), ptr(p0), stream_ptr()))
     return xp, p0
 
 
@@ -69,8 +115,9 @@ def renoise(z, noise, src_frame, alpha):
     Q = noise.shape[2]
     out = torch.empty_like(noise)
     src_h, alpha_h = host_i32(src_frame), host_f32(alpha)
-    check(lib().moca_renoise(ctx(z.device.index), ptr(z), ptr(noise), C.cast(src_h, C.c_void_p),
-                             C.cast(alpha_h, C.c_void_p), B, Cc, Fz, Q, H, W, ptr(out), stream_ptr()))
+    with torch.cuda.device(z.device):
+        check(lib().moca_renoise(ctx(z.device.index), ptr(z), ptr(noise), C.cast(src_h, C.c_void_p),
+                                 C.cast(alpha_h, C.c_void_p), B, Cc, Fz, Q, H, W, ptr(out), stream_ptr()))
     return out
 
 
@@ -79,7 +126,8 @@ def queue_shift(queue, tail):
     queue = _f32c(queue, "queue"); tail = _f32c(tail, "tail")
     B, Cc, Q, H, W = queue.shape
     out = torch.empty_like(queue)
-    check(lib().moca_queue_shift(ctx(queue.device.index), ptr(queue), ptr(tail), B, Cc, Q, H, W, ptr(out), stream_ptr()))
+    with torch.cuda.device(queue.device):
+        check(lib().moca_queue_shift(ctx(queue.device.index), ptr(queue), ptr(tail), B, Cc, Q, H, W, ptr(out), stream_ptr()))
     return out
 
 
@@ -87,7 +135,8 @@ def window_gather(queue, start, Fw):
     queue = _f32c(queue, "queue")
     B, Cc, Q, H, W = queue.shape
     win = torch.empty((B, Cc, Fw, H, W), device=queue.device, dtype=torch.float32)
-    check(lib().moca_window_gather(ctx(queue.device.index), ptr(queue), B, Cc, Q, H, W, int(start), int(Fw), ptr(win), stream_ptr()))
+    with torch.cuda.device(queue.device):
+        check(lib().moca_window_gather(ctx(queue.device.index), ptr(queue), B, Cc, Q, H, W, int(start), int(Fw), ptr(win), stream_ptr()))
     return win
 
 
@@ -96,8 +145,9 @@ def window_scatter(queue, win, win_off, start, Fw):
     assert queue.is_cuda and queue.dtype == torch.float32 and queue.is_contiguous()
     win = _f32c(win, "win")
     B, Cc, Q, H, W = queue.shape
-    check(lib().moca_window_scatter(ctx(queue.device.index), ptr(win), win.shape[2], int(win_off), B, Cc, Q, H, W, int(start),
-                                    int(Fw), ptr(queue), stream_ptr()))
+    with torch.cuda.device(queue.device):
+        check(lib().moca_window_scatter(ctx(queue.device.index), ptr(win), win.shape[2], int(win_off), B, Cc, Q, H, W, int(start),
+                                        int(Fw), ptr(queue), stream_ptr()))
     return queue
 
 
@@ -110,6 +160,8 @@ def freeinit_filter(shape, device, filter_type="gaussian", n=4, d_s=0.25, d_t=0.
         raise NotImplementedError(filter_type)
     T, H, W = shape[-3], shape[-2], shape[-1]
     dev = torch.device(device)
+    if dev.type != "cuda":
+        raise _lib.MocaError("freeinit_filter: the filter is built on a CUDA device (no CPU path exists)")
     lpf = torch.empty((T, H, W), device=dev, dtype=torch.float32)
     with torch.cuda.device(dev):
         check(lib().moca_freeinit_filter(ctx(dev.index), FILTER_TYPES[filter_type], int(n), float(d_s), float(d_t), T, H, W,
@@ -125,7 +177,8 @@ def freq_mix_3d(x, noise, lpf):
     NV = x.numel() // (T * H * W)
     y = torch.empty_like(x)
     work = torch.empty(lib().moca_freeinit_work_bytes(NV, T, H, W), device=x.device, dtype=torch.uint8)
-    check(lib().moca_freeinit_mix(ctx(x.device.index), ptr(x), ptr(noise), ptr(lpf), NV, T, H, W, ptr(y), ptr(work), stream_ptr()))
+    with torch.cuda.device(x.device):
+        check(lib().moca_freeinit_mix(ctx(x.device.index), ptr(x), ptr(noise), ptr(lpf), NV, T, H, W, ptr(y), ptr(work), stream_ptr()))
     return y
 
 
@@ -134,7 +187,8 @@ def gemm_bf16(a, w, bias=None, out_bf16=False):
     M, K = a.shape
     N = w.shape[0]
     out = torch.empty((M, N), device=a.device, dtype=torch.bfloat16 if out_bf16 else torch.float32)
-    check(lib().moca_gemm_bf16(ctx(a.device.index), ptr(a), ptr(w), ptr(bias), M, N, K, ptr(out), int(out_bf16), stream_ptr()))
+    with torch.cuda.device(a.device):
+        check(lib().moca_gemm_bf16(ctx(a.device.index), ptr(a), ptr(w), ptr(bias), M, N, K, ptr(out), int(out_bf16), stream_ptr()))
     return out
 
 
@@ -142,7 +196,8 @@ def geglu(a_bf16, w, bias):
     M, K = a_bf16.shape
     N = w.shape[0]
     out = torch.empty((M, N // 2), device=a_bf16.device, dtype=torch.bfloat16)
-    check(lib().moca_geglu_f32(ctx(a_bf16.device.index), ptr(a_bf16), ptr(w), ptr(bias), M, N, K, ptr(out), stream_ptr()))
+    with torch.cuda.device(a_bf16.device):
+        check(lib().moca_geglu_f32(ctx(a_bf16.device.index), ptr(a_bf16), ptr(w), ptr(bias), M, N, K, ptr(out), stream_ptr()))
     return out
 
 
@@ -150,7 +205,8 @@ def conv3x3_nhwc(x, w, bias, stride=1):
     NF, H, W, Cin = x.shape
     Cout = w.shape[0]
     y = torch.empty((NF, H // stride, W // stride, Cout), device=x.device, dtype=torch.float32)
-    check(lib().moca_conv3x3_f32(ctx(x.device.index), ptr(x), ptr(w), ptr(bias), NF, H, W, Cin, Cout, stride, ptr(y), stream_ptr()))
+    with torch.cuda.device(x.device):
+        check(lib().moca_conv3x3_f32(ctx(x.device.index), ptr(x), ptr(w), ptr(bias), NF, H, W, Cin, Cout, stride, ptr(y), stream_ptr()))
     return y
 
 
@@ -158,29 +214,33 @@ def tconv_tokens(x, w, bias):
     B, T, HW, Cin = x.shape
     Cout = w.shape[0]
     y = torch.empty((B, T, HW, Cout), device=x.device, dtype=torch.float32)
-    check(lib().moca_tconv_f32(ctx(x.device.index), ptr(x), ptr(w), ptr(bias), B, T, HW, Cin, Cout, ptr(y), stream_ptr()))
+    with torch.cuda.device(x.device):
+        check(lib().moca_tconv_f32(ctx(x.device.index), ptr(x), ptr(w), ptr(bias), B, T, HW, Cin, Cout, ptr(y), stream_ptr()))
     return y
 
 
 def groupnorm_bf16(x, gamma, beta, rows_per_stat, eps, silu):
     rows, Cc = x.shape
     out = torch.empty((rows, Cc), device=x.device, dtype=torch.bfloat16)
-    check(lib().moca_groupnorm_bf16(ctx(x.device.index), ptr(x), ptr(gamma), ptr(beta), rows, Cc, rows_per_stat, float(eps),
-                                    int(silu), ptr(out), stream_ptr()))
+    with torch.cuda.device(x.device):
+        check(lib().moca_groupnorm_bf16(ctx(x.device.index), ptr(x), ptr(gamma), ptr(beta), rows, Cc, rows_per_stat, float(eps),
+                                        int(silu), ptr(out), stream_ptr()))
     return out
 
 
 def layernorm_bf16(x, gamma, beta):
     rows, Cc = x.shape
     out = torch.empty((rows, Cc), device=x.device, dtype=torch.bfloat16)
-    check(lib().moca_layernorm_bf16(ctx(x.device.index), ptr(x), ptr(gamma), ptr(beta), rows, Cc, ptr(out), stream_ptr()))
+    with torch.cuda.device(x.device):
+        check(lib().moca_layernorm_bf16(ctx(x.device.index), ptr(x), ptr(gamma), ptr(beta), rows, Cc, ptr(out), stream_ptr()))
     return out
 
 
 def attention_bf16(q, k, v, batch, heads, Lq, Lk, Lk_valid=None, temporal_inner=0):
     """q [batch*Lq, heads*64], k/v [batch*Lk, heads*64] bf16 (row pitch = tensor stride(0))."""
     out = torch.empty((q.shape[0], heads * 64), device=q.device, dtype=torch.bfloat16)
-    check(lib().moca_attention_bf16(ctx(q.device.index), ptr(q), ptr(k), ptr(v), batch, heads, Lq, Lk,
-                                    Lk if Lk_valid is None else Lk_valid, q.stride(0), k.stride(0), ptr(out), out.stride(0),
-                                    int(temporal_inner), stream_ptr()))
+    with torch.cuda.device(q.device):
+        check(lib().moca_attention_bf16(ctx(q.device.index), ptr(q), ptr(k), ptr(v), batch, heads, Lq, Lk,
+                                        Lk if Lk_valid is None else Lk_valid, q.stride(0), k.stride(0), ptr(out), out.stride(0),
+                                        int(temporal_inner), stream_ptr()))
     return out

@@ -6,31 +6,44 @@ CrossAttention to xformers (lvdm/modules/attention.py:73-74).  Call after ``sys.
 
     import moca_video_b200 as mb; mb.patch_reference()
 
-Rebound:
-  lvdm.modules.networks.openaimodel3d.UNetModel.forward         -> UNet3D.forward (weights packed on first call)
-  lvdm.models.samplers.ddim.DDIMSampler.unet / fifo_onestep / ddim_step / p_sample_ddim / make_schedule
+Rebound (``REBOUND`` lists them; tests/test_patch.py checks each against the reference's own signature):
+  lvdm.modules.networks.openaimodel3d.UNetModel.forward          -> UNet3D.forward (weights packed on first call)
+  lvdm.models.samplers.ddim.DDIMSampler.make_schedule / unet / fifo_onestep / ddim_step / p_sample_ddim
   utils.freeinit_utils.freq_mix_3d / get_freq_filter
-  scripts.evaluation.funcs.prepare_latents / shift_latents / fifo_ddim_sampling
+  scripts.evaluation.funcs.prepare_latents / shift_latents / fifo_ddim_sampling (+ its imported FreeInit names)
+Not rebound: VAE decode / encode (``model.decode_first_stage_2DAE``) — the rebound ``fifo_ddim_sampling`` calls
+the reference's own decoder on every popped frame, exactly where the reference does (funcs.py:359-365).
 """
 import importlib
+import os
 
 import torch
 
 from . import fifo, ops
+from ._lib import MocaError
 from .sampler import DDIMSampler as _B200Sampler
 from .unet import UNet3D
 
+REBOUND = {
+    "lvdm.modules.networks.openaimodel3d": ["UNetModel.forward"],
+    "lvdm.models.samplers.ddim": ["DDIMSampler.make_schedule", "DDIMSampler.unet", "DDIMSampler.fifo_onestep", "DDIMSampler.ddim_step",
+                                  "DDIMSampler.p_sample_ddim"],
+    "utils.freeinit_utils": ["freq_mix_3d", "get_freq_filter"],
+    "scripts.evaluation.funcs": ["prepare_latents", "shift_latents", "fifo_ddim_sampling", "freq_mix_3d", "get_freq_filter"],
+}
 
-def _unet_forward(self, x, timesteps, context=None, features_adapter=None, fps=16, **kwargs):
-    """Replacement body of UNetModel.forward (openaimodel3d.py:534-578)."""
-    eng = getattr(self, "_moca_engine", None)
-    if eng is None:
-        mult = tuple(self.channel_mult) if hasattr(self, "channel_mult") else (1, 2, 4, 4)
-        eng = UNet3D(self.in_channels, self.out_channels, self.model_channels, tuple(self.attention_resolutions),
-                     self.num_res_blocks, mult, 64, _context_dim(self), device=x.device)
-        eng.load_state_dict(self.state_dict())
-        object.__setattr__(self, "_moca_engine", eng)
-    return eng.forward(x, timesteps, context=context, fps=fps)     # [b] or per-frame [b*t] timesteps (is_fifo, :535)
+# constructor options of UNetModel that select code the library implements; anything else must fail loudly (UNet3D checks)
+_UNET_FLAGS = ("use_linear", "temporal_conv", "temporal_attention", "temporal_selfatt_only", "use_relative_position",
+               "use_causal_attention", "addition_attention", "fps_cond", "image_cross_attention", "use_scale_shift_norm",
+               "resblock_updown", "conv_resample", "dims")
+
+
+def _head_channels(unet):
+    for m in unet.modules():
+        if m.__class__.__name__ == "SpatialTransformer":
+            a = m.transformer_blocks[0].attn1
+            return a.to_q.out_features // a.heads
+    return 64
 
 
 def _context_dim(unet):
@@ -38,6 +51,30 @@ def _context_dim(unet):
         if m.__class__.__name__ == "SpatialTransformer":
             return m.transformer_blocks[0].attn2.to_k.in_features
     return 1024
+
+
+def _init_attn_heads(unet):
+    ia = getattr(unet, "init_attn", None)
+    if ia is None:
+        return 8
+    for m in ia.modules():
+        if m.__class__.__name__ == "CrossAttention":
+            return m.heads
+    return 8
+
+
+def _unet_forward(self, x, timesteps, context=None, features_adapter=None, fps=16, ctx_len=None, **kwargs):
+    """Replacement body of UNetModel.forward (openaimodel3d.py:534-578).  ``ctx_len`` is the one addition: true context
+    lengths when the caller batches samples with different prompt lengths (the patched sampler's b=2 CFG launch)."""
+    eng = getattr(self, "_moca_engine", None)
+    if eng is None:
+        mult = tuple(self.channel_mult) if hasattr(self, "channel_mult") else (1, 2, 4, 4)
+        flags = {k: getattr(self, k) for k in _UNET_FLAGS if hasattr(self, k)}      # unsupported options raise in UNet3D
+        eng = UNet3D(self.in_channels, self.out_channels, self.model_channels, tuple(self.attention_resolutions),
+                     self.num_res_blocks, mult, _head_channels(self), _context_dim(self), _init_attn_heads(self), device=x.device, **flags)
+        eng.load_state_dict(self.state_dict())
+        object.__setattr__(self, "_moca_engine", eng)
+    return eng.forward(x, timesteps, context=context, features_adapter=features_adapter, fps=fps, ctx_len=ctx_len)
 
 
 def _get_freq_filter(shape, device, filter_type, n, d_s, d_t):
@@ -51,10 +88,37 @@ def _freq_mix_3d(x, noise, LPF):
     return y.squeeze(0)
 
 
+def _make_fifo_ddim_sampling(funcs_mod):
+    def fifo_ddim_sampling(args, model, conditioning, noise_shape, ddim_sampler, cfg_scale=1.0, output_dir=None, latents_dir=None,
+                           save_frames=False, conditioned_image=None, targets=None, gamma=0.5, use_self_attention=False,
+                           davis_data=None, anchor_frame=None, **kwargs):
+        """scripts/evaluation/funcs.py:243-371 with the latent loop in the library (windows sharded over the ranks of the
+        default process group when there is one); every popped latent frame goes through the reference's own VAE decoder
+        and ``tensor2image`` (funcs.py:359-365).  Returns the list of PIL frames like the reference."""
+        if davis_data is not None:
+            raise NotImplementedError("fifo_ddim_sampling: the DAVIS-video branch needs the VAE encoder in shift_latents (SURVEY N1)")
+        frames = []
+        fifo_dir = None
+        if getattr(args, "save_frames", False):                       # funcs.py:283-285
+            fifo_dir = os.path.join(output_dir, "fifo")
+            os.makedirs(fifo_dir, exist_ok=True)
+
+        def on_frame(i, z):
+            image = funcs_mod.tensor2image(model.decode_first_stage_2DAE(z))
+            if save_frames and fifo_dir is not None:
+                image.save(os.path.join(fifo_dir, f"{i}.png"))
+            frames.append(image)
+        fifo.fifo_ddim_sampling(args, model, conditioning, noise_shape, ddim_sampler, cfg_scale=cfg_scale, output_dir=output_dir,
+                                latents_dir=latents_dir, save_frames=save_frames, conditioned_image=conditioned_image,
+                                targets=targets, gamma=gamma, use_self_attention=use_self_attention, on_frame=on_frame, **kwargs)
+        return frames
+    return fifo_ddim_sampling
+
+
 def patch_reference():
     mods = {}
-    for name in ("lvdm.modules.networks.openaimodel3d", "lvdm.models.samplers.ddim", "utils.freeinit_utils",
-                 "scripts.evaluation.funcs"):
+    last = None
+    for name in REBOUND:
         try:
             mods[name] = importlib.import_module(name)
         except Exception as e:  # noqa: BLE001  (a caller may only use part of the surface)
@@ -68,9 +132,10 @@ def patch_reference():
     m = mods["lvdm.models.samplers.ddim"]
     if m is not None:
         S = m.DDIMSampler
-        for meth in ("make_schedule", "unet", "_eps_pair", "fifo_onestep", "ddim_step", "_step", "p_sample_ddim"):
+        for meth in ("make_schedule", "unet", "_eps_pair", "fifo_onestep", "ddim_step", "_step", "_step_sam", "p_sample_ddim"):
             setattr(S, meth, getattr(_B200Sampler, meth))
         S.parity_quirks = True
+        S.segment_fn = None
         S.noise_fn = staticmethod(lambda shape, device, generator=None: torch.randn(shape, device=device))
     m = mods["utils.freeinit_utils"]
     if m is not None:
@@ -80,6 +145,7 @@ def patch_reference():
     if m is not None:
         m.prepare_latents = fifo.prepare_latents
         m.shift_latents = fifo.shift_latents
+        m.fifo_ddim_sampling = _make_fifo_ddim_sampling(m)
         m.get_freq_filter = _get_freq_filter
         m.freq_mix_3d = _freq_mix_3d
     return {k: v is not None for k, v in mods.items()}

@@ -12,11 +12,15 @@ All tensor arithmetic runs in libmoca_b200.so.  Differences from the reference, 
     length, SURVEY Q11) when the model exposes ``apply_model_cfg``; the guidance combine happens inside the step kernel;
   * noise is drawn by the caller-visible ``noise_fn`` in the reference's order (one N(0,1) draw per frame, ddim.py:561),
     never inside a kernel;
-  * masks are an input (``davis_masks`` or ``masks=``): SAM-2 / Grounding-DINO mask *generation* is third-party and out
-    of scope (SURVEY §2.1 row 3); debug PNG dumps are dropped;
+  * masks are an input: ``davis_masks`` (DAVIS branch, ddim.py:565-590), or — SAM branch, ddim.py:591-606 — per-frame
+    ``sam_masks`` / a ``segment_fn(image_u8, target)`` callback standing in for Grounding-DINO + SAM-2 (third-party
+    networks without weights).  The glue around the segmenter (uint8 image, no-box fallback, IoU gate,
+    80 % coverage reset, gain-2 blend; ddim.py:739-943) runs in the library; debug PNG dumps are dropped;
   * reference quirks are reproduced by default and can be turned off: ``gamma`` never reaches ddim_step (Q1),
     the clobbered mask index (Q3).
 """
+import warnings
+
 import numpy as np
 import torch
 
@@ -29,9 +33,44 @@ def noise_like(shape, device, generator=None):
     return torch.randn(shape, device=device, generator=generator)
 
 
+def _merge_cfg_conditioning(x, t, c, uc):
+    """cond / uncond of classifier-free guidance as one batch of 2b samples: contexts concatenated along tokens
+    (DiffusionWrapper 'crossattn', ddpm3d.py:710-712), zero-padded to the longer one, true lengths returned.
+    None when the conditioning is not the {c_crossattn, fps} dict the driver builds (videocrafter_main.py:196-211)."""
+    if not (isinstance(c, dict) and isinstance(uc, dict)) or set(c) - {"c_crossattn", "fps"} or set(uc) - {"c_crossattn", "fps"}:
+        return None
+    if "c_crossattn" not in c or "c_crossattn" not in uc:
+        return None
+    cat = lambda v: torch.cat(list(v), dim=1) if isinstance(v, (list, tuple)) else v
+    cc, cu = cat(c["c_crossattn"]), cat(uc["c_crossattn"])
+    b = x.shape[0]
+    if cc.shape[0] != b or cu.shape[0] != b:
+        return None
+    Lc, Lu = cc.shape[1], cu.shape[1]
+    ctx = torch.zeros((2 * b, max(Lc, Lu), cc.shape[2]), device=cc.device, dtype=cc.dtype)
+    ctx[:b, :Lc] = cc
+    ctx[b:, :Lu] = cu
+    cond2 = {"c_crossattn": [ctx]}
+    if "fps" in c:
+        f = c["fps"]
+        cond2["fps"] = torch.cat([f.reshape(-1), f.reshape(-1)]) if isinstance(f, torch.Tensor) and f.numel() == b else f
+    if isinstance(t, torch.Tensor):
+        t2 = torch.cat([t, t])
+    else:
+        t2 = list(t) + list(t)
+    return torch.cat([x, x], dim=0), t2, cond2, [Lc] * b + [Lu] * b
+
+
 class DDIMSampler:
-    def __init__(self, model, schedule="linear", use_self_attention=True, parity_quirks=True, noise_fn=None, **kwargs):
+    segment_fn = None                               # class default so a patched reference sampler has the attribute too
+    _warned_no_segmenter = False
+
+    def __init__(self, model, schedule="linear", use_self_attention=True, parity_quirks=True, noise_fn=None, segment_fn=None,
+                 **kwargs):
+        """``segment_fn(image_u8[H,W,3] numpy, target: str) -> masks [N,H,W] (numpy / tensor) or None`` stands in for the
+        reference's Grounding-DINO + SAM-2 pair (ddim.py:764-806) in the SAM branch of ddim_step."""
         self.model = model
+        self.segment_fn = segment_fn
         self.ddpm_num_timesteps = model.num_timesteps
         self.schedule = schedule
         self.counter = 0
@@ -60,11 +99,20 @@ class DDIMSampler:
 
     # ---- UNet with classifier-free guidance -------------------------------------------------------------------
     def _eps_pair(self, x, c, t, unconditional_guidance_scale, unconditional_conditioning, **kwargs):
-        """Returns (e_cond, e_uncond or None): the two apply_model calls of ddim.py:368-370 / :298-299."""
+        """Returns (e_cond, e_uncond or None): the two apply_model calls of ddim.py:368-370 / :298-299, issued as ONE b=2
+        launch whenever the conditioning allows it."""
         if unconditional_conditioning is None or unconditional_guidance_scale == 1.0:
             return self.model.apply_model(x, t, c, **kwargs), None
         if hasattr(self.model, "apply_model_cfg"):
             return self.model.apply_model_cfg(x, t, c, unconditional_conditioning, **kwargs)
+        merged = _merge_cfg_conditioning(x, t, c, unconditional_conditioning)
+        if merged is not None:
+            # the reference's LatentDiffusion.apply_model -> DiffusionWrapper.forward passes extra kwargs through to
+            # UNetModel.forward (ddpm3d.py:512-527, 702-712), so the per-sample context length reaches the patched forward
+            x2, t2, cond2, lens = merged
+            e = self.model.apply_model(x2, t2, cond2, ctx_len=lens, **kwargs)
+            b = x.shape[0]
+            return e[:b], e[b:]
         return self.model.apply_model(x, t, c, **kwargs), self.model.apply_model(x, t, unconditional_conditioning, **kwargs)
 
     @torch.no_grad()
@@ -79,7 +127,7 @@ class DDIMSampler:
     @torch.no_grad()
     def fifo_onestep(self, cond, shape, latents=None, timesteps=None, indices=None, unconditional_guidance_scale=1.0,
                      unconditional_conditioning=None, cond_image=None, target=None, use_self_attention=False,
-                     davis_masks=None, noise=None, **kwargs):
+                     davis_masks=None, noise=None, sam_masks=None, **kwargs):
         """ddim.py:255-271.  ``gamma`` in kwargs is swallowed exactly like the reference does (it lands in the UNet's
         **kwargs) unless parity_quirks is off, in which case it is routed to ddim_step."""
         ts = [int(v) for v in np.asarray(timesteps).tolist()]
@@ -88,21 +136,71 @@ class DDIMSampler:
             gamma = float(kwargs["gamma"])
         kw = {k: v for k, v in kwargs.items() if k not in ("gamma", "clean_cond")}
         e_c, e_u = self._eps_pair(latents, cond, ts, unconditional_guidance_scale, unconditional_conditioning, **kw)
-        return self._step(latents, e_c, e_u, unconditional_guidance_scale, indices, cond_image, ts, gamma, davis_masks, noise)
+        return self._step(latents, e_c, e_u, unconditional_guidance_scale, indices, cond_image, ts, gamma, davis_masks, noise,
+                          target, sam_masks)
 
     @torch.no_grad()
     def ddim_step(self, sample, noise_pred, indices, cond_image, target, ts, gamma=0.5, use_self_attention=False,
-                  davis_masks=None, noise=None):
+                  davis_masks=None, noise=None, sam_masks=None):
         """ddim.py:377-649 on an already guidance-combined ``noise_pred``."""
         ts = [int(v) for v in (ts.tolist() if isinstance(ts, torch.Tensor) else np.asarray(ts).tolist())]
-        return self._step(sample, noise_pred, None, 1.0, indices, cond_image, ts, gamma, davis_masks, noise)
+        return self._step(sample, noise_pred, None, 1.0, indices, cond_image, ts, gamma, davis_masks, noise, target, sam_masks)
 
-    def _step(self, x, e_c, e_u, cfg, indices, cond_image, ts, gamma, masks, noise):
+    def _step_sam(self, x, e_c, e_u, cfg, coef, cond_image, ts, gamma, noise, target, sam_masks):
+        """SAM branch (ddim.py:591-606): frames with t <= 300 are blended with the masks of the segmenter.  The masks of a
+        frame depend on that frame's own momentum-corrected prediction, so the step runs in two kernels: K13 with gamma 0
+        (x_prev and p'), then moca_sam_blend once the per-frame mask lists are known."""
+        B, C, F, H, W = x.shape
+        if B != 1:
+            raise ops._lib.MocaError("ddim_step (SAM branch): the reference squeezes the batch dimension (ddim.py:747); b must be 1")
+        x_prev, p_corr = ops.cfg_ddim_step(x, e_c, e_u, noise, cfg, coef, ts, gamma=0.0)
+        if cond_image.shape[1] == 3:                                     # RGB -> RGBA with ones (ddim.py:838-843)
+            cond_image = torch.cat([cond_image, torch.ones_like(cond_image[:, :1])], dim=1)
+        tgt = target if (target is None or target.endswith(".")) else target + "."      # ddim.py:741-742
+        per_frame, pre = [None] * F, None
+        for i in range(F):
+            if ts[i] > 300:
+                continue
+            if sam_masks is not None:
+                new = sam_masks[i]
+            elif self.segment_fn is not None:
+                new = self.segment_fn(ops.latent_to_u8(p_corr, i).cpu().numpy(), tgt)
+            else:
+                if not DDIMSampler._warned_no_segmenter:
+                    DDIMSampler._warned_no_segmenter = True
+                    warnings.warn("ddim_step: cond_image given without davis_masks, sam_masks or a segment_fn; frames with t <= 300 "
+                                  "are left unblended, which is what the reference does when Grounding-DINO finds no box "
+                                  "(ddim.py:787-790).  Pass DDIMSampler(segment_fn=...) or sam_masks= to blend.")
+                new = None
+            if new is not None:
+                new = torch.as_tensor(np.asarray(new) if not isinstance(new, torch.Tensor) else new, dtype=torch.float32,
+                                      device=x.device).reshape(-1, H, W)
+            if new is None or new.shape[0] == 0:
+                cur = pre                                                # no box: previous masks (ddim.py:787-793)
+            elif pre is not None and ops.mask_iou(new, pre) < 0.5:
+                cur = pre                                                # ddim.py:809-813
+            else:
+                cur = new
+            per_frame[i], pre = cur, cur
+        nmax = max([m.shape[0] for m in per_frame if m is not None], default=0)
+        masks = None
+        if nmax > 0:
+            masks = torch.zeros((F, nmax, H, W), device=x.device, dtype=torch.float32)
+            for i, m in enumerate(per_frame):
+                if m is not None:
+                    masks[i, :m.shape[0]] = m
+        n_masks = [0 if m is None else int(m.shape[0]) for m in per_frame]
+        pred = ops.sam_blend(p_corr, noise, coef[2], cond_image, masks, n_masks, gamma, 2.0, 0.8)
+        return x_prev, pred
+
+    def _step(self, x, e_c, e_u, cfg, indices, cond_image, ts, gamma, masks, noise, target=None, sam_masks=None):
         B, C, F, H, W = x.shape
         if noise is None:
             # one draw per frame in frame order, like `noise_like(pred_x0.shape)` inside the frame loop (ddim.py:561)
             noise = torch.cat([self.noise_fn((B, C, 1, H, W), x.device) for _ in range(F)], dim=2)
         coef = self.tables.coef(indices)
+        if masks is None and cond_image is not None and any(t <= 300 for t in ts):
+            return self._step_sam(x, e_c, e_u, cfg, coef, cond_image, ts, gamma, noise, target, sam_masks)
         mask_idx = None
         if masks is not None:
             Fm = masks.shape[2]
@@ -111,7 +209,7 @@ class DDIMSampler:
             if cond_image is not None and cond_image.shape[1] == 3:      # RGB -> RGBA with ones (ddim.py:574-577)
                 cond_image = torch.cat([cond_image, torch.ones_like(cond_image[:, :1])], dim=1)
         return ops.cfg_ddim_step(x, e_c, e_u, noise, cfg, coef, ts, masks, mask_idx, cond_image if masks is not None else None,
-                                 gamma, 1.5, 1.0, 300, 2.0)
+                                 gamma, 1.5, 1.0, 300, 0.0)      # DAVIS branch: gains 1.5 / 1.0, no coverage test (ddim.py:584-590)
 
     # ---- plain DDIM -------------------------------------------------------------------------------------------
     @torch.no_grad()

@@ -62,15 +62,22 @@ class UNet3D:
         if strict and (missing or unexpected):
             raise _lib.MocaError(f"load_state_dict: missing {missing[:4]} unexpected {unexpected[:4]}")
         with torch.cuda.device(self.device):
+            names, tensors = [], []
             for k, shp in self.shapes.items():
                 if k not in sd:
                     continue
                 t = sd[k]
                 if tuple(t.shape) != tuple(shp):
                     raise _lib.MocaError(f"load_state_dict: {k} has shape {tuple(t.shape)}, expected {tuple(shp)}")
-                t = t.detach().to(device=self.device, dtype=torch.float32).contiguous()
-                check(lib().moca_unet_load(self._h, k.encode(), ptr(t), t.numel(), stream_ptr()))
-                torch.cuda.current_stream().synchronize()      # t may be a temporary: keep it alive until packed
+                names.append(k.encode())
+                tensors.append(t.detach().to(device=self.device, dtype=torch.float32).contiguous())
+            # one packing launch for the whole state_dict (the fp32 copies stay alive until the call returns)
+            n = len(names)
+            c_names = (C.c_char_p * n)(*names)
+            c_ptrs = (C.c_void_p * n)(*[t.data_ptr() for t in tensors])
+            c_numel = (C.c_int64 * n)(*[t.numel() for t in tensors])
+            check(lib().moca_unet_load_many(self._h, n, c_names, c_ptrs, c_numel, stream_ptr()))
+            del tensors
             check(lib().moca_unet_finalize(self._h))
         self._loaded = True
         return self

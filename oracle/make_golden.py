@@ -97,6 +97,135 @@ def gen_ddim_step():
     np.savez_compressed(os.path.join(GOLD, "step_ddim.npz"), **cases)
 
 
+def gen_ddim_step_sam():
+    """ddim_step WITHOUT DAVIS masks (ddim.py:591-606): frames with t <= 300 run the unmodified
+    ``_apply_segmentation`` (:739-903) — uint8 conversion, no-box fallback, IoU gate, >80 % coverage reset, blend with
+    gain 2 — with Grounding-DINO / SAM-2 replaced by scripted stubs (third-party nets without weights; their outputs are
+    the stored ``seg_*`` arrays).  As shipped, the blend's ``torch.where`` broadcasts [1,C,H,W] against [1,C,1,H,W] and
+    returns C identical copies of the frame along dim 2; the generator checks the copies are identical and stores one."""
+    refimport.setup()
+    import lvdm.models.samplers.ddim as D
+
+    class T(torch.Tensor):                       # ``v.to("cuda")`` of the processor outputs (ddim.py:770-775) on a CPU box
+        def to(self, *a, **k):
+            return self
+
+    cases = {}
+    for name, (H, W, win) in {"a": (12, 16, 1), "b": (10, 12, 2)}.items():
+        rng = np.random.default_rng(300 + ord(name))
+        shape = (1, 4, 16, H, W)
+        x = rng.standard_normal(shape).astype(np.float32)
+        if name == "b":
+            x *= 0.05                              # small latents: floor(max) <= 1 for some frames -> the x255 branch
+        e = rng.standard_normal(shape).astype(np.float32) * (0.05 if name == "b" else 1.0)
+        cond = rng.random((1, 4, 1, H, W)).astype(np.float32)
+        m = refimport.ShimModel(None)
+        s = refimport.make_sampler(m, 64, 1.0)
+        ts_q = np.concatenate([np.full((8,), s.ddim_timesteps[0]), s.ddim_timesteps])
+        idx_q = np.concatenate([np.full((8,), 0), np.arange(64)])
+        t = ts_q[8 * win:8 * win + 16]; idx = idx_q[8 * win:8 * win + 16]
+
+        def blob(frac):
+            return (rng.random((H, W)) < frac).astype(np.float32)
+
+        def grow(mk, frac):                                                   # superset of mk covering ~frac of the frame
+            return np.maximum(mk, blob(max(0.0, (frac - mk.mean()) / max(1e-6, 1.0 - mk.mean()))))
+
+        def jitter(mk):                                                       # a few flipped pixels: IoU stays high
+            out = mk.copy(); out[0, :2] = 1.0 - out[0, :2]; return out
+        n1, big, n2 = blob(0.3), blob(0.7), blob(0.2)
+        if name == "a":
+            base = np.stack([n1, big, n2])
+            k4 = np.stack([jitter(n1), grow(big, 0.86), jitter(n2)])
+            script = [None,                                                   # no box, no previous masks: frame untouched
+                      base,                                                   # three masks, all below 80 % coverage
+                      np.stack([blob(0.3), blob(0.3), blob(0.3)]),            # unrelated: mean IoU < 0.5 -> previous masks kept
+                      None,                                                   # no box -> previous masks
+                      k4,                                                     # accepted; middle mask > 80 %: RESET, then the last mask
+                      np.stack([jitter(m_) for m_ in k4]),                    # accepted (IoU with call 4), reset again
+                      jitter(k4[0])[None],                                    # fewer masks than before: zip() compares the first pair only
+                      np.stack([jitter(k4[0]), blob(0.5)])]                   # more masks than before
+        else:
+            huge = blob(0.9)
+            script = [huge[None],                                             # only an over-covering mask: frame untouched
+                      jitter(huge)[None],
+                      None,
+                      np.stack([np.minimum(huge, blob(0.85))]),               # subset at ~76 %: accepted and blended
+                      np.stack([blob(0.1)]),                                  # rejected by the IoU gate
+                      np.stack([np.minimum(huge, blob(0.85)), blob(0.3)])]
+        while len(script) < 16:
+            script.append(np.stack([blob(0.3)]) if len(script) % 2 else None)
+        log = {"images": [], "calls": 0, "dims": []}
+
+        class Proc:
+            def __call__(self, images=None, text=None, return_tensors=None):
+                return {"input_ids": torch.zeros((1, 1), dtype=torch.long).as_subclass(T)}
+
+            def post_process_grounded_object_detection(self, outputs, ids, box_threshold=None, text_threshold=None, target_sizes=None):
+                k = log["calls"]
+                nb = 0 if script[k] is None else len(script[k])
+                return [{"boxes": torch.zeros((nb, 4))}]
+
+        class Sam:
+            def set_image(self, img):
+                log["images"].append(np.array(img))
+
+            def predict(self, point_coords=None, point_labels=None, box=None, multimask_output=False):
+                return script[log["calls"]].copy(), None, None
+
+        s.processor = Proc(); s.sam2_predictor = Sam(); s.grounding_model = lambda **kw: None
+        orig_apply = s.apply_cond_img
+
+        def apply_rec(pred_x0, *a, **k):
+            out, masks = orig_apply(pred_x0, *a, **k)
+            log["calls"] += 1
+            log["dims"].append(int(out.shape[2]))
+            return out, masks
+        s.apply_cond_img = apply_rec
+        draws = []
+        orig = D.noise_like
+
+        def rec(shape_, device, repeat=False):
+            n = orig(shape_, device, repeat); draws.append(n.clone()); return n
+        D.noise_like = rec
+        torch.manual_seed(17)
+        cwd = os.getcwd()
+        import warnings
+        with tempfile.TemporaryDirectory() as td, warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            os.chdir(td)
+            try:
+                xp, p0 = s.ddim_step(torch.from_numpy(x), torch.from_numpy(e), idx, torch.from_numpy(cond), "cat",
+                                     torch.from_numpy(t).long(), use_self_attention=False, davis_masks=None)
+            finally:
+                os.chdir(cwd); D.noise_like = orig
+        n_seg = int((t <= 300).sum())
+        assert log["calls"] == n_seg and len(log["images"]) == n_seg, (log["calls"], n_seg)
+        # undo the replicated frames (see docstring)
+        frames, pos, k = [], 0, 0
+        p0 = _np(p0)
+        for i in range(16):
+            d = 1
+            if t[i] <= 300:
+                d = log["dims"][k]; k += 1
+            blk = p0[:, :, pos:pos + d]
+            for j in range(1, d):
+                assert np.array_equal(blk[:, :, j], blk[:, :, 0])
+            frames.append(blk[:, :, :1]); pos += d
+        assert pos == p0.shape[2]
+        print(f"ddim_step_sam[{name}]: {n_seg} segmented frames, replicated dims {log['dims']}")
+        nmax = max(len(m_) for m_ in script[:n_seg] if m_ is not None)
+        seg = np.zeros((n_seg, nmax, H, W), np.float32); seg_n = np.full((n_seg,), -1, np.int32)
+        for k in range(n_seg):
+            if script[k] is not None:
+                seg_n[k] = len(script[k]); seg[k, :len(script[k])] = script[k]
+        cases.update({f"{name}_x": x, f"{name}_e": e, f"{name}_cond": cond, f"{name}_t": t, f"{name}_idx": idx,
+                      f"{name}_noise": torch.cat(draws, dim=2).numpy(), f"{name}_x_prev": _np(xp),
+                      f"{name}_pred_x0": np.concatenate(frames, axis=2), f"{name}_seg": seg, f"{name}_seg_n": seg_n,
+                      f"{name}_images": np.stack(log["images"])})
+    np.savez_compressed(os.path.join(GOLD, "step_ddim_sam.npz"), **cases)
+
+
 def gen_p_sample():
     import lvdm.models.samplers.ddim as D
     rng = np.random.default_rng(5)
@@ -291,7 +420,7 @@ def gen_unet_full():
 
 if __name__ == "__main__":
     os.makedirs(GOLD, exist_ok=True)
-    which = sys.argv[1:] or ["tables", "ddim_step", "p_sample", "queue", "unet_small", "unet_small64", "unet_full"]
+    which = sys.argv[1:] or ["tables", "ddim_step", "ddim_step_sam", "p_sample", "queue", "unet_small", "unet_small64", "unet_full"]
     for w in which:
         print("==", w)
         globals()["gen_" + w]()

@@ -98,14 +98,15 @@ def cfg_combine(e_c, e_u, scale):
 
 
 def moca_ddim_step(x, e, noise, coef, ts, mask=None, mask_idx=None, cond_img=None, gamma=0.5,
-                   enh_lo=1.5, enh_hi=1.0, t_thresh=300, cover_max=2.0, sqrt=np.sqrt):
+                   enh_lo=1.5, enh_hi=1.0, t_thresh=300, cover_max=0.0, sqrt=np.sqrt):
     """DDIMSampler.ddim_step, ddim.py:377-649 with SURVEY Q1-Q5 resolved (Appendix B).
 
     x, e, noise: [B,C,F,H,W] float32 (``noise`` = the N(0,1) draws of ddim.py:561, frame order).
     coef: float32 [4,F] (A, A_prev, sigma, sqrt(1-A));  ts: int [F].
     mask: [B,1,Fm,H,W] or None; mask_idx[f] = mask frame used by frame f (-1: no blend).
     cond_img: [B,C,1,H,W].  enh_hi == 0 disables the blend for t > t_thresh (SAM branch :592);
-    cover_max: skip masks whose sum exceeds cover_max*numel (ddim.py:826-828; DAVIS branch: no limit).
+    cover_max: skip masks whose sum exceeds cover_max*numel; <= 0 (default) = no coverage test, which is what the DAVIS
+    branch does (ddim.py:587); the SAM branch's 80 % rule is ``sam_blend_frame``.
     sqrt: scalar float32 square root.  Default = IEEE correctly rounded (numpy; CUDA ``sqrtf`` is the same,
     and the reference runs on CUDA).  torch's *CPU* sqrt is 1 ulp off for some inputs, so the test that
     compares with the CPU-generated goldens passes ``torch_cpu_sqrt`` to get bit equality.
@@ -136,11 +137,92 @@ def moca_ddim_step(x, e, noise, coef, ts, mask=None, mask_idx=None, cond_img=Non
             k = enh_lo if ts[i] <= t_thresh else enh_hi                  # :584 / :592,:845
             mk = mask[:, :, mask_idx[i]].astype(F32)                     # [B,1,H,W]
             s = float(mk.astype(np.float64).sum())
-            if k != 0 and s != 0 and s <= cover_max * mk.size:           # :587 / :826
+            if k != 0 and s != 0 and (cover_max <= 0 or s <= cover_max * mk.size):     # :587
                 ci = cond_img[:, :, 0].astype(F32) * F32(k)
                 p = np.where(mk > 0.5, ci, p)                            # :588-590
         pred[:, :, i] = F32(1 - gamma) * p + F32(gamma) * n              # :609
     return x_prev, pred
+
+
+# --------------------------------------------------------------------------------------------
+# SAM branch of ddim_step (no DAVIS masks): segmentation glue + blend
+# --------------------------------------------------------------------------------------------
+def latent_frame_to_u8(frame):
+    """DDIMSampler._apply_segmentation, ddim.py:745-761: the [C,H,W] x0 prediction of one frame -> the uint8 RGB image
+    handed to Grounding-DINO / SAM-2.  First three channels (a single channel is repeated); values are scaled by 255
+    when floor(max) <= 1, else taken as they are; ``astype(np.uint8)`` of a float truncates toward zero and wraps
+    modulo 256 (what numpy does on x86-64 for values inside the int32 range; the golden pins it)."""
+    f = np.transpose(np.asarray(frame, F32), (1, 2, 0))
+    if f.shape[-1] != 3:
+        f = np.repeat(f, 3, axis=-1) if f.shape[-1] == 1 else f[:, :, :3]
+    if np.floor(f.max()) <= 1.0:
+        f = f * F32(255)
+    return (np.trunc(f).astype(np.int64) & 255).astype(np.uint8)
+
+
+def mask_iou(m1, m2):
+    """DDIMSampler.calculate_iou, ddim.py:905-943: mean IoU over zip(masks1, masks2) of the masks binarised at 0.5
+    (an empty pair list gives nan, which never triggers the ``iou < 0.5`` fallback)."""
+    ious = []
+    for a, b in zip(np.asarray(m1) > 0.5, np.asarray(m2) > 0.5):
+        inter = F32(np.logical_and(a, b).sum())
+        union = F32(np.logical_or(a, b).sum())
+        ious.append(F32(1.0) if union == 0 else inter / union)
+    return float(np.mean(np.asarray(ious, F32), dtype=F32)) if ious else float("nan")
+
+
+def sam_gate_masks(new_masks, pre_masks):
+    """ddim.py:787-813: masks to blend with for this frame.  ``new_masks`` None / empty = the detector found no box:
+    fall back to the previous frame's masks (None: no blend at all); otherwise the new masks unless their mean IoU
+    with the previous ones is below 0.5."""
+    if new_masks is None or len(new_masks) == 0:
+        return pre_masks
+    if pre_masks is not None and mask_iou(new_masks, pre_masks) < 0.5:
+        return pre_masks
+    return np.asarray(new_masks, F32)
+
+
+def sam_blend_frame(p, cond_img, masks, gain=2.0, cover_max=0.8):
+    """ddim.py:818-901 for one frame.  p [B,C,H,W]; cond_img [B,C,H,W]; masks [N,H,W].  Masks are applied in order;
+    a mask covering more than ``cover_max`` of the frame RESETS the result to the unblended prediction (:826-828) and
+    is otherwise skipped.  (As shipped the reference's ``torch.where`` broadcasts [1,C,H,W] against [1,C,1,H,W] and
+    returns C identical copies along dim 2; this restatement returns one of them, SURVEY Q2: every caller drops it.)"""
+    out = p
+    for mk in np.asarray(masks, F32):
+        if float(mk.astype(np.float64).sum()) > cover_max * mk.size:
+            out = p
+            continue
+        out = np.where(mk[None, None] > 0.5, cond_img.astype(F32) * F32(gain), out)
+    return out.astype(F32)
+
+
+def moca_ddim_step_sam(x, e, noise, coef, ts, cond_img, segment_fn, gamma=0.5, t_thresh=300, sqrt=np.sqrt):
+    """DDIMSampler.ddim_step without DAVIS masks (ddim.py:377-430, 557-562, 591-609): frames with t <= 300 go through
+    apply_cond_img -> _apply_segmentation (:739-903).  ``segment_fn(frame_index, image_u8[H,W,3])`` stands in for
+    Grounding-DINO + SAM-2 and returns masks [N,H,W] or None (no box).  Returns x_prev, pred_x0, the per-frame mask
+    lists actually blended and the uint8 images shown to the segmenter."""
+    x = x.astype(F32); e = e.astype(F32); noise = noise.astype(F32)
+    B, C, Fr, H, W = x.shape
+    # momentum-corrected predictions and x_prev are what moca_ddim_step computes without masks (gamma = 0 returns p')
+    x_prev, p_corr = moca_ddim_step(x, e, noise, coef, ts, gamma=0.0, sqrt=sqrt)
+    pred = np.empty_like(x)
+    pre = None
+    used, images = [], []
+    for i in range(Fr):
+        p = p_corr[:, :, i]
+        if ts[i] <= t_thresh:
+            img = latent_frame_to_u8(p[0])
+            images.append(img)
+            masks = sam_gate_masks(segment_fn(i, img), pre)
+            if masks is not None:
+                p = sam_blend_frame(p, cond_img[:, :, 0], masks)
+            pre = masks
+            used.append(masks)
+        else:
+            used.append(None)
+        n = F32(coef[2, i]) * noise[:, :, i]
+        pred[:, :, i] = F32(1 - gamma) * p + F32(gamma) * n              # :609
+    return x_prev, pred, used, images
 
 
 def torch_cpu_sqrt(v):

@@ -27,13 +27,25 @@ def _rel(a, b):
     return float(np.linalg.norm(a - b) / (np.linalg.norm(b) + 1e-30))
 
 
-@pytest.mark.parametrize("name", ["a", "b", "c"])
+def _step_inputs(g, name):
+    if name == "d":          # BASELINE size [1,4,16,40,64]: the golden stores outputs only, inputs are re-drawn from its seeds
+        rng = np.random.default_rng(100 + ord("d"))
+        shape = (1, 4, 16, 40, 64)
+        x, e_c, e_u = (rng.standard_normal(shape).astype(np.float32) for _ in range(3))
+        torch.manual_seed(int(g["d_noise_seed"]))
+        noise = torch.cat([torch.randn((1, 4, 1, 40, 64)) for _ in range(16)], dim=2).numpy()
+        return x, e_c, e_u, noise
+    return tuple(g[f"{name}_{k}"] for k in ("x", "e_c", "e_u", "noise"))
+
+
+@pytest.mark.parametrize("name", ["a", "b", "c", "d"])
 def test_cfg_ddim_step_bitexact_vs_oracle_and_golden(name):
+    """Cases a-c: reduced sizes; d: the full-size window the unmodified reference ran at [1,4,16,40,64] (DAVIS masks, cfg 12)."""
     from moca_video_b200 import ops
     from oracle import step_ref as R
     g = np.load(os.path.join(GOLDEN, "step_ddim.npz"))
     tables = R.make_tables(64, 1.0)
-    x, e_c, e_u, noise = (g[f"{name}_{k}"] for k in ("x", "e_c", "e_u", "noise"))
+    x, e_c, e_u, noise = _step_inputs(g, name)
     mask, cond, t, idx = g[f"{name}_mask"], g[f"{name}_cond"], g[f"{name}_t"], g[f"{name}_idx"]
     with_mask = bool(int(g[f"{name}_with_mask"]))
     coef = R.coef_rows(tables, idx)
@@ -77,6 +89,72 @@ def test_cfg_ddim_step_full_size_properties():
     d = ops.cfg_ddim_step(_t(x), _t(e_c), None, _t(nz), 12.0, coef, t)
     e = ops.cfg_ddim_step(_t(x), _t(e_c), _t(e_u), _t(nz), 1.0, coef, t)
     assert torch.equal(d[0], e[0]) and torch.equal(d[1], e[1])
+
+
+def _table_model():
+    import types
+    from moca_video_b200.schedule import cumprod_alphas_f32
+    return types.SimpleNamespace(num_timesteps=1000, alphas_cumprod=torch.tensor(cumprod_alphas_f32()), use_scale=False)
+
+
+@pytest.mark.parametrize("name", ["a", "b"])
+def test_ddim_step_sam_branch_vs_oracle_and_golden(name):
+    """ddim_step without DAVIS masks (ddim.py:591-606 -> _apply_segmentation :739-903) through the sampler mirror:
+    scripted segmenter outputs, the library does the uint8 image, the no-box fallback, the IoU gate, the > 80 % coverage
+    reset and the gain-2 blend.  Golden = the unmodified reference with Grounding-DINO / SAM-2 stubbed by the same script."""
+    from moca_video_b200.sampler import DDIMSampler
+    from oracle import step_ref as R
+    g = np.load(os.path.join(GOLDEN, "step_ddim_sam.npz"))
+    seg, seg_n = g[name + "_seg"], g[name + "_seg_n"]
+    seen = []
+
+    def segment_fn(img, target):
+        assert target == "cat."                                           # ddim.py:741-742
+        k = len(seen); seen.append(img)
+        return None if seg_n[k] < 0 else seg[k, :seg_n[k]]
+    s = DDIMSampler(_table_model(), segment_fn=segment_fn)
+    s.make_schedule(64, ddim_eta=1.0, verbose=False)
+    x, e, noise, cond, t, idx = (g[f"{name}_{k}"] for k in ("x", "e", "noise", "cond", "t", "idx"))
+    xp, p0 = s.ddim_step(_t(x), _t(e), idx, _t(cond), "cat", t, noise=_t(noise))
+    assert np.array_equal(np.stack(seen), g[name + "_images"])            # the images the segmenter is shown, bit for bit
+    k = [0]
+
+    def oracle_fn(i, img):
+        j = k[0]; k[0] += 1
+        return None if seg_n[j] < 0 else seg[j, :seg_n[j]]
+    xo, po, used, _ = R.moca_ddim_step_sam(x, e, noise, R.coef_rows(R.make_tables(64, 1.0), idx), t, cond, oracle_fn, 0.5)
+    assert np.array_equal(xp.cpu().numpy(), xo) and np.array_equal(p0.cpu().numpy(), po)
+    assert _rel(xp.cpu().numpy(), g[name + "_x_prev"]) < 1e-5 and _rel(p0.cpu().numpy(), g[name + "_pred_x0"]) < 1e-5
+    # precomputed per-frame masks (sam_masks=) take the same route; no segmenter and no masks warns and leaves pred_x0 unblended
+    j = iter(range(len(seg_n)))
+    pre = [None if tt > 300 else (lambda q: None if seg_n[q] < 0 else seg[q, :seg_n[q]])(next(j)) for tt in t]
+    s2 = DDIMSampler(_table_model()); s2.make_schedule(64, ddim_eta=1.0, verbose=False)
+    xp2, p02 = s2.ddim_step(_t(x), _t(e), idx, _t(cond), "cat", t, noise=_t(noise), sam_masks=pre)
+    assert torch.equal(xp2, xp) and torch.equal(p02, p0)
+    DDIMSampler._warned_no_segmenter = False
+    with pytest.warns(UserWarning, match="segment_fn"):
+        xp3, p03 = s2.ddim_step(_t(x), _t(e), idx, _t(cond), "cat", t, noise=_t(noise))
+    plain = s2.ddim_step(_t(x), _t(e), idx, None, "cat", t, noise=_t(noise))
+    assert torch.equal(xp3, plain[0]) and torch.equal(p03, plain[1]) and torch.equal(xp3, xp)
+
+
+def test_sam_glue_primitives():
+    """moca_latent_to_u8 / moca_mask_iou edge cases: x255 branch, wrap-around of out-of-range values, empty masks (IoU 1),
+    unequal list lengths (zip), no pairs (nan)."""
+    from moca_video_b200 import ops
+    from oracle import step_ref as R
+    rng = np.random.default_rng(5)
+    for scale in (0.2, 3.0, 400.0):
+        p = (rng.standard_normal((1, 4, 3, 10, 12)) * scale).astype(np.float32)
+        for f in range(3):
+            assert np.array_equal(ops.latent_to_u8(_t(p), f).cpu().numpy(), R.latent_frame_to_u8(p[0, :, f]))
+    p1 = rng.random((1, 1, 2, 6, 8)).astype(np.float32)                    # one channel is repeated (ddim.py:752-753)
+    assert np.array_equal(ops.latent_to_u8(_t(p1), 1).cpu().numpy(), R.latent_frame_to_u8(p1[0, :, 1]))
+    a = (rng.random((3, 10, 12)) < 0.4).astype(np.float32); b = (rng.random((2, 10, 12)) < 0.4).astype(np.float32)
+    b[1] = 0.0; a[1] = 0.0
+    assert abs(ops.mask_iou(_t(a), _t(b)) - R.mask_iou(a, b)) < 1e-6
+    assert ops.mask_iou(_t(a[1:2]), _t(b[1:2])) == 1.0                     # both empty: IoU 1 (ddim.py:932-934)
+    assert np.isnan(ops.mask_iou(_t(a[:0]), _t(b)))
 
 
 def test_cfg_ddim_step_errors():

@@ -150,6 +150,69 @@ def test_fifo_onestep_vs_oracle(small):
         assert rel(xp.cpu(), torch.from_numpy(xo)) < TOL and rel(p0.cpu(), torch.from_numpy(po)) < 6e-2
 
 
+def _dump(name, rec):
+    """Parity numbers of the full-size tests, for DESIGN.md / BASELINE.md (gpurun_out/ travels back from the GPU box)."""
+    import json
+    d = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    if os.path.isdir(d):
+        with open(os.path.join(d, name), "w") as f:
+            json.dump(rec, f, indent=1)
+
+
+def test_fifo_onestep_full_size_vs_oracle(full):
+    """fifo_onestep at the BASELINE size: latent [1,4,16,40,64], conditioned prompt (ctx 154) + empty prompt (ctx 77) as one b=2
+    launch, cfg 12, DAVIS masks + cond image, FIFO windows 0 / 3 / 7, against oracle/unet_ref.py (fp32, TF32 off) +
+    oracle/step_ref.py.  Also measures what torch's own bf16 autocast of the same modules gives on the same inputs: the
+    x0 prediction multiplies the bf16 error of e_c - e_u by the guidance scale."""
+    from moca_video_b200.model import LatentDiffusionB200
+    from moca_video_b200.sampler import DDIMSampler
+    from moca_video_b200.schedule import fifo_queue_tables
+    from oracle import step_ref as R
+    from oracle.unet_ref import unet_forward
+    cfg, sd, net = full
+    sampler = DDIMSampler(LatentDiffusionB200(net, fps=10))
+    sampler.make_schedule(64, ddim_eta=1.0, verbose=False)
+    g = torch.Generator(device=DEV).manual_seed(13)
+    shape = (1, 4, 16, 40, 64)
+    x = torch.randn(shape, device=DEV, generator=g)
+    c1 = torch.randn((1, 77, 1024), device=DEV, generator=g); c2 = torch.randn((1, 77, 1024), device=DEV, generator=g)
+    u = torch.randn((1, 77, 1024), device=DEV, generator=g)
+    noise = torch.randn(shape, device=DEV, generator=g)
+    mask = (torch.rand((1, 1, 16, 40, 64), device=DEV, generator=g) < 0.3).float()
+    cimg = torch.rand((1, 4, 1, 40, 64), device=DEV, generator=g)
+    ts_q, idx_q = fifo_queue_tables(64, 16, True)
+    tables = R.make_tables(64, 1.0)
+    cc = torch.cat([c1, c2], dim=1)
+    rec = {}
+    for win in (0, 3, 7):
+        t, idx = ts_q[8 * win:8 * win + 16], idx_q[8 * win:8 * win + 16]
+        xp, p0 = sampler.fifo_onestep(cond={"c_crossattn": [c1, c2], "fps": 10}, shape=shape, latents=x, timesteps=t, indices=idx,
+                                      unconditional_guidance_scale=12.0, unconditional_conditioning={"c_crossattn": [u], "fps": 10},
+                                      cond_image=cimg, target="cat", gamma=0.9, davis_masks=mask, noise=noise, clean_cond=True)
+        tt = torch.from_numpy(np.asarray(t)).to(DEV)
+        coef, mi = R.coef_rows(tables, idx), R.parity_mask_index(16, 40)
+
+        def step(e_c, e_u):
+            e = R.cfg_combine(e_c.float().cpu().numpy(), e_u.float().cpu().numpy(), 12.0)
+            return R.moca_ddim_step(x.cpu().numpy(), e, noise.cpu().numpy(), coef, t, mask.cpu().numpy(), mi, cimg.cpu().numpy(), 0.5)
+        ec, eu = unet_forward(sd, cfg, x, tt, cc, fps=10), unet_forward(sd, cfg, x, tt, u, fps=10)
+        xo, po = step(ec, eu)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            ecb, eub = unet_forward(sd, cfg, x, tt, cc, fps=10), unet_forward(sd, cfg, x, tt, u, fps=10)
+        xb, pb = step(ecb, eub)
+        e_mine = net(torch.cat([x, x]), list(t) + list(t), torch.cat([cc, torch.cat([u, torch.zeros_like(u)], 1)]), fps=10, ctx_len=[154, 77])
+        r = dict(x_prev=rel(xp.cpu(), torch.from_numpy(xo)), pred_x0=rel(p0.cpu(), torch.from_numpy(po)),
+                 e_c=rel(e_mine[0:1], ec), e_u=rel(e_mine[1:2], eu), e_diff=rel(e_mine[0:1] - e_mine[1:2], ec - eu),
+                 torch_bf16_x_prev=rel(torch.from_numpy(xb), torch.from_numpy(xo)), torch_bf16_pred_x0=rel(torch.from_numpy(pb), torch.from_numpy(po)),
+                 torch_bf16_e_c=rel(ecb.float(), ec), torch_bf16_e_diff=rel((ecb.float() - eub.float()), ec - eu))
+        rec[f"window{win}"] = r
+        print(f"fifo_onestep full size, window {win}: " + " ".join(f"{k}={v:.3e}" for k, v in r.items()))
+    _dump("parity_fifo_onestep_full.json", rec)
+    for win, r in rec.items():
+        assert r["x_prev"] < TOL and r["e_c"] < TOL and r["e_u"] < TOL, (win, r)
+        assert r["pred_x0"] < TOL, (win, r)
+
+
 def test_fifo_iterations_vs_oracle(small):
     """Two FIFO iterations (8 windows each + FreeInit shift) against oracle.fifo_iteration / shift_latents driven by the
     oracle UNet; identical pre-drawn noise (funcs.py:305-371)."""

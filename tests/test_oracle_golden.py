@@ -60,6 +60,35 @@ def test_ddim_step_matches_reference(c):
     np.testing.assert_allclose(p02, g[c + "_pred_x0"], rtol=0, atol=5e-5)
 
 
+def sam_script(g, c):
+    """segment_fn replaying the scripted Grounding-DINO / SAM-2 outputs the golden was generated with."""
+    seg, seg_n = g[c + "_seg"], g[c + "_seg_n"]
+    calls = []
+
+    def fn(i, img):
+        k = len(calls)
+        calls.append(img)
+        return None if seg_n[k] < 0 else seg[k, :seg_n[k]]
+    return fn, calls
+
+
+@pytest.mark.parametrize("c", ["a", "b"])
+def test_ddim_step_sam_branch_matches_reference(c):
+    """ddim_step without DAVIS masks: the unmodified ``_apply_segmentation`` (uint8 image, no-box fallback, IoU gate,
+    >80 % coverage reset, gain-2 blend) vs the oracle restatement, scripted segmenter outputs."""
+    g = load("step_ddim_sam.npz")
+    tab = R.make_tables(64, 1.0)
+    fn, calls = sam_script(g, c)
+    xp, p0, used, images = R.moca_ddim_step_sam(g[c + "_x"], g[c + "_e"], g[c + "_noise"], R.coef_rows(tab, g[c + "_idx"]),
+                                                g[c + "_t"], g[c + "_cond"], fn, gamma=0.5, sqrt=R.torch_cpu_sqrt)
+    assert len(calls) == len(g[c + "_images"]) == int((g[c + "_t"] <= 300).sum())
+    assert np.array_equal(np.stack(images), g[c + "_images"])          # what the segmenter is shown
+    assert np.array_equal(xp, g[c + "_x_prev"])
+    assert np.array_equal(p0, g[c + "_pred_x0"])
+    blended = [u is not None for u in used]
+    assert any(blended) and not all(blended)
+
+
 def test_p_sample_ddim_matches_reference():
     g = load("step_psample.npz")
     tab = R.make_tables(50, 1.0)
