@@ -38,10 +38,15 @@ extern "C" {
 #define MOCA_MAX_MASKS 1024    /* F * masks-per-frame of the SAM branch; also the scratch size of the mask pre-passes */
 
 typedef struct moca_ctx moca_ctx;       /* one per process / GPU; not thread-safe */
-typedef struct moca_unet moca_unet;     /* packed bf16 weights + execution plan of one UNet */
+typedef struct moca_unet moca_unet;     /* packed 16-bit weights + execution plan of one UNet */
 
 const char* moca_last_error(void);
 int32_t moca_abi_version(void);
+/* 16-bit operand type this build uses for every tensor-core contraction and for the "op16" buffers of the test
+ * primitives below: MOCA_DTYPE_F16 (default; IEEE half, saturating conversions) or MOCA_DTYPE_BF16 (-DMOCA_OPERAND_BF16). */
+#define MOCA_DTYPE_F16 0
+#define MOCA_DTYPE_BF16 1
+int32_t moca_operand_dtype(void);
 
 /* ---- context ------------------------------------------------------------------------------------------ */
 int32_t moca_ctx_create(int32_t device, moca_ctx** out);
@@ -129,7 +134,7 @@ int32_t moca_freeinit_mix(moca_ctx* ctx, const float* x, const float* noise, con
 /* ---- UNet: UNetModel (lvdm/modules/networks/openaimodel3d.py:279-578) ---------------------------------------
  * moca_unet_create: architecture integers of the yaml (configs/inference_t2v_512_v2.0.yaml:22-50).
  * moca_unet_load:   one call per state_dict tensor (name = state_dict key, fp32 DEVICE pointer, element count);
- *                   the library converts to its packed bf16 layouts and keeps its own copy.
+ *                   the library converts to its packed 16-bit layouts and keeps its own copy.
  * moca_unet_finalize: checks every parameter arrived.
  * moca_unet_forward: UNetModel.forward (openaimodel3d.py:534-578).
  *   x, y      [B,Cin,T,H,W] fp32 (reference layout)
@@ -175,28 +180,28 @@ int64_t moca_unet_profile(moca_unet* net, int32_t iters, char* buf, int64_t cap,
 int64_t moca_unet_weight_bytes(moca_unet* net);
 
 /* ---- primitives exposed for unit parity tests (tests/test_gpu_ops.py): the same kernels the UNet plan launches ----
- * moca_gemm_bf16: D[M,N] = A[M,K] * W[N,K]^T (+bias[N]) on the tcgen05 core; A, W bf16 row-major (K contiguous),
- *   D fp32 or bf16 (out_bf16).  K % 64 == 0.                                    (nn.Linear, attention.py:54-57)
+ * moca_gemm_op16: D[M,N] = A[M,K] * W[N,K]^T (+bias[N]) on the tcgen05 core; A, W op16 (moca_operand_dtype) row-major (K contiguous),
+ *   D fp32 or op16 (out_op16).  K % 64 == 0.                                    (nn.Linear, attention.py:54-57)
  * moca_geglu_f32: FeedForward's GEGLU projection (attention.py:376-383) with the gate fused in the GEMM epilogue.
  * moca_conv3x3_f32: Conv2d 3x3 padding 1 stride 1|2 on channels-last tokens  (openaimodel3d.py:149-153, 66-70)
  * moca_tconv_f32:   Conv3d (3,1,1) padding (1,0,0) on tokens [B,T,HW,C]       (openaimodel3d.py:252-263)
- * moca_groupnorm_bf16 / moca_layernorm_bf16: normalisation (+SiLU) producing the bf16 GEMM operand
+ * moca_groupnorm_op16 / moca_layernorm_op16: normalisation (+SiLU) producing the 16-bit GEMM operand
  *                                                          (basics.py:76-87; attention.py:199-201)
- * moca_attention_bf16: softmax(q k^T / 8) v, head dim 64                      (attention.py:92-114)
+ * moca_attention_op16: softmax(q k^T / 8) v, head dim 64                      (attention.py:92-114)
  * These helpers allocate scratch and synchronise; they are a test surface, not the hot path. */
-int32_t moca_gemm_bf16(moca_ctx* ctx, const void* A, const void* Wt, const float* bias, int32_t M, int32_t N, int32_t K,
-                       void* D, int32_t out_bf16, void* stream);
-int32_t moca_geglu_f32(moca_ctx* ctx, const void* A_bf16, const float* w, const float* bias, int32_t M, int32_t N, int32_t K,
-                       void* out_bf16, void* stream);
+int32_t moca_gemm_op16(moca_ctx* ctx, const void* A, const void* Wt, const float* bias, int32_t M, int32_t N, int32_t K,
+                       void* D, int32_t out_op16, void* stream);
+int32_t moca_geglu_f32(moca_ctx* ctx, const void* A_op16, const float* w, const float* bias, int32_t M, int32_t N, int32_t K,
+                       void* out_op16, void* stream);
 int32_t moca_conv3x3_f32(moca_ctx* ctx, const float* x_nhwc, const float* w_oihw, const float* bias, int32_t NF,
                          int32_t H, int32_t W, int32_t Cin, int32_t Cout, int32_t stride, float* y_nhwc, void* stream);
 int32_t moca_tconv_f32(moca_ctx* ctx, const float* x, const float* w, const float* bias, int32_t B, int32_t T, int32_t HW,
                        int32_t Cin, int32_t Cout, float* y, void* stream);
-int32_t moca_groupnorm_bf16(moca_ctx* ctx, const float* x, const float* gamma, const float* beta, int64_t rows, int32_t C,
-                            int32_t rows_per_stat, float eps, int32_t silu, void* out_bf16, void* stream);
-int32_t moca_layernorm_bf16(moca_ctx* ctx, const float* x, const float* gamma, const float* beta, int64_t rows, int32_t C,
-                            void* out_bf16, void* stream);
-int32_t moca_attention_bf16(moca_ctx* ctx, const void* q, const void* k, const void* v, int32_t batch, int32_t heads,
+int32_t moca_groupnorm_op16(moca_ctx* ctx, const float* x, const float* gamma, const float* beta, int64_t rows, int32_t C,
+                            int32_t rows_per_stat, float eps, int32_t silu, void* out_op16, void* stream);
+int32_t moca_layernorm_op16(moca_ctx* ctx, const float* x, const float* gamma, const float* beta, int64_t rows, int32_t C,
+                            void* out_op16, void* stream);
+int32_t moca_attention_op16(moca_ctx* ctx, const void* q, const void* k, const void* v, int32_t batch, int32_t heads,
                             int32_t Lq, int32_t Lk, int32_t Lk_valid, int32_t q_stride, int32_t kv_stride, void* out,
                             int32_t o_stride, int32_t temporal_inner, void* stream);
 

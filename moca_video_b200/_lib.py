@@ -15,6 +15,7 @@ pi32, pi64 = C.POINTER(C.c_int32), C.POINTER(C.c_int64)
 SIGNATURES = {
     "moca_last_error": (cp, []),
     "moca_abi_version": (i32, []),
+    "moca_operand_dtype": (i32, []),
     "moca_ctx_create": (i32, [i32, C.POINTER(vp)]),
     "moca_ctx_destroy": (i32, [vp]),
     "moca_cfg_ddim_step": (i32, [vp, vp, vp, vp, vp, f32, vp, vp, vp, i32, vp, vp, f64, f32, f32, i32, f32,
@@ -47,13 +48,13 @@ SIGNATURES = {
     "moca_unet_workspace_bytes": (i64, [vp]),
     "moca_unet_profile": (i64, [vp, i32, cp, i64, vp]),
     "moca_unet_weight_bytes": (i64, [vp]),
-    "moca_gemm_bf16": (i32, [vp, vp, vp, vp, i32, i32, i32, vp, i32, vp]),
+    "moca_gemm_op16": (i32, [vp, vp, vp, vp, i32, i32, i32, vp, i32, vp]),
     "moca_geglu_f32": (i32, [vp, vp, vp, vp, i32, i32, i32, vp, vp]),
     "moca_conv3x3_f32": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, vp]),
     "moca_tconv_f32": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp]),
-    "moca_groupnorm_bf16": (i32, [vp, vp, vp, vp, i64, i32, i32, f32, i32, vp, vp]),
-    "moca_layernorm_bf16": (i32, [vp, vp, vp, vp, i64, i32, vp, vp]),
-    "moca_attention_bf16": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, i32, i32, vp]),
+    "moca_groupnorm_op16": (i32, [vp, vp, vp, vp, i64, i32, i32, f32, i32, vp, vp]),
+    "moca_layernorm_op16": (i32, [vp, vp, vp, vp, i64, i32, vp, vp]),
+    "moca_attention_op16": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, i32, i32, vp]),
     "moca_halfwin_pack": (i32, [vp, vp, i32, i32, i32, i32, i32, i32, vp, vp]),
     "moca_halfwin_unpack": (i32, [vp, vp, i32, vp, i32, i32, i32, i32, i32, i32, vp, vp]),
 }

@@ -20,7 +20,8 @@ void set_error(const char* fmt, ...) {
 using namespace moca;
 
 extern "C" const char* moca_last_error(void) { return g_err; }
-extern "C" int32_t moca_abi_version(void) { return 1; }
+extern "C" int32_t moca_abi_version(void) { return 2; }
+extern "C" int32_t moca_operand_dtype(void) { return MOCA_OP_IS_BF16 ? MOCA_DTYPE_BF16 : MOCA_DTYPE_F16; }
 
 extern "C" int32_t moca_ctx_create(int32_t device, moca_ctx** out) {
     MOCA_REQUIRE(out != nullptr, MOCA_E_ARG, "moca_ctx_create: out is NULL");
@@ -33,14 +34,23 @@ extern "C" int32_t moca_ctx_create(int32_t device, moca_ctx** out) {
     // no fallback by design: the kernels are sm_100a SASS (tcgen05 / TMEM / TMA)
     MOCA_REQUIRE(prop.major == 10, MOCA_E_ARCH, "moca_ctx_create: device %d is sm_%d%d; this library is built for sm_100a only",
                  device, prop.major, prop.minor);
+    // allocate on `device` without changing the caller's current device
+    int prev_dev = 0;
+    MOCA_CHECK_CUDA(cudaGetDevice(&prev_dev));
     MOCA_CHECK_CUDA(cudaSetDevice(device));
     moca_ctx* c = new moca_ctx();
     c->c.device = device;
     c->c.num_sms = prop.multiProcessorCount;
     c->c.cc_major = prop.major;
     c->c.cc_minor = prop.minor;
-    MOCA_CHECK_CUDA(cudaMalloc(&c->c.d_mask_sums, sizeof(double) * MOCA_MAX_MASKS));
-    MOCA_CHECK_CUDA(cudaMemset(c->c.d_mask_sums, 0, sizeof(double) * MOCA_MAX_MASKS));
+    cudaError_t e1 = cudaMalloc(&c->c.d_mask_sums, sizeof(double) * MOCA_MAX_MASKS);
+    cudaError_t e2 = e1 == cudaSuccess ? cudaMemset(c->c.d_mask_sums, 0, sizeof(double) * MOCA_MAX_MASKS) : e1;
+    cudaSetDevice(prev_dev);
+    if (e2 != cudaSuccess) {
+        set_error("moca_ctx_create: scratch allocation failed: %s", cudaGetErrorString(e2));
+        delete c;
+        return MOCA_E_CUDA;
+    }
     *out = c;
     return MOCA_OK;
 }

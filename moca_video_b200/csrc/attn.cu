@@ -31,21 +31,21 @@ __device__ __forceinline__ void ldsm_x4_t(uint32_t addr, uint32_t& r0, uint32_t&
     asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
 }
 __device__ __forceinline__ void mma_bf16(float* c, const uint32_t* a, uint32_t b0, uint32_t b1) {
-    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32." MOCA_MMA_OP_STR ".f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
                  : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
                  : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 __device__ __forceinline__ uint32_t pack2(float a, float b) {
-    __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+    op2_t v = floats2op2(a, b);
     return *reinterpret_cast<uint32_t*>(&v);
 }
 
 __device__ __forceinline__ int64_t first_row(const SeqMap& m, int o) { return (int64_t)(o / m.div) * m.mul_a + (int64_t)(o % m.div) * m.mul_b; }
 
 struct AttnP {
-    const __nv_bfloat16* q; int ldq; SeqMap qmap;
-    const __nv_bfloat16* k; const __nv_bfloat16* v; int ldkv; SeqMap kvmap;
-    __nv_bfloat16* out; int ldo;
+    const op_t* q; int ldq; SeqMap qmap;
+    const op_t* k; const op_t* v; int ldkv; SeqMap kvmap;
+    op_t* out; int ldo;
     int n_outer, heads, Lq, Lk;
     const int* kv_len; int kv_len_div;
     float scale_log2;
@@ -53,13 +53,13 @@ struct AttnP {
 
 // loads ROWS x 64 bf16 (rows r0.. of a sequence) into a swizzled tile; rows >= L are zero-filled
 template <int ROWS, int THREADS>
-__device__ __forceinline__ void load_tile(__nv_bfloat16* s, const __nv_bfloat16* g, int64_t row0, int step, int ld, int r0, int L,
+__device__ __forceinline__ void load_tile(op_t* s, const op_t* g, int64_t row0, int step, int ld, int r0, int L,
                                           int tid) {
 #pragma unroll
     for (int i = tid; i < ROWS * 8; i += THREADS) {
         const int r = i >> 3, ch = i & 7;
         const bool ok = (r0 + r) < L;
-        const __nv_bfloat16* src = g + (row0 + (int64_t)(ok ? r0 + r : 0) * step) * ld + ch * 8;
+        const op_t* src = g + (row0 + (int64_t)(ok ? r0 + r : 0) * step) * ld + ch * 8;
         cp_async16(s + r * D + ((ch ^ (r & 7)) << 3), src, ok);
     }
 }
@@ -68,9 +68,9 @@ __device__ __forceinline__ void load_tile(__nv_bfloat16* s, const __nv_bfloat16*
 
 // ---------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128) attn_flash_kernel(const __grid_constant__ AttnP P) {
-    __shared__ __align__(128) __nv_bfloat16 sQ[64 * D];
-    __shared__ __align__(128) __nv_bfloat16 sK[2][64 * D];
-    __shared__ __align__(128) __nv_bfloat16 sV[2][64 * D];
+    __shared__ __align__(128) op_t sQ[64 * D];
+    __shared__ __align__(128) op_t sK[2][64 * D];
+    __shared__ __align__(128) op_t sV[2][64 * D];
     pdl_wait();
     pdl_launch_dependents();
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -79,9 +79,9 @@ __global__ void __launch_bounds__(128) attn_flash_kernel(const __grid_constant__
     const int q0 = blockIdx.x * 64;
     const int Lk = P.kv_len ? P.kv_len[o / P.kv_len_div] : P.Lk;
     const int64_t qrow0 = first_row(P.qmap, o), kvrow0 = first_row(P.kvmap, o);
-    const __nv_bfloat16* qg = P.q + h * D;
-    const __nv_bfloat16* kg = P.k + h * D;
-    const __nv_bfloat16* vg = P.v + h * D;
+    const op_t* qg = P.q + h * D;
+    const op_t* kg = P.k + h * D;
+    const op_t* vg = P.v + h * D;
     const int ntiles = (Lk + 63) / 64;
 
     load_tile<64, 128>(sQ, qg, qrow0, P.qmap.step, P.ldq, q0, P.Lq, tid);
@@ -187,7 +187,7 @@ __global__ void __launch_bounds__(128) attn_flash_kernel(const __grid_constant__
     l1 += __shfl_xor_sync(0xffffffffu, l1, 1); l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
     const float i0 = 1.0f / l0, i1 = 1.0f / l1;
     const int r0 = q0 + warp * 16 + g, r1 = r0 + 8;
-    __nv_bfloat16* og = P.out + h * D + 2 * t;
+    op_t* og = P.out + h * D + 2 * t;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
         if (r0 < P.Lq)
@@ -201,7 +201,7 @@ __global__ void __launch_bounds__(128) attn_flash_kernel(const __grid_constant__
 // One warp per (outer, head) sequence of L <= 16 elements (temporal attention: sequence = the T frames of one
 // spatial position, rows `step` = H*W apart in the channels-last token matrix — no rearrange copy is ever made).
 __global__ void __launch_bounds__(128) attn_short_kernel(const __grid_constant__ AttnP P) {
-    __shared__ __align__(128) __nv_bfloat16 sm[4][3][16 * D];
+    __shared__ __align__(128) op_t sm[4][3][16 * D];
     pdl_wait();
     pdl_launch_dependents();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -211,9 +211,9 @@ __global__ void __launch_bounds__(128) attn_short_kernel(const __grid_constant__
     const int o = item / P.heads, h = item - o * P.heads;
     const int L = P.Lq;
     const int64_t qrow0 = first_row(P.qmap, o), kvrow0 = first_row(P.kvmap, o);
-    __nv_bfloat16* sQ = sm[warp][0];
-    __nv_bfloat16* sK = sm[warp][1];
-    __nv_bfloat16* sV = sm[warp][2];
+    op_t* sQ = sm[warp][0];
+    op_t* sK = sm[warp][1];
+    op_t* sV = sm[warp][2];
     load_tile<16, 32>(sQ, P.q + h * D, qrow0, P.qmap.step, P.ldq, 0, L, lane);
     load_tile<16, 32>(sK, P.k + h * D, kvrow0, P.kvmap.step, P.ldkv, 0, L, lane);
     load_tile<16, 32>(sV, P.v + h * D, kvrow0, P.kvmap.step, P.ldkv, 0, L, lane);
@@ -269,7 +269,7 @@ __global__ void __launch_bounds__(128) attn_short_kernel(const __grid_constant__
         mma_bf16(oacc[2 * dp + 1], pa, b2, b3);
     }
     const float i0 = 1.0f / l0, i1 = 1.0f / l1;
-    __nv_bfloat16* og = P.out + h * D + 2 * t;
+    op_t* og = P.out + h * D + 2 * t;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
         if (g < L) *reinterpret_cast<uint32_t*>(og + (qrow0 + (int64_t)g * P.qmap.step) * P.ldo + i * 8) = pack2(oacc[i][0] * i0, oacc[i][1] * i0);

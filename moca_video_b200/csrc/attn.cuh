@@ -12,9 +12,9 @@ struct SeqMap {
 };
 
 struct AttnArgs {
-    const __nv_bfloat16* q = nullptr; int ldq = 0; SeqMap qmap;     // q row r of outer o, head h: q[(row)*ldq + h*64 ..]
-    const __nv_bfloat16* k = nullptr; const __nv_bfloat16* v = nullptr; int ldkv = 0; SeqMap kvmap;
-    __nv_bfloat16* out = nullptr; int ldo = 0;                       // addressed with qmap
+    const op_t* q = nullptr; int ldq = 0; SeqMap qmap;     // q row r of outer o, head h: q[(row)*ldq + h*64 ..]
+    const op_t* k = nullptr; const op_t* v = nullptr; int ldkv = 0; SeqMap kvmap;
+    op_t* out = nullptr; int ldo = 0;                       // addressed with qmap
     int n_outer = 0, heads = 0, Lq = 0, Lk = 0;
     int64_t q_rows = 0, kv_rows = 0;   // rows of the q / kv buffers (TMA bounds of the tcgen05 kernel; 0: unknown -> mma.sync kernel)
     const int* kv_len = nullptr;   // optional device int[n_outer / kv_len_div]: valid keys (cross-attention)

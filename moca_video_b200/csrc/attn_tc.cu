@@ -29,7 +29,7 @@ constexpr size_t kSmem = 6 * kTileBytes + 128 + 1024;    // + barriers + alignme
 
 struct AttnTcP {
     CUtensorMap tmQ, tmK, tmV;
-    __nv_bfloat16* out; int ldo;
+    op_t* out; int ldo;
     SeqMap qmap, kvmap;
     int heads, Lq, Lk;
     const int* kv_len; int kv_len_div;
@@ -43,7 +43,7 @@ __device__ __forceinline__ float ex2(float x) {
 }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ uint32_t pack2(float a, float b) {
-    __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+    op2_t v = floats2op2(a, b);
     return *reinterpret_cast<uint32_t*>(&v);
 }
 __device__ __forceinline__ int64_t first_row(const SeqMap& m, int o) { return (int64_t)(o / m.div) * m.mul_a + (int64_t)(o % m.div) * m.mul_b; }
@@ -232,7 +232,7 @@ __global__ void __launch_bounds__(kThreads, 2) attn_tc_kernel(const __grid_const
         const int qr = q0 + row;
         if (qr < P.Lq) {
             const float inv = 1.0f / l;
-            __nv_bfloat16* op = P.out + ((int64_t)qrow0 + qr) * P.ldo + h * kD;
+            op_t* op = P.out + ((int64_t)qrow0 + qr) * P.ldo + h * kD;
 #pragma unroll
             for (int u = 0; u < 8; ++u) {
                 *reinterpret_cast<uint4*>(op + u * 8) =
@@ -469,7 +469,7 @@ __global__ void __launch_bounds__(kThreads2, 1) attn_tc2_kernel(const __grid_con
             tc_fence_after();
             const int qr = q0 + x * kTileQ + row;
             const float inv = 1.0f / l;
-            __nv_bfloat16* op = P.out + ((int64_t)qrow0 + qr) * P.ldo + h * kD;
+            op_t* op = P.out + ((int64_t)qrow0 + qr) * P.ldo + h * kD;
 #pragma unroll
             for (int c = 0; c < 2; ++c) {
                 uint32_t ov[32];

@@ -67,7 +67,7 @@ __device__ __forceinline__ float gelu_fast(float g) {
 #endif
 
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
-    __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+    op2_t v = floats2op2(a, b);
     return *reinterpret_cast<uint32_t*>(&v);
 }
 
@@ -691,11 +691,11 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA>::THREADS), 1) ge
 #pragma unroll
                             for (int e = 0; e < 8; ++e) v[e] += bb[e];
                         }
-                        __nv_bfloat16* o = P.outb + (size_t)orow * P.ldo + col;
+                        op_t* o = P.outb + (size_t)orow * P.ldo + col;
                         if (nvalid >= 8) {
                             *reinterpret_cast<uint4*>(o) = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
                         } else {
-                            for (int e = 0; e < nvalid; ++e) o[e] = __float2bfloat16_rn(v[e]);
+                            for (int e = 0; e < nvalid; ++e) o[e] = float2op(v[e]);
                         }
                     }
                     __syncwarp();
@@ -762,7 +762,7 @@ int make_tmap_bf16(CUtensorMap* tm, const void* ptr, int64_t rows, int64_t cols,
     cuuint64_t strides[1] = {(cuuint64_t)pitch * 2};
     cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+    CUresult r = enc(tm, MOCA_TMAP_OP16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     MOCA_REQUIRE(r == CUDA_SUCCESS, MOCA_E_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d (rows %lld cols %lld pitch %lld)",
@@ -797,7 +797,7 @@ int make_tmap_bf16_chunk(CUtensorMap* tm, const void* ptr, int64_t rows, int64_t
     cuuint64_t strides[1] = {(cuuint64_t)pitch * 2};
     cuuint32_t box[2] = {32, 32};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+    CUresult r = enc(tm, MOCA_TMAP_OP16, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                      CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     MOCA_REQUIRE(r == CUDA_SUCCESS, MOCA_E_CUDA, "cuTensorMapEncodeTiled (bf16 chunk) failed with CUresult %d", (int)r);
     return MOCA_OK;
@@ -928,7 +928,7 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
     p.M = d.M; p.N = d.N; p.ntaps = d.ntaps; p.Kp = d.Kp; p.kblocks = d.Kp / 64;
     for (int i = 0; i < 9; ++i) p.tap_shift[i] = d.tap_shift[i];
     p.mode = d.mode; p.g_rows = d.g_rows; p.g_w = d.g_w; p.g_H = d.g_H; p.g_W = d.g_W; p.stride = d.stride;
-    p.outf = (float*)d.out; p.outb = (__nv_bfloat16*)d.out; p.ldo = d.ldo;
+    p.outf = (float*)d.out; p.outb = (op_t*)d.out; p.ldo = d.ldo;
     p.bias = d.bias; p.rowbias = d.rowbias; p.rb_ld = d.rb_ld; p.rows_per_frame = d.rows_per_frame > 0 ? d.rows_per_frame : 1;
     p.residual = d.residual; p.epi = d.epi;
     p.cstat = d.chan_stats; p.stat_rpf = d.stat_rows_per_frame > 0 ? d.stat_rows_per_frame : 1;

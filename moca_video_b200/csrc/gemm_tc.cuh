@@ -38,7 +38,7 @@ struct GemmParams {
     int g_H, g_W;             // SPATIAL: H, W          TIME: g_H = T
     int stride;               // SPATIAL: 1 or 2 (Downsample)
     float* outf;
-    __nv_bfloat16* outb;
+    op_t* outb;
     int ldo;                  // output row pitch (elements)
     const float* bias;        // [N] or null
     const float* rowbias;     // [frames, rb_ld] or null (ResBlock emb_layers output, openaimodel3d.py:221-226)

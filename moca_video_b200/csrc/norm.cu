@@ -6,7 +6,7 @@
 namespace moca {
 
 // ---------------------------------------------------------------------------------------------------------------
-__global__ void pack_weight_kernel(const float* __restrict__ src, int N, int K, int taps, int Kp, __nv_bfloat16* __restrict__ dst,
+__global__ void pack_weight_kernel(const float* __restrict__ src, int N, int K, int taps, int Kp, op_t* __restrict__ dst,
                                    int64_t pitch, int row0, int geglu_bn) {
     const int64_t total = (int64_t)N * taps * Kp;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -22,11 +22,11 @@ __global__ void pack_weight_kernel(const float* __restrict__ src, int N, int K, 
             const int j = n < half ? n : n - half;
             r = (j / hb) * geglu_bn + (n < half ? 0 : hb) + (j % hb);
         }
-        dst[(int64_t)(row0 + r) * pitch + (int64_t)tap * Kp + k] = __float2bfloat16_rn(v);
+        dst[(int64_t)(row0 + r) * pitch + (int64_t)tap * Kp + k] = float2op(v);
     }
 }
 
-int pack_weight(const float* src, int N, int K, int taps, int Kp, __nv_bfloat16* dst, int64_t dst_pitch, int row0, int geglu_bn,
+int pack_weight(const float* src, int N, int K, int taps, int Kp, op_t* dst, int64_t dst_pitch, int row0, int geglu_bn,
                 cudaStream_t st) {
     const int64_t total = (int64_t)N * taps * Kp;
     const int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
@@ -261,7 +261,7 @@ struct ApplyP {
     int NF, H, W;        // source geometry
     int T, HW;
     int dst_rows;        // rows of the destination layout
-    __nv_bfloat16* dst; __nv_bfloat16* raw;
+    op_t* dst; op_t* raw;
     FastDiv d_stat;      // rows_per_stat
     FastDiv d_outer;     // TIME_PAD: HW * (T + 2)      SPATIAL: (Hd + 2) * (Wd + 2)
     FastDiv d_inner;     // TIME_PAD: HW                SPATIAL: Wd + 2
@@ -294,7 +294,7 @@ __device__ __forceinline__ int apply_src_row(const ApplyP& P, int drow) {
 }
 
 __device__ __forceinline__ uint2 pack4(const float* x) {
-    __nv_bfloat162 a = __floats2bfloat162_rn(x[0], x[1]), b = __floats2bfloat162_rn(x[2], x[3]);
+    op2_t a = floats2op2(x[0], x[1]), b = floats2op2(x[2], x[3]);
     return make_uint2(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&b));
 }
 
@@ -479,7 +479,7 @@ int gn_apply(const ApplyArgs& a, cudaStream_t st) {
 template <int SLOTS, int R>
 __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
                                                         const float* __restrict__ beta, int64_t rows, int C,
-                                                        __nv_bfloat16* __restrict__ out) {
+                                                        op_t* __restrict__ out) {
     pdl_wait();
     pdl_launch_dependents();
     const int lane = threadIdx.x & 31;
@@ -533,15 +533,15 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict_
             if (i < nvec) {
                 float4 gu, bu;
                 if constexpr (R > 1) { gu = g[u]; bu = b[u]; } else { gu = __ldg(g4 + i); bu = __ldg(b4 + i); }
-                __nv_bfloat162 lo = __floats2bfloat162_rn((v[r][u].x - mean) * rstd * gu.x + bu.x, (v[r][u].y - mean) * rstd * gu.y + bu.y);
-                __nv_bfloat162 hi = __floats2bfloat162_rn((v[r][u].z - mean) * rstd * gu.z + bu.z, (v[r][u].w - mean) * rstd * gu.w + bu.w);
+                op2_t lo = floats2op2((v[r][u].x - mean) * rstd * gu.x + bu.x, (v[r][u].y - mean) * rstd * gu.y + bu.y);
+                op2_t hi = floats2op2((v[r][u].z - mean) * rstd * gu.z + bu.z, (v[r][u].w - mean) * rstd * gu.w + bu.w);
                 orow[i] = make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
             }
         }
     }
 }
 
-int layernorm_bf16(const float* x, const float* gamma, const float* beta, int64_t rows, int C, __nv_bfloat16* out, cudaStream_t st) {
+int layernorm_op16(const float* x, const float* gamma, const float* beta, int64_t rows, int C, op_t* out, cudaStream_t st) {
     MOCA_REQUIRE(C % 4 == 0 && C <= 1280, MOCA_E_SHAPE, "layernorm: C=%d unsupported (multiple of 4, <= 1280)", C);
     if (C <= 384) launch_pdl(layernorm_kernel<3, 4>, dim3(cdiv(rows, 32)), dim3(256), 0, st, x, gamma, beta, rows, C, out);
     else if (C <= 640) launch_pdl(layernorm_kernel<5, 2>, dim3(cdiv(rows, 16)), dim3(256), 0, st, x, gamma, beta, rows, C, out);
@@ -551,7 +551,7 @@ int layernorm_bf16(const float* x, const float* gamma, const float* beta, int64_
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-__global__ void timestep_embedding_kernel(const int* __restrict__ t, int n, int dim, __nv_bfloat16* __restrict__ out) {
+__global__ void timestep_embedding_kernel(const int* __restrict__ t, int n, int dim, op_t* __restrict__ out) {
     pdl_wait();
     pdl_launch_dependents();
     const int half = dim / 2;
@@ -560,11 +560,11 @@ __global__ void timestep_embedding_kernel(const int* __restrict__ t, int n, int 
     const int j = i % half, r = i / half;
     const float f = expf(-9.210340371976184f * (float)j / (float)half);      // -log(10000) * j / half
     const float a = (float)t[r] * f;
-    out[(int64_t)r * dim + j] = __float2bfloat16_rn(cosf(a));
-    out[(int64_t)r * dim + half + j] = __float2bfloat16_rn(sinf(a));
+    out[(int64_t)r * dim + j] = float2op(cosf(a));
+    out[(int64_t)r * dim + half + j] = float2op(sinf(a));
 }
 
-int timestep_embedding_bf16(const int* t_dev, int n, int dim, __nv_bfloat16* out, cudaStream_t st) {
+int timestep_embedding_bf16(const int* t_dev, int n, int dim, op_t* out, cudaStream_t st) {
     MOCA_REQUIRE(dim % 2 == 0, MOCA_E_SHAPE, "timestep_embedding: odd dim %d", dim);
     launch_pdl(timestep_embedding_kernel, dim3(cdiv((int64_t)n * dim / 2, 256)), dim3(256), 0, st, t_dev, n, dim, out);
     MOCA_LAUNCH_CHECK();
@@ -572,25 +572,25 @@ int timestep_embedding_bf16(const int* t_dev, int n, int dim, __nv_bfloat16* out
 }
 
 __global__ void silu_add_kernel(const float* __restrict__ a, const float* __restrict__ b, int64_t n, int do_silu,
-                                __nv_bfloat16* __restrict__ out) {
+                                op_t* __restrict__ out) {
     pdl_wait();
     pdl_launch_dependents();
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
         float v = a[i];
         if (b) v += b[i];
         if (do_silu) v = v / (1.0f + expf(-v));
-        out[i] = __float2bfloat16_rn(v);
+        out[i] = float2op(v);
     }
 }
 
-int silu_add_bf16(const float* a, const float* b, int64_t n, __nv_bfloat16* out, cudaStream_t st) {
+int silu_add_bf16(const float* a, const float* b, int64_t n, op_t* out, cudaStream_t st) {
     const int blocks = (int)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
     launch_pdl(silu_add_kernel, dim3(blocks), dim3(256), 0, st, a, b, n, 1, out);
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
 }
 
-int f32_to_bf16(const float* a, int64_t n, __nv_bfloat16* out, cudaStream_t st) {
+int f32_to_bf16(const float* a, int64_t n, op_t* out, cudaStream_t st) {
     const int blocks = (int)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
     launch_pdl(silu_add_kernel, dim3(blocks), dim3(256), 0, st, a, (const float*)nullptr, n, 0, out);
     MOCA_LAUNCH_CHECK();
@@ -599,7 +599,7 @@ int f32_to_bf16(const float* a, int64_t n, __nv_bfloat16* out, cudaStream_t st) 
 
 // ---------------------------------------------------------------------------------------------------------------
 __global__ void ncthw_to_pad_kernel(const float* __restrict__ x, int B, int C, int T, int H, int W, int Cp,
-                                    __nv_bfloat16* __restrict__ dst) {
+                                    op_t* __restrict__ dst) {
     pdl_wait();
     pdl_launch_dependents();
     const int Hp = H + 2, Wp = W + 2;
@@ -614,11 +614,11 @@ __global__ void ncthw_to_pad_kernel(const float* __restrict__ x, int B, int C, i
             const int b = f / T, t = f % T;
             v = x[((((int64_t)b * C + c) * T + t) * H + (hp - 1)) * W + (wp - 1)];
         }
-        dst[i] = __float2bfloat16_rn(v);
+        dst[i] = float2op(v);
     }
 }
 
-int ncthw_to_pad(const float* x, int B, int C, int T, int H, int W, int Cp, __nv_bfloat16* dst, cudaStream_t st) {
+int ncthw_to_pad(const float* x, int B, int C, int T, int H, int W, int Cp, op_t* dst, cudaStream_t st) {
     const int64_t total = (int64_t)B * T * (H + 2) * (W + 2) * Cp;
     const int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
     launch_pdl(ncthw_to_pad_kernel, dim3(blocks), dim3(256), 0, st, x, B, C, T, H, W, Cp, dst);
@@ -648,7 +648,7 @@ int tokens_to_ncthw(const float* tok, int ld, int B, int C, int T, int H, int W,
     return MOCA_OK;
 }
 
-int nhwc_to_pad(const float* x, int NF, int H, int W, int C, __nv_bfloat16* dst, cudaStream_t st) {
+int nhwc_to_pad(const float* x, int NF, int H, int W, int C, op_t* dst, cudaStream_t st) {
     ApplyArgs a;
     a.x1 = x; a.C1 = C; a.rows = (int64_t)NF * H * W; a.rows_per_stat = 0; a.dst_mode = DST_SPATIAL_PAD;
     a.NF = NF; a.H = H; a.W = W; a.dst = dst;

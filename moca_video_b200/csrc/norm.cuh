@@ -10,7 +10,7 @@ enum ApplyDst { DST_LINEAR = 0, DST_SPATIAL_PAD = 1, DST_SPATIAL_PAD_UP2 = 2, DS
 // fp32 [N, K, taps] (taps innermost, the torch conv weight layout [O, I, kh, kw] / [O, I, kt, 1, 1]; taps = 1 for Linear)
 // -> bf16 dst[(row0 + perm(n)), tap*Kp + k], zero for k >= K.  geglu_bn > 0 permutes rows so that each geglu_bn-row
 // tile holds geglu_bn/2 value rows followed by their geglu_bn/2 gate rows (GEGLU: attention.py:376-383).
-int pack_weight(const float* src, int N, int K, int taps, int Kp, __nv_bfloat16* dst, int64_t dst_pitch, int row0, int geglu_bn,
+int pack_weight(const float* src, int N, int K, int taps, int Kp, op_t* dst, int64_t dst_pitch, int row0, int geglu_bn,
                 cudaStream_t st);
 
 // Sum / sum of squares per (stat group, channel group) in double.  Tokens are channels-last fp32 [rows, C1] (+ optional
@@ -50,25 +50,25 @@ struct ApplyArgs {
     int dst_mode = DST_LINEAR;
     int NF = 0, H = 0, W = 0;       // spatial geometry of the SOURCE tokens (DST_SPATIAL_*)
     int B = 0, T = 0, HW = 0;       // DST_TIME_PAD
-    __nv_bfloat16* dst = nullptr;   // [.., C1+C2]
-    __nv_bfloat16* raw = nullptr;   // optional un-normalised bf16 copy [rows, C1+C2] (ResBlock.skip_connection input)
+    op_t* dst = nullptr;   // [.., C1+C2]
+    op_t* raw = nullptr;   // optional un-normalised bf16 copy [rows, C1+C2] (ResBlock.skip_connection input)
 };
 int gn_apply(const ApplyArgs& a, cudaStream_t st);
 
 // nn.LayerNorm(C), eps 1e-5 (attention.py:199-201): fp32 [rows, C] -> bf16 [rows, C]
-int layernorm_bf16(const float* x, const float* gamma, const float* beta, int64_t rows, int C, __nv_bfloat16* out, cudaStream_t st);
+int layernorm_op16(const float* x, const float* gamma, const float* beta, int64_t rows, int C, op_t* out, cudaStream_t st);
 
 // timestep_embedding (utils_diffusion.py:8-28): out bf16 [n, dim] = [cos(t*f), sin(t*f)]
-int timestep_embedding_bf16(const int* t_dev, int n, int dim, __nv_bfloat16* out, cudaStream_t st);
+int timestep_embedding_bf16(const int* t_dev, int n, int dim, op_t* out, cudaStream_t st);
 // out bf16 = silu(a (+ b)); optionally also writes the fp32 sum
-int silu_add_bf16(const float* a, const float* b, int64_t n, __nv_bfloat16* out, cudaStream_t st);
-int f32_to_bf16(const float* a, int64_t n, __nv_bfloat16* out, cudaStream_t st);
+int silu_add_bf16(const float* a, const float* b, int64_t n, op_t* out, cudaStream_t st);
+int f32_to_bf16(const float* a, int64_t n, op_t* out, cudaStream_t st);
 
 // x [B, C, T, H, W] fp32 (reference layout) -> zero-bordered bf16 [B*T, H+2, W+2, Cp] (channels >= C zero)
-int ncthw_to_pad(const float* x, int B, int C, int T, int H, int W, int Cp, __nv_bfloat16* dst, cudaStream_t st);
+int ncthw_to_pad(const float* x, int B, int C, int T, int H, int W, int Cp, op_t* dst, cudaStream_t st);
 // tokens fp32 [B*T*H*W, ld] (first C columns) -> [B, C, T, H, W] fp32
 int tokens_to_ncthw(const float* tok, int ld, int B, int C, int T, int H, int W, float* y, cudaStream_t st);
 // NHWC fp32 <-> padded bf16 helpers for the conv unit test
-int nhwc_to_pad(const float* x, int NF, int H, int W, int C, __nv_bfloat16* dst, cudaStream_t st);
+int nhwc_to_pad(const float* x, int NF, int H, int W, int C, op_t* dst, cudaStream_t st);
 
 }  // namespace moca

@@ -19,13 +19,13 @@ static T* dmalloc(size_t n) {
 static int round_up64(int v) { return (v + 63) / 64 * 64; }
 }  // namespace
 
-extern "C" int32_t moca_gemm_bf16(moca_ctx* ctx, const void* A, const void* Wt, const float* bias, int32_t M, int32_t N, int32_t K,
-                                  void* D, int32_t out_bf16, void* stream) {
-    MOCA_REQUIRE(ctx && A && Wt && D, MOCA_E_ARG, "moca_gemm_bf16: NULL argument");
-    MOCA_REQUIRE(K % 64 == 0, MOCA_E_SHAPE, "moca_gemm_bf16: K=%d must be a multiple of 64", K);
+extern "C" int32_t moca_gemm_op16(moca_ctx* ctx, const void* A, const void* Wt, const float* bias, int32_t M, int32_t N, int32_t K,
+                                  void* D, int32_t out_op16, void* stream) {
+    MOCA_REQUIRE(ctx && A && Wt && D, MOCA_E_ARG, "moca_gemm_op16: NULL argument");
+    MOCA_REQUIRE(K % 64 == 0, MOCA_E_SHAPE, "moca_gemm_op16: K=%d must be a multiple of 64", K);
     GemmDesc d;
     d.A = A; d.a_rows = M; d.a_cols = K; d.a_pitch = K; d.Wt = Wt; d.N = N; d.ntaps = 1; d.Kp = K;
-    d.mode = GEMM_LINEAR; d.M = M; d.epi = out_bf16 ? EPI_BF16 : EPI_F32; d.out = D; d.ldo = N; d.bias = bias;
+    d.mode = GEMM_LINEAR; d.M = M; d.epi = out_op16 ? EPI_BF16 : EPI_F32; d.out = D; d.ldo = N; d.bias = bias;
     GemmLaunch L;
     int rc = gemm_plan(ctx->c, d, &L);
     if (rc) return rc;
@@ -33,12 +33,12 @@ extern "C" int32_t moca_gemm_bf16(moca_ctx* ctx, const void* A, const void* Wt, 
 }
 
 // GEGLU-fused FeedForward first layer (attention.py:376-383): out bf16 [M, N/2] from fp32 weight [N, K], bias [N]
-extern "C" int32_t moca_geglu_f32(moca_ctx* ctx, const void* A_bf16, const float* w, const float* bias, int32_t M, int32_t N, int32_t K,
-                                  void* out_bf16, void* stream) {
-    MOCA_REQUIRE(ctx && A_bf16 && w && bias && out_bf16, MOCA_E_ARG, "moca_geglu_f32: NULL argument");
+extern "C" int32_t moca_geglu_f32(moca_ctx* ctx, const void* A_op16, const float* w, const float* bias, int32_t M, int32_t N, int32_t K,
+                                  void* out_op16, void* stream) {
+    MOCA_REQUIRE(ctx && A_op16 && w && bias && out_op16, MOCA_E_ARG, "moca_geglu_f32: NULL argument");
     cudaStream_t st = (cudaStream_t)stream;
     const int Kp = round_up64(K);
-    __nv_bfloat16* wp = dmalloc<__nv_bfloat16>((size_t)N * Kp);
+    op_t* wp = dmalloc<op_t>((size_t)N * Kp);
     float* bp = dmalloc<float>(N);
     MOCA_REQUIRE(wp && bp, MOCA_E_CUDA, "moca_geglu_f32: allocation failed");
     cudaMemsetAsync(wp, 0, (size_t)N * Kp * 2, st);
@@ -54,8 +54,8 @@ extern "C" int32_t moca_geglu_f32(moca_ctx* ctx, const void* A_bf16, const float
     }
     cudaMemcpy(bp, hp.data(), N * sizeof(float), cudaMemcpyHostToDevice);
     GemmDesc d;
-    d.A = A_bf16; d.a_rows = M; d.a_cols = K; d.a_pitch = K; d.Wt = wp; d.N = N; d.ntaps = 1; d.Kp = Kp;
-    d.mode = GEMM_LINEAR; d.M = M; d.epi = EPI_GEGLU; d.out = out_bf16; d.ldo = N / 2; d.bias = bp;
+    d.A = A_op16; d.a_rows = M; d.a_cols = K; d.a_pitch = K; d.Wt = wp; d.N = N; d.ntaps = 1; d.Kp = Kp;
+    d.mode = GEMM_LINEAR; d.M = M; d.epi = EPI_GEGLU; d.out = out_op16; d.ldo = N / 2; d.bias = bp;
     GemmLaunch L;
     if (!rc) rc = gemm_plan(ctx->c, d, &L);
     if (!rc) rc = gemm_run(L, st);
@@ -71,8 +71,8 @@ extern "C" int32_t moca_conv3x3_f32(moca_ctx* ctx, const float* x_nhwc, const fl
     MOCA_REQUIRE(Cin % 8 == 0 && (stride == 1 || stride == 2), MOCA_E_SHAPE, "moca_conv3x3_f32: Cin %% 8 and stride in {1,2}");
     cudaStream_t st = (cudaStream_t)stream;
     const int Kp = round_up64(Cin), Hp = H + 2, Wp = W + 2;
-    __nv_bfloat16* wp = dmalloc<__nv_bfloat16>((size_t)Cout * 9 * Kp);
-    __nv_bfloat16* pad = dmalloc<__nv_bfloat16>((size_t)NF * Hp * Wp * Cin);
+    op_t* wp = dmalloc<op_t>((size_t)Cout * 9 * Kp);
+    op_t* pad = dmalloc<op_t>((size_t)NF * Hp * Wp * Cin);
     MOCA_REQUIRE(wp && pad, MOCA_E_CUDA, "moca_conv3x3_f32: allocation failed");
     int rc = pack_weight(w_oihw, Cout, Cin, 9, Kp, wp, (int64_t)9 * Kp, 0, 0, st);
     if (!rc) rc = nhwc_to_pad(x_nhwc, NF, H, W, Cin, pad, st);
@@ -97,8 +97,8 @@ extern "C" int32_t moca_tconv_f32(moca_ctx* ctx, const float* x, const float* w,
     MOCA_REQUIRE(Cin % 8 == 0, MOCA_E_SHAPE, "moca_tconv_f32: Cin %% 8");
     cudaStream_t st = (cudaStream_t)stream;
     const int Kp = round_up64(Cin);
-    __nv_bfloat16* wp = dmalloc<__nv_bfloat16>((size_t)Cout * 3 * Kp);
-    __nv_bfloat16* pad = dmalloc<__nv_bfloat16>((size_t)B * (T + 2) * HW * Cin);
+    op_t* wp = dmalloc<op_t>((size_t)Cout * 3 * Kp);
+    op_t* pad = dmalloc<op_t>((size_t)B * (T + 2) * HW * Cin);
     MOCA_REQUIRE(wp && pad, MOCA_E_CUDA, "moca_tconv_f32: allocation failed");
     int rc = pack_weight(w, Cout, Cin, 3, Kp, wp, (int64_t)3 * Kp, 0, 0, st);
     ApplyArgs a;
@@ -118,41 +118,41 @@ extern "C" int32_t moca_tconv_f32(moca_ctx* ctx, const float* x, const float* w,
 }
 
 // GroupNorm(32) (+SiLU) on tokens [rows, C] fp32 -> bf16 [rows, C]; rows_per_stat rows share statistics
-extern "C" int32_t moca_groupnorm_bf16(moca_ctx* ctx, const float* x, const float* gamma, const float* beta, int64_t rows, int32_t C,
-                                       int32_t rows_per_stat, float eps, int32_t silu, void* out_bf16, void* stream) {
-    MOCA_REQUIRE(ctx && x && gamma && beta && out_bf16, MOCA_E_ARG, "moca_groupnorm_bf16: NULL argument");
+extern "C" int32_t moca_groupnorm_op16(moca_ctx* ctx, const float* x, const float* gamma, const float* beta, int64_t rows, int32_t C,
+                                       int32_t rows_per_stat, float eps, int32_t silu, void* out_op16, void* stream) {
+    MOCA_REQUIRE(ctx && x && gamma && beta && out_op16, MOCA_E_ARG, "moca_groupnorm_op16: NULL argument");
     cudaStream_t st = (cudaStream_t)stream;
     const int nstat = (int)(rows / rows_per_stat);
     double* acc = dmalloc<double>((size_t)nstat * 64);
     float2* table = dmalloc<float2>((size_t)nstat * 32);
     unsigned* counter = dmalloc<unsigned>((size_t)nstat);
-    MOCA_REQUIRE(acc && table && counter, MOCA_E_CUDA, "moca_groupnorm_bf16: allocation failed");
+    MOCA_REQUIRE(acc && table && counter, MOCA_E_CUDA, "moca_groupnorm_op16: allocation failed");
     cudaMemsetAsync(acc, 0, (size_t)nstat * 64 * sizeof(double), st);
     cudaMemsetAsync(counter, 0, (size_t)nstat * sizeof(unsigned), st);
     int rc = gn_stats(x, C, nullptr, 0, rows, rows_per_stat, 32, acc, eps, table, counter, st);
     ApplyArgs a;
     a.x1 = x; a.C1 = C; a.rows = rows; a.rows_per_stat = rows_per_stat; a.table = table; a.gamma = gamma; a.beta = beta; a.eps = eps;
-    a.silu = silu; a.dst_mode = DST_LINEAR; a.dst = (__nv_bfloat16*)out_bf16;
+    a.silu = silu; a.dst_mode = DST_LINEAR; a.dst = (op_t*)out_op16;
     if (!rc) rc = gn_apply(a, st);
     cudaStreamSynchronize(st);
     cudaFree(acc); cudaFree(table); cudaFree(counter);
     return rc;
 }
 
-extern "C" int32_t moca_layernorm_bf16(moca_ctx* ctx, const float* x, const float* gamma, const float* beta, int64_t rows, int32_t C,
-                                       void* out_bf16, void* stream) {
-    MOCA_REQUIRE(ctx && x && gamma && beta && out_bf16, MOCA_E_ARG, "moca_layernorm_bf16: NULL argument");
-    return layernorm_bf16(x, gamma, beta, rows, C, (__nv_bfloat16*)out_bf16, (cudaStream_t)stream);
+extern "C" int32_t moca_layernorm_op16(moca_ctx* ctx, const float* x, const float* gamma, const float* beta, int64_t rows, int32_t C,
+                                       void* out_op16, void* stream) {
+    MOCA_REQUIRE(ctx && x && gamma && beta && out_op16, MOCA_E_ARG, "moca_layernorm_op16: NULL argument");
+    return layernorm_op16(x, gamma, beta, rows, C, (op_t*)out_op16, (cudaStream_t)stream);
 }
 
 // softmax(q k^T / 8) v, head dim 64.  q [batch*Lq, heads*64] (pitch q_stride), k/v [batch*Lk, heads*64] (pitch kv_stride).
 // temporal != 0: sequences are interleaved (element i of sequence o is row (o / inner)*L*inner + (o % inner) + i*inner), Lq == Lk <= 16.
-extern "C" int32_t moca_attention_bf16(moca_ctx* ctx, const void* q, const void* k, const void* v, int32_t batch, int32_t heads,
+extern "C" int32_t moca_attention_op16(moca_ctx* ctx, const void* q, const void* k, const void* v, int32_t batch, int32_t heads,
                                        int32_t Lq, int32_t Lk, int32_t Lk_valid, int32_t q_stride, int32_t kv_stride, void* out,
                                        int32_t o_stride, int32_t temporal_inner, void* stream) {
-    MOCA_REQUIRE(ctx && q && k && v && out, MOCA_E_ARG, "moca_attention_bf16: NULL argument");
+    MOCA_REQUIRE(ctx && q && k && v && out, MOCA_E_ARG, "moca_attention_op16: NULL argument");
     AttnArgs a;
-    a.q = (const __nv_bfloat16*)q; a.k = (const __nv_bfloat16*)k; a.v = (const __nv_bfloat16*)v; a.out = (__nv_bfloat16*)out;
+    a.q = (const op_t*)q; a.k = (const op_t*)k; a.v = (const op_t*)v; a.out = (op_t*)out;
     a.ldq = q_stride; a.ldkv = kv_stride; a.ldo = o_stride; a.n_outer = batch; a.heads = heads; a.Lq = Lq; a.Lk = Lk_valid;
     a.scale = 0.125f;
     if (temporal_inner > 0) {

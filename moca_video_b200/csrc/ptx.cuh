@@ -6,6 +6,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include "common.cuh"
 
 namespace moca {
 namespace ptx {
@@ -244,10 +245,10 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
     return d;
 }
 
-// kind::f16 instruction descriptor: D fp32 (bits 4-5 = 1), A/B bf16 (bits 7-9, 10-12 = 1), both K-major (bits 15,16 = 0),
+// kind::f16 instruction descriptor: D fp32 (bits 4-5 = 1), A/B format (bits 7-9, 10-12: 0 = fp16, 1 = bf16; op_t of common.cuh), both K-major (bits 15,16 = 0),
 // N>>3 at bits 17-22, M>>4 at bits 24-28.
 __host__ __device__ constexpr uint32_t umma_idesc_bf16(uint32_t M, uint32_t N) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((N >> 3) << 17) | ((M >> 4) << 24);
+    return (1u << 4) | (MOCA_UMMA_OP_FMT << 7) | (MOCA_UMMA_OP_FMT << 10) | ((N >> 3) << 17) | ((M >> 4) << 24);
 }
 
 }  // namespace ptx

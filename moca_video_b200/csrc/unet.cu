@@ -41,7 +41,7 @@ static NormW reg_norm(moca_unet* n, const std::string& prefix, int C) {
 static PackedW alloc_packed(moca_unet* n, int N, int K, int taps, bool bias) {
     PackedW w;
     w.N = N; w.K = K; w.taps = taps; w.Kp = round_up(K, 64);
-    w.w = (__nv_bfloat16*)dalloc(n, (size_t)N * taps * w.Kp * sizeof(__nv_bfloat16));
+    w.w = (op_t*)dalloc(n, (size_t)N * taps * w.Kp * sizeof(op_t));
     if (bias) w.b = (float*)dalloc(n, (size_t)N * sizeof(float));
     return w;
 }
@@ -255,7 +255,7 @@ __global__ void copy_bias_kernel(const float* __restrict__ src, float* __restric
 struct LoadJob {
     const float* src;
     float* dst_f32;
-    __nv_bfloat16* dst;
+    op_t* dst;
     long long pitch, start;
     int kind, N, K, taps, Kp, row0, geglu_bn, pad;
 };
@@ -296,7 +296,7 @@ __global__ void __launch_bounds__(256) load_many_kernel(const LoadJob* __restric
                 const int tap = (int)((i / J.Kp) % J.taps);
                 const int n = (int)(i / ((long long)J.Kp * J.taps));
                 const float v = k < J.K ? J.src[((long long)n * J.K + k) * J.taps + tap] : 0.0f;
-                J.dst[(long long)(J.row0 + geglu_row(n, J.N, J.geglu_bn)) * J.pitch + (long long)tap * J.Kp + k] = __float2bfloat16_rn(v);
+                J.dst[(long long)(J.row0 + geglu_row(n, J.N, J.geglu_bn)) * J.pitch + (long long)tap * J.Kp + k] = float2op(v);
             }
         }
     }

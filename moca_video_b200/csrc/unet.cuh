@@ -18,7 +18,7 @@
 namespace moca {
 
 struct PackedW {               // bf16 [N, taps*Kp]
-    __nv_bfloat16* w = nullptr;
+    op_t* w = nullptr;
     float* b = nullptr;        // fp32 [N] or null
     int N = 0, K = 0, Kp = 0, taps = 1;
 };
@@ -67,7 +67,7 @@ struct BlockW {
 struct LoadSlot {
     enum Kind { COPY_F32, PACK } kind = COPY_F32;
     float* dst_f32 = nullptr;
-    __nv_bfloat16* dst = nullptr;
+    op_t* dst = nullptr;
     int N = 0, K = 0, taps = 1, Kp = 0, row0 = 0, geglu_bn = 0;
     int64_t pitch = 0;
     int64_t numel = 0;

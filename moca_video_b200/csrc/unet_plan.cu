@@ -124,7 +124,7 @@ struct Builder {
                  L.p.num_m_tiles * L.p.num_n_tiles, d.epi, d.mode);
         raw_push([L](cudaStream_t st) { return gemm_run(L, st); }, buf, useful_flops);
     }
-    void linear(const __nv_bfloat16* A, int64_t rows, int K, const PackedW& w, int epi, void* out, int ldo, const float* residual,
+    void linear(const op_t* A, int64_t rows, int K, const PackedW& w, int epi, void* out, int ldo, const float* residual,
                 int n_override = 0, const StatSrc* ss = nullptr, int rpf = 0) {
         GemmDesc d;
         d.A = A; d.a_rows = rows; d.a_cols = K; d.a_pitch = K;
@@ -134,7 +134,7 @@ struct Builder {
         d.stat_rows_per_frame = rpf; d.stat_sample_rows = T * rpf;
         gemm(d, 2.0 * rows * d.N * K);
     }
-    void conv3x3(const __nv_bfloat16* pad, int H, int W, int Cin, const PackedW& w, int stride, float* out, const float* rowbias,
+    void conv3x3(const op_t* pad, int H, int W, int Cin, const PackedW& w, int stride, float* out, const float* rowbias,
                  int rb_ld, const float* residual, const StatSrc* ss) {
         GemmDesc d;
         const int Hp = H + 2, Wp = W + 2;
@@ -149,7 +149,7 @@ struct Builder {
         d.stat_rows_per_frame = d.rows_per_frame; d.stat_sample_rows = T * Hp * Wp;
         gemm(d, 2.0 * NF * (H / stride) * (W / stride) * w.N * 9.0 * w.K);
     }
-    void tconv(const __nv_bfloat16* padT, int HW, int C, const PackedW& w, float* out, const float* residual, const StatSrc* ss) {
+    void tconv(const op_t* padT, int HW, int C, const PackedW& w, float* out, const float* residual, const StatSrc* ss) {
         GemmDesc d;
         d.A = padT; d.a_rows = (int64_t)B * (T + 2) * HW; d.a_cols = C; d.a_pitch = C;
         d.Wt = w.w; d.N = w.N; d.ntaps = 3; d.Kp = w.Kp;
@@ -163,7 +163,7 @@ struct Builder {
 
     // ---- normalisation flavours ----------------------------------------------------------------------------
     void gnorm(const float* x1, const StatSrc& s1, int C1, const float* x2, const StatSrc& s2in, int C2, int64_t rows, int rows_per_stat,
-               const NormW& w, float eps, int silu, int dst_mode, int H, int W, __nv_bfloat16* dst, __nv_bfloat16* raw) {
+               const NormW& w, float eps, int silu, int dst_mode, int H, int W, op_t* dst, op_t* raw) {
         const int slot = stat_slot();
         float2* table = dry ? nullptr : plan->mr_table + (size_t)slot * NF * 32;
         const int nstat = (int)(rows / rows_per_stat), fps = rows_per_stat / (H * W), rpf = H * W, Tn = T;
@@ -182,14 +182,14 @@ struct Builder {
         push([=](cudaStream_t st) { return gn_finalize(s1, s2, nstat, fps, Tn, rpf, eps, table, st, gam, bet, ab); }, 1, "gn_finalize" + dims);
         push([=](cudaStream_t st) { return gn_apply(a, st); }, 1, "gn_apply" + dims);
     }
-    void convert(const float* x, int C, int64_t rows, int dst_mode, int H, int W, __nv_bfloat16* dst) {
+    void convert(const float* x, int C, int64_t rows, int dst_mode, int H, int W, op_t* dst) {
         ApplyArgs a;
         a.x1 = x; a.C1 = C; a.rows = rows; a.rows_per_stat = 0; a.dst_mode = dst_mode;
         a.NF = NF; a.H = H; a.W = W; a.B = B; a.T = T; a.HW = H * W; a.dst = dst;
         push([=](cudaStream_t st) { return gn_apply(a, st); }, 1, "convert rows=" + std::to_string(rows) + " C=" + std::to_string(C) + " dst=" + std::to_string(dst_mode));
     }
-    void lnorm(const float* x, const NormW& w, int64_t rows, int C, __nv_bfloat16* out) {
-        push([=](cudaStream_t st) { return layernorm_bf16(x, w.g, w.b, rows, C, out, st); }, 1, "layernorm rows=" + std::to_string(rows) + " C=" + std::to_string(C));
+    void lnorm(const float* x, const NormW& w, int64_t rows, int C, op_t* out) {
+        push([=](cudaStream_t st) { return layernorm_op16(x, w.g, w.b, rows, C, out, st); }, 1, "layernorm rows=" + std::to_string(rows) + " C=" + std::to_string(C));
     }
     void tap(const std::string& name, const Act& a) {
         if (!plan->with_taps) return;
@@ -208,7 +208,7 @@ struct Builder {
     }
 
     Act res_block(const LayerW& L, const Act& x, const Act* skip, const float* embout);
-    void transformer(const LayerW& L, Act& x, const __nv_bfloat16* kv);
+    void transformer(const LayerW& L, Act& x, const op_t* kv);
     void build();
 };
 
@@ -223,8 +223,8 @@ Act Builder::res_block(const LayerW& L, const Act& x, const Act* skip, const flo
     if (Cin != r.cin) { set_error("plan: %s expects %d input channels, got %d", L.name.c_str(), r.cin, Cin); fail(MOCA_E_SHAPE); }
     if (skip && !r.has_skip) { set_error("plan: %s concatenates a skip tensor but has an identity skip_connection", L.name.c_str()); fail(MOCA_E_SHAPE); }
     const size_t pad_elems = (size_t)NF * (H + 2) * (W + 2);
-    __nv_bfloat16* pad = scratch<__nv_bfloat16>(S_PAD, pad_elems * (Cin > r.cout ? Cin : r.cout));
-    __nv_bfloat16* raw = r.has_skip ? scratch<__nv_bfloat16>(S_RAW, (size_t)rows * Cin) : nullptr;
+    op_t* pad = scratch<op_t>(S_PAD, pad_elems * (Cin > r.cout ? Cin : r.cout));
+    op_t* raw = r.has_skip ? scratch<op_t>(S_RAW, (size_t)rows * Cin) : nullptr;
     float* t1 = scratch<float>(S_F32A, (size_t)rows * r.cout);
     float* t2 = scratch<float>(S_F32B, (size_t)rows * r.cout);
     Act out;
@@ -245,7 +245,7 @@ Act Builder::res_block(const LayerW& L, const Act& x, const Act* skip, const flo
     }
     // TemporalConvBlock: 4 x [GN over (C/32, T, H, W) -> SiLU -> Conv3d (3,1,1)] + identity
     const size_t padt_elems = (size_t)B * (T + 2) * HW * r.cout;
-    __nv_bfloat16* padT = scratch<__nv_bfloat16>(S_PAD, padt_elems);
+    op_t* padT = scratch<op_t>(S_PAD, padt_elems);
     const float* src = out.p;
     float* dsts[4] = {t1, t2, t1, out.p};
     for (int i = 0; i < 4; ++i) {
@@ -261,17 +261,17 @@ Act Builder::res_block(const LayerW& L, const Act& x, const Act* skip, const flo
 
 // SpatialTransformer.forward (attention.py:262-278) / TemporalTransformer.forward (:331-373) with one
 // BasicTransformerBlock (:216-220): x += attn1(LN1 x); x += attn2(LN2 x, ctx); x += ff(LN3 x).  Runs in place on x.
-void Builder::transformer(const LayerW& L, Act& x, const __nv_bfloat16* kv) {
+void Builder::transformer(const LayerW& L, Act& x, const op_t* kv) {
     const TfW& t = L.tf;
     scope = L.name;
     const int H = x.H, W = x.W, HW = H * W;
     const int64_t rows = (int64_t)NF * HW;
     const int C = t.C, I = t.inner;
     if (x.C != C) { set_error("plan: %s expects %d channels, got %d", L.name.c_str(), C, x.C); fail(MOCA_E_SHAPE); }
-    __nv_bfloat16* lin = scratch<__nv_bfloat16>(S_LIN, (size_t)rows * (C > I ? C : I));
-    __nv_bfloat16* qkv = scratch<__nv_bfloat16>(S_QKV, (size_t)rows * 3 * I);
-    __nv_bfloat16* att = scratch<__nv_bfloat16>(S_ATT, (size_t)rows * I);
-    __nv_bfloat16* ffh = scratch<__nv_bfloat16>(S_FFH, (size_t)rows * 4 * I);
+    op_t* lin = scratch<op_t>(S_LIN, (size_t)rows * (C > I ? C : I));
+    op_t* qkv = scratch<op_t>(S_QKV, (size_t)rows * 3 * I);
+    op_t* att = scratch<op_t>(S_ATT, (size_t)rows * I);
+    op_t* ffh = scratch<op_t>(S_FFH, (size_t)rows * 4 * I);
     float* y = scratch<float>(S_Y, (size_t)rows * I);
     // norm (GroupNorm eps 1e-6; spatial: per frame, temporal: 5-D input so statistics span all T frames)
     gnorm(x.p, x.st, C, nullptr, StatSrc(), 0, rows, t.spatial ? HW : T * HW, t.gn, 1e-6f, 0, DST_LINEAR, H, W, lin, nullptr);
@@ -361,16 +361,16 @@ void Builder::build() {
     plan->d_fps = (int*)palloc(128 * sizeof(int));
     plan->d_ctxlen = (int*)palloc(16 * sizeof(int));
     plan->out_tok = (float*)palloc((size_t)rows0 * n->out_ch * sizeof(float));
-    __nv_bfloat16* te_bf = (__nv_bfloat16*)palloc((size_t)NF * mc * 2);
-    __nv_bfloat16* fe_bf = (__nv_bfloat16*)palloc((size_t)NF * mc * 2);
+    op_t* te_bf = (op_t*)palloc((size_t)NF * mc * 2);
+    op_t* fe_bf = (op_t*)palloc((size_t)NF * mc * 2);
     float* e1 = (float*)palloc((size_t)NF * te * 4);
-    __nv_bfloat16* e1_bf = (__nv_bfloat16*)palloc((size_t)NF * te * 2);
+    op_t* e1_bf = (op_t*)palloc((size_t)NF * te * 2);
     float* temb = (float*)palloc((size_t)NF * te * 4);
     float* femb = (float*)palloc((size_t)NF * te * 4);
-    __nv_bfloat16* semb = (__nv_bfloat16*)palloc((size_t)NF * te * 2);
+    op_t* semb = (op_t*)palloc((size_t)NF * te * 2);
     float* embout = (float*)palloc((size_t)NF * n->n_emb * 4);
-    __nv_bfloat16* ctx_bf = (__nv_bfloat16*)palloc((size_t)B * Lmax * n->ctx_dim * 2);
-    __nv_bfloat16* kv = (__nv_bfloat16*)palloc((size_t)B * Lmax * (n->n_kv > 0 ? n->n_kv : 16) * 2);
+    op_t* ctx_bf = (op_t*)palloc((size_t)B * Lmax * n->ctx_dim * 2);
+    op_t* kv = (op_t*)palloc((size_t)B * Lmax * (n->n_kv > 0 ? n->n_kv : 16) * 2);
     scope = "embed";
     if (!dry) {
         double* stats = plan->stats;
@@ -404,7 +404,7 @@ void Builder::build() {
     Act cur;
     cur.C = mc; cur.H = H0; cur.W = W0;
     {
-        __nv_bfloat16* pad = scratch<__nv_bfloat16>(S_PAD, (size_t)NF * (H0 + 2) * (W0 + 2) * 64);
+        op_t* pad = scratch<op_t>(S_PAD, (size_t)NF * (H0 + 2) * (W0 + 2) * 64);
         const float* x_in = plan->x_in;
         const int b = B, c = n->in_ch, t = T, h = H0, w = W0;
         push([=](cudaStream_t st) { return ncthw_to_pad(x_in, b, c, t, h, w, 64, pad, st); });
@@ -424,7 +424,7 @@ void Builder::build() {
             } else if (L.kind == "down") {
                 scope = L.name;
                 const int64_t rows = (int64_t)NF * cur.H * cur.W;
-                __nv_bfloat16* pad = scratch<__nv_bfloat16>(S_PAD, (size_t)NF * (cur.H + 2) * (cur.W + 2) * cur.C);
+                op_t* pad = scratch<op_t>(S_PAD, (size_t)NF * (cur.H + 2) * (cur.W + 2) * cur.C);
                 convert(cur.p, cur.C, rows, DST_SPATIAL_PAD, cur.H, cur.W, pad);
                 Act o; o.C = L.cout; o.H = cur.H / 2; o.W = cur.W / 2;
                 o.p = (float*)palloc((size_t)NF * o.H * o.W * o.C * 4);
@@ -435,7 +435,7 @@ void Builder::build() {
                 scope = L.name;
                 const int64_t rows = (int64_t)NF * cur.H * cur.W;
                 const int H2 = cur.H * 2, W2 = cur.W * 2;
-                __nv_bfloat16* pad = scratch<__nv_bfloat16>(S_PAD, (size_t)NF * (H2 + 2) * (W2 + 2) * cur.C);
+                op_t* pad = scratch<op_t>(S_PAD, (size_t)NF * (H2 + 2) * (W2 + 2) * cur.C);
                 convert(cur.p, cur.C, rows, DST_SPATIAL_PAD_UP2, cur.H, cur.W, pad);
                 Act o; o.C = L.cout; o.H = H2; o.W = W2;
                 o.p = (float*)palloc((size_t)NF * H2 * W2 * o.C * 4);
@@ -463,7 +463,7 @@ void Builder::build() {
     scope = "out";
     {
         const int64_t rows = rows0;
-        __nv_bfloat16* pad = scratch<__nv_bfloat16>(S_PAD, (size_t)NF * (H0 + 2) * (W0 + 2) * cur.C);
+        op_t* pad = scratch<op_t>(S_PAD, (size_t)NF * (H0 + 2) * (W0 + 2) * cur.C);
         gnorm(cur.p, cur.st, cur.C, nullptr, StatSrc(), 0, rows, H0 * W0, n->gn_out, 1e-5f, 1, DST_SPATIAL_PAD, H0, W0, pad, nullptr);
         conv3x3(pad, H0, W0, cur.C, n->conv_out, 1, plan->out_tok, nullptr, 0, nullptr, nullptr);
     }

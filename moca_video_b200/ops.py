@@ -12,6 +12,11 @@ from . import _lib
 from ._lib import check, ctx, host_f32, host_i32, lib, ptr, stream_ptr
 
 
+def op_dtype():
+    """torch dtype of the library's 16-bit operand buffers (moca_operand_dtype: fp16 by default, bf16 with -DMOCA_OPERAND_BF16)."""
+    return torch.bfloat16 if lib().moca_operand_dtype() == 1 else torch.float16
+
+
 def _f32c(t, name):
     if not (isinstance(t, torch.Tensor) and t.is_cuda):
         raise _lib.MocaError(f"{name} must be a CUDA tensor (no CPU path exists)")
@@ -183,19 +188,19 @@ def freq_mix_3d(x, noise, lpf):
 
 
 # ---- unit-test primitives -------------------------------------------------------------------------------------
-def gemm_bf16(a, w, bias=None, out_bf16=False):
+def gemm_op16(a, w, bias=None, out_op16=False):
     M, K = a.shape
     N = w.shape[0]
-    out = torch.empty((M, N), device=a.device, dtype=torch.bfloat16 if out_bf16 else torch.float32)
+    out = torch.empty((M, N), device=a.device, dtype=op_dtype() if out_op16 else torch.float32)
     with torch.cuda.device(a.device):
-        check(lib().moca_gemm_bf16(ctx(a.device.index), ptr(a), ptr(w), ptr(bias), M, N, K, ptr(out), int(out_bf16), stream_ptr()))
+        check(lib().moca_gemm_op16(ctx(a.device.index), ptr(a), ptr(w), ptr(bias), M, N, K, ptr(out), int(out_op16), stream_ptr()))
     return out
 
 
 def geglu(a_bf16, w, bias):
     M, K = a_bf16.shape
     N = w.shape[0]
-    out = torch.empty((M, N // 2), device=a_bf16.device, dtype=torch.bfloat16)
+    out = torch.empty((M, N // 2), device=a_bf16.device, dtype=op_dtype())
     with torch.cuda.device(a_bf16.device):
         check(lib().moca_geglu_f32(ctx(a_bf16.device.index), ptr(a_bf16), ptr(w), ptr(bias), M, N, K, ptr(out), stream_ptr()))
     return out
@@ -219,28 +224,28 @@ def tconv_tokens(x, w, bias):
     return y
 
 
-def groupnorm_bf16(x, gamma, beta, rows_per_stat, eps, silu):
+def groupnorm_op16(x, gamma, beta, rows_per_stat, eps, silu):
     rows, Cc = x.shape
-    out = torch.empty((rows, Cc), device=x.device, dtype=torch.bfloat16)
+    out = torch.empty((rows, Cc), device=x.device, dtype=op_dtype())
     with torch.cuda.device(x.device):
-        check(lib().moca_groupnorm_bf16(ctx(x.device.index), ptr(x), ptr(gamma), ptr(beta), rows, Cc, rows_per_stat, float(eps),
+        check(lib().moca_groupnorm_op16(ctx(x.device.index), ptr(x), ptr(gamma), ptr(beta), rows, Cc, rows_per_stat, float(eps),
                                         int(silu), ptr(out), stream_ptr()))
     return out
 
 
-def layernorm_bf16(x, gamma, beta):
+def layernorm_op16(x, gamma, beta):
     rows, Cc = x.shape
-    out = torch.empty((rows, Cc), device=x.device, dtype=torch.bfloat16)
+    out = torch.empty((rows, Cc), device=x.device, dtype=op_dtype())
     with torch.cuda.device(x.device):
-        check(lib().moca_layernorm_bf16(ctx(x.device.index), ptr(x), ptr(gamma), ptr(beta), rows, Cc, ptr(out), stream_ptr()))
+        check(lib().moca_layernorm_op16(ctx(x.device.index), ptr(x), ptr(gamma), ptr(beta), rows, Cc, ptr(out), stream_ptr()))
     return out
 
 
-def attention_bf16(q, k, v, batch, heads, Lq, Lk, Lk_valid=None, temporal_inner=0):
+def attention_op16(q, k, v, batch, heads, Lq, Lk, Lk_valid=None, temporal_inner=0):
     """q [batch*Lq, heads*64], k/v [batch*Lk, heads*64] bf16 (row pitch = tensor stride(0))."""
-    out = torch.empty((q.shape[0], heads * 64), device=q.device, dtype=torch.bfloat16)
+    out = torch.empty((q.shape[0], heads * 64), device=q.device, dtype=op_dtype())
     with torch.cuda.device(q.device):
-        check(lib().moca_attention_bf16(ctx(q.device.index), ptr(q), ptr(k), ptr(v), batch, heads, Lq, Lk,
+        check(lib().moca_attention_op16(ctx(q.device.index), ptr(q), ptr(k), ptr(v), batch, heads, Lq, Lk,
                                         Lk if Lk_valid is None else Lk_valid, q.stride(0), k.stride(0), ptr(out), out.stride(0),
                                         int(temporal_inner), stream_ptr()))
     return out

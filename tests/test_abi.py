@@ -36,7 +36,7 @@ def test_ctypes_table_matches_header(built):
     from moca_video_b200 import _lib
     assert sorted(_lib.SIGNATURES) == header_functions()
     _lib.lib()
-    assert _lib.lib().moca_abi_version() == 1
+    assert _lib.lib().moca_abi_version() == 2
 
 
 def test_header_cites_reference_lines():

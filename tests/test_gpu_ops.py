@@ -33,30 +33,30 @@ GEMM_SHAPES = [(128, 128, 64), (1, 16, 64), (127, 144, 192), (256, 256, 128), (1
 def test_gemm_tcgen05(M, N, K):
     from moca_video_b200 import ops
     g = torch.Generator(device=DEV).manual_seed(M + N + K)
-    a = torch.randn(M, K, device=DEV, generator=g).bfloat16()
-    w = (torch.randn(N, K, device=DEV, generator=g) / K ** 0.5).bfloat16()
+    a = torch.randn(M, K, device=DEV, generator=g).to(ops.op_dtype())
+    w = (torch.randn(N, K, device=DEV, generator=g) / K ** 0.5).to(ops.op_dtype())
     b = torch.randn(N, device=DEV, generator=g)
     ref = a.float() @ w.float().t()
-    assert rel(ops.gemm_bf16(a, w, b, False), ref + b) < 2e-5
-    assert rel(ops.gemm_bf16(a, w, None, False), ref) < 2e-5
-    assert rel(ops.gemm_bf16(a, w, b, True), ref + b) < 4e-3
+    assert rel(ops.gemm_op16(a, w, b, False), ref + b) < 2e-5
+    assert rel(ops.gemm_op16(a, w, None, False), ref) < 2e-5
+    assert rel(ops.gemm_op16(a, w, b, True), ref + b) < 4e-3
 
 
 def test_gemm_rejects_bad_k():
     from moca_video_b200 import MocaError, ops
-    a = torch.zeros(8, 40, device=DEV).bfloat16()
+    a = torch.zeros(8, 40, device=DEV).to(ops.op_dtype())
     with pytest.raises(MocaError):
-        ops.gemm_bf16(a, a, None, False)
+        ops.gemm_op16(a, a, None, False)
 
 
 @pytest.mark.parametrize("M,N,K", [(3000, 2560, 320), (130, 512, 64), (640, 10240, 1280)])
 def test_geglu_epilogue(M, N, K):
     from moca_video_b200 import ops
     g = torch.Generator(device=DEV).manual_seed(5)
-    a = torch.randn(M, K, device=DEV, generator=g).bfloat16()
+    a = torch.randn(M, K, device=DEV, generator=g).to(ops.op_dtype())
     w = torch.randn(N, K, device=DEV, generator=g) / K ** 0.5
     b = torch.randn(N, device=DEV, generator=g)
-    h = a.float() @ w.bfloat16().float().t() + b
+    h = a.float() @ w.to(ops.op_dtype()).float().t() + b
     v, gate = h.chunk(2, dim=-1)
     assert rel(ops.geglu(a, w, b), v * F.gelu(gate)) < 4e-3
 
@@ -72,7 +72,7 @@ def test_conv3x3_implicit_gemm(NF, H, W, Ci, Co, s):
     x = torch.randn(NF, H, W, Ci, device=DEV, generator=g)
     w = torch.randn(Co, Ci, 3, 3, device=DEV, generator=g) / (9 * Ci) ** 0.5
     b = torch.randn(Co, device=DEV, generator=g)
-    ref = F.conv2d(x.bfloat16().float().permute(0, 3, 1, 2), w.bfloat16().float(), b, stride=s, padding=1).permute(0, 2, 3, 1)
+    ref = F.conv2d(x.to(ops.op_dtype()).float().permute(0, 3, 1, 2), w.to(ops.op_dtype()).float(), b, stride=s, padding=1).permute(0, 2, 3, 1)
     assert rel(ops.conv3x3_nhwc(x, w, b, s), ref) < 2e-5
 
 
@@ -83,8 +83,8 @@ def test_temporal_conv_implicit_gemm(B, T, HW, C):
     x = torch.randn(B, T, HW, C, device=DEV, generator=g)
     w = torch.randn(C, C, 3, 1, 1, device=DEV, generator=g) / (3 * C) ** 0.5
     b = torch.randn(C, device=DEV, generator=g)
-    x5 = x.bfloat16().float().permute(0, 3, 1, 2).reshape(B, C, T, HW, 1)
-    ref = F.conv3d(x5, w.bfloat16().float(), b, padding=(1, 0, 0)).reshape(B, C, T, HW).permute(0, 2, 3, 1)
+    x5 = x.to(ops.op_dtype()).float().permute(0, 3, 1, 2).reshape(B, C, T, HW, 1)
+    ref = F.conv3d(x5, w.to(ops.op_dtype()).float(), b, padding=(1, 0, 0)).reshape(B, C, T, HW).permute(0, 2, 3, 1)
     assert rel(ops.tconv_tokens(x, w, b), ref) < 2e-5
 
 
@@ -95,7 +95,7 @@ def test_groupnorm(NF, HW, C, span, eps, silu):
     g = torch.Generator(device=DEV).manual_seed(C)
     x = torch.randn(NF * HW, C, device=DEV, generator=g) * 2 + 0.5
     ga = torch.randn(C, device=DEV, generator=g); be = torch.randn(C, device=DEV, generator=g)
-    y = ops.groupnorm_bf16(x, ga, be, HW * span, eps, silu)
+    y = ops.groupnorm_op16(x, ga, be, HW * span, eps, silu)
     ref = F.group_norm(x.reshape(NF // span, span * HW, C).permute(0, 2, 1), 32, ga, be, eps)
     ref = (F.silu(ref) if silu else ref).permute(0, 2, 1).reshape(NF * HW, C)
     assert rel(y, ref) < 4e-3
@@ -107,7 +107,7 @@ def test_layernorm(rows, C):
     g = torch.Generator(device=DEV).manual_seed(rows)
     x = torch.randn(rows, C, device=DEV, generator=g) * 3 + 1
     ga = torch.randn(C, device=DEV, generator=g); be = torch.randn(C, device=DEV, generator=g)
-    assert rel(ops.layernorm_bf16(x, ga, be), F.layer_norm(x, (C,), ga, be, 1e-5)) < 4e-3
+    assert rel(ops.layernorm_op16(x, ga, be), F.layer_norm(x, (C,), ga, be, 1e-5)) < 4e-3
 
 
 def _ref_attn(q, k, v, batch, heads, Lq, Lk, Lv):
@@ -124,10 +124,10 @@ def _ref_attn(q, k, v, batch, heads, Lq, Lk, Lv):
 def test_attention_flash(batch, heads, Lq, Lk, Lv):
     from moca_video_b200 import ops
     g = torch.Generator(device=DEV).manual_seed(Lq + Lk)
-    q = torch.randn(batch * Lq, heads * 64, device=DEV, generator=g).bfloat16()
-    k = torch.randn(batch * Lk, heads * 64, device=DEV, generator=g).bfloat16()
-    v = torch.randn(batch * Lk, heads * 64, device=DEV, generator=g).bfloat16()
-    assert rel(ops.attention_bf16(q, k, v, batch, heads, Lq, Lk, Lv), _ref_attn(q, k, v, batch, heads, Lq, Lk, Lv)) < 5e-3
+    q = torch.randn(batch * Lq, heads * 64, device=DEV, generator=g).to(ops.op_dtype())
+    k = torch.randn(batch * Lk, heads * 64, device=DEV, generator=g).to(ops.op_dtype())
+    v = torch.randn(batch * Lk, heads * 64, device=DEV, generator=g).to(ops.op_dtype())
+    assert rel(ops.attention_op16(q, k, v, batch, heads, Lq, Lk, Lv), _ref_attn(q, k, v, batch, heads, Lq, Lk, Lv)) < 5e-3
 
 
 @pytest.mark.parametrize("B,T,HW,heads", [(1, 16, 40, 5), (2, 16, 160, 20), (1, 4, 64, 1), (1, 16, 2560, 5), (1, 1, 7, 2)])
@@ -136,9 +136,9 @@ def test_attention_temporal(B, T, HW, heads):
     from moca_video_b200 import ops
     C = heads * 64
     g = torch.Generator(device=DEV).manual_seed(T * HW)
-    qkv = torch.randn(B * T * HW, 3 * C, device=DEV, generator=g).bfloat16()
+    qkv = torch.randn(B * T * HW, 3 * C, device=DEV, generator=g).to(ops.op_dtype())
     q, k, v = qkv[:, :C], qkv[:, C:2 * C], qkv[:, 2 * C:]
-    y = ops.attention_bf16(q, k, v, B * HW, heads, T, T, T, temporal_inner=HW)
+    y = ops.attention_op16(q, k, v, B * HW, heads, T, T, T, temporal_inner=HW)
     perm = lambda t: t.float().reshape(B, T, HW, C).permute(0, 2, 1, 3).reshape(B * HW * T, C)
     r = _ref_attn(perm(q), perm(k), perm(v), B * HW, heads, T, T, T).reshape(B, HW, T, C).permute(0, 2, 1, 3).reshape(B * T * HW, C)
     assert rel(y, r) < 5e-3
@@ -156,10 +156,10 @@ sys.path.insert(0, {root!r})
 from moca_video_b200 import ops
 torch.backends.cuda.matmul.allow_tf32 = False
 g = torch.Generator(device="cuda").manual_seed(1)
-a = torch.randn({M}, {K}, device="cuda", generator=g).bfloat16()
-w = (torch.randn({N}, {K}, device="cuda", generator=g) / {K} ** 0.5).bfloat16()
+a = torch.randn({M}, {K}, device="cuda", generator=g).to(ops.op_dtype())
+w = (torch.randn({N}, {K}, device="cuda", generator=g) / {K} ** 0.5).to(ops.op_dtype())
 b = torch.randn({N}, device="cuda", generator=g)
-y = ops.gemm_bf16(a, w, b, False)
+y = ops.gemm_op16(a, w, b, False)
 ref = a.float() @ w.float().t() + b
 print("REL", float((y - ref).norm() / ref.norm()))
 """

@@ -8,11 +8,11 @@ import torch, torch.nn.functional as F
 from moca_video_b200 import ops
 g = torch.Generator(device='cuda').manual_seed(5)
 for M,N,K in [(3000,2560,320),(640,10240,1280)]:
-    a = torch.randn(M, K, device='cuda', generator=g).bfloat16()
+    a = torch.randn(M, K, device='cuda', generator=g).to(ops.op_dtype())
     w = torch.randn(N, K, device='cuda', generator=g) / K ** 0.5
     b = torch.randn(N, device='cuda', generator=g)
-    h = a.float() @ w.bfloat16().float().t() + b
+    h = a.float() @ w.to(ops.op_dtype()).float().t() + b
     v, gate = h.chunk(2, dim=-1)
     ref = v * F.gelu(gate); out = ops.geglu(a, w, b).float()
-    refb = ref.bfloat16().float()
+    refb = ref.to(ops.op_dtype()).float()
     print(M,N,K,'rel', ((out-ref).norm()/ref.norm()).item(), 'bf16-rounding-only rel', ((refb-ref).norm()/ref.norm()).item(), 'maxabs', (out-ref).abs().max().item())

@@ -88,24 +88,24 @@ def sec_gemm():
     g = torch.Generator(device=dev).manual_seed(0)
     for (M, N, K) in [(128, 128, 64), (128, 128, 256), (256, 256, 128), (1000, 320, 320), (77, 2560, 1024), (16, 1280, 320),
                       (2560, 3840, 1280), (40960, 320, 320), (3000, 640, 1920), (5000, 4, 320), (300, 160, 64), (40960, 960, 320)]:
-        a = torch.randn(M, K, device=dev, generator=g).bfloat16()
-        w = (torch.randn(N, K, device=dev, generator=g) / K ** 0.5).bfloat16()
+        a = torch.randn(M, K, device=dev, generator=g).to(ops.op_dtype())
+        w = (torch.randn(N, K, device=dev, generator=g) / K ** 0.5).to(ops.op_dtype())
         b = torch.randn(N, device=dev, generator=g)
         ref = a.float() @ w.float().t() + b
         try:
-            y = ops.gemm_bf16(a, w, b, False)
+            y = ops.gemm_op16(a, w, b, False)
             torch.cuda.synchronize()
-            yb = ops.gemm_bf16(a, w, None, True)
+            yb = ops.gemm_op16(a, w, None, True)
             torch.cuda.synchronize()
             print(f"gemm M{M} N{N} K{K}: fp32-out rel {rel(y, ref):.3e}  bf16-out rel {rel(yb, ref - b):.3e}")
         except Exception as e:  # noqa: BLE001
             print(f"gemm M{M} N{N} K{K}: EXC {e}")
             return
     M, K, N = 3000, 320, 2560
-    a = torch.randn(M, K, device=dev, generator=g).bfloat16()
+    a = torch.randn(M, K, device=dev, generator=g).to(ops.op_dtype())
     w = torch.randn(N, K, device=dev, generator=g) / K ** 0.5
     b = torch.randn(N, device=dev, generator=g)
-    h = a.float() @ w.bfloat16().float().t() + b
+    h = a.float() @ w.to(ops.op_dtype()).float().t() + b
     v, gate = h.chunk(2, dim=-1)
     ref = v * torch.nn.functional.gelu(gate)
     y = ops.geglu(a, w, b)
@@ -120,7 +120,7 @@ def sec_conv():
         x = torch.randn(NF, H, W, Ci, device=dev, generator=g)
         w = torch.randn(Co, Ci, 3, 3, device=dev, generator=g) / (9 * Ci) ** 0.5
         b = torch.randn(Co, device=dev, generator=g)
-        ref = F.conv2d(x.bfloat16().float().permute(0, 3, 1, 2), w.bfloat16().float(), b, stride=s, padding=1).permute(0, 2, 3, 1)
+        ref = F.conv2d(x.to(ops.op_dtype()).float().permute(0, 3, 1, 2), w.to(ops.op_dtype()).float(), b, stride=s, padding=1).permute(0, 2, 3, 1)
         try:
             y = ops.conv3x3_nhwc(x, w, b, s)
             print(f"conv3x3 NF{NF} {H}x{W} {Ci}->{Co} s{s}: rel {rel(y, ref):.3e}")
@@ -131,8 +131,8 @@ def sec_conv():
         x = torch.randn(B, T, HW, C, device=dev, generator=g)
         w = torch.randn(C, C, 3, 1, 1, device=dev, generator=g) / (3 * C) ** 0.5
         b = torch.randn(C, device=dev, generator=g)
-        x5 = x.bfloat16().float().permute(0, 3, 1, 2).reshape(B, C, T, HW, 1)
-        ref = F.conv3d(x5, w.bfloat16().float(), b, padding=(1, 0, 0)).reshape(B, C, T, HW).permute(0, 2, 3, 1)
+        x5 = x.to(ops.op_dtype()).float().permute(0, 3, 1, 2).reshape(B, C, T, HW, 1)
+        ref = F.conv3d(x5, w.to(ops.op_dtype()).float(), b, padding=(1, 0, 0)).reshape(B, C, T, HW).permute(0, 2, 3, 1)
         y = ops.tconv_tokens(x, w, b)
         print(f"tconv B{B} T{T} HW{HW} C{C}: rel {rel(y, ref):.3e}")
 
@@ -144,7 +144,7 @@ def sec_norm():
                                                (2, 40, 2560, 2, 1e-5, 1), (8, 64, 64, 1, 1e-5, 1)]:
         x = torch.randn(NF * HW, C, device=dev, generator=g) * 2 + 0.5
         ga = torch.randn(C, device=dev, generator=g); be = torch.randn(C, device=dev, generator=g)
-        y = ops.groupnorm_bf16(x, ga, be, HW * rps_frames, eps, silu)
+        y = ops.groupnorm_op16(x, ga, be, HW * rps_frames, eps, silu)
         xr = x.reshape(NF // rps_frames, rps_frames * HW, C).permute(0, 2, 1)
         ref = F.group_norm(xr, 32, ga, be, eps)
         if silu:
@@ -154,7 +154,7 @@ def sec_norm():
     for (rows, C) in [(1000, 320), (333, 1280), (64, 64), (4096, 640), (100, 512)]:
         x = torch.randn(rows, C, device=dev, generator=g) * 3 + 1
         ga = torch.randn(C, device=dev, generator=g); be = torch.randn(C, device=dev, generator=g)
-        y = ops.layernorm_bf16(x, ga, be)
+        y = ops.layernorm_op16(x, ga, be)
         print(f"layernorm rows{rows} C{C}: rel {rel(y, F.layer_norm(x, (C,), ga, be, 1e-5)):.3e}")
 
 
@@ -170,11 +170,11 @@ def sec_attn():
 
     for (batch, heads, Lq, Lk, Lv) in [(2, 1, 64, 64, 64), (3, 5, 40, 40, 40), (2, 20, 160, 160, 160), (4, 10, 640, 640, 640),
                                        (2, 5, 2560, 2560, 2560), (4, 5, 640, 154, 77), (2, 20, 40, 77, 77), (2, 5, 100, 154, 154)]:
-        q = torch.randn(batch * Lq, heads * 64, device=dev, generator=g).bfloat16()
-        k = torch.randn(batch * Lk, heads * 64, device=dev, generator=g).bfloat16()
-        v = torch.randn(batch * Lk, heads * 64, device=dev, generator=g).bfloat16()
+        q = torch.randn(batch * Lq, heads * 64, device=dev, generator=g).to(ops.op_dtype())
+        k = torch.randn(batch * Lk, heads * 64, device=dev, generator=g).to(ops.op_dtype())
+        v = torch.randn(batch * Lk, heads * 64, device=dev, generator=g).to(ops.op_dtype())
         try:
-            y = ops.attention_bf16(q, k, v, batch, heads, Lq, Lk, Lv)
+            y = ops.attention_op16(q, k, v, batch, heads, Lq, Lk, Lv)
             print(f"attention b{batch} h{heads} Lq{Lq} Lk{Lk} valid{Lv}: rel {rel(y, ref_attn(q, k, v, batch, heads, Lq, Lk, Lv)):.3e}")
         except Exception as e:  # noqa: BLE001
             print(f"attention b{batch} h{heads} Lq{Lq} Lk{Lk}: EXC {e}")
@@ -182,9 +182,9 @@ def sec_attn():
     # temporal: rows ordered (b, t, hw); sequence o = (b, hw)
     for (B, T, HW, heads) in [(1, 16, 40, 5), (2, 16, 160, 20), (1, 4, 64, 1), (1, 16, 2560, 5)]:
         C = heads * 64
-        qkv = torch.randn(B * T * HW, 3 * C, device=dev, generator=g).bfloat16()
+        qkv = torch.randn(B * T * HW, 3 * C, device=dev, generator=g).to(ops.op_dtype())
         q, k, v = qkv[:, :C], qkv[:, C:2 * C], qkv[:, 2 * C:]
-        y = ops.attention_bf16(q, k, v, B * HW, heads, T, T, T, temporal_inner=HW)
+        y = ops.attention_op16(q, k, v, B * HW, heads, T, T, T, temporal_inner=HW)
         perm = lambda t: t.float().reshape(B, T, HW, C).permute(0, 2, 1, 3).reshape(B * HW * T, C)
         r = ref_attn(perm(q), perm(k), perm(v), B * HW, heads, T, T, T)
         r = r.reshape(B, HW, T, C).permute(0, 2, 1, 3).reshape(B * T * HW, C)

@@ -20,7 +20,7 @@ def timeit(fn, n=20):
 for rows, C in [(81920, 320), (20480, 640), (5120, 1280)]:
     x = torch.randn(rows, C, device=dev)
     ga = torch.randn(C, device=dev); be = torch.randn(C, device=dev)
-    us = timeit(lambda: ops.layernorm_bf16(x, ga, be))
+    us = timeit(lambda: ops.layernorm_op16(x, ga, be))
     print(f"layernorm rows={rows} C={C}: {us:7.1f} us  {rows * C * 6 / us / 1e3:7.0f} GB/s (incl. output allocation)")
-    us = timeit(lambda: ops.groupnorm_bf16(x, ga, be, rows // 32, 1e-5, 1))
+    us = timeit(lambda: ops.groupnorm_op16(x, ga, be, rows // 32, 1e-5, 1))
     print(f"groupnorm (stats + apply) rows={rows} C={C}: {us:7.1f} us  {rows * C * 10 / us / 1e3:7.0f} GB/s")
