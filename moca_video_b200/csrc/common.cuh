@@ -112,7 +112,7 @@ static inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 // the kernel, before any early return and before any global-memory access; it returns when all earlier kernels have
 // completed and their writes are visible.  MOCA_PDL=0 in the environment turns the attribute off (the instructions are
 // then no-ops).
-int pdl_level();      // MOCA_PDL: 0 off, 1 tensor-core kernels only, 2 every kernel
+int pdl_level();      // MOCA_PDL: 0 off, 1 tensor-core kernels only, 2 every kernel, 3 only the non-tensor-core (norm / glue) kernels
 #ifdef __CUDACC__
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
@@ -125,7 +125,8 @@ static inline cudaError_t launch_pdl_lvl(int level, void (*kernel)(KArgs...), di
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = pdl_level() >= level ? 1 : 0;
+    const int L = pdl_level();
+    cfg.numAttrs = (level == 2 ? (L >= 2) : (L == 1 || L == 2)) ? 1 : 0;
     return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 #define launch_pdl(...) launch_pdl_lvl(2, __VA_ARGS__)

@@ -14,17 +14,18 @@ constexpr int kABytes = kBM * kBK * 2;        // 16 KB, 128 rows of 128 B
 // TEPI: TMA-store epilogue variants.  fp32: 3 stages, per epilogue warp 4 KB output staging + two 4 KB residual buffers.
 // GEGLU: 16 epilogue warps (one 32-column output chunk each, the GELU arithmetic needs the extra warps to hide its
 // latencies), 2 KB bf16 staging per warp.
-template <int BN, bool TEPI = false, int EPI = EPI_F32, int NCTA = 1>
+// RES (bf16 thread = row epilogue only): a 16-bit residual chunk arrives by TMA in two more 2 KB boxes per warp.
+template <int BN, bool TEPI = false, int EPI = EPI_F32, int NCTA = 1, bool RES = false>
 struct GemmCfg {
     static constexpr bool GT = TEPI && EPI == EPI_GEGLU;
     static constexpr int B_BYTES = (BN / NCTA) * kBK * 2;                   // CTA pair: each CTA holds half of the B rows
     static constexpr int STAGE_BYTES = kABytes + B_BYTES;                   // multiple of 1024 for BN in {128, 160, 256}
     static constexpr bool BT = TEPI && EPI == EPI_BF16;      // bf16 thread = row epilogue: classic ring, two 2 KB staging boxes per warp
-    static constexpr int STAGES = NCTA == 2 ? 6 : (GT ? 4 : ((TEPI && !BT) ? (BN == 128 ? 4 : 3) : ((BN == 256) ? 4 : (BN == 160 ? 5 : 6))));
+    static constexpr int STAGES = NCTA == 2 ? 6 : (GT ? 4 : ((TEPI && !BT) ? (BN == 128 ? 4 : 3) : ((BN == 256) ? (RES ? 3 : 4) : (BN == 160 ? (RES ? 4 : 5) : (RES ? 5 : 6)))));
     static constexpr int TMEM_COLS = (2 * BN <= 256) ? 256 : 512;
     static constexpr int EPI_WARPS = GT ? 16 : 8;
     static constexpr int THREADS = 64 + 32 * EPI_WARPS;
-    static constexpr int WARP_STG = GT ? 2048 : ((TEPI && !BT) ? 12288 : 4096);      // epilogue staging per warp
+    static constexpr int WARP_STG = GT ? 2048 : ((TEPI && !BT) ? 12288 : (RES ? 8192 : 4096));      // epilogue staging per warp
     static constexpr int OFF_STG = STAGES * STAGE_BYTES;                    // 1024-byte aligned
     static constexpr int OFF_BAR = OFF_STG + EPI_WARPS * WARP_STG;
     static constexpr size_t SMEM = (size_t)OFF_BAR + 512 /*barriers*/ + 1024 /*align slack*/;
@@ -99,9 +100,11 @@ __device__ __forceinline__ bool map_row(const GemmParams& P, int row, int& out_r
     return true;
 }
 
+// STATS: GroupNorm statistics of the stored values (EPI_F32); for the bf16 thread = row epilogue (TEPI && EPI_BF16) the same
+// flag selects the variant that adds a 16-bit residual (RES16).
 template <int BN, int EPI, bool STATS, bool TEPI = false, int NCTA = 1>
-__global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA>::THREADS), 1) gemm_tc_kernel(const __grid_constant__ GemmParams P) {
-    using Cfg = GemmCfg<BN, TEPI, EPI, NCTA>;
+__global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == EPI_BF16 && STATS>::THREADS), 1) gemm_tc_kernel(const __grid_constant__ GemmParams P) {
+    using Cfg = GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == EPI_BF16 && STATS>;
     static_assert(EPI == EPI_F32 || EPI == EPI_GEGLU || EPI == EPI_BF16, "unknown epilogue");
     static_assert(NCTA == 1 || (NCTA == 2 && !TEPI && EPI == EPI_F32), "the CTA-pair shape exists for the staged fp32 epilogue");
     constexpr int STAGES = Cfg::STAGES;
@@ -275,10 +278,39 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA>::THREADS), 1) ge
         }
         if (lane == 0) bulk_wait0();
     } else if constexpr (TEPI && EPI == EPI_BF16) {
-        // ===== bf16 output, thread = row: TMEM -> (+ bias) -> bf16 row segment in one of two 32 x 64-byte staging boxes -> TMA store
+        // ===== 16-bit output, thread = row: TMEM -> (+ bias) (+ 16-bit residual) -> 16-bit row segment in one of two 32 x 64-byte
+        // staging boxes -> TMA store.  RES16: the residual chunk of the same rows / columns arrives by TMA in one of two more boxes,
+        // requested two chunks ahead (the output may alias the residual: a chunk is read before it is stored).
+        constexpr bool RES16 = STATS;
         const int w = warp - 2, q = warp & 3, half = w >> 2;
         uint8_t* stgb = base + Cfg::OFF_STG + (size_t)w * Cfg::WARP_STG;
+        uint64_t* rbar = rfull + 2 * w;
         constexpr int kChunks = BN / 32;
+        // the two warps of a lane quarter take alternate 32-column chunks; with an odd chunk count (BN = 160: 3 + 2) they swap
+        // roles from one tile of this CTA to the next, so that over two tiles (= the two accumulator stages) both do 5 chunks
+        auto first_chunk = [&](int t) { return (kChunks & 1) ? (half ^ (((t - tile0) / tstep) & 1)) : half; };
+        int pt = tile0, pc = first_chunk(tile0);
+        uint32_t n_issued = 0, n_waited = 0;
+        auto norm = [&](int& t, int& c) {
+            while (t < ntiles && !(c < kChunks && (t % P.num_n_tiles) * BN + c * 32 < P.N)) { t += tstep; c = first_chunk(t); }
+        };
+        auto issue_res = [&]() {                               // lane 0 only
+            while (pt < ntiles) {
+                const int prow0 = MT(pt) * kBM + q * 32;
+                const int pn0 = (pt % P.num_n_tiles) * BN + pc * 32;
+                pc += 2; norm(pt, pc);
+                if (prow0 >= P.M) continue;
+                const uint32_t slot = n_issued & 1u;
+                mbar_expect_tx(&rbar[slot], 2048);
+                tma_load_2d(stgb + 4096 + slot * 2048, &P.tmRes, &rbar[slot], pn0, prow0);
+                ++n_issued;
+                return;
+            }
+        };
+        if constexpr (RES16) {
+            norm(pt, pc);
+            if (lane == 0) { issue_res(); issue_res(); }
+        }
         int as = 0;
         uint32_t aphase = 0, nst = 0;
         for (int tile = tile0; tile < ntiles; tile += tstep) {
@@ -288,11 +320,13 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA>::THREADS), 1) ge
             tc_fence_after();
             const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN);
             if (row0 < P.M) {
-                for (int c = half; c < kChunks; c += 2) {
+                for (int c = first_chunk(tile); c < kChunks; c += 2) {
                     const int n0 = nt * BN + c * 32;
                     if (n0 >= P.N) break;
                     uint32_t r[32];
                     tmem_ld32(t_row + (uint32_t)(c * 32), r);
+                    const uint4* rsrc = reinterpret_cast<const uint4*>(stgb + 4096 + (n_waited & 1u) * 2048 + lane * 64);
+                    if constexpr (RES16) mbar_wait(&rbar[n_waited & 1u], (n_waited >> 1) & 1u);
                     if (lane == 0) bulk_wait_read1();          // the store issued two chunks ago has released this box
                     __syncwarp();
                     tmem_ld_wait();
@@ -308,6 +342,13 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA>::THREADS), 1) ge
                             v[0] += b1.x; v[1] += b1.y; v[2] += b1.z; v[3] += b1.w;
                             v[4] += b2.x; v[5] += b2.y; v[6] += b2.z; v[7] += b2.w;
                         }
+                        if constexpr (RES16) {
+                            const uint4 t4 = rsrc[u];
+                            const float2 f0 = op22float2(*reinterpret_cast<const op2_t*>(&t4.x)), f1 = op22float2(*reinterpret_cast<const op2_t*>(&t4.y));
+                            const float2 f2 = op22float2(*reinterpret_cast<const op2_t*>(&t4.z)), f3 = op22float2(*reinterpret_cast<const op2_t*>(&t4.w));
+                            v[0] += f0.x; v[1] += f0.y; v[2] += f1.x; v[3] += f1.y;
+                            v[4] += f2.x; v[5] += f2.y; v[6] += f3.x; v[7] += f3.y;
+                        }
                         dst[u] = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
                     }
                     fence_proxy_async_smem();
@@ -315,8 +356,10 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA>::THREADS), 1) ge
                     if (lane == 0) {
                         tma_store_2d(&P.tmOut, stgb + (nst & 1u) * 2048, n0, row0);
                         bulk_commit_group();
+                        if constexpr (RES16) issue_res();      // the residual box just read is free again
                     }
                     ++nst;
+                    if constexpr (RES16) ++n_waited;
                 }
             }
             tc_fence_before();
@@ -338,6 +381,7 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA>::THREADS), 1) ge
         uint64_t* rbar = rfull + 2 * w;
         constexpr int kChunks = BN / 32;
         const bool has_res = P.residual != nullptr;
+        const bool out16 = P.out16 != 0;
         // slice of 32 input-space rows -> first output row (or -1: padding frame / beyond M)
         auto slice_row = [&](int tile) -> int {
             const int row0 = MT(tile) * kBM + q * 32;
@@ -347,13 +391,15 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA>::THREADS), 1) ge
             const int a = r / P.g_w, b = r - a * P.g_w;
             return (a < 1 || a > P.g_H) ? -1 : (f * P.g_H + (a - 1)) * P.g_w + b;
         };
-        // chunk cursor: (tile, c) with c = half, half + 2, ..; normalised so that the chunk exists
+        // chunk cursor: (tile, c) with c = c0, c0 + 2, ..; normalised so that the chunk exists.  With an odd chunk count
+        // (BN = 160: 3 + 2) the two warps of a lane quarter swap roles from one tile of this CTA to the next.
+        auto first_chunk = [&](int t) { return (kChunks & 1) ? (half ^ (((t - tile0) / tstep) & 1)) : half; };
         auto norm = [&](int& t, int& c) {
-            while (t < ntiles && !(c < kChunks && (t % P.num_n_tiles) * BN + c * 32 < P.N)) { t += tstep; c = half; }
+            while (t < ntiles && !(c < kChunks && (t % P.num_n_tiles) * BN + c * 32 < P.N)) { t += tstep; c = first_chunk(t); }
         };
         auto next = [&](int& t, int& c) { c += 2; norm(t, c); };
         // producer cursor runs two loaded chunks ahead
-        int pt = tile0, pc = half;
+        int pt = tile0, pc = first_chunk(tile0);
         uint32_t n_issued = 0, n_waited = 0;
         norm(pt, pc);
         auto issue_res = [&]() {                               // lane 0 only
@@ -379,7 +425,7 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA>::THREADS), 1) ge
             tc_fence_after();
             const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN);
             if (orow0 >= 0) {
-                for (int c = half; c < kChunks; c += 2) {
+                for (int c = first_chunk(tile); c < kChunks; c += 2) {
                     const int n0 = col_tile0 + c * 32;
                     if (n0 >= P.N) break;
                     uint32_t r[32];
@@ -390,7 +436,7 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA>::THREADS), 1) ge
                     if (lane == 0) bulk_wait_read0();
                     __syncwarp();
                     tmem_ld_wait();
-                    uint8_t* dst = wbuf + lane * 128;
+                    uint8_t* dst = wbuf + (out16 ? lane * 64 : lane * 128);
 #pragma unroll
                     for (int j = 0; j < 8; ++j) {
                         float4 v = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]),
@@ -404,7 +450,9 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA>::THREADS), 1) ge
                             const float4 t4 = *reinterpret_cast<const float4*>(rsrc + sw);
                             v.x += t4.x; v.y += t4.y; v.z += t4.z; v.w += t4.w;
                         }
-                        *reinterpret_cast<float4*>(dst + sw) = v;
+                        // 16-bit output: plain 32 x 64-byte box (row = 32 op_t), else the 128-byte-swizzled fp32 box
+                        if (out16) *reinterpret_cast<uint2*>(dst + j * 8) = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
+                        else *reinterpret_cast<float4*>(dst + sw) = v;
                     }
                     fence_proxy_async_smem();
                     __syncwarp();
@@ -418,6 +466,26 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA>::THREADS), 1) ge
                         // lane = column: sum / sum of squares over the 32 rows of the staging box (conflict-free: one row per step)
                         // (same association as the staged epilogue: rows 4i + g summed over i for g = 0..3, then (p0 + p1) + (p2 + p3),
                         // so both epilogues give bit-identical statistics and the result does not depend on the tile width)
+                        // one statistics entry (frame or sample) per 32-row slice: stat_rpf % 32 == 0 (gemm_plan)
+                        double* dbase = P.cstat + ((size_t)(orow0 / P.stat_rpf) * P.N + n0) * 2;
+                        if (out16) {
+                            // statistics of the stored (rounded) values: lane = (column pair, row parity), 16 rows each (conflict-free:
+                            // even rows use banks 0-15, odd rows 16-31), parities combined by one shuffle
+                            const int cp = lane & 15, rp = lane >> 4;
+                            float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+#pragma unroll
+                            for (int i = 0; i < 16; ++i) {
+                                const float2 x = op22float2(*reinterpret_cast<const op2_t*>(wbuf + (2 * i + rp) * 64 + cp * 4));
+                                s0 += x.x; s1 += x.y;
+                                q0 = fmaf(x.x, x.x, q0); q1 = fmaf(x.y, x.y, q1);
+                            }
+                            s0 += __shfl_xor_sync(0xffffffffu, s0, 16); s1 += __shfl_xor_sync(0xffffffffu, s1, 16);
+                            q0 += __shfl_xor_sync(0xffffffffu, q0, 16); q1 += __shfl_xor_sync(0xffffffffu, q1, 16);
+                            // lanes 0-15 publish the sums, lanes 16-31 the sums of squares of their two columns
+                            double* d = dbase + (size_t)cp * 4 + rp;
+                            atomicAdd(d, (double)(rp ? q0 : s0));
+                            atomicAdd(d + 2, (double)(rp ? q1 : s1));
+                        } else {
                         float ps[4] = {0.f, 0.f, 0.f, 0.f}, pq[4] = {0.f, 0.f, 0.f, 0.f};
                         const int cj = lane >> 2, ce = (lane & 3) << 2;
 #pragma unroll
@@ -426,8 +494,10 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA>::THREADS), 1) ge
                             ps[rr & 3] += x;
                             pq[rr & 3] = fmaf(x, x, pq[rr & 3]);
                         }
-                        P.spart[(size_t)(MT(tile) * (kBM / 32) + q) * P.N + n0 + lane] =
-                            make_float2((ps[0] + ps[1]) + (ps[2] + ps[3]), (pq[0] + pq[1]) + (pq[2] + pq[3]));
+                        double* d = dbase + (size_t)lane * 2;
+                        atomicAdd(d, (double)((ps[0] + ps[1]) + (ps[2] + ps[3])));
+                        atomicAdd(d + 1, (double)((pq[0] + pq[1]) + (pq[2] + pq[3])));
+                        }
                     }
                 }
             }
@@ -465,7 +535,7 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA>::THREADS), 1) ge
                 const int fr = out_row / P.stat_rpf;
                 const int lo = __reduce_min_sync(0xffffffffu, valid ? fr : 0x7fffffff);
                 const int hi = __reduce_max_sync(0xffffffffu, valid ? fr : -1);
-                if (lo == hi && (P.stat_fast || P.spart)) frame_u = lo;
+                if (lo == hi && P.stat_fast) frame_u = lo;
             }
         };
         auto col0_of = [&](int tile) {
@@ -554,7 +624,15 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA>::THREADS), 1) ge
                         if (nvalid >= 4) {
                             v.x += b4.x; v.y += b4.y; v.z += b4.z; v.w += b4.w;
                             if (have_pre) { v.x += pre[i].x; v.y += pre[i].y; v.z += pre[i].z; v.w += pre[i].w; }
-                            *reinterpret_cast<float4*>(P.outf + o) = v;
+                            if (P.out16) {
+                                // statistics are those of the stored (rounded) values, as in the TMA-store epilogue
+                                const uint2 h = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
+                                *reinterpret_cast<uint2*>(P.outb + o) = h;
+                                const float2 lo = op22float2(*reinterpret_cast<const op2_t*>(&h.x)), hi = op22float2(*reinterpret_cast<const op2_t*>(&h.y));
+                                v = make_float4(lo.x, lo.y, hi.x, hi.y);
+                            } else {
+                                *reinterpret_cast<float4*>(P.outf + o) = v;
+                            }
                             vv[i] = v;
                         } else {                                     // ragged last columns (N % 4 != 0): scalar path
                             const float sv[4] = {v.x, v.y, v.z, v.w};
@@ -562,7 +640,8 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA>::THREADS), 1) ge
                                 float t = sv[e] + (P.bias ? P.bias[col + e] : 0.f);
                                 if (P.rowbias) t += P.rowbias[(size_t)(orow / P.rows_per_frame) * P.rb_ld + col + e];
                                 if (P.residual) t += P.residual[o + e];
-                                P.outf[o + e] = t;
+                                if (P.out16) P.outb[o + e] = float2op(t);
+                                else P.outf[o + e] = t;
                             }
                         }
                     }
@@ -587,12 +666,7 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA>::THREADS), 1) ge
                             const int e = lane >> 3;                   // lane group e publishes column col + e
                             const float s1 = e == 0 ? cs.x : (e == 1 ? cs.y : (e == 2 ? cs.z : cs.w));
                             const float s2 = e == 0 ? cq.x : (e == 1 ? cq.y : (e == 2 ? cq.z : cq.w));
-                            if (P.spart) {
-                                // partial-sum mode: one {sum, sumsq} per (32-row slice, column), plain coalesced stores;
-                                // gn_finalize adds the slices of a frame in a fixed order
-                                if (nvalid >= 4)
-                                    P.spart[(size_t)(MT(tile) * (kBM / 32) + q) * P.N + col + e] = make_float2(s1, s2);
-                            } else if (nvalid >= 4) {
+                            if (nvalid >= 4) {
                                 double* d = P.cstat + ((size_t)frame_u * P.N + col + e) * 2;
                                 atomicAdd(d, (double)s1);
                                 atomicAdd(d + 1, (double)s2);
@@ -690,6 +764,12 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA>::THREADS), 1) ge
                         } else {
 #pragma unroll
                             for (int e = 0; e < 8; ++e) v[e] += bb[e];
+                            if (P.res16) {
+                                const op_t* rr16 = P.res16 + (size_t)orow * P.ldo + col;
+#pragma unroll
+                                for (int e = 0; e < 8; ++e)
+                                    if (e < nvalid) v[e] += op2float(rr16[e]);
+                            }
                         }
                         op_t* o = P.outb + (size_t)orow * P.ldo + col;
                         if (nvalid >= 8) {
@@ -832,7 +912,7 @@ static int set_attr() {
     static bool done = false;
     if (!done) {
         MOCA_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI, STATS, TEPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)GemmCfg<BN, TEPI, EPI>::SMEM));
+                                             (int)GemmCfg<BN, TEPI, EPI, 1, TEPI && EPI == EPI_BF16 && STATS>::SMEM));
         done = true;
     }
     return MOCA_OK;
@@ -874,7 +954,11 @@ static int set_attr_bn(int epi, int tepi) {
         int rc = set_attr<BN, EPI_F32, true>();
         return rc ? rc : set_attr<BN, EPI_F32>();
     }
-    if (epi == EPI_BF16) return tepi ? set_attr<BN, EPI_BF16, false, true>() : set_attr<BN, EPI_BF16>();
+    if (epi == EPI_BF16) {
+        if (!tepi) return set_attr<BN, EPI_BF16>();
+        int rc = set_attr<BN, EPI_BF16, false, true>();
+        return rc ? rc : set_attr<BN, EPI_BF16, true, true>();
+    }
     if (tepi) {
         if constexpr (BN == 256) return set_attr<BN, EPI_GEGLU, false, true>();
     }
@@ -883,7 +967,7 @@ static int set_attr_bn(int epi, int tepi) {
 
 template <int BN>
 static void launch_bn(const GemmLaunch& l, cudaStream_t st) {
-    const bool stats = l.p.cstat || l.p.spart;
+    const bool stats = l.p.cstat != nullptr;
     if (l.p.ncta == 2) {
         if constexpr (BN != 128) {
             if (stats) launch_pair(gemm_tc_kernel<BN, EPI_F32, true, false, 2>, l.grid, kGemmThreads, l.smem, st, l.p);
@@ -896,6 +980,7 @@ static void launch_bn(const GemmLaunch& l, cudaStream_t st) {
         }
     } else if (l.p.epi == EPI_F32 && stats) launch_pdl_tc(gemm_tc_kernel<BN, EPI_F32, true>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
     else if (l.p.epi == EPI_F32) launch_pdl_tc(gemm_tc_kernel<BN, EPI_F32, false>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
+    else if (l.p.epi == EPI_BF16 && l.p.tepi && l.p.res16) launch_pdl_tc(gemm_tc_kernel<BN, EPI_BF16, true, true>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
     else if (l.p.epi == EPI_BF16 && l.p.tepi) launch_pdl_tc(gemm_tc_kernel<BN, EPI_BF16, false, true>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
     else if (l.p.epi == EPI_BF16) launch_pdl_tc(gemm_tc_kernel<BN, EPI_BF16, false>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
     else if (l.p.tepi) {
@@ -930,15 +1015,13 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
     p.mode = d.mode; p.g_rows = d.g_rows; p.g_w = d.g_w; p.g_H = d.g_H; p.g_W = d.g_W; p.stride = d.stride;
     p.outf = (float*)d.out; p.outb = (op_t*)d.out; p.ldo = d.ldo;
     p.bias = d.bias; p.rowbias = d.rowbias; p.rb_ld = d.rb_ld; p.rows_per_frame = d.rows_per_frame > 0 ? d.rows_per_frame : 1;
-    p.residual = d.residual; p.epi = d.epi;
+    p.residual = d.residual; p.res16 = d.residual16; p.epi = d.epi; p.out16 = d.out16;
+    MOCA_REQUIRE(!d.out16 || (d.epi == EPI_F32 && d.ldo % 4 == 0 && d.N % 4 == 0), MOCA_E_ARG, "gemm_plan: out16 needs the fp32 epilogue and 4-element aligned rows");
+    MOCA_REQUIRE(!d.residual16 || (d.epi == EPI_BF16 && !d.residual), MOCA_E_ARG, "gemm_plan: a 16-bit residual needs the 16-bit epilogue");
     p.cstat = d.chan_stats; p.stat_rpf = d.stat_rows_per_frame > 0 ? d.stat_rows_per_frame : 1;
     // fp32 warp-slice partial sums only when every sample starts on a 32-row slice boundary, so that the grouping (and
     // with it every rounding) is the same whatever the batch size; otherwise exact double partials
     p.stat_fast = d.stat_sample_rows > 0 && d.stat_sample_rows % 32 == 0;
-    p.spart = d.stat_partials;
-    MOCA_REQUIRE(!d.stat_partials || (!d.chan_stats && d.epi == EPI_F32 && d.N % 4 == 0 && d.stat_rows_per_frame % 32 == 0 &&
-                                      (d.mode == GEMM_LINEAR || (d.mode == GEMM_TIME_PAD && d.g_w % 32 == 0))),
-                 MOCA_E_ARG, "gemm_plan: slice partial statistics need 32-row aligned frames (linear / time-padded rows)");
     MOCA_REQUIRE(!d.chan_stats || (d.epi == EPI_F32 && d.N % 4 == 0 && d.stat_rows_per_frame > 0), MOCA_E_ARG,
                  "gemm_plan: channel statistics need the fp32 epilogue, N %% 4 == 0 and rows per frame");
     p.num_m_tiles = cdiv(d.M, kBM);
@@ -956,16 +1039,22 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
     static const int tepi_maxk128 = [] { const char* e = getenv("MOCA_GEMM_TEPI_MAXK128"); return e ? atoi(e) : 15; }();    // 4-stage ring
     const int tepi_maxk = L.BN == 128 ? tepi_maxk128 : tepi_maxk160;
     const bool rows_ok = (d.mode == GEMM_LINEAR && d.M % 32 == 0) || (d.mode == GEMM_TIME_PAD && d.g_w % 32 == 0 && d.g_rows % 32 == 0);
-    p.tepi = tepi_on && ncta == 1 && d.epi == EPI_F32 && L.BN != 256 && rows_ok && d.N % 32 == 0 && d.ldo % 4 == 0 && !d.rowbias && !d.chan_stats &&
+    p.tepi = tepi_on && ncta == 1 && d.epi == EPI_F32 && L.BN != 256 && rows_ok && d.N % 32 == 0 && d.ldo % 4 == 0 && (!d.out16 || d.ldo % 8 == 0) && !d.rowbias && (!d.chan_stats || d.stat_rows_per_frame % 32 == 0) &&
              d.ntaps * p.kblocks <= tepi_maxk && (((uintptr_t)d.out | (uintptr_t)d.residual | (uintptr_t)d.bias) & 15) == 0;
     const bool gt = tepi_on && d.epi == EPI_GEGLU && L.BN == 256 && d.mode == GEMM_LINEAR && d.M % 32 == 0 && (d.N / 2) % 32 == 0 &&
                     d.ldo % 8 == 0 && (((uintptr_t)d.out | (uintptr_t)d.bias) & 15) == 0;
     const bool bt = tepi_on && d.epi == EPI_BF16 && d.mode == GEMM_LINEAR && d.M % 32 == 0 && d.N % 32 == 0 && d.ldo % 8 == 0 &&
-                    (((uintptr_t)d.out | (uintptr_t)d.bias) & 15) == 0;
+                    (((uintptr_t)d.out | (uintptr_t)d.bias | (uintptr_t)d.residual16) & 15) == 0;
     if (bt) {
         p.tepi = 1;
         rc = make_tmap_bf16_chunk(&p.tmOut, d.out, d.M, d.N, d.ldo);
         if (rc) return rc;
+        if (d.residual16) {
+            rc = make_tmap_bf16_chunk(&p.tmRes, d.residual16, d.M, d.N, d.ldo);
+            if (rc) return rc;
+            L.smem = L.BN == 256 ? GemmCfg<256, true, EPI_BF16, 1, true>::SMEM
+                                 : (L.BN == 160 ? GemmCfg<160, true, EPI_BF16, 1, true>::SMEM : GemmCfg<128, true, EPI_BF16, 1, true>::SMEM);
+        } else
         L.smem = L.BN == 256 ? GemmCfg<256, true, EPI_BF16>::SMEM : (L.BN == 160 ? GemmCfg<160, true, EPI_BF16>::SMEM : GemmCfg<128, true, EPI_BF16>::SMEM);
     } else if (gt) {
         p.tepi = 1;
@@ -974,9 +1063,10 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
         L.smem = GemmCfg<256, true, EPI_GEGLU>::SMEM;
     } else if (p.tepi) {
         const int64_t out_rows = d.mode == GEMM_LINEAR ? d.M : (int64_t)(d.M / d.g_rows) * d.g_H * d.g_w;
-        rc = make_tmap_f32_chunk(&p.tmOut, d.out, out_rows, d.N, d.ldo);
+        rc = d.out16 ? make_tmap_bf16_chunk(&p.tmOut, d.out, out_rows, d.N, d.ldo) : make_tmap_f32_chunk(&p.tmOut, d.out, out_rows, d.N, d.ldo);
         if (rc) return rc;
-        rc = make_tmap_f32_chunk(&p.tmRes, d.residual ? (const void*)d.residual : d.out, out_rows, d.N, d.ldo);
+        if (d.out16 && !d.residual) p.tmRes = p.tmOut;      // never loaded from; keeps the prefetched descriptor valid
+        else rc = make_tmap_f32_chunk(&p.tmRes, d.residual ? (const void*)d.residual : d.out, out_rows, d.N, d.ldo);
         if (rc) return rc;
         L.smem = L.BN == 160 ? GemmCfg<160, true>::SMEM : GemmCfg<128, true>::SMEM;
     } else {

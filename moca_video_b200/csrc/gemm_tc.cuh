@@ -44,12 +44,13 @@ struct GemmParams {
     const float* rowbias;     // [frames, rb_ld] or null (ResBlock emb_layers output, openaimodel3d.py:221-226)
     int rb_ld, rows_per_frame;
     const float* residual;    // fp32 [out_rows, ldo] or null
+    const op_t* res16;        // EPI_BF16 only: 16-bit residual [out_rows, ldo] or null (may alias the output: in-place stream update)
     int epi;
+    int out16;                // EPI_F32 epilogues: store the result as op_t (outb) instead of fp32; statistics unchanged
     int num_m_tiles, num_n_tiles;
     double* cstat;            // optional per-(frame, output channel) {sum, sum of squares} of the stored fp32 values
     int stat_rpf;             // output rows per frame (frame = out_row / stat_rpf)
     int stat_fast;
-    float2* spart;            // optional {sum, sumsq} per (32-row slice of the input-row space, column): [ceil(M/32)][N]
 };
 
 struct GemmDesc {
@@ -63,17 +64,18 @@ struct GemmDesc {
     int g_rows = 0, g_w = 0, g_H = 0, g_W = 0, stride = 1;
     int M = 0;
     int epi = EPI_F32;
+    int out16 = 0;                    // EPI_F32 only: the fp32 epilogue (bias / row bias / residual / statistics) stores op_t
     void* out = nullptr;
     int ldo = 0;
     const float* bias = nullptr;
     const float* rowbias = nullptr;
     int rb_ld = 0, rows_per_frame = 1;
     const float* residual = nullptr;
+    const op_t* residual16 = nullptr; // EPI_BF16 only: out = op16(acc + bias + residual16); may alias out
     // EPI_F32 only: accumulate {sum, sumsq} of the stored values into chan_stats[frame][N][2] (doubles, zeroed by the
     // caller) — the GroupNorm that consumes this tensor needs no statistics pass of its own.
     double* chan_stats = nullptr;
     int stat_rows_per_frame = 0;
-    float2* stat_partials = nullptr;  // alternative to chan_stats for 32-row aligned frames: [ceil(M/32)][N] float2, no atomics
     int stat_sample_rows = 0;         // rows of one sample in the GEMM's input-row space (0: unknown -> exact double partials)
 };
 

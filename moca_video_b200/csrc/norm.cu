@@ -1,5 +1,6 @@
 // See norm.cuh.  All kernels here are bandwidth-bound: 16-byte vector accesses, channels-last (tokens x C) layout.
 #include <stdlib.h>
+#include <type_traits>
 #include "norm.cuh"
 #include "ptx.cuh"
 
@@ -154,79 +155,56 @@ int gn_stats(const float* x1, int C1, const float* x2, int C2, int64_t rows, int
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// GroupNorm statistics from what the GEMM epilogues left behind (gemm_tc.cuh): per-(frame, channel) {sum, sumsq} doubles
-// (atomic mode) or per-(32-row slice, channel) float2 partials (slice mode).  One block per (channel group, statistics
-// group); every thread adds a fixed strided subset in double, then a fixed-order block reduction -> (mean, rstd).
-__device__ __forceinline__ void stat_accumulate(const StatSrc& S, int c0, int c1, int stat, int fps, int T, double& s, double& q) {
-    const int nch = c1 - c0;
-    if (nch <= 0) return;
-    if (S.part) {
-        const int per_f = S.spf * nch, n = fps * per_f;
-        for (int i = threadIdx.x; i < n; i += blockDim.x) {
-            const int fl = i / per_f, r = i - fl * per_f;
-            const int k = r / nch, ch = c0 + r - k * nch;
-            const int f = stat * fps + fl;
-            const size_t slice = (size_t)((f / T) * S.tpad + (f % T) + S.toff) * S.spf + k;
-            const float2 v = __ldcg(S.part + slice * S.C + ch);
-            s += (double)v.x; q += (double)v.y;
-        }
-    } else {
-        const int n = fps * nch;
-        for (int i = threadIdx.x; i < n; i += blockDim.x) {
-            const int fl = i / nch, ch = c0 + i - fl * nch;
-            const double2 v = __ldcg(reinterpret_cast<const double2*>(S.cs) + (size_t)(stat * fps + fl) * S.C + ch);
-            s += v.x; q += v.y;
-        }
-    }
-}
-
-__global__ void __launch_bounds__(1024) gn_finalize_kernel(const StatSrc S1, const StatSrc S2, int frames_per_stat, int T,
-                                                          int rows_per_frame, float eps, float2* __restrict__ table,
-                                                          const float* __restrict__ gamma, const float* __restrict__ beta,
-                                                          float2* __restrict__ ab) {
+// GroupNorm statistics -> per-(statistics group, channel) (scale, shift) from what the GEMM epilogues left behind (gemm_tc.cuh):
+// {sum, sumsq} doubles per (frame, channel).  One warp per (channel group, statistics group): lanes add a fixed strided subset
+// of the group's channels x frames in double, xor-shuffle + fixed-order block reduction, then write (rstd * gamma, beta - mean * rstd *
+// gamma) for the group's channels.  The channel groups are those of the virtual concat of the two sources.
+__global__ void __launch_bounds__(128) gn_finalize_kernel(const double2* __restrict__ cs1, int C1, const double2* __restrict__ cs2, int C2,
+                                                         int fps, double inv_cnt, float eps,
+                                                         const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                         float2* __restrict__ ab) {
     pdl_wait();
     pdl_launch_dependents();
-    __shared__ double red[2][32];
-    __shared__ float s_mr[2];
+    __shared__ double red[2][4];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int g = blockIdx.x, stat = blockIdx.y;
-    const int Cg = (S1.C + S2.C) >> 5;
-    const int lo = g * Cg, hi = lo + Cg;                 // channel range of the group in the (virtual) concat
+    const int C = C1 + C2, Cg = C >> 5, n = Cg * fps;
+    // affine parameters of this thread's channel (Cg <= 96 < 128), requested before the sums are waited for
+    float ga = 0.f, be = 0.f;
+    if ((int)threadIdx.x < Cg) { ga = __ldg(gamma + g * Cg + threadIdx.x); be = __ldg(beta + g * Cg + threadIdx.x); }
     double s = 0.0, q = 0.0;
-    stat_accumulate(S1, min(lo, S1.C), min(hi, S1.C), stat, frames_per_stat, T, s, q);
-    if (S2.C > 0) stat_accumulate(S2, max(lo, S1.C) - S1.C, max(hi, S1.C) - S1.C, stat, frames_per_stat, T, s, q);
+    for (int i = threadIdx.x; i < n; i += 128) {
+        const int fl = i / Cg, c = g * Cg + (i - fl * Cg);
+        const size_t e = (size_t)stat * fps + fl;
+        const double2 v = c < C1 ? __ldcg(cs1 + e * C1 + c) : __ldcg(cs2 + e * C2 + (c - C1));
+        s += v.x; q += v.y;
+    }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) { s += __shfl_xor_sync(0xffffffffu, s, o); q += __shfl_xor_sync(0xffffffffu, q, o); }
-    if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = s; red[1][threadIdx.x >> 5] = q; }
+    if (lane == 0) { red[0][warp] = s; red[1][warp] = q; }
     __syncthreads();
-    if (threadIdx.x == 0) {
-        double ts = 0.0, tq = 0.0;
-        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) { ts += red[0][w]; tq += red[1][w]; }
-        const double cnt = (double)frames_per_stat * Cg * rows_per_frame;
-        const double m = ts / cnt;
-        double var = tq / cnt - m * m;
-        var = var < 0.0 ? 0.0 : var;
-        const float rstd = rsqrtf((float)var + eps);
-        table[(size_t)stat * 32 + g] = make_float2((float)m, rstd);
-        s_mr[0] = (float)m; s_mr[1] = rstd;
-    }
-    if (ab) {
-        __syncthreads();
-        const int C = S1.C + S2.C;
-        for (int c = lo + threadIdx.x; c < hi; c += blockDim.x) {
-            const float a = s_mr[1] * gamma[c];
-            ab[(size_t)stat * C + c] = make_float2(a, beta[c] - s_mr[0] * a);
-        }
+    const double ts = (red[0][0] + red[0][1]) + (red[0][2] + red[0][3]);
+    const double tq = (red[1][0] + red[1][1]) + (red[1][2] + red[1][3]);
+    const double m = ts * inv_cnt;
+    double var = tq * inv_cnt - m * m;
+    var = var < 0.0 ? 0.0 : var;
+    const float rstd = rsqrtf((float)var + eps), mf = (float)m;
+    if ((int)threadIdx.x < Cg) {
+        const float a = rstd * ga;
+        ab[(size_t)stat * C + g * Cg + threadIdx.x] = make_float2(a, be - mf * a);
     }
 }
 
-int gn_finalize(const StatSrc& s1, const StatSrc& s2, int nstat, int frames_per_stat, int T, int rows_per_frame, float eps,
-                float2* table, cudaStream_t st, const float* gamma, const float* beta, float2* ab) {
-    MOCA_REQUIRE(!ab || (gamma && beta), MOCA_E_ARG, "gn_finalize: the affine table needs gamma and beta");
-    MOCA_REQUIRE((s1.cs || s1.part) && table && (s2.C == 0 || s2.cs || s2.part), MOCA_E_ARG, "gn_finalize: NULL argument");
-    MOCA_REQUIRE((s1.C + s2.C) % 32 == 0 && nstat > 0 && frames_per_stat > 0 && rows_per_frame > 0 && T > 0, MOCA_E_SHAPE,
-                 "gn_finalize: unsupported geometry C=%d nstat=%d", s1.C + s2.C, nstat);
-    // statistics that span the frames of a sample have few (group, sample) blocks with long sums: 1024 threads each
-    launch_pdl(gn_finalize_kernel, dim3(32, nstat), dim3(frames_per_stat > 1 ? 1024 : 256), 0, st, s1, s2, frames_per_stat, T, rows_per_frame, eps, table, gamma, beta, ab);
+int gn_finalize(const StatSrc& s1, const StatSrc& s2, int nstat, int rows_per_stat, float eps, const float* gamma, const float* beta,
+                float2* ab, cudaStream_t st) {
+    MOCA_REQUIRE(s1.cs && gamma && beta && ab && (s2.C == 0 || s2.cs), MOCA_E_ARG, "gn_finalize: NULL argument");
+    const int C = s1.C + s2.C;
+    MOCA_REQUIRE(C % 32 == 0 && nstat > 0 && s1.rows > 0 && rows_per_stat % s1.rows == 0 && (s2.C == 0 || s2.rows == s1.rows), MOCA_E_SHAPE,
+                 "gn_finalize: unsupported geometry C=%d nstat=%d rows %d / %d", C, nstat, rows_per_stat, s1.rows);
+    MOCA_REQUIRE(C <= 128 * 32, MOCA_E_SHAPE, "gn_finalize: C=%d > 4096", C);
+    launch_pdl(gn_finalize_kernel, dim3(32, nstat), dim3(128), 0, st, reinterpret_cast<const double2*>(s1.cs), s1.C,
+               reinterpret_cast<const double2*>(s2.cs), s2.C, rows_per_stat / s1.rows, 1.0 / ((double)rows_per_stat * (C / 32)), eps,
+               gamma, beta, ab);
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
 }
@@ -257,6 +235,7 @@ struct ApplyP {
     int rows_per_stat; int Cg;
     const float2* table; const float* gamma; const float* beta;
     const float2* ab;
+    int in16;            // x1 is 16-bit (op_t), single source
     int silu; int mode;
     int NF, H, W;        // source geometry
     int T, HW;
@@ -317,12 +296,20 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const __grid_constant__ A
     const float4* s1 = reinterpret_cast<const float4*>(P.x1 + (size_t)sr * P.C1);
     const float4* s2 = P.x2 ? reinterpret_cast<const float4*>(P.x2 + (size_t)sr * P.C2) : nullptr;
     const int nv1 = P.C1 >> 2;
+    const uint2* h1 = reinterpret_cast<const uint2*>(reinterpret_cast<const op_t*>(P.x1) + (size_t)sr * P.C1);      // in16
     for (int v0 = lane; v0 < nvec; v0 += 128) {
         float4 t[4];
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
             const int v = v0 + 32 * k;
-            if (v < nvec) t[k] = v < nv1 ? __ldg(s1 + v) : __ldg(s2 + (v - nv1));
+            if (v >= nvec) continue;
+            if (P.in16) {
+                const uint2 h = __ldg(h1 + v);
+                const float2 lo = op22float2(*reinterpret_cast<const op2_t*>(&h.x)), hi = op22float2(*reinterpret_cast<const op2_t*>(&h.y));
+                t[k] = make_float4(lo.x, lo.y, hi.x, hi.y);
+            } else {
+                t[k] = v < nv1 ? __ldg(s1 + v) : __ldg(s2 + (v - nv1));
+            }
         }
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
@@ -366,8 +353,10 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const __grid_constant__ A
 // Affine-table path for narrow rows (C <= 128 * SLOTS): a warp handles R consecutive destination rows, issues all of their
 // loads first and keeps the (scale, shift) pairs of its channels in registers while the rows stay in one statistics group
 // (they do except at frame boundaries), so a row costs its own 16-byte loads only.
-template <int SLOTS, int R>
+// IN16: the (single) source is 16-bit: 8-byte loads kept raw in registers, so R can be twice as large for the same bytes in flight.
+template <int SLOTS, int R, bool IN16>
 __global__ void __launch_bounds__(256) gn_apply_ab_kernel(const __grid_constant__ ApplyP P) {
+    using LoadT = typename std::conditional<IN16, uint2, float4>::type;
     pdl_wait();
     pdl_launch_dependents();
     const int lane = threadIdx.x & 31;
@@ -376,19 +365,26 @@ __global__ void __launch_bounds__(256) gn_apply_ab_kernel(const __grid_constant_
     const int C = P.C1 + P.C2;
     const int nvec = C >> 2, nv1 = P.C1 >> 2;
     int sr[R];
-    float4 t[R][SLOTS];
+    LoadT t[R][SLOTS];
     int st0 = -1;
 #pragma unroll
     for (int r = 0; r < R; ++r) {
         sr[r] = drow0 + r < P.dst_rows ? apply_src_row(P, drow0 + r) : -2;
         if (sr[r] >= 0) {
             if (st0 < 0) st0 = P.d_stat.div(sr[r]);
-            const float4* s1 = reinterpret_cast<const float4*>(P.x1 + (size_t)sr[r] * P.C1);
-            const float4* s2 = P.x2 ? reinterpret_cast<const float4*>(P.x2 + (size_t)sr[r] * P.C2) : nullptr;
+            if constexpr (IN16) {
+                const uint2* s1 = reinterpret_cast<const uint2*>(reinterpret_cast<const op_t*>(P.x1) + (size_t)sr[r] * P.C1);
 #pragma unroll
-            for (int u = 0; u < SLOTS; ++u) {
-                const int v = lane + 32 * u;
-                if (v < nvec) t[r][u] = v < nv1 ? __ldg(s1 + v) : __ldg(s2 + (v - nv1));
+                for (int u = 0; u < SLOTS; ++u)
+                    if (lane + 32 * u < nvec) t[r][u] = __ldg(s1 + lane + 32 * u);
+            } else {
+                const float4* s1 = reinterpret_cast<const float4*>(P.x1 + (size_t)sr[r] * P.C1);
+                const float4* s2 = P.x2 ? reinterpret_cast<const float4*>(P.x2 + (size_t)sr[r] * P.C2) : nullptr;
+#pragma unroll
+                for (int u = 0; u < SLOTS; ++u) {
+                    const int v = lane + 32 * u;
+                    if (v < nvec) t[r][u] = v < nv1 ? __ldg(s1 + v) : __ldg(s2 + (v - nv1));
+                }
             }
         }
     }
@@ -418,8 +414,14 @@ __global__ void __launch_bounds__(256) gn_apply_ab_kernel(const __grid_constant_
         for (int u = 0; u < SLOTS; ++u) {
             const int v = lane + 32 * u;
             if (v >= nvec) continue;
-            float x[4] = {t[r][u].x, t[r][u].y, t[r][u].z, t[r][u].w};
-            if (P.raw) *reinterpret_cast<uint2*>(P.raw + (size_t)sr[r] * C + (v << 2)) = pack4(x);
+            float x[4];
+            if constexpr (IN16) {
+                const float2 lo = op22float2(*reinterpret_cast<const op2_t*>(&t[r][u].x)), hi = op22float2(*reinterpret_cast<const op2_t*>(&t[r][u].y));
+                x[0] = lo.x; x[1] = lo.y; x[2] = hi.x; x[3] = hi.y;
+            } else {
+                x[0] = t[r][u].x; x[1] = t[r][u].y; x[2] = t[r][u].z; x[3] = t[r][u].w;
+                if (P.raw) *reinterpret_cast<uint2*>(P.raw + (size_t)sr[r] * C + (v << 2)) = pack4(x);
+            }
             x[0] = fmaf(x[0], a0[u].x, a0[u].y); x[1] = fmaf(x[1], a0[u].z, a0[u].w);
             x[2] = fmaf(x[2], a1[u].x, a1[u].y); x[3] = fmaf(x[3], a1[u].z, a1[u].w);
             if (P.silu) {
@@ -431,11 +433,13 @@ __global__ void __launch_bounds__(256) gn_apply_ab_kernel(const __grid_constant_
     }
 }
 
+
 int gn_apply(const ApplyArgs& a, cudaStream_t st) {
     const int C = a.C1 + a.C2;
     MOCA_REQUIRE(C % 4 == 0 && a.C1 % 4 == 0 && C <= 256 * kStatSlots * 4, MOCA_E_SHAPE, "gn_apply: channels C1=%d C2=%d unsupported", a.C1, a.C2);
     MOCA_REQUIRE(a.rows_per_stat == 0 || a.ab || (a.groups == 32 && C % 32 == 0 && C / 32 >= 2 && a.table && a.gamma && a.beta), MOCA_E_ARG,
                  "gn_apply: bad normalisation arguments");
+    MOCA_REQUIRE(!a.in16 || (a.ab && !a.x2 && !a.raw), MOCA_E_ARG, "gn_apply: a 16-bit input needs the affine-table path and a single source");
     MOCA_REQUIRE(a.rows_per_stat == 0 || a.rows % a.rows_per_stat == 0, MOCA_E_SHAPE, "gn_apply: bad statistics span");
     ApplyP P;
     P.x1 = a.x1; P.C1 = a.C1; P.x2 = a.x2; P.C2 = a.C2;
@@ -443,6 +447,7 @@ int gn_apply(const ApplyArgs& a, cudaStream_t st) {
     P.table = a.table; P.gamma = a.gamma; P.beta = a.beta; P.ab = a.rows_per_stat > 0 ? a.ab : nullptr; P.silu = a.silu; P.mode = a.dst_mode;
     P.NF = a.NF; P.H = a.H; P.W = a.W; P.T = a.T; P.HW = a.HW;
     P.dst = a.dst; P.raw = a.raw;
+    P.in16 = a.in16;
     int64_t dst_rows = 0;
     switch (a.dst_mode) {
         case DST_LINEAR: dst_rows = a.rows; break;
@@ -466,8 +471,13 @@ int gn_apply(const ApplyArgs& a, cudaStream_t st) {
         P.d_outer = FastDiv(((a.H << up) + 2) * ((a.W << up) + 2)); P.d_inner = FastDiv((a.W << up) + 2);
     }
     static const int rows_on = [] { const char* e = getenv("MOCA_GN_ROWS"); return e ? atoi(e) : 1; }();
-    if (rows_on && P.ab && C <= 384) launch_pdl(gn_apply_ab_kernel<3, 4>, dim3(cdiv(dst_rows, 32)), dim3(256), 0, st, P);
-    else if (rows_on && P.ab && C <= 768) launch_pdl(gn_apply_ab_kernel<6, 2>, dim3(cdiv(dst_rows, 16)), dim3(256), 0, st, P);
+    static const int r16 = [] { const char* e = getenv("MOCA_GN_R16"); return e ? atoi(e) : 1; }();     // row multiplier of the 16-bit input kernels (measured: 1 = 25.0 us, 2 = 32.6 us at 81920 x 320)
+    if (rows_on && P.ab && P.in16 && C <= 384 && r16 == 2) launch_pdl(gn_apply_ab_kernel<3, 8, true>, dim3(cdiv(dst_rows, 64)), dim3(256), 0, st, P);
+    else if (rows_on && P.ab && P.in16 && C <= 384) launch_pdl(gn_apply_ab_kernel<3, 4, true>, dim3(cdiv(dst_rows, 32)), dim3(256), 0, st, P);
+    else if (rows_on && P.ab && P.in16 && C <= 768 && r16 == 2) launch_pdl(gn_apply_ab_kernel<6, 4, true>, dim3(cdiv(dst_rows, 32)), dim3(256), 0, st, P);
+    else if (rows_on && P.ab && P.in16 && C <= 768) launch_pdl(gn_apply_ab_kernel<6, 2, true>, dim3(cdiv(dst_rows, 16)), dim3(256), 0, st, P);
+    else if (rows_on && P.ab && C <= 384) launch_pdl(gn_apply_ab_kernel<3, 4, false>, dim3(cdiv(dst_rows, 32)), dim3(256), 0, st, P);
+    else if (rows_on && P.ab && C <= 768) launch_pdl(gn_apply_ab_kernel<6, 2, false>, dim3(cdiv(dst_rows, 16)), dim3(256), 0, st, P);
     else launch_pdl(gn_apply_kernel, dim3(cdiv(dst_rows, 8)), dim3(256), 0, st, P);
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
@@ -476,8 +486,9 @@ int gn_apply(const ApplyArgs& a, cudaStream_t st) {
 // ---------------------------------------------------------------------------------------------------------------
 // One warp normalises R consecutive rows; all R * SLOTS float4 loads of a lane are issued before the first use so that a
 // warp keeps R rows of HBM traffic in flight (C = 320: 4 rows = 5 KB per warp).  C <= 128 * SLOTS.
-template <int SLOTS, int R>
-__global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+// IN16: the input rows are 16-bit (op_t, the transformer's inner residual stream) instead of fp32.
+template <int SLOTS, int R, bool IN16>
+__global__ void __launch_bounds__(256) layernorm_kernel(const void* __restrict__ xin, const float* __restrict__ gamma,
                                                         const float* __restrict__ beta, int64_t rows, int C,
                                                         op_t* __restrict__ out) {
     pdl_wait();
@@ -489,12 +500,28 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict_
     float4 v[R][SLOTS];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-        const float4* xr = reinterpret_cast<const float4*>(x + (row0 + r) * C);
+        if constexpr (IN16) {
+            const uint2* xr = reinterpret_cast<const uint2*>(reinterpret_cast<const op_t*>(xin) + (row0 + r) * C);
+            uint2 t[SLOTS];
 #pragma unroll
-        for (int u = 0; u < SLOTS; ++u) {
-            const int i = lane + 32 * u;
-            v[r][u] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (i < nvec && row0 + r < rows) v[r][u] = __ldg(xr + i);
+            for (int u = 0; u < SLOTS; ++u) {
+                const int i = lane + 32 * u;
+                t[u] = make_uint2(0u, 0u);
+                if (i < nvec && row0 + r < rows) t[u] = __ldg(xr + i);
+            }
+#pragma unroll
+            for (int u = 0; u < SLOTS; ++u) {
+                const float2 a = op22float2(*reinterpret_cast<const op2_t*>(&t[u].x)), b = op22float2(*reinterpret_cast<const op2_t*>(&t[u].y));
+                v[r][u] = make_float4(a.x, a.y, b.x, b.y);
+            }
+        } else {
+            const float4* xr = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(xin) + (row0 + r) * C);
+#pragma unroll
+            for (int u = 0; u < SLOTS; ++u) {
+                const int i = lane + 32 * u;
+                v[r][u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (i < nvec && row0 + r < rows) v[r][u] = __ldg(xr + i);
+            }
         }
     }
     const float4* g4 = reinterpret_cast<const float4*>(gamma);
@@ -541,13 +568,20 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict_
     }
 }
 
-int layernorm_op16(const float* x, const float* gamma, const float* beta, int64_t rows, int C, op_t* out, cudaStream_t st) {
+template <bool IN16>
+static int layernorm_launch(const void* x, const float* gamma, const float* beta, int64_t rows, int C, op_t* out, cudaStream_t st) {
     MOCA_REQUIRE(C % 4 == 0 && C <= 1280, MOCA_E_SHAPE, "layernorm: C=%d unsupported (multiple of 4, <= 1280)", C);
-    if (C <= 384) launch_pdl(layernorm_kernel<3, 4>, dim3(cdiv(rows, 32)), dim3(256), 0, st, x, gamma, beta, rows, C, out);
-    else if (C <= 640) launch_pdl(layernorm_kernel<5, 2>, dim3(cdiv(rows, 16)), dim3(256), 0, st, x, gamma, beta, rows, C, out);
-    else launch_pdl(layernorm_kernel<10, 1>, dim3(cdiv(rows, 8)), dim3(256), 0, st, x, gamma, beta, rows, C, out);
+    if (C <= 384) launch_pdl(layernorm_kernel<3, 4, IN16>, dim3(cdiv(rows, 32)), dim3(256), 0, st, x, gamma, beta, rows, C, out);
+    else if (C <= 640) launch_pdl(layernorm_kernel<5, 2, IN16>, dim3(cdiv(rows, 16)), dim3(256), 0, st, x, gamma, beta, rows, C, out);
+    else launch_pdl(layernorm_kernel<10, 1, IN16>, dim3(cdiv(rows, 8)), dim3(256), 0, st, x, gamma, beta, rows, C, out);
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
+}
+int layernorm_op16(const float* x, const float* gamma, const float* beta, int64_t rows, int C, op_t* out, cudaStream_t st) {
+    return layernorm_launch<false>(x, gamma, beta, rows, C, out, st);
+}
+int layernorm_op16_in16(const op_t* x, const float* gamma, const float* beta, int64_t rows, int C, op_t* out, cudaStream_t st) {
+    return layernorm_launch<true>(x, gamma, beta, rows, C, out, st);
 }
 
 // ---------------------------------------------------------------------------------------------------------------

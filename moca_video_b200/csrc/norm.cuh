@@ -21,20 +21,20 @@ int pack_weight(const float* src, int N, int K, int taps, int Kp, op_t* dst, int
 int gn_stats(const float* x1, int C1, const float* x2, int C2, int64_t rows, int rows_per_stat, int groups, double* acc,
              float eps, float2* table, unsigned* counter, cudaStream_t st);
 
-// Statistics a GEMM epilogue left behind for the tensor it wrote (gemm_tc.cuh): either per-(frame, channel) {sum, sumsq}
-// doubles cs [frames, C, 2] (atomic mode) or float2 partials part [slices, C] per 32-row slice of the GEMM's input-row space
-// (slice mode; frame f owns slices ((f / T) * tpad + f % T + toff) * spf .. + spf).
+// Statistics a GEMM epilogue left behind for the tensor it wrote (gemm_tc.cuh): {sum, sumsq} doubles per (entry, channel),
+// cs [n, C, 2]; entry e covers output rows [e * rows, (e + 1) * rows) — a frame (rows = H*W) or a sample (rows = T*H*W),
+// whichever the GroupNorm that consumes the tensor normalises over (a per-frame source can also feed a per-sample norm).
 struct StatSrc {
     const double* cs = nullptr;
-    const float2* part = nullptr;
     int C = 0;
-    int spf = 0, tpad = 0, toff = 0;
+    int rows = 0;
 };
-// (mean, rstd) table [nstat, 32] of GroupNorm(32) over the virtual channel concat of s1 and s2 (s2.C == 0: single source)
-// ab (optional, with gamma / beta): per-(statistics group, channel) affine form of the normalisation, [nstat, C] float2
-// (rstd * gamma, beta - mean * rstd * gamma), so that gn_apply is one FMA per element with no group arithmetic.
-int gn_finalize(const StatSrc& s1, const StatSrc& s2, int nstat, int frames_per_stat, int T, int rows_per_frame, float eps,
-                float2* table, cudaStream_t st, const float* gamma = nullptr, const float* beta = nullptr, float2* ab = nullptr);
+
+// (scale, shift) = (rstd * gamma, beta - mean * rstd * gamma) per (statistics group, channel) of GroupNorm(32) over the virtual
+// channel concat of s1 and s2 (s2.C == 0: single source), rows_per_stat rows per group (a multiple of the sources' rows per entry):
+// ab [nstat, C1 + C2] float2, so that gn_apply is one FMA per element with no group arithmetic.
+int gn_finalize(const StatSrc& s1, const StatSrc& s2, int nstat, int rows_per_stat, float eps, const float* gamma, const float* beta,
+                float2* ab, cudaStream_t st);
 
 struct ApplyArgs {
     const float* x1 = nullptr; int C1 = 0;
@@ -44,7 +44,8 @@ struct ApplyArgs {
     int groups = 32;
     const float2* table = nullptr;  // (mean, rstd) per (statistics group, channel group), written by gn_stats
     const float* gamma = nullptr; const float* beta = nullptr;
-    const float2* ab = nullptr;     // optional [nstat, C1+C2] (scale, shift) written by gn_finalize; replaces table/gamma/beta
+    const float2* ab = nullptr;     // optional [nstat, C1+C2] precomputed (scale, shift); replaces table/gamma/beta
+    int in16 = 0;                   // x1 points to 16-bit (op_t) rows instead of fp32 (affine-table path, single source, no raw copy)
     float eps = 1e-5f;
     int silu = 0;
     int dst_mode = DST_LINEAR;
@@ -57,6 +58,8 @@ int gn_apply(const ApplyArgs& a, cudaStream_t st);
 
 // nn.LayerNorm(C), eps 1e-5 (attention.py:199-201): fp32 [rows, C] -> bf16 [rows, C]
 int layernorm_op16(const float* x, const float* gamma, const float* beta, int64_t rows, int C, op_t* out, cudaStream_t st);
+// same with a 16-bit input (the transformer's inner residual stream is carried in op_t, unet_plan.cu); out may not alias x
+int layernorm_op16_in16(const op_t* x, const float* gamma, const float* beta, int64_t rows, int C, op_t* out, cudaStream_t st);
 
 // timestep_embedding (utils_diffusion.py:8-28): out bf16 [n, dim] = [cos(t*f), sin(t*f)]
 int timestep_embedding_bf16(const int* t_dev, int n, int dim, op_t* out, cudaStream_t st);

@@ -34,10 +34,7 @@ struct Plan {
     float* out_tok = nullptr;
     double* stats = nullptr;
     size_t stats_bytes = 0;
-    float2* parts = nullptr;          // slice-partial statistics (bump allocated; fully rewritten by every forward)
-    float2* mr_table = nullptr;       // (mean, rstd) tables written by gn_stats, one slot per GroupNorm
     float2* ab_table = nullptr;       // (scale, shift) per (statistics group, channel) of the GroupNorm being applied (shared)
-    unsigned* stat_counters = nullptr;
     cudaGraphExec_t gexec = nullptr;
     std::vector<Tap> taps;
     bool with_taps = false;
@@ -63,9 +60,7 @@ struct Builder {
     int rc = MOCA_OK;
     size_t need[S_COUNT] = {0};
     void* sptr[S_COUNT] = {nullptr};
-    int stat_slots = 0;
-    size_t cs_doubles = 0;    // bump allocator over plan->stats (atomic mode, zeroed at the start of every forward)
-    size_t part_elems = 0;    // bump allocator over plan->parts (slice mode)
+    size_t cs_doubles = 0;    // bump allocator over plan->stats (zeroed at the start of every forward)
     int B, T, H0, W0, NF, Lmax;
     std::string scope;
 
@@ -93,21 +88,18 @@ struct Builder {
         plan->launches += nlaunch;
         if (!dry) raw_push(std::move(op), label, flops);
     }
-    int stat_slot() { return stat_slots++; }
-    // producer: 0 = linear GEMM over tokens, 1 = Conv3d (3,1,1) over time-padded rows, 2 = 3x3 conv over bordered rows
-    StatSrc stat_alloc(int C, int HW, int producer) {
+    // Statistics buffer of a tensor with C channels: {sum, sumsq} per (frame, channel), accumulated by the producing GEMM's epilogue
+    // with fp64 atomics.  Always per frame, also when the consumer normalises over the T frames of a sample (the 5-D GroupNorms
+    // of TemporalConvBlock / TemporalTransformer; the apply kernel adds the T entries): per-sample entries would put
+    // every atomic of the GEMM on B*C addresses, and same-address fp64 atomics serialise at ~40 ns each in L2 (measured:
+    // the 81920 x 320 proj_out GEMM went from 56 to 107 us).
+    StatSrc stat_alloc(int C, int HW) {
         StatSrc r;
         r.C = C;
-        if (producer != 2 && HW % 32 == 0) {
-            r.spf = HW / 32; r.tpad = producer == 1 ? T + 2 : T; r.toff = producer == 1 ? 1 : 0;
-            const size_t off = part_elems;
-            part_elems += (size_t)B * r.tpad * r.spf * C;
-            r.part = dry ? (const float2*)16 : plan->parts + off;
-        } else {
-            const size_t off = cs_doubles;
-            cs_doubles += (size_t)NF * C * 2;
-            r.cs = dry ? (const double*)16 : plan->stats + off;
-        }
+        r.rows = HW;
+        const size_t off = cs_doubles;
+        cs_doubles += (size_t)NF * C * 2;
+        r.cs = dry ? (const double*)16 : plan->stats + off;
         return r;
     }
 
@@ -125,17 +117,17 @@ struct Builder {
         raw_push([L](cudaStream_t st) { return gemm_run(L, st); }, buf, useful_flops);
     }
     void linear(const op_t* A, int64_t rows, int K, const PackedW& w, int epi, void* out, int ldo, const float* residual,
-                int n_override = 0, const StatSrc* ss = nullptr, int rpf = 0) {
+                int n_override = 0, const StatSrc* ss = nullptr, int rpf = 0, const op_t* residual16 = nullptr) {
         GemmDesc d;
         d.A = A; d.a_rows = rows; d.a_cols = K; d.a_pitch = K;
         d.Wt = w.w; d.N = n_override ? n_override : w.N; d.ntaps = 1; d.Kp = w.Kp;
-        d.mode = GEMM_LINEAR; d.M = (int)rows; d.epi = epi; d.out = out; d.ldo = ldo; d.bias = w.b; d.residual = residual;
-        if (ss) { d.chan_stats = (double*)ss->cs; d.stat_partials = (float2*)ss->part; }
-        d.stat_rows_per_frame = rpf; d.stat_sample_rows = T * rpf;
+        d.mode = GEMM_LINEAR; d.M = (int)rows; d.epi = epi; d.out = out; d.ldo = ldo; d.bias = w.b; d.residual = residual; d.residual16 = residual16;
+        if (ss) { d.chan_stats = (double*)ss->cs; d.stat_rows_per_frame = ss->rows; }
+        d.stat_sample_rows = T * rpf;
         gemm(d, 2.0 * rows * d.N * K);
     }
-    void conv3x3(const op_t* pad, int H, int W, int Cin, const PackedW& w, int stride, float* out, const float* rowbias,
-                 int rb_ld, const float* residual, const StatSrc* ss) {
+    void conv3x3(const op_t* pad, int H, int W, int Cin, const PackedW& w, int stride, void* out, const float* rowbias,
+                 int rb_ld, const float* residual, const StatSrc* ss, int out16 = 0) {
         GemmDesc d;
         const int Hp = H + 2, Wp = W + 2;
         d.A = pad; d.a_rows = (int64_t)NF * Hp * Wp; d.a_cols = Cin; d.a_pitch = Cin;
@@ -143,43 +135,49 @@ struct Builder {
         for (int ky = 0; ky < 3; ++ky)
             for (int kx = 0; kx < 3; ++kx) d.tap_shift[ky * 3 + kx] = (ky - 1) * Wp + (kx - 1);
         d.mode = GEMM_SPATIAL_PAD; d.g_rows = Hp * Wp; d.g_w = Wp; d.g_H = H; d.g_W = W; d.stride = stride;
-        d.M = (int)d.a_rows; d.epi = EPI_F32; d.out = out; d.ldo = w.N; d.bias = w.b;
+        d.M = (int)d.a_rows; d.epi = EPI_F32; d.out = out; d.ldo = w.N; d.bias = w.b; d.out16 = out16;
         d.rowbias = rowbias; d.rb_ld = rb_ld; d.rows_per_frame = (H / stride) * (W / stride); d.residual = residual;
-        if (ss) d.chan_stats = (double*)ss->cs;
-        d.stat_rows_per_frame = d.rows_per_frame; d.stat_sample_rows = T * Hp * Wp;
+        if (ss) { d.chan_stats = (double*)ss->cs; d.stat_rows_per_frame = ss->rows; }
+        d.stat_sample_rows = T * Hp * Wp;
         gemm(d, 2.0 * NF * (H / stride) * (W / stride) * w.N * 9.0 * w.K);
     }
-    void tconv(const op_t* padT, int HW, int C, const PackedW& w, float* out, const float* residual, const StatSrc* ss) {
+    void tconv(const op_t* padT, int HW, int C, const PackedW& w, void* out, const float* residual, const StatSrc* ss, int out16 = 0) {
         GemmDesc d;
         d.A = padT; d.a_rows = (int64_t)B * (T + 2) * HW; d.a_cols = C; d.a_pitch = C;
         d.Wt = w.w; d.N = w.N; d.ntaps = 3; d.Kp = w.Kp;
         for (int dt = 0; dt < 3; ++dt) d.tap_shift[dt] = (dt - 1) * HW;
         d.mode = GEMM_TIME_PAD; d.g_rows = (T + 2) * HW; d.g_w = HW; d.g_H = T;
-        d.M = (int)d.a_rows; d.epi = EPI_F32; d.out = out; d.ldo = w.N; d.bias = w.b; d.residual = residual;
-        if (ss) { d.chan_stats = (double*)ss->cs; d.stat_partials = (float2*)ss->part; }
-        d.stat_rows_per_frame = HW; d.stat_sample_rows = (T + 2) * HW;
+        d.M = (int)d.a_rows; d.epi = EPI_F32; d.out = out; d.ldo = w.N; d.bias = w.b; d.residual = residual; d.out16 = out16;
+        if (ss) { d.chan_stats = (double*)ss->cs; d.stat_rows_per_frame = ss->rows; }
+        d.stat_sample_rows = (T + 2) * HW;
         gemm(d, 2.0 * NF * HW * w.N * 3.0 * C);
     }
 
     // ---- normalisation flavours ----------------------------------------------------------------------------
-    void gnorm(const float* x1, const StatSrc& s1, int C1, const float* x2, const StatSrc& s2in, int C2, int64_t rows, int rows_per_stat,
-               const NormW& w, float eps, int silu, int dst_mode, int H, int W, op_t* dst, op_t* raw) {
-        const int slot = stat_slot();
-        float2* table = dry ? nullptr : plan->mr_table + (size_t)slot * NF * 32;
-        const int nstat = (int)(rows / rows_per_stat), fps = rows_per_stat / (H * W), rpf = H * W, Tn = T;
+    // GroupNorm(32) (+ SiLU) of x1 (fp32, or 16-bit with in16) [+ virtual channel concat with x2] over rows_per_stat rows per group,
+    // statistics from the producers' epilogues (finalised inside the apply kernel), scattered into the consumer's operand layout.
+    void gnorm(const void* x1, const StatSrc& s1, int C1, const float* x2, const StatSrc& s2in, int C2, int64_t rows, int rows_per_stat,
+               const NormW& w, float eps, int silu, int dst_mode, int H, int W, op_t* dst, op_t* raw, int in16 = 0) {
         StatSrc s2 = s2in;
         if (!x2) s2 = StatSrc();
-        if (!dry && (s1.C != C1 || s2.C != C2)) { set_error("plan: statistics source does not match the GroupNorm input (%d/%d vs %d/%d)", s1.C, s2.C, C1, C2); fail(MOCA_E_STATE); }
+        if (!dry && (s1.C != C1 || s2.C != C2 || !s1.cs || (x2 && !s2.cs))) {
+            set_error("plan: statistics source does not match the GroupNorm input (%d/%d vs %d/%d)", s1.C, s2.C, C1, C2); fail(MOCA_E_STATE);
+        }
+        if (!dry && (s1.rows <= 0 || rows_per_stat % s1.rows != 0 || (x2 && s2.rows != s1.rows))) {
+            set_error("plan: statistics of %d rows per entry cannot feed a GroupNorm over %d rows", s1.rows, rows_per_stat); fail(MOCA_E_STATE);
+        }
         ApplyArgs a;
-        a.x1 = x1; a.C1 = C1; a.x2 = x2; a.C2 = C2; a.rows = rows; a.rows_per_stat = rows_per_stat; a.table = table;
-        a.gamma = w.g; a.beta = w.b; a.eps = eps; a.silu = silu; a.dst_mode = dst_mode;
+        a.x1 = (const float*)x1; a.C1 = C1; a.x2 = x2; a.C2 = C2; a.rows = rows; a.rows_per_stat = rows_per_stat;
+        a.gamma = w.g; a.beta = w.b; a.eps = eps; a.silu = silu; a.dst_mode = dst_mode; a.in16 = in16;
         a.NF = NF; a.H = H; a.W = W; a.B = B; a.T = T; a.HW = H * W; a.dst = dst; a.raw = raw;
         // (scale, shift) per (statistics group, channel): one buffer for all GroupNorms, finalize -> apply are adjacent in the stream
         float2* ab = dry ? nullptr : plan->ab_table;
         a.ab = ab;
+        const int nstat = (int)(rows / rows_per_stat);
         const float* gam = w.g; const float* bet = w.b;
-        const std::string dims = " rows=" + std::to_string(rows) + " C=" + std::to_string(C1 + C2) + " dst=" + std::to_string(dst_mode);
-        push([=](cudaStream_t st) { return gn_finalize(s1, s2, nstat, fps, Tn, rpf, eps, table, st, gam, bet, ab); }, 1, "gn_finalize" + dims);
+        const std::string dims = " rows=" + std::to_string(rows) + " C=" + std::to_string(C1 + C2) + " dst=" + std::to_string(dst_mode) +
+                                 (in16 ? " in16" : "");
+        push([=](cudaStream_t st) { return gn_finalize(s1, s2, nstat, rows_per_stat, eps, gam, bet, ab, st); }, 1, "gn_finalize" + dims);
         push([=](cudaStream_t st) { return gn_apply(a, st); }, 1, "gn_apply" + dims);
     }
     void convert(const float* x, int C, int64_t rows, int dst_mode, int H, int W, op_t* dst) {
@@ -188,8 +186,8 @@ struct Builder {
         a.NF = NF; a.H = H; a.W = W; a.B = B; a.T = T; a.HW = H * W; a.dst = dst;
         push([=](cudaStream_t st) { return gn_apply(a, st); }, 1, "convert rows=" + std::to_string(rows) + " C=" + std::to_string(C) + " dst=" + std::to_string(dst_mode));
     }
-    void lnorm(const float* x, const NormW& w, int64_t rows, int C, op_t* out) {
-        push([=](cudaStream_t st) { return layernorm_op16(x, w.g, w.b, rows, C, out, st); }, 1, "layernorm rows=" + std::to_string(rows) + " C=" + std::to_string(C));
+    void lnorm(const op_t* x, const NormW& w, int64_t rows, int C, op_t* out) {
+        push([=](cudaStream_t st) { return layernorm_op16_in16(x, w.g, w.b, rows, C, out, st); }, 1, "layernorm rows=" + std::to_string(rows) + " C=" + std::to_string(C));
     }
     void tap(const std::string& name, const Act& a) {
         if (!plan->with_taps) return;
@@ -225,18 +223,19 @@ Act Builder::res_block(const LayerW& L, const Act& x, const Act* skip, const flo
     const size_t pad_elems = (size_t)NF * (H + 2) * (W + 2);
     op_t* pad = scratch<op_t>(S_PAD, pad_elems * (Cin > r.cout ? Cin : r.cout));
     op_t* raw = r.has_skip ? scratch<op_t>(S_RAW, (size_t)rows * Cin) : nullptr;
-    float* t1 = scratch<float>(S_F32A, (size_t)rows * r.cout);
-    float* t2 = scratch<float>(S_F32B, (size_t)rows * r.cout);
+    // tensors consumed only by the next GroupNorm are kept in 16 bits (their statistics come from the fp32 accumulators' epilogue)
+    op_t* t1 = scratch<op_t>(S_F32A, (size_t)rows * r.cout);
+    op_t* t2 = scratch<op_t>(S_F32B, (size_t)rows * r.cout);
     Act out;
     out.C = r.cout; out.H = H; out.W = W;
     out.p = (float*)palloc((size_t)rows * r.cout * sizeof(float));
     // in_layers: GN(fp32, eps 1e-5) -> SiLU -> conv3x3 ; + emb_layers(emb)[:, :, None, None]
     gnorm(x.p, x.st, x.C, skip ? skip->p : nullptr, skip ? skip->st : StatSrc(), C2, rows, HW, r.gn1, 1e-5f, 1, DST_SPATIAL_PAD, H, W, pad, raw);
-    const StatSrc st_t1 = stat_alloc(r.cout, HW, 2);
-    conv3x3(pad, H, W, Cin, r.conv1, 1, t1, embout + r.emb_off, net->n_emb, nullptr, &st_t1);
+    const StatSrc st_t1 = stat_alloc(r.cout, HW);
+    conv3x3(pad, H, W, Cin, r.conv1, 1, t1, embout + r.emb_off, net->n_emb, nullptr, &st_t1, 1);
     // out_layers: GN -> SiLU -> (dropout) -> conv3x3 ; + skip_connection(x)
-    gnorm(t1, st_t1, r.cout, nullptr, StatSrc(), 0, rows, HW, r.gn2, 1e-5f, 1, DST_SPATIAL_PAD, H, W, pad, nullptr);
-    StatSrc st_cur = stat_alloc(r.cout, HW, 2);
+    gnorm(t1, st_t1, r.cout, nullptr, StatSrc(), 0, rows, HW, r.gn2, 1e-5f, 1, DST_SPATIAL_PAD, H, W, pad, nullptr, 1);
+    StatSrc st_cur = stat_alloc(r.cout, HW);
     if (r.has_skip) {
         linear(raw, rows, Cin, r.skip, EPI_F32, out.p, r.cout, nullptr);
         conv3x3(pad, H, W, r.cout, r.conv2, 1, out.p, nullptr, 0, out.p, &st_cur);
@@ -246,12 +245,12 @@ Act Builder::res_block(const LayerW& L, const Act& x, const Act* skip, const flo
     // TemporalConvBlock: 4 x [GN over (C/32, T, H, W) -> SiLU -> Conv3d (3,1,1)] + identity
     const size_t padt_elems = (size_t)B * (T + 2) * HW * r.cout;
     op_t* padT = scratch<op_t>(S_PAD, padt_elems);
-    const float* src = out.p;
-    float* dsts[4] = {t1, t2, t1, out.p};
+    const void* src = out.p;
+    void* dsts[4] = {t1, t2, t1, out.p};
     for (int i = 0; i < 4; ++i) {
-        gnorm(src, st_cur, r.cout, nullptr, StatSrc(), 0, rows, T * HW, r.tgn[i], 1e-5f, 1, DST_TIME_PAD, H, W, padT, nullptr);
-        st_cur = stat_alloc(r.cout, HW, 1);
-        tconv(padT, HW, r.cout, r.tconv[i], dsts[i], i == 3 ? out.p : nullptr, &st_cur);
+        gnorm(src, st_cur, r.cout, nullptr, StatSrc(), 0, rows, T * HW, r.tgn[i], 1e-5f, 1, DST_TIME_PAD, H, W, padT, nullptr, i > 0);
+        st_cur = stat_alloc(r.cout, HW);
+        tconv(padT, HW, r.cout, r.tconv[i], dsts[i], i == 3 ? out.p : nullptr, &st_cur, i < 3);
         src = dsts[i];
     }
     out.st = st_cur;
@@ -272,10 +271,11 @@ void Builder::transformer(const LayerW& L, Act& x, const op_t* kv) {
     op_t* qkv = scratch<op_t>(S_QKV, (size_t)rows * 3 * I);
     op_t* att = scratch<op_t>(S_ATT, (size_t)rows * I);
     op_t* ffh = scratch<op_t>(S_FFH, (size_t)rows * 4 * I);
-    float* y = scratch<float>(S_Y, (size_t)rows * I);
+    // inner residual stream of the block (proj_in output + attn1 + attn2 + ff): 16-bit, updated in place by the 16-bit epilogues
+    op_t* y = scratch<op_t>(S_Y, (size_t)rows * I);
     // norm (GroupNorm eps 1e-6; spatial: per frame, temporal: 5-D input so statistics span all T frames)
     gnorm(x.p, x.st, C, nullptr, StatSrc(), 0, rows, t.spatial ? HW : T * HW, t.gn, 1e-6f, 0, DST_LINEAR, H, W, lin, nullptr);
-    linear(lin, rows, C, t.proj_in, EPI_F32, y, I, nullptr);
+    linear(lin, rows, C, t.proj_in, EPI_BF16, y, I, nullptr);
 
     AttnArgs self;
     self.q = qkv; self.k = qkv + I; self.v = qkv + 2 * I; self.ldq = 3 * I; self.ldkv = 3 * I;
@@ -303,7 +303,7 @@ void Builder::transformer(const LayerW& L, Act& x, const op_t* kv) {
     lnorm(y, t.ln1, rows, I, lin);
     linear(lin, rows, I, t.qkv1, EPI_BF16, qkv, 3 * I, nullptr);
     push(run_self, 1, "attn_self", attn_flops); plan->flops += attn_flops;
-    linear(att, rows, I, t.out1, EPI_F32, y, I, y);
+    linear(att, rows, I, t.out1, EPI_BF16, y, I, nullptr, 0, nullptr, 0, y);
     // attn2: cross-attention on the text context (spatial) or a second self-attention (temporal_selfatt_only, attention.py:313-314)
     lnorm(y, t.ln2, rows, I, lin);
     if (t.spatial) {
@@ -324,15 +324,14 @@ void Builder::transformer(const LayerW& L, Act& x, const op_t* kv) {
         linear(lin, rows, I, t.qkv2, EPI_BF16, qkv, 3 * I, nullptr);
         push(run_self, 1, "attn_self", attn_flops); plan->flops += attn_flops;
     }
-    linear(att, rows, I, t.out2, EPI_F32, y, I, y);
+    linear(att, rows, I, t.out2, EPI_BF16, y, I, nullptr, 0, nullptr, 0, y);
     // feed-forward: Linear(C -> 8C) with the GEGLU gate fused into the GEMM epilogue, Linear(4C -> C) + residual
     lnorm(y, t.ln3, rows, I, lin);
     linear(lin, rows, I, t.ff1, EPI_GEGLU, ffh, 4 * I, nullptr);
-    linear(ffh, rows, 4 * I, t.ff2, EPI_F32, y, I, y);
-    // proj_out + x_in
-    convert(y, I, rows, DST_LINEAR, H, W, lin);
-    x.st = stat_alloc(C, HW, 0);
-    linear(lin, rows, I, t.proj_out, EPI_F32, x.p, C, x.p, 0, &x.st, HW);
+    linear(ffh, rows, 4 * I, t.ff2, EPI_BF16, y, I, nullptr, 0, nullptr, 0, y);
+    // proj_out + x_in (reads the 16-bit stream directly)
+    x.st = stat_alloc(C, HW);
+    linear(y, rows, I, t.proj_out, EPI_F32, x.p, C, x.p, 0, &x.st, HW);
 }
 
 
@@ -409,7 +408,7 @@ void Builder::build() {
         const int b = B, c = n->in_ch, t = T, h = H0, w = W0;
         push([=](cudaStream_t st) { return ncthw_to_pad(x_in, b, c, t, h, w, 64, pad, st); });
         cur.p = (float*)palloc((size_t)rows0 * mc * 4);
-        cur.st = stat_alloc(mc, H0 * W0, 2);
+        cur.st = stat_alloc(mc, H0 * W0);
         conv3x3(pad, H0, W0, 64, n->inp[0].layers[0].conv, 1, cur.p, nullptr, 0, nullptr, &cur.st);
         tap("input_blocks.0.0", cur);
     }
@@ -428,7 +427,7 @@ void Builder::build() {
                 convert(cur.p, cur.C, rows, DST_SPATIAL_PAD, cur.H, cur.W, pad);
                 Act o; o.C = L.cout; o.H = cur.H / 2; o.W = cur.W / 2;
                 o.p = (float*)palloc((size_t)NF * o.H * o.W * o.C * 4);
-                o.st = stat_alloc(o.C, o.H * o.W, 2);
+                o.st = stat_alloc(o.C, o.H * o.W);
                 conv3x3(pad, cur.H, cur.W, cur.C, L.conv, 2, o.p, nullptr, 0, nullptr, &o.st);
                 cur = o;
             } else if (L.kind == "up") {
@@ -439,7 +438,7 @@ void Builder::build() {
                 convert(cur.p, cur.C, rows, DST_SPATIAL_PAD_UP2, cur.H, cur.W, pad);
                 Act o; o.C = L.cout; o.H = H2; o.W = W2;
                 o.p = (float*)palloc((size_t)NF * H2 * W2 * o.C * 4);
-                o.st = stat_alloc(o.C, H2 * W2, 2);
+                o.st = stat_alloc(o.C, H2 * W2);
                 conv3x3(pad, H2, W2, cur.C, L.conv, 1, o.p, nullptr, 0, nullptr, &o.st);
                 cur = o;
             }
@@ -488,12 +487,10 @@ static int get_plan(moca_unet* n, int B, int T, int H, int W, int Lmax, Plan** o
     dry.build();
     if (dry.rc) return dry.rc;
     Builder real = dry;
-    real.dry = false; real.stat_slots = 0; real.cs_doubles = 0; real.part_elems = 0;
+    real.dry = false; real.cs_doubles = 0;
     plan->launches = 0; plan->flops = 0;
     plan->stats_bytes = dry.cs_doubles * sizeof(double);
     plan->stats = (double*)real.palloc(plan->stats_bytes);
-    plan->parts = (float2*)real.palloc(dry.part_elems * sizeof(float2));
-    plan->mr_table = (float2*)real.palloc((size_t)dry.stat_slots * B * T * 32 * sizeof(float2));
     plan->ab_table = (float2*)real.palloc((size_t)B * T * 3072 * sizeof(float2));      // gn_apply supports C <= 3072
     for (int i = 0; i < S_COUNT; ++i) {
         real.sptr[i] = real.palloc(dry.need[i] + 256);

