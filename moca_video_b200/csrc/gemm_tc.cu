@@ -100,6 +100,110 @@ __device__ __forceinline__ bool map_row(const GemmParams& P, int row, int& out_r
     return true;
 }
 
+// ---- stream-K tail -------------------------------------------------------------------------------------------------
+// A persistent grid of G CTAs runs floor(ntiles / G) full waves data-parallel (CTA g: tiles g, g + G, ..).  The R < G tiles
+// that remain would cost a whole wave; with sk_on their R * kiters k-block iterations are dealt out evenly instead, CTA g
+// taking units [g U / G, (g + 1) U / G) of U = R * kiters.  Such a range touches at most two tiles.  The part that reaches
+// the END of a tile makes its CTA that tile's OWNER (it runs the normal epilogue, after adding the partial accumulators of
+// the CTAs that hold the earlier k ranges of the tile: CTAs g_lo .. g - 1); any other part is a CONTRIBUTION: the raw fp32
+// accumulator goes to sk_ws[g] and every epilogue warp bumps sk_flags[g].  A CTA has at most one contribution and does it
+// before its owner part, so an owner only ever waits for CTAs that are not waiting themselves.  The owner's warps bump the
+// counters again when they have read the partials; the last one resets them to zero for the next launch.
+struct SkPlan {
+    int n_dp = 0;                       // data-parallel tiles of this CTA: tile0 + i * tstep
+    bool has_c = false, has_o = false;
+    int c_tile = 0, c_k0 = 0, c_k1 = 0;  // contribution: k-block iterations [c_k0, c_k1) of c_tile
+    int o_tile = 0, o_k0 = 0;            // owner part: iterations [o_k0, kiters) of o_tile (o_k0 == 0: a whole tile)
+    int g_lo = 0;                       // contributors of o_tile: CTAs g_lo .. g - 1
+};
+
+__device__ __forceinline__ SkPlan sk_decompose(const GemmParams& P, int g, int G, int ntiles, int kiters) {
+    SkPlan s;
+    if (!P.sk_on) {
+        s.n_dp = g < ntiles ? (ntiles - g + G - 1) / G : 0;
+        return s;
+    }
+    const int n_full = ntiles / G, tail0 = n_full * G, R = ntiles - tail0;
+    s.n_dp = n_full;
+    const long long U = (long long)R * kiters;
+    const long long b0 = (long long)g * U / G, b1 = (long long)(g + 1) * U / G;
+    if (b1 > b0) {
+        const int ta = (int)(b0 / kiters), ka = (int)(b0 - (long long)ta * kiters), len = (int)(b1 - b0);
+        const int enda = min(kiters, ka + len);
+        if (enda == kiters) { s.has_o = true; s.o_tile = tail0 + ta; s.o_k0 = ka; }
+        else { s.has_c = true; s.c_tile = tail0 + ta; s.c_k0 = ka; s.c_k1 = enda; }
+        const int rem = len - (enda - ka);
+        if (rem > 0) { s.has_c = true; s.c_tile = tail0 + ta + 1; s.c_k0 = 0; s.c_k1 = rem; }
+        if (s.has_o && s.o_k0 > 0) {
+            const long long tu = (long long)ta * kiters;          // first unit of the owner's tile
+            int gl = (int)(tu * G / U);
+            while ((long long)(gl + 1) * U / G <= tu) ++gl;
+            while (gl > 0 && (long long)gl * U / G > tu) --gl;
+            s.g_lo = gl;
+        }
+    }
+    return s;
+}
+
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// contribution of one epilogue warp (lane quarter q, warp widx of the nwq warps that share the quarter): its 32 accumulator rows,
+// every nwq-th 32-column chunk, raw fp32 into sk_ws[g]; then the warp announces itself
+// Workspace layout of one slot: [BN / 4 column quads][128 rows] float4 — a warp's store / load of one quad for its 32 rows is 512
+// contiguous bytes.
+template <int BN, int EPI_WARPS>
+__device__ __forceinline__ void sk_contribute(const GemmParams& P, uint32_t t_row, int g, int q, int widx, int lane) {
+    float4* wsq = reinterpret_cast<float4*>(P.sk_ws + (size_t)g * kBM * BN) + q * 32 + lane;
+    constexpr int nwq = EPI_WARPS / 4;
+    for (int c = widx; c < BN / 32; c += nwq) {
+        uint32_t r[32];
+        tmem_ld32(t_row + (uint32_t)(c * 32), r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            wsq[(size_t)(c * 8 + j) * kBM] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+    }
+    __threadfence();
+    __syncwarp();
+    if (lane == 0) atomicAdd(P.sk_flags + g, 1u);
+}
+// owner: wait until every epilogue warp of the contributing CTAs g_lo .. g - 1 has written its part
+template <int EPI_WARPS>
+__device__ __forceinline__ void sk_wait(const GemmParams& P, int g_lo, int g, int lane) {
+    if (lane == 0)
+        for (int gp = g_lo; gp < g; ++gp)
+            while (ld_acquire_u32(P.sk_flags + gp) < (unsigned)EPI_WARPS) __nanosleep(64);
+    __syncwarp();
+    __threadfence();
+}
+// owner: r[0..31] (thread = accumulator row `row` of the tile, columns col .. col + 31) += the partials, in CTA order
+template <int BN>
+__device__ __forceinline__ void sk_add32(const GemmParams& P, int g_lo, int g, int row, int col, uint32_t* r) {
+    for (int gp = g_lo; gp < g; ++gp) {
+        const float4* src = reinterpret_cast<const float4*>(P.sk_ws + (size_t)gp * kBM * BN) + (size_t)(col >> 2) * kBM + row;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float4 t = __ldcg(src + (size_t)j * kBM);
+            r[4 * j] = __float_as_uint(__uint_as_float(r[4 * j]) + t.x);
+            r[4 * j + 1] = __float_as_uint(__uint_as_float(r[4 * j + 1]) + t.y);
+            r[4 * j + 2] = __float_as_uint(__uint_as_float(r[4 * j + 2]) + t.z);
+            r[4 * j + 3] = __float_as_uint(__uint_as_float(r[4 * j + 3]) + t.w);
+        }
+    }
+}
+// owner, when the tile is done: the last of the 2 * EPI_WARPS arrivals (contributors + readers) clears the counter
+template <int EPI_WARPS>
+__device__ __forceinline__ void sk_release(const GemmParams& P, int g_lo, int g, int lane) {
+    __syncwarp();
+    if (lane == 0)
+        for (int gp = g_lo; gp < g; ++gp)
+            if (atomicAdd(P.sk_flags + gp, 1u) == 2u * EPI_WARPS - 1u) atomicExch(P.sk_flags + gp, 0u);
+}
+
 // STATS: GroupNorm statistics of the stored values (EPI_F32); for the bf16 thread = row epilogue (TEPI && EPI_BF16) the same
 // flag selects the variant that adds a 16-bit residual (RES16).
 template <int BN, int EPI, bool STATS, bool TEPI = false, int NCTA = 1>
@@ -128,6 +232,7 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
     const int ntiles = NCTA == 2 ? ((P.num_m_tiles + 1) >> 1) * P.num_n_tiles : P.num_m_tiles * P.num_n_tiles;
     auto MT = [&](int tile) { return NCTA == 2 ? 2 * (tile / P.num_n_tiles) + cta_rank : tile / P.num_n_tiles; };
     const int kiters = P.ntaps * P.kblocks;
+    const SkPlan sk = sk_decompose(P, tile0, tstep, ntiles, kiters);      // NCTA == 2 never runs with sk_on
 
     if (threadIdx.x == 0) {
         prefetch_tmap(&P.tmA);
@@ -165,27 +270,30 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
             // ===== TMA producer =====
             int stage = 0;
             uint32_t phase = 0;
-            for (int tile = tile0; tile < ntiles; tile += tstep) {
+            auto produce = [&](int tile, int k0, int k1) {
                 const int mt = MT(tile), nt = tile % P.num_n_tiles;
-                for (int tap = 0; tap < P.ntaps; ++tap) {
+                int tap = k0 / P.kblocks, kb = k0 - tap * P.kblocks;
+                for (int it = k0; it < k1; ++it) {
                     const int arow = mt * kBM + P.tap_shift[tap];
-                    for (int kb = 0; kb < P.kblocks; ++kb) {
-                        mbar_wait(&empty[stage], phase ^ 1);
-                        uint8_t* sa = base + (size_t)stage * Cfg::STAGE_BYTES;
-                        if constexpr (NCTA == 2) {
-                            // both CTAs load their A rows and their half of the B rows; all bytes are counted on the leader's barrier
-                            if (cta_rank == 0) mbar_expect_tx(&full[stage], 2 * Cfg::STAGE_BYTES);
-                            tma_load_2d_pair(sa, &P.tmA, &full[stage], kb * kBK, arow);
-                            tma_load_2d_pair(sa + kABytes, &P.tmB, &full[stage], tap * P.Kp + kb * kBK, nt * BN + cta_rank * (BN / 2));
-                        } else {
-                            mbar_expect_tx(&full[stage], Cfg::STAGE_BYTES);
-                            tma_load_2d(sa, &P.tmA, &full[stage], kb * kBK, arow);
-                            tma_load_2d(sa + kABytes, &P.tmB, &full[stage], tap * P.Kp + kb * kBK, nt * BN);
-                        }
-                        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                    mbar_wait(&empty[stage], phase ^ 1);
+                    uint8_t* sa = base + (size_t)stage * Cfg::STAGE_BYTES;
+                    if constexpr (NCTA == 2) {
+                        // both CTAs load their A rows and their half of the B rows; all bytes are counted on the leader's barrier
+                        if (cta_rank == 0) mbar_expect_tx(&full[stage], 2 * Cfg::STAGE_BYTES);
+                        tma_load_2d_pair(sa, &P.tmA, &full[stage], kb * kBK, arow);
+                        tma_load_2d_pair(sa + kABytes, &P.tmB, &full[stage], tap * P.Kp + kb * kBK, nt * BN + cta_rank * (BN / 2));
+                    } else {
+                        mbar_expect_tx(&full[stage], Cfg::STAGE_BYTES);
+                        tma_load_2d(sa, &P.tmA, &full[stage], kb * kBK, arow);
+                        tma_load_2d(sa + kABytes, &P.tmB, &full[stage], tap * P.Kp + kb * kBK, nt * BN);
                     }
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                    if (++kb == P.kblocks) { kb = 0; ++tap; }
                 }
-            }
+            };
+            for (int i = 0; i < sk.n_dp; ++i) produce(tile0 + i * tstep, 0, kiters);
+            if (sk.has_c) produce(sk.c_tile, sk.c_k0, sk.c_k1);
+            if (sk.has_o) produce(sk.o_tile, sk.o_k0, kiters);
         }
     } else if (warp == 1) {
         if (lane == 0 && cta_rank == 0) {
@@ -195,11 +303,11 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
             uint32_t phase = 0;
             int as = 0;
             uint32_t aphase = 0;
-            for (int tile = tile0; tile < ntiles; tile += tstep) {
+            auto mma_part = [&](int nk) {
                 mbar_wait(&tempty[as], aphase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + (uint32_t)(as * BN);
-                for (int it = 0; it < kiters; ++it) {
+                for (int it = 0; it < nk; ++it) {
                     mbar_wait(&full[stage], phase);
                     tc_fence_after();
                     const uint32_t sa = smem_u32(base + (size_t)stage * Cfg::STAGE_BYTES);
@@ -219,7 +327,10 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
                 else umma_commit(&tfull[as]);
                 as ^= 1;
                 if (as == 0) aphase ^= 1;
-            }
+            };
+            for (int i = 0; i < sk.n_dp; ++i) mma_part(kiters);
+            if (sk.has_c) mma_part(sk.c_k1 - sk.c_k0);
+            if (sk.has_o) mma_part(kiters - sk.o_k0);
         }
     } else if constexpr (TEPI && EPI == EPI_GEGLU) {
         // ===== GEGLU, thread = row, 16 warps: warp (q, c) owns output columns c*32 .. +31 of the tile's 128 for the rows of
@@ -288,17 +399,21 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
         constexpr int kChunks = BN / 32;
         // the two warps of a lane quarter take alternate 32-column chunks; with an odd chunk count (BN = 160: 3 + 2) they swap
         // roles from one tile of this CTA to the next, so that over two tiles (= the two accumulator stages) both do 5 chunks
-        auto first_chunk = [&](int t) { return (kChunks & 1) ? (half ^ (((t - tile0) / tstep) & 1)) : half; };
-        int pt = tile0, pc = first_chunk(tile0);
+        // epilogue items of this CTA: its data-parallel tiles, then (stream-K) the tile it owns the end of
+        const int n_items = sk.n_dp + (sk.has_o ? 1 : 0);
+        auto item_tile = [&](int i) { return i < sk.n_dp ? tile0 + i * tstep : sk.o_tile; };
+        auto first_chunk = [&](int i) { return (kChunks & 1) ? (half ^ (i & 1)) : half; };
+        int pi = 0, pc = first_chunk(0);
         uint32_t n_issued = 0, n_waited = 0;
-        auto norm = [&](int& t, int& c) {
-            while (t < ntiles && !(c < kChunks && (t % P.num_n_tiles) * BN + c * 32 < P.N)) { t += tstep; c = first_chunk(t); }
+        auto norm = [&](int& i, int& c) {
+            while (i < n_items && !(c < kChunks && (item_tile(i) % P.num_n_tiles) * BN + c * 32 < P.N)) { ++i; c = first_chunk(i); }
         };
         auto issue_res = [&]() {                               // lane 0 only
-            while (pt < ntiles) {
+            while (pi < n_items) {
+                const int pt = item_tile(pi);
                 const int prow0 = MT(pt) * kBM + q * 32;
                 const int pn0 = (pt % P.num_n_tiles) * BN + pc * 32;
-                pc += 2; norm(pt, pc);
+                pc += 2; norm(pi, pc);
                 if (prow0 >= P.M) continue;
                 const uint32_t slot = n_issued & 1u;
                 mbar_expect_tx(&rbar[slot], 2048);
@@ -308,19 +423,35 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
             }
         };
         if constexpr (RES16) {
-            norm(pt, pc);
+            norm(pi, pc);
             if (lane == 0) { issue_res(); issue_res(); }
         }
         int as = 0;
         uint32_t aphase = 0, nst = 0;
-        for (int tile = tile0; tile < ntiles; tile += tstep) {
+        bool contrib_pending = sk.has_c;
+        auto do_contrib = [&]() {
+            mbar_wait(&tfull[as], aphase);
+            tc_fence_after();
+            sk_contribute<BN, Cfg::EPI_WARPS>(P, tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN), tile0, q, half, lane);
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty[as]);
+            as ^= 1;
+            if (as == 0) aphase ^= 1;
+            contrib_pending = false;
+        };
+        for (int ii = 0; ii < n_items; ++ii) {
+            if (ii == sk.n_dp && contrib_pending) do_contrib();
+            const int tile = item_tile(ii);
+            const bool fix = ii == sk.n_dp && sk.o_k0 > 0;
             const int mt = MT(tile), nt = tile % P.num_n_tiles;
             const int row0 = mt * kBM + q * 32;
             mbar_wait(&tfull[as], aphase);
             tc_fence_after();
+            if (fix) sk_wait<Cfg::EPI_WARPS>(P, sk.g_lo, tile0, lane);
             const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN);
             if (row0 < P.M) {
-                for (int c = first_chunk(tile); c < kChunks; c += 2) {
+                for (int c = first_chunk(ii); c < kChunks; c += 2) {
                     const int n0 = nt * BN + c * 32;
                     if (n0 >= P.N) break;
                     uint32_t r[32];
@@ -330,6 +461,7 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
                     if (lane == 0) bulk_wait_read1();          // the store issued two chunks ago has released this box
                     __syncwarp();
                     tmem_ld_wait();
+                    if (fix) sk_add32<BN>(P, sk.g_lo, tile0, q * 32 + lane, c * 32, r);
                     uint4* dst = reinterpret_cast<uint4*>(stgb + (nst & 1u) * 2048 + lane * 64);
 #pragma unroll
                     for (int u = 0; u < 4; ++u) {
@@ -362,12 +494,14 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
                     if constexpr (RES16) ++n_waited;
                 }
             }
+            if (fix) sk_release<Cfg::EPI_WARPS>(P, sk.g_lo, tile0, lane);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&tempty[as]);
             as ^= 1;
             if (as == 0) aphase ^= 1;
         }
+        if (contrib_pending) do_contrib();
         if (lane == 0) bulk_wait0();
     } else if constexpr (TEPI) {
         // ===== TMA-store epilogue (linear / time-padded rows, 32-row slices that map to 32 consecutive output rows) =====
@@ -562,26 +696,47 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
             }
         };
 
-        int tile = tile0;
+        // epilogue items of this CTA: its data-parallel tiles, then (stream-K) the tile it owns the end of; a contribution to
+        // another tile's owner, if any, is dumped between the two
+        const int n_items = sk.n_dp + (sk.has_o ? 1 : 0);
+        auto item_tile = [&](int i) { return i < sk.n_dp ? tile0 + i * tstep : sk.o_tile; };
+        bool contrib_pending = sk.has_c;
+        auto do_contrib = [&]() {
+            mbar_wait(&tfull[as], aphase);
+            tc_fence_after();
+            sk_contribute<BN, Cfg::EPI_WARPS>(P, tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN), tile0, q, half, lane);
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty[as]);
+            as ^= 1;
+            if (as == 0) aphase ^= 1;
+            contrib_pending = false;
+        };
         int out_row = 0, nxt_row = 0;
         int frame_u = -1, nxt_frame = -1;
         uint32_t vmask = 0, nxt_mask = 0;
         float4 pre[8];
         bool have_pre = false;
-        if (tile < ntiles) {
+        if (n_items > 0) {
+            const int tile = item_tile(0);
             tile_rows(tile, out_row, vmask, frame_u);
             if (EPI == EPI_F32 && col0_of(tile) + half * 32 < ncols_total) {
                 prefetch(pre, out_row, vmask, col0_of(tile) + half * 32);
                 have_pre = true;
             }
         }
-        for (; tile < ntiles; tile += tstep) {
+        for (int ii = 0; ii < n_items; ++ii) {
+            if (ii == sk.n_dp && contrib_pending) do_contrib();
+            const int tile = item_tile(ii);
+            const bool fix = ii == sk.n_dp && sk.o_k0 > 0;
             const int nt = tile % P.num_n_tiles;
             const int col_tile0 = col0_of(tile);
-            const int ntile = tile + tstep;
+            const bool has_next = ii + 1 < n_items;
+            const int ntile = has_next ? item_tile(ii + 1) : 0;
             bool nxt_ready = false;
             mbar_wait(&tfull[as], aphase);
             tc_fence_after();
+            if (fix) sk_wait<Cfg::EPI_WARPS>(P, sk.g_lo, tile0, lane);
             const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN);
             for (int c = half; c < kChunks; c += 2) {
                 const int n0 = col_tile0 + c * 32;                 // first output column of this chunk
@@ -595,7 +750,7 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
                     if (c + 2 < kChunks && n0 + 64 < ncols_total) {
                         prefetch(nxt, out_row, vmask, n0 + 64);
                         have_nxt = true;
-                    } else if (ntile < ntiles) {
+                    } else if (has_next) {
                         if (!nxt_ready) { tile_rows(ntile, nxt_row, nxt_mask, nxt_frame); nxt_ready = true; }
                         if (col0_of(ntile) + half * 32 < ncols_total) {
                             prefetch(nxt, nxt_row, nxt_mask, col0_of(ntile) + half * 32);
@@ -603,6 +758,7 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
                         }
                     }
                     tmem_ld_wait();
+                    if (fix) sk_add32<BN>(P, sk.g_lo, tile0, q * 32 + lane, c * 32, r);
 #pragma unroll
                     for (int j = 0; j < 8; ++j)
                         *reinterpret_cast<uint4*>(stg + lane * 32 + ((j ^ (lane & 7)) << 2)) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
@@ -743,6 +899,7 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
                         for (int e = 0; e < 8; ++e) { bb[e] = __ldg(bvp + e); bg[e] = __ldg(bvp + BN / 2 + e); }
                     } else {
                         tmem_ld_wait();
+                        if (fix) sk_add32<BN>(P, sk.g_lo, tile0, q * 32 + lane, c * 32, r);
 #pragma unroll
                         for (int e = 0; e < 8; ++e) bb[e] = (P.bias && e < nvalid) ? P.bias[col + e] : 0.f;
                     }
@@ -781,6 +938,7 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
                     __syncwarp();
                 }
             }
+            if (fix) sk_release<Cfg::EPI_WARPS>(P, sk.g_lo, tile0, lane);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) {
@@ -790,12 +948,13 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
             as ^= 1;
             if (as == 0) aphase ^= 1;
             if (EPI == EPI_F32) {
-                if (!nxt_ready && ntile < ntiles) tile_rows(ntile, nxt_row, nxt_mask, nxt_frame);
+                if (!nxt_ready && has_next) tile_rows(ntile, nxt_row, nxt_mask, nxt_frame);
                 out_row = nxt_row; vmask = nxt_mask; frame_u = nxt_frame;
-            } else if (ntile < ntiles) {
+            } else if (has_next) {
                 tile_rows(ntile, out_row, vmask, frame_u);
             }
         }
+        if (contrib_pending) do_contrib();
     }
     tc_fence_before();
     if constexpr (NCTA == 2) cluster_sync_all();             // no CTA of the pair exits while its peer can still reach its smem / TMEM
@@ -1071,6 +1230,26 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
         L.smem = L.BN == 160 ? GemmCfg<160, true>::SMEM : GemmCfg<128, true>::SMEM;
     } else {
         L.smem = L.BN == 256 ? GemmCfg<256>::SMEM : (L.BN == 160 ? GemmCfg<160>::SMEM : GemmCfg<128>::SMEM);
+    }
+    // stream-K tail (see SkPlan): staged fp32 / 16-bit epilogues and the 16-bit thread = row epilogue, main loops long enough
+    // that a tile is worth splitting, a tail that leaves at least 20 % of the last wave idle, and at least 4 k-block
+    // iterations per CTA in the tail.  Off under programmatic dependent launch (two GEMMs could share the workspace).
+    // OFF BY DEFAULT (MOCA_GEMM_STREAMK=1 turns it on): measured on the b=2 forward it loses.  The fix-up (contributor dump,
+    // fence, flag, owner's wait and 128 KB reads per contributor) is a serial ~15-20 us at the end of the kernel, more than the
+    // fraction of a 13-150 us wave it saves: 200 tiles x K 1280: 25.1 -> 34.7 us, 225-tile (3,1,1) conv 60.4 -> 74.3 us,
+    // 561-tile 3x3 conv 153.8 -> 166.3 us, forward 41.3 -> 41.9 ms (profiles/README.md, round 2 negative results).
+    {
+        static const int sk_env = [] { const char* e = getenv("MOCA_GEMM_STREAMK"); return e ? atoi(e) : 0; }();
+        static const int sk_mink = [] { const char* e = getenv("MOCA_GEMM_STREAMK_MINK"); return e ? atoi(e) : 16; }();
+        const int kiters = d.ntaps * p.kblocks, G = ctx.num_sms, R = ntiles % G;
+        const bool epi_ok = ncta == 1 && ((d.epi == EPI_F32 && !p.tepi) || (d.epi == EPI_BF16 && (bt || !p.tepi)));
+        p.sk_on = sk_env && pdl_level() == 0 && epi_ok && ctx.d_sk_ws && kiters >= sk_mink && R > 0 && R * 10 <= G * 8 &&
+                  (long long)R * kiters >= 4ll * G;
+        if (p.sk_on) {
+            L.grid = G;
+            p.sk_ws = ctx.d_sk_ws;
+            p.sk_flags = ctx.d_sk_flags;
+        }
     }
     L.flops = 2.0 * (double)d.M * d.N * d.ntaps * d.a_cols;
     if (ncta == 2) {

@@ -47,6 +47,10 @@ struct GemmParams {
     const op_t* res16;        // EPI_BF16 only: 16-bit residual [out_rows, ldo] or null (may alias the output: in-place stream update)
     int epi;
     int out16;                // EPI_F32 epilogues: store the result as op_t (outb) instead of fp32; statistics unchanged
+    // stream-K tail (gemm_tc.cu): the tiles beyond the last full wave are split along K over all CTAs of the grid
+    int sk_on;
+    float* sk_ws;             // [grid][128][BN] fp32 partial accumulators, one slot per contributing CTA
+    unsigned* sk_flags;       // [grid] arrival counters (zero between launches)
     int num_m_tiles, num_n_tiles;
     double* cstat;            // optional per-(frame, output channel) {sum, sum of squares} of the stored fp32 values
     int stat_rpf;             // output rows per frame (frame = out_row / stat_rpf)

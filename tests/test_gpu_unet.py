@@ -14,6 +14,7 @@ from conftest import GOLDEN
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda"
+VARIANT_TOL = 4e-3      # two realisations of the 16-bit rounding noise (see test_gemm_epilogue_variants_agree)
 TOL = 2e-2
 
 
@@ -115,7 +116,9 @@ def test_unet_full_cfg_batch_equals_separate_forwards(full):
     ctx = torch.zeros(2, 154, 1024, device=DEV)
     ctx[0] = c[0]; ctx[1, :77] = u[0]; ctx[1, 77:] = 1e4          # poison the padding
     e2 = net(torch.cat([x, x]), ts + ts, ctx, fps=10, ctx_len=[154, 77])
-    assert rel(e2[0:1], e_c) < 1e-3 and rel(e2[1:2], e_u) < 1e-3     # same kernels and statistics chunks; only fp64 atomics order differs
+    # same kernels; the batch size changes the tile / stream-K split of the GEMMs (fp32 summation order) and the atomics order:
+    # two realisations of the 16-bit rounding noise (VARIANT_TOL, see test_gemm_epilogue_variants_agree)
+    assert rel(e2[0:1], e_c) < VARIANT_TOL and rel(e2[1:2], e_u) < VARIANT_TOL
 
 
 def test_fifo_onestep_vs_oracle(small):
@@ -255,8 +258,6 @@ def test_fifo_iterations_vs_oracle(small):
     assert rel(out["latents"].cpu(), torch.from_numpy(lat)) < TOL
 
 
-VARIANT_TOL = 4e-3      # two realisations of the 16-bit rounding noise (see test_gemm_epilogue_variants_agree)
-
 _VARIANT_SCRIPT = r"""
 import sys, torch
 sys.path.insert(0, {root!r})
@@ -311,6 +312,15 @@ def test_programmatic_dependent_launch_same_result(tmp_path):
     y0 = _variant_output({"MOCA_PDL": "0"}, tmp_path, "pdl0")
     y2 = _variant_output({"MOCA_PDL": "2"}, tmp_path, "pdl2")
     assert rel(y0, y2) < VARIANT_TOL
+
+
+def test_stream_k_tail_same_result(tmp_path):
+    """MOCA_GEMM_STREAMK=1: the tiles beyond the last full wave of a long-K GEMM / conv are split along K over all CTAs, partial
+    accumulators meet in a global workspace (gemm_tc.cu SkPlan).  Kept as a tested switch; off by default (it loses, see there).
+    The 256-channel 3x3 convs of the reduced model (36 k-block iterations, < 148 tiles) take the path."""
+    y0 = _variant_output({"MOCA_GEMM_STREAMK": "0"}, tmp_path, "sk0")
+    y1 = _variant_output({"MOCA_GEMM_STREAMK": "1"}, tmp_path, "sk1")
+    assert float(y1.abs().mean()) > 0 and rel(y1, y0) < VARIANT_TOL
 
 
 def test_cta_pair_gemm_same_result(tmp_path):
