@@ -204,6 +204,25 @@ __device__ __forceinline__ void sk_release(const GemmParams& P, int g_lo, int g,
             if (atomicAdd(P.sk_flags + gp, 1u) == 2u * EPI_WARPS - 1u) atomicExch(P.sk_flags + gp, 0u);
 }
 
+// LayerNorm fold, consumer side: mean and rstd of accumulator row `row` from the producer's partial sums.  Split in two so that
+// the loads (all issued back to back: the slot count is even and at most 10, gemm_plan) run one tile ahead of their use.
+struct LnRow { float4 v[5]; };
+__device__ __forceinline__ void ln_row_load(const GemmParams& P, int row, LnRow& t) {
+    const float4* src = reinterpret_cast<const float4*>(P.ln_rs + (size_t)row * P.ln_slots);
+    const int nq = row < P.M ? (P.ln_slots >> 1) : 0;
+#pragma unroll
+    for (int i = 0; i < 5; ++i) t.v[i] = i < nq ? __ldcg(src + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+}
+__device__ __forceinline__ void ln_row_finish(const GemmParams& P, const LnRow& t, float& rstd, float& nmr) {
+    float sx = 0.f, sq = 0.f;
+#pragma unroll
+    for (int i = 0; i < 5; ++i) { sx += t.v[i].x + t.v[i].z; sq += t.v[i].y + t.v[i].w; }
+    const float mean = sx * P.ln_inv_c;
+    const float var = fmaxf(sq * P.ln_inv_c - mean * mean, 0.f);
+    rstd = rsqrtf(var + P.ln_eps);
+    nmr = -mean * rstd;
+}
+
 // STATS: GroupNorm statistics of the stored values (EPI_F32); for the bf16 thread = row epilogue (TEPI && EPI_BF16) the same
 // flag selects the variant that adds a 16-bit residual (RES16).
 template <int BN, int EPI, bool STATS, bool TEPI = false, int NCTA = 1>
@@ -341,10 +360,17 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
         const int ncols_total = P.N >> 1;
         int as = 0;
         uint32_t aphase = 0;
+        LnRow lnr;                                             // LayerNorm fold: row statistics, requested one tile ahead
+        if (P.ln_s && tile0 < ntiles) ln_row_load(P, MT(tile0) * kBM + q * 32 + lane, lnr);
         for (int tile = tile0; tile < ntiles; tile += tstep) {
             const int mt = MT(tile), nt = tile % P.num_n_tiles;
             const int row0 = mt * kBM + q * 32;
             const int n0 = nt * (BN / 2) + c * 32;
+            float rstd = 1.f, nmr = 0.f;
+            if (P.ln_s) {
+                ln_row_finish(P, lnr, rstd, nmr);
+                if (tile + tstep < ntiles) ln_row_load(P, MT(tile + tstep) * kBM + q * 32 + lane, lnr);
+            }
             mbar_wait(&tfull[as], aphase);
             tc_fence_after();
             const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN);
@@ -360,13 +386,21 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
                     const float4* bg = reinterpret_cast<const float4*>(P.bias + (size_t)nt * BN + BN / 2 + c * 32 + h * 16);
                     tmem_ld_wait();
                     uint32_t pk[8];
+                    const float4* sv = reinterpret_cast<const float4*>(P.ln_s + (size_t)nt * BN + c * 32 + h * 16);
+                    const float4* sg = reinterpret_cast<const float4*>(P.ln_s + (size_t)nt * BN + BN / 2 + c * 32 + h * 16);
 #pragma unroll
                     for (int u = 0; u < 4; ++u) {
-                        const float4 b1 = __ldg(bv + u), b2 = __ldg(bg + u);
-                        const float o0 = (__uint_as_float(rv[4 * u]) + b1.x) * gelu_fast(__uint_as_float(rg[4 * u]) + b2.x);
-                        const float o1 = (__uint_as_float(rv[4 * u + 1]) + b1.y) * gelu_fast(__uint_as_float(rg[4 * u + 1]) + b2.y);
-                        const float o2 = (__uint_as_float(rv[4 * u + 2]) + b1.z) * gelu_fast(__uint_as_float(rg[4 * u + 2]) + b2.z);
-                        const float o3 = (__uint_as_float(rv[4 * u + 3]) + b1.w) * gelu_fast(__uint_as_float(rg[4 * u + 3]) + b2.w);
+                        float4 b1 = __ldg(bv + u), b2 = __ldg(bg + u);
+                        if (P.ln_s) {
+                            // LayerNorm fold: rstd * (acc - mean s[n]) + bias[n] = fma(rstd, acc, fma(-mean rstd, s[n], bias[n]))
+                            const float4 s1 = __ldg(sv + u), s2 = __ldg(sg + u);
+                            b1.x = fmaf(nmr, s1.x, b1.x); b1.y = fmaf(nmr, s1.y, b1.y); b1.z = fmaf(nmr, s1.z, b1.z); b1.w = fmaf(nmr, s1.w, b1.w);
+                            b2.x = fmaf(nmr, s2.x, b2.x); b2.y = fmaf(nmr, s2.y, b2.y); b2.z = fmaf(nmr, s2.z, b2.z); b2.w = fmaf(nmr, s2.w, b2.w);
+                        }
+                        const float o0 = fmaf(rstd, __uint_as_float(rv[4 * u]), b1.x) * gelu_fast(fmaf(rstd, __uint_as_float(rg[4 * u]), b2.x));
+                        const float o1 = fmaf(rstd, __uint_as_float(rv[4 * u + 1]), b1.y) * gelu_fast(fmaf(rstd, __uint_as_float(rg[4 * u + 1]), b2.y));
+                        const float o2 = fmaf(rstd, __uint_as_float(rv[4 * u + 2]), b1.z) * gelu_fast(fmaf(rstd, __uint_as_float(rg[4 * u + 2]), b2.z));
+                        const float o3 = fmaf(rstd, __uint_as_float(rv[4 * u + 3]), b1.w) * gelu_fast(fmaf(rstd, __uint_as_float(rg[4 * u + 3]), b2.w));
                         pk[2 * u] = pack_bf16(o0, o1);
                         pk[2 * u + 1] = pack_bf16(o2, o3);
                     }
@@ -440,12 +474,20 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
             if (as == 0) aphase ^= 1;
             contrib_pending = false;
         };
+        LnRow lnr;                                             // LayerNorm fold, consumer: row statistics, requested one tile ahead
+        if (P.ln_s && n_items > 0) ln_row_load(P, MT(item_tile(0)) * kBM + q * 32 + lane, lnr);
         for (int ii = 0; ii < n_items; ++ii) {
             if (ii == sk.n_dp && contrib_pending) do_contrib();
             const int tile = item_tile(ii);
             const bool fix = ii == sk.n_dp && sk.o_k0 > 0;
             const int mt = MT(tile), nt = tile % P.num_n_tiles;
             const int row0 = mt * kBM + q * 32;
+            float rstd = 1.f, nmr = 0.f;
+            if (P.ln_s) {
+                ln_row_finish(P, lnr, rstd, nmr);
+                if (ii + 1 < n_items) ln_row_load(P, MT(item_tile(ii + 1)) * kBM + q * 32 + lane, lnr);
+            }
+            float rs_sum = 0.f, rs_sq = 0.f;                   // LayerNorm fold, producer: this thread's row, this warp's columns
             mbar_wait(&tfull[as], aphase);
             tc_fence_after();
             if (fix) sk_wait<Cfg::EPI_WARPS>(P, sk.g_lo, tile0, lane);
@@ -468,7 +510,17 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
                         float v[8];
 #pragma unroll
                         for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[8 * u + e]);
-                        if (P.bias) {
+                        if (P.ln_s) {
+                            // LayerNorm fold: rstd * (acc - mean s[n]) + bias[n] = fma(rstd, acc, fma(-mean rstd, s[n], bias[n]))
+                            const float4 s1 = __ldg(reinterpret_cast<const float4*>(P.ln_s + n0) + 2 * u);
+                            const float4 s2 = __ldg(reinterpret_cast<const float4*>(P.ln_s + n0) + 2 * u + 1);
+                            const float4 b1 = __ldg(reinterpret_cast<const float4*>(P.bias + n0) + 2 * u);
+                            const float4 b2 = __ldg(reinterpret_cast<const float4*>(P.bias + n0) + 2 * u + 1);
+                            v[0] = fmaf(rstd, v[0], fmaf(nmr, s1.x, b1.x)); v[1] = fmaf(rstd, v[1], fmaf(nmr, s1.y, b1.y));
+                            v[2] = fmaf(rstd, v[2], fmaf(nmr, s1.z, b1.z)); v[3] = fmaf(rstd, v[3], fmaf(nmr, s1.w, b1.w));
+                            v[4] = fmaf(rstd, v[4], fmaf(nmr, s2.x, b2.x)); v[5] = fmaf(rstd, v[5], fmaf(nmr, s2.y, b2.y));
+                            v[6] = fmaf(rstd, v[6], fmaf(nmr, s2.z, b2.z)); v[7] = fmaf(rstd, v[7], fmaf(nmr, s2.w, b2.w));
+                        } else if (P.bias) {
                             const float4 b1 = __ldg(reinterpret_cast<const float4*>(P.bias + n0) + 2 * u);
                             const float4 b2 = __ldg(reinterpret_cast<const float4*>(P.bias + n0) + 2 * u + 1);
                             v[0] += b1.x; v[1] += b1.y; v[2] += b1.z; v[3] += b1.w;
@@ -481,7 +533,18 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
                             v[0] += f0.x; v[1] += f0.y; v[2] += f1.x; v[3] += f1.y;
                             v[4] += f2.x; v[5] += f2.y; v[6] += f3.x; v[7] += f3.y;
                         }
-                        dst[u] = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+                        const uint4 pk = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+                        dst[u] = pk;
+                        if (P.rs_out) {
+                            // statistics of the values before their 16-bit rounding: over a row of C >= 64 values the rounding
+                            // moves the mean by 2^-12 rms / sqrt(C), far below the rounding of the stored values themselves
+                            rs_sum += ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
+                            float q0 = v[0] * v[0], q1 = v[1] * v[1];
+                            q0 = fmaf(v[2], v[2], q0); q1 = fmaf(v[3], v[3], q1);
+                            q0 = fmaf(v[4], v[4], q0); q1 = fmaf(v[5], v[5], q1);
+                            q0 = fmaf(v[6], v[6], q0); q1 = fmaf(v[7], v[7], q1);
+                            rs_sq += q0 + q1;
+                        }
                     }
                     fence_proxy_async_smem();
                     __syncwarp();
@@ -493,6 +556,7 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
                     ++nst;
                     if constexpr (RES16) ++n_waited;
                 }
+                if (P.rs_out) P.rs_out[(size_t)(row0 + lane) * P.rs_slots + 2 * nt + half] = make_float2(rs_sum, rs_sq);
             }
             if (fix) sk_release<Cfg::EPI_WARPS>(P, sk.g_lo, tile0, lane);
             tc_fence_before();
@@ -1204,6 +1268,11 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
                     d.ldo % 8 == 0 && (((uintptr_t)d.out | (uintptr_t)d.bias) & 15) == 0;
     const bool bt = tepi_on && d.epi == EPI_BF16 && d.mode == GEMM_LINEAR && d.M % 32 == 0 && d.N % 32 == 0 && d.ldo % 8 == 0 &&
                     (((uintptr_t)d.out | (uintptr_t)d.bias | (uintptr_t)d.residual16) & 15) == 0;
+    // LayerNorm fold: only the thread = row epilogues implement it; the caller reads rs_ok / ln_ok
+    L.rs_ok = d.rowstat_out && bt;
+    L.ln_ok = d.ln_s && d.ln_rowstat && d.ln_slots > 0 && d.ln_slots <= 10 && d.ln_slots % 2 == 0 && d.ln_C > 0 && (bt || gt) && d.bias;
+    if (L.rs_ok) { p.rs_out = d.rowstat_out; p.rs_slots = 2 * p.num_n_tiles; }
+    if (L.ln_ok) { p.ln_s = d.ln_s; p.ln_rs = d.ln_rowstat; p.ln_slots = d.ln_slots; p.ln_inv_c = 1.0f / (float)d.ln_C; p.ln_eps = d.ln_eps; }
     if (bt) {
         p.tepi = 1;
         rc = make_tmap_bf16_chunk(&p.tmOut, d.out, d.M, d.N, d.ldo);

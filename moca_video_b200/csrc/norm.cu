@@ -526,12 +526,14 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const void* __restrict__
     }
     const float4* g4 = reinterpret_cast<const float4*>(gamma);
     const float4* b4 = reinterpret_cast<const float4*>(beta);
+    // gamma == nullptr: plain normalisation (x - mean) * rstd (the affine part is folded into the consuming GEMM's weight)
+    const float4 one4 = make_float4(1.f, 1.f, 1.f, 1.f), zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
     float4 g[R > 1 ? SLOTS : 1], b[R > 1 ? SLOTS : 1];     // shared by the R rows; a single-row warp reads them at the point of use
     if constexpr (R > 1) {
 #pragma unroll
         for (int u = 0; u < SLOTS; ++u) {
             const int i = lane + 32 * u;
-            if (i < nvec) { g[u] = __ldg(g4 + i); b[u] = __ldg(b4 + i); }
+            if (i < nvec) { g[u] = gamma ? __ldg(g4 + i) : one4; b[u] = gamma ? __ldg(b4 + i) : zero4; }
         }
     }
     const float inv_c = 1.0f / (float)C;
@@ -559,7 +561,7 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const void* __restrict__
             const int i = lane + 32 * u;
             if (i < nvec) {
                 float4 gu, bu;
-                if constexpr (R > 1) { gu = g[u]; bu = b[u]; } else { gu = __ldg(g4 + i); bu = __ldg(b4 + i); }
+                if constexpr (R > 1) { gu = g[u]; bu = b[u]; } else { gu = gamma ? __ldg(g4 + i) : one4; bu = gamma ? __ldg(b4 + i) : zero4; }
                 op2_t lo = floats2op2((v[r][u].x - mean) * rstd * gu.x + bu.x, (v[r][u].y - mean) * rstd * gu.y + bu.y);
                 op2_t hi = floats2op2((v[r][u].z - mean) * rstd * gu.z + bu.z, (v[r][u].w - mean) * rstd * gu.w + bu.w);
                 orow[i] = make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
