@@ -79,6 +79,16 @@ __device__ __forceinline__ bool map_row(const GemmParams& P, int row, int& out_r
         out_row = row;
         return true;
     }
+    if (P.mode == GEMM_SPATIAL_4D) {
+        // row = (tile, frame in tile, image row in tile, column); tile = (frame group, row group)
+        const int mt = row >> 7, r = row & 127;
+        const int fg = mt / P.c4_th, th = mt - fg * P.c4_th;
+        const int per_f = P.c4_bh * P.g_W;
+        const int fl = r / per_f, rr = r - fl * per_f;
+        const int hl = rr / P.g_W, w = rr - hl * P.g_W;
+        out_row = ((fg * P.c4_bf + fl) * P.g_H + th * P.c4_bh + hl) * P.g_W + w;
+        return true;
+    }
     const int f = row / P.g_rows;
     const int r = row - f * P.g_rows;
     const int a = r / P.g_w;
@@ -292,11 +302,19 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
             auto produce = [&](int tile, int k0, int k1) {
                 const int mt = MT(tile), nt = tile % P.num_n_tiles;
                 int tap = k0 / P.kblocks, kb = k0 - tap * P.kblocks;
+                // GEMM_SPATIAL_4D: first frame / first input image row of the tile
+                const int c4_fg = P.mode == GEMM_SPATIAL_4D ? mt / P.c4_th : 0;
+                const int c4_f0 = c4_fg * P.c4_bf, c4_h0 = (mt - c4_fg * P.c4_th) * P.c4_bh * P.stride;
                 for (int it = k0; it < k1; ++it) {
                     const int arow = mt * kBM + P.tap_shift[tap];
                     mbar_wait(&empty[stage], phase ^ 1);
                     uint8_t* sa = base + (size_t)stage * Cfg::STAGE_BYTES;
-                    if constexpr (NCTA == 2) {
+                    if (NCTA == 1 && P.mode == GEMM_SPATIAL_4D) {
+                        const int dy = tap / 3, dx = tap - dy * 3;
+                        mbar_expect_tx(&full[stage], Cfg::STAGE_BYTES);
+                        tma_load_4d(sa, &P.tmA, &full[stage], kb * kBK, dx - 1, c4_h0 + dy - 1, c4_f0);
+                        tma_load_2d(sa + kABytes, &P.tmB, &full[stage], tap * P.Kp + kb * kBK, nt * BN);
+                    } else if constexpr (NCTA == 2) {
                         // both CTAs load their A rows and their half of the B rows; all bytes are counted on the leader's barrier
                         if (cta_rank == 0) mbar_expect_tx(&full[stage], 2 * Cfg::STAGE_BYTES);
                         tma_load_2d_pair(sa, &P.tmA, &full[stage], kb * kBK, arow);
@@ -1073,6 +1091,44 @@ int make_tmap_bf16(CUtensorMap* tm, const void* ptr, int64_t rows, int64_t cols,
     return MOCA_OK;
 }
 
+// GEMM_SPATIAL_4D geometry
+static bool conv4d_geometry(int NF, int H, int W, int stride, int* bh, int* bf) {
+    if (stride != 1 && stride != 2) return false;
+    if (H % stride || W % stride) return false;
+    const int Ho = H / stride, Wo = W / stride;
+    if (Wo < 1 || Wo > 128 || (Wo & (Wo - 1)) != 0) return false;
+    int best = 0;
+    for (int h = 1; h <= Ho && Wo * h <= 128; ++h)
+        if (Ho % h == 0 && 128 % (Wo * h) == 0) best = h;
+    if (!best) return false;
+    const int f = 128 / (Wo * best);
+    if (NF % f) return false;
+    *bh = best; *bf = f;
+    return true;
+}
+bool conv4d_supported(int NF, int H, int W, int stride) {
+    static const int on = [] { const char* e = getenv("MOCA_CONV4D"); return e ? atoi(e) : 1; }();
+    int bh, bf;
+    return on && conv4d_geometry(NF, H, W, stride, &bh, &bf);
+}
+
+// op_t tokens [NF, H, W, C] -> 4-D map (C, W, H, NF), box 64 channels x (Wo x bh x bf) pixels with element stride `stride` in w, h
+static int make_tmap_conv4d(CUtensorMap* tm, const void* ptr, int NF, int H, int W, int C, int pitch, int stride, int bh, int bf) {
+    EncodeTiledFn enc = get_encode();
+    MOCA_REQUIRE(enc != nullptr, MOCA_E_CUDA, "cuTensorMapEncodeTiled entry point not available");
+    MOCA_REQUIRE(((uintptr_t)ptr & 15) == 0 && (pitch * 2) % 16 == 0, MOCA_E_ALIGN, "TMA conv tensor %p pitch %d not 16-byte aligned", ptr, pitch);
+    const int Wo = W / stride;
+    cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)NF};
+    cuuint64_t strides[3] = {(cuuint64_t)pitch * 2, (cuuint64_t)W * pitch * 2, (cuuint64_t)H * W * pitch * 2};
+    cuuint32_t box[4] = {64, (cuuint32_t)(Wo * stride), (cuuint32_t)(bh * stride), (cuuint32_t)bf};
+    cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
+    CUresult r = enc(tm, MOCA_TMAP_OP16, 4, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    MOCA_REQUIRE(r == CUDA_SUCCESS, MOCA_E_CUDA, "cuTensorMapEncodeTiled (conv 4-D, NF %d H %d W %d C %d stride %d box %dx%dx%d) failed with CUresult %d",
+                 NF, H, W, C, stride, Wo, bh, bf, (int)r);
+    return MOCA_OK;
+}
+
 // fp32 row-major [rows, cols] (pitch elements) -> box of 32 columns (128 bytes) x 32 rows, 128-byte swizzle: the per-warp
 // epilogue chunk of the TMA-store epilogue (residual load and output store)
 int make_tmap_f32_chunk(CUtensorMap* tm, const void* ptr, int64_t rows, int64_t cols, int64_t pitch) {
@@ -1223,12 +1279,23 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
     GemmLaunch L;
     memset(&L.p, 0, sizeof(L.p));
     L.BN = pick_bn(d, ctx.num_sms);
-    int rc = make_tmap_bf16(&L.p.tmA, d.A, d.a_rows, d.a_cols, d.a_pitch, kBM);
+    int rc = MOCA_OK;
+    int c4_bh = 0, c4_bf = 0;
+    if (d.mode == GEMM_SPATIAL_4D) {
+        // d.g_H / d.g_W: INPUT image size, d.a_rows = NF * H * W, d.M = NF * Ho * Wo
+        const int NF = (int)(d.a_rows / ((int64_t)d.g_H * d.g_W));
+        MOCA_REQUIRE(d.ntaps == 9 && conv4d_geometry(NF, d.g_H, d.g_W, d.stride, &c4_bh, &c4_bf) && d.M % kBM == 0, MOCA_E_SHAPE,
+                     "gemm_plan: unsupported 4-D conv geometry NF=%d H=%d W=%d stride=%d", NF, d.g_H, d.g_W, d.stride);
+        rc = make_tmap_conv4d(&L.p.tmA, d.A, NF, d.g_H, d.g_W, d.a_cols, d.a_pitch, d.stride, c4_bh, c4_bf);
+    } else {
+        rc = make_tmap_bf16(&L.p.tmA, d.A, d.a_rows, d.a_cols, d.a_pitch, kBM);
+    }
     if (rc) return rc;
     // CTA-pair shape (MOCA_GEMM_2CTA=1): staged fp32 epilogue, 160- / 256-wide tiles, long main loops
     static const int pair_on = [] { const char* e = getenv("MOCA_GEMM_2CTA"); return e ? atoi(e) : 0; }();
     static const int pair_mink = [] { const char* e = getenv("MOCA_GEMM_2CTA_MINK"); return e ? atoi(e) : 16; }();
-    const int ncta = (pair_on && d.epi == EPI_F32 && L.BN != 128 && d.ntaps * (d.Kp / 64) >= pair_mink && ctx.num_sms >= 2) ? 2 : 1;
+    const int ncta = (pair_on && d.epi == EPI_F32 && L.BN != 128 && d.ntaps * (d.Kp / 64) >= pair_mink && ctx.num_sms >= 2 &&
+                      d.mode != GEMM_SPATIAL_4D) ? 2 : 1;
     rc = make_tmap_bf16(&L.p.tmB, d.Wt, d.N, (int64_t)d.ntaps * d.Kp, (int64_t)d.ntaps * d.Kp, L.BN / ncta);
     if (rc) return rc;
     L.p.ncta = ncta;
@@ -1236,6 +1303,10 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
     p.M = d.M; p.N = d.N; p.ntaps = d.ntaps; p.Kp = d.Kp; p.kblocks = d.Kp / 64;
     for (int i = 0; i < 9; ++i) p.tap_shift[i] = d.tap_shift[i];
     p.mode = d.mode; p.g_rows = d.g_rows; p.g_w = d.g_w; p.g_H = d.g_H; p.g_W = d.g_W; p.stride = d.stride;
+    if (d.mode == GEMM_SPATIAL_4D) {
+        p.g_H = d.g_H / d.stride; p.g_W = d.g_W / d.stride;            // output image size from here on
+        p.c4_bh = c4_bh; p.c4_bf = c4_bf; p.c4_th = p.g_H / c4_bh;
+    }
     p.outf = (float*)d.out; p.outb = (op_t*)d.out; p.ldo = d.ldo;
     p.bias = d.bias; p.rowbias = d.rowbias; p.rb_ld = d.rb_ld; p.rows_per_frame = d.rows_per_frame > 0 ? d.rows_per_frame : 1;
     p.residual = d.residual; p.res16 = d.residual16; p.epi = d.epi; p.out16 = d.out16;

@@ -21,7 +21,10 @@
 
 namespace moca {
 
-enum GemmMode { GEMM_LINEAR = 0, GEMM_SPATIAL_PAD = 1, GEMM_TIME_PAD = 2 };
+// GEMM_SPATIAL_4D: 3x3 conv on the UNPADDED token matrix [NF, H, W, C] through a 4-D tensor map (C, W, H, frame): an M tile is
+// bf frames x bh image rows x Wo columns = 128 output pixels, tap (dy, dx) is the same box moved by (dx - 1, dy - 1) with the
+// halo zero-filled by TMA, stride 2 is the tensor map's element stride — no border rows are computed, no 3/4 of the rows dropped.
+enum GemmMode { GEMM_LINEAR = 0, GEMM_SPATIAL_PAD = 1, GEMM_TIME_PAD = 2, GEMM_SPATIAL_4D = 3 };
 enum GemmEpi { EPI_F32 = 0, EPI_BF16 = 1, EPI_GEGLU = 2 };
 
 struct GemmParams {
@@ -37,6 +40,7 @@ struct GemmParams {
     int g_w;                  // SPATIAL: W+2           TIME: HW
     int g_H, g_W;             // SPATIAL: H, W          TIME: g_H = T
     int stride;               // SPATIAL: 1 or 2 (Downsample)
+    int c4_bh, c4_bf, c4_th;  // SPATIAL_4D: output image rows / frames per M tile, M tiles per frame group (Ho / bh); g_H, g_W = Ho, Wo
     float* outf;
     op_t* outb;
     int ldo;                  // output row pitch (elements)
@@ -112,6 +116,8 @@ struct GemmLaunch {
 
 // 2-D bf16 tensor map, box = 64 columns x box_rows rows, SWIZZLE_128B, out-of-bounds rows/columns read as zero
 int make_tmap_bf16(CUtensorMap* tm, const void* ptr, int64_t rows, int64_t cols, int64_t pitch, int box_rows);
+// GEMM_SPATIAL_4D geometry: W / stride a power of two <= 128, an image-row count bh | Ho with Wo * bh | 128, NF % (128 / (Wo bh)) == 0
+bool conv4d_supported(int NF, int H, int W, int stride);
 int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out);
 int gemm_run(const GemmLaunch& l, cudaStream_t st);
 

@@ -264,6 +264,11 @@ __device__ __forceinline__ int apply_src_row(const ApplyP& P, int drow) {
         const int tp = P.d_inner.div(r), hw = r - tp * P.HW;
         return (tp < 1 || tp > P.T) ? -1 : (b * P.T + (tp - 1)) * P.HW + hw;
     }
+    if (P.mode == DST_UP2) {
+        const int f = P.d_outer.div(drow), r = drow - f * P.d_outer.d;
+        const int h2 = P.d_inner.div(r), w2 = r - h2 * P.d_inner.d;
+        return (f * P.H + (h2 >> 1)) * P.W + (w2 >> 1);
+    }
     const int up = P.mode == DST_SPATIAL_PAD_UP2 ? 1 : 0;
     const int Hd = P.H << up, Wd = P.W << up, Wp = Wd + 2;
     const int f = P.d_outer.div(drow), r = drow - f * P.d_outer.d;
@@ -457,6 +462,9 @@ int gn_apply(const ApplyArgs& a, cudaStream_t st) {
         case DST_SPATIAL_PAD_UP2:
             MOCA_REQUIRE((int64_t)a.NF * a.H * a.W == a.rows, MOCA_E_SHAPE, "gn_apply: spatial geometry does not match rows");
             dst_rows = (int64_t)a.NF * (2 * a.H + 2) * (2 * a.W + 2); break;
+        case DST_UP2:
+            MOCA_REQUIRE((int64_t)a.NF * a.H * a.W == a.rows, MOCA_E_SHAPE, "gn_apply: spatial geometry does not match rows");
+            dst_rows = (int64_t)a.NF * 4 * a.H * a.W; break;
         case DST_TIME_PAD:
             MOCA_REQUIRE((int64_t)a.B * a.T * a.HW == a.rows, MOCA_E_SHAPE, "gn_apply: time geometry does not match rows");
             dst_rows = (int64_t)a.B * (a.T + 2) * a.HW; break;
@@ -466,6 +474,7 @@ int gn_apply(const ApplyArgs& a, cudaStream_t st) {
     P.dst_rows = (int)dst_rows;
     P.d_stat = FastDiv(a.rows_per_stat);
     if (a.dst_mode == DST_TIME_PAD) { P.d_outer = FastDiv(a.HW * (a.T + 2)); P.d_inner = FastDiv(a.HW); }
+    else if (a.dst_mode == DST_UP2) { P.d_outer = FastDiv(4 * a.H * a.W); P.d_inner = FastDiv(2 * a.W); }
     else if (a.dst_mode != DST_LINEAR) {
         const int up = a.dst_mode == DST_SPATIAL_PAD_UP2 ? 1 : 0;
         P.d_outer = FastDiv(((a.H << up) + 2) * ((a.W << up) + 2)); P.d_inner = FastDiv((a.W << up) + 2);
@@ -652,6 +661,29 @@ __global__ void ncthw_to_pad_kernel(const float* __restrict__ x, int B, int C, i
         }
         dst[i] = float2op(v);
     }
+}
+
+__global__ void ncthw_to_tokens_kernel(const float* __restrict__ x, int B, int C, int T, int H, int W, int Cp, op_t* __restrict__ dst) {
+    pdl_wait();
+    pdl_launch_dependents();
+    const int64_t total = (int64_t)B * T * H * W * Cp;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int c = (int)(i % Cp);
+        const int w = (int)((i / Cp) % W);
+        const int h = (int)((i / ((int64_t)Cp * W)) % H);
+        const int f = (int)(i / ((int64_t)Cp * W * H));
+        float v = 0.f;
+        if (c < C) v = x[((((int64_t)(f / T) * C + c) * T + (f % T)) * H + h) * W + w];
+        dst[i] = float2op(v);
+    }
+}
+
+int ncthw_to_tokens(const float* x, int B, int C, int T, int H, int W, int Cp, op_t* dst, cudaStream_t st) {
+    const int64_t total = (int64_t)B * T * H * W * Cp;
+    const int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+    launch_pdl(ncthw_to_tokens_kernel, dim3(blocks), dim3(256), 0, st, x, B, C, T, H, W, Cp, dst);
+    MOCA_LAUNCH_CHECK();
+    return MOCA_OK;
 }
 
 int ncthw_to_pad(const float* x, int B, int C, int T, int H, int W, int Cp, op_t* dst, cudaStream_t st) {

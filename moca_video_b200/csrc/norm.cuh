@@ -5,7 +5,7 @@
 
 namespace moca {
 
-enum ApplyDst { DST_LINEAR = 0, DST_SPATIAL_PAD = 1, DST_SPATIAL_PAD_UP2 = 2, DST_TIME_PAD = 3 };
+enum ApplyDst { DST_LINEAR = 0, DST_SPATIAL_PAD = 1, DST_SPATIAL_PAD_UP2 = 2, DST_TIME_PAD = 3, DST_UP2 = 4 /* nearest x2, no border */ };
 
 // fp32 [N, K, taps] (taps innermost, the torch conv weight layout [O, I, kh, kw] / [O, I, kt, 1, 1]; taps = 1 for Linear)
 // -> bf16 dst[(row0 + perm(n)), tap*Kp + k], zero for k >= K.  geglu_bn > 0 permutes rows so that each geglu_bn-row
@@ -69,6 +69,8 @@ int f32_to_bf16(const float* a, int64_t n, op_t* out, cudaStream_t st);
 
 // x [B, C, T, H, W] fp32 (reference layout) -> zero-bordered bf16 [B*T, H+2, W+2, Cp] (channels >= C zero)
 int ncthw_to_pad(const float* x, int B, int C, int T, int H, int W, int Cp, op_t* dst, cudaStream_t st);
+// same without the border: tokens [B*T, H, W, Cp] (the 4-D tensor-map convolution reads its halo as TMA zero fill)
+int ncthw_to_tokens(const float* x, int B, int C, int T, int H, int W, int Cp, op_t* dst, cudaStream_t st);
 // tokens fp32 [B*T*H*W, ld] (first C columns) -> [B, C, T, H, W] fp32
 int tokens_to_ncthw(const float* tok, int ld, int B, int C, int T, int H, int W, float* y, cudaStream_t st);
 // NHWC fp32 <-> padded bf16 helpers for the conv unit test

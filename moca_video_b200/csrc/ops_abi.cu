@@ -75,13 +75,25 @@ extern "C" int32_t moca_conv3x3_f32(moca_ctx* ctx, const float* x_nhwc, const fl
     op_t* pad = dmalloc<op_t>((size_t)NF * Hp * Wp * Cin);
     MOCA_REQUIRE(wp && pad, MOCA_E_CUDA, "moca_conv3x3_f32: allocation failed");
     int rc = pack_weight(w_oihw, Cout, Cin, 9, Kp, wp, (int64_t)9 * Kp, 0, 0, st);
-    if (!rc) rc = nhwc_to_pad(x_nhwc, NF, H, W, Cin, pad, st);
     GemmDesc d;
-    d.A = pad; d.a_rows = (int64_t)NF * Hp * Wp; d.a_cols = Cin; d.a_pitch = Cin; d.Wt = wp; d.N = Cout; d.ntaps = 9; d.Kp = Kp;
-    for (int ky = 0; ky < 3; ++ky)
-        for (int kx = 0; kx < 3; ++kx) d.tap_shift[ky * 3 + kx] = (ky - 1) * Wp + (kx - 1);
-    d.mode = GEMM_SPATIAL_PAD; d.g_rows = Hp * Wp; d.g_w = Wp; d.g_H = H; d.g_W = W; d.stride = stride;
-    d.M = (int)d.a_rows; d.epi = EPI_F32; d.out = y_nhwc; d.ldo = Cout; d.bias = bias; d.rows_per_frame = (H / stride) * (W / stride);
+    d.a_cols = Cin; d.a_pitch = Cin; d.Wt = wp; d.N = Cout; d.ntaps = 9; d.Kp = Kp;
+    d.g_H = H; d.g_W = W; d.stride = stride;
+    d.A = pad;
+    if (conv4d_supported(NF, H, W, stride)) {
+        // unpadded tokens through the 4-D tensor map (the path the UNet plan takes for its own geometries)
+        ApplyArgs a;
+        a.x1 = x_nhwc; a.C1 = Cin; a.rows = (int64_t)NF * H * W; a.rows_per_stat = 0; a.dst_mode = DST_LINEAR; a.NF = NF; a.H = H; a.W = W; a.dst = pad;
+        if (!rc) rc = gn_apply(a, st);
+        d.a_rows = (int64_t)NF * H * W; d.mode = GEMM_SPATIAL_4D; d.M = NF * (H / stride) * (W / stride);
+    } else {
+        if (!rc) rc = nhwc_to_pad(x_nhwc, NF, H, W, Cin, pad, st);
+        d.a_rows = (int64_t)NF * Hp * Wp;
+        for (int ky = 0; ky < 3; ++ky)
+            for (int kx = 0; kx < 3; ++kx) d.tap_shift[ky * 3 + kx] = (ky - 1) * Wp + (kx - 1);
+        d.mode = GEMM_SPATIAL_PAD; d.g_rows = Hp * Wp; d.g_w = Wp;
+        d.M = (int)d.a_rows;
+    }
+    d.epi = EPI_F32; d.out = y_nhwc; d.ldo = Cout; d.bias = bias; d.rows_per_frame = (H / stride) * (W / stride);
     GemmLaunch L;
     if (!rc) rc = gemm_plan(ctx->c, d, &L);
     if (!rc) rc = gemm_run(L, st);

@@ -147,20 +147,34 @@ struct Builder {
         }
         return gemm(d, 2.0 * rows * d.N * K);
     }
-    void conv3x3(const op_t* pad, int H, int W, int Cin, const PackedW& w, int stride, void* out, const float* rowbias,
+    // 3x3 conv of the 16-bit operand `src`: unpadded tokens [NF, H, W, Cin] through the 4-D tensor map when the geometry allows
+    // (conv_dst / conv4d tell the producer of src which layout to write), else the zero-bordered [NF, H+2, W+2, Cin] buffer
+    bool conv4d(int H, int W, int stride) const { return conv4d_supported(NF, H, W, stride); }
+    int conv_dst(int H, int W, int stride) const { return conv4d(H, W, stride) ? DST_LINEAR : DST_SPATIAL_PAD; }
+    void conv3x3(const op_t* src, int H, int W, int Cin, const PackedW& w, int stride, void* out, const float* rowbias,
                  int rb_ld, const float* residual, const StatSrc* ss, int out16 = 0) {
         GemmDesc d;
-        const int Hp = H + 2, Wp = W + 2;
-        d.A = pad; d.a_rows = (int64_t)NF * Hp * Wp; d.a_cols = Cin; d.a_pitch = Cin;
+        const int Ho = H / stride, Wo = W / stride;
+        d.a_cols = Cin; d.a_pitch = Cin;
         d.Wt = w.w; d.N = w.N; d.ntaps = 9; d.Kp = w.Kp;
-        for (int ky = 0; ky < 3; ++ky)
-            for (int kx = 0; kx < 3; ++kx) d.tap_shift[ky * 3 + kx] = (ky - 1) * Wp + (kx - 1);
-        d.mode = GEMM_SPATIAL_PAD; d.g_rows = Hp * Wp; d.g_w = Wp; d.g_H = H; d.g_W = W; d.stride = stride;
-        d.M = (int)d.a_rows; d.epi = EPI_F32; d.out = out; d.ldo = w.N; d.bias = w.b; d.out16 = out16;
-        d.rowbias = rowbias; d.rb_ld = rb_ld; d.rows_per_frame = (H / stride) * (W / stride); d.residual = residual;
+        d.g_H = H; d.g_W = W; d.stride = stride;
+        if (conv4d(H, W, stride)) {
+            d.A = src; d.a_rows = (int64_t)NF * H * W;
+            d.mode = GEMM_SPATIAL_4D; d.M = NF * Ho * Wo;
+            d.stat_sample_rows = T * Ho * Wo;
+        } else {
+            const int Hp = H + 2, Wp = W + 2;
+            d.A = src; d.a_rows = (int64_t)NF * Hp * Wp;
+            for (int ky = 0; ky < 3; ++ky)
+                for (int kx = 0; kx < 3; ++kx) d.tap_shift[ky * 3 + kx] = (ky - 1) * Wp + (kx - 1);
+            d.mode = GEMM_SPATIAL_PAD; d.g_rows = Hp * Wp; d.g_w = Wp;
+            d.M = (int)d.a_rows;
+            d.stat_sample_rows = T * Hp * Wp;
+        }
+        d.epi = EPI_F32; d.out = out; d.ldo = w.N; d.bias = w.b; d.out16 = out16;
+        d.rowbias = rowbias; d.rb_ld = rb_ld; d.rows_per_frame = Ho * Wo; d.residual = residual;
         if (ss) { d.chan_stats = (double*)ss->cs; d.stat_rows_per_frame = ss->rows; }
-        d.stat_sample_rows = T * Hp * Wp;
-        gemm(d, 2.0 * NF * (H / stride) * (W / stride) * w.N * 9.0 * w.K);
+        gemm(d, 2.0 * NF * Ho * Wo * w.N * 9.0 * w.K);
     }
     void tconv(const op_t* padT, int HW, int C, const PackedW& w, void* out, const float* residual, const StatSrc* ss, int out16 = 0) {
         GemmDesc d;
@@ -266,11 +280,11 @@ Act Builder::res_block(const LayerW& L, const Act& x, const Act* skip, const flo
     out.C = r.cout; out.H = H; out.W = W;
     out.p = (float*)palloc((size_t)rows * r.cout * sizeof(float));
     // in_layers: GN(fp32, eps 1e-5) -> SiLU -> conv3x3 ; + emb_layers(emb)[:, :, None, None]
-    gnorm(x.p, x.st, x.C, skip ? skip->p : nullptr, skip ? skip->st : StatSrc(), C2, rows, HW, r.gn1, 1e-5f, 1, DST_SPATIAL_PAD, H, W, pad, raw);
+    gnorm(x.p, x.st, x.C, skip ? skip->p : nullptr, skip ? skip->st : StatSrc(), C2, rows, HW, r.gn1, 1e-5f, 1, conv_dst(H, W, 1), H, W, pad, raw);
     const StatSrc st_t1 = stat_alloc(r.cout, HW);
     conv3x3(pad, H, W, Cin, r.conv1, 1, t1, embout + r.emb_off, net->n_emb, nullptr, &st_t1, 1);
     // out_layers: GN -> SiLU -> (dropout) -> conv3x3 ; + skip_connection(x)
-    gnorm(t1, st_t1, r.cout, nullptr, StatSrc(), 0, rows, HW, r.gn2, 1e-5f, 1, DST_SPATIAL_PAD, H, W, pad, nullptr, 1);
+    gnorm(t1, st_t1, r.cout, nullptr, StatSrc(), 0, rows, HW, r.gn2, 1e-5f, 1, conv_dst(H, W, 1), H, W, pad, nullptr, 1);
     StatSrc st_cur = stat_alloc(r.cout, HW);
     if (r.has_skip) {
         linear(raw, rows, Cin, r.skip, EPI_F32, out.p, r.cout, nullptr);
@@ -443,7 +457,8 @@ void Builder::build() {
         op_t* pad = scratch<op_t>(S_PAD, (size_t)NF * (H0 + 2) * (W0 + 2) * 64);
         const float* x_in = plan->x_in;
         const int b = B, c = n->in_ch, t = T, h = H0, w = W0;
-        push([=](cudaStream_t st) { return ncthw_to_pad(x_in, b, c, t, h, w, 64, pad, st); });
+        const bool c4 = conv4d(H0, W0, 1);
+        push([=](cudaStream_t st) { return c4 ? ncthw_to_tokens(x_in, b, c, t, h, w, 64, pad, st) : ncthw_to_pad(x_in, b, c, t, h, w, 64, pad, st); });
         cur.p = (float*)palloc((size_t)rows0 * mc * 4);
         cur.st = stat_alloc(mc, H0 * W0);
         conv3x3(pad, H0, W0, 64, n->inp[0].layers[0].conv, 1, cur.p, nullptr, 0, nullptr, &cur.st);
@@ -461,7 +476,7 @@ void Builder::build() {
                 scope = L.name;
                 const int64_t rows = (int64_t)NF * cur.H * cur.W;
                 op_t* pad = scratch<op_t>(S_PAD, (size_t)NF * (cur.H + 2) * (cur.W + 2) * cur.C);
-                convert(cur.p, cur.C, rows, DST_SPATIAL_PAD, cur.H, cur.W, pad);
+                convert(cur.p, cur.C, rows, conv_dst(cur.H, cur.W, 2), cur.H, cur.W, pad);
                 Act o; o.C = L.cout; o.H = cur.H / 2; o.W = cur.W / 2;
                 o.p = (float*)palloc((size_t)NF * o.H * o.W * o.C * 4);
                 o.st = stat_alloc(o.C, o.H * o.W);
@@ -472,7 +487,7 @@ void Builder::build() {
                 const int64_t rows = (int64_t)NF * cur.H * cur.W;
                 const int H2 = cur.H * 2, W2 = cur.W * 2;
                 op_t* pad = scratch<op_t>(S_PAD, (size_t)NF * (H2 + 2) * (W2 + 2) * cur.C);
-                convert(cur.p, cur.C, rows, DST_SPATIAL_PAD_UP2, cur.H, cur.W, pad);
+                convert(cur.p, cur.C, rows, conv4d(H2, W2, 1) ? DST_UP2 : DST_SPATIAL_PAD_UP2, cur.H, cur.W, pad);
                 Act o; o.C = L.cout; o.H = H2; o.W = W2;
                 o.p = (float*)palloc((size_t)NF * H2 * W2 * o.C * 4);
                 o.st = stat_alloc(o.C, H2 * W2);
@@ -500,7 +515,7 @@ void Builder::build() {
     {
         const int64_t rows = rows0;
         op_t* pad = scratch<op_t>(S_PAD, (size_t)NF * (H0 + 2) * (W0 + 2) * cur.C);
-        gnorm(cur.p, cur.st, cur.C, nullptr, StatSrc(), 0, rows, H0 * W0, n->gn_out, 1e-5f, 1, DST_SPATIAL_PAD, H0, W0, pad, nullptr);
+        gnorm(cur.p, cur.st, cur.C, nullptr, StatSrc(), 0, rows, H0 * W0, n->gn_out, 1e-5f, 1, conv_dst(H0, W0, 1), H0, W0, pad, nullptr);
         conv3x3(pad, H0, W0, cur.C, n->conv_out, 1, plan->out_tok, nullptr, 0, nullptr, nullptr);
     }
 }
