@@ -400,6 +400,8 @@ def main():
         saved_stdout = os.dup(1)
         os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=dev)
+        from moca_video_b200 import ops as _ops
+        _ops.comm_init()                 # the library's own NCCL communicator: the per-iteration hand-off is moca_queue_handoff
         r, net = run_fifo(args, dev, rank, world)
         dist.barrier()
         dist.destroy_process_group()

@@ -172,6 +172,16 @@ double moca_unet_flops(moca_unet* net);
 /* Host-only architecture listing: moca_unet_create with ctx == NULL builds the parameter table without touching a
  * device; param_count / param_info enumerate the state_dict keys the loader expects (CPU tests compare them with
  * the reference's own state_dict listing). */
+/* Per-module entry points: one ResBlock (with its TemporalConvBlock; lvdm/modules/networks/openaimodel3d.py:208-234, 269-276),
+ * SpatialTransformer (lvdm/modules/attention.py:262-278) or TemporalTransformer (:331-373) of the loaded network, named as in the
+ * reference's state_dict ("input_blocks.1.0", "middle_block.1", "init_attn.0", ...).  x, y: [B, C, T, H, W] fp32 (the reference
+ * modules' [(b t), c, h, w] / [b, c, t, h, w] inputs are views of this).  emb: [B*T, 4*model_channels] fp32, the embedding
+ * ResBlock.forward receives (ResBlock only).  context: [B, Lmax, context_dim] fp32 with ctx_len[B] valid tokens (SpatialTransformer
+ * only; the reference repeats it per frame).  The same kernels and plan fragments as moca_unet_forward. */
+int32_t moca_unet_layer_forward(moca_unet* net, const char* layer, const float* x, const float* emb, const float* context,
+                                const int32_t* ctx_len, int32_t Lmax, int32_t B, int32_t T, int32_t H, int32_t W, float* y,
+                                void* stream);
+int32_t moca_unet_layer_channels(moca_unet* net, const char* layer, int32_t* c_in, int32_t* c_out);
 int32_t moca_unet_param_count(moca_unet* net);
 int32_t moca_unet_param_info(moca_unet* net, int32_t i, char* name, int32_t name_cap, int64_t* numel);
 int64_t moca_unet_workspace_bytes(moca_unet* net);
@@ -207,8 +217,16 @@ int32_t moca_attention_op16(moca_ctx* ctx, const void* q, const void* k, const v
 
 /* ---- multi-GPU queue hand-off (replaces the mp.Queue/CUDA-IPC exchange of
  *      scripts/evaluation/funcs_mp.py:197-236) -----------------------------------------------------------------
- * The exchange itself is issued by the host shim through torch.distributed (NCCL all_gather of the updated
- * half-windows); these two kernels pack / unpack the half-windows of the windows a rank owns. */
+ * One process per GPU.  moca_comm_unique_id (rank 0) -> the 128 bytes reach every rank through any channel ->
+ * moca_comm_init(ctx, id, nranks, rank) creates the NCCL communicator of this context (libnccl.so.2 is resolved with dlopen,
+ * in a PyTorch process the copy torch loaded).  moca_queue_handoff is the per-iteration exchange of the updated half-windows:
+ * an all-gather of `count` floats per rank on the caller's stream (packed: count floats, gathered: nranks * count).
+ * moca_halfwin_pack / _unpack move the half-windows of the windows a rank owns in and out of those staging buffers. */
+int32_t moca_comm_unique_id(void* id_out_128_bytes);
+int32_t moca_comm_init(moca_ctx* ctx, const void* id_128_bytes, int32_t nranks, int32_t rank);
+int32_t moca_queue_handoff(moca_ctx* ctx, const float* packed, float* gathered, int64_t count, void* stream);
+int32_t moca_comm_destroy(moca_ctx* ctx);
+int32_t moca_comm_size(moca_ctx* ctx);          /* 0: no communicator */
 int32_t moca_halfwin_pack(moca_ctx* ctx, const float* xprev, int32_t Fwin, int32_t half, int32_t B, int32_t C, int32_t H,
                           int32_t W, float* packed, void* stream);
 int32_t moca_halfwin_unpack(moca_ctx* ctx, const float* packed, int32_t n_windows, const int32_t* window_start,

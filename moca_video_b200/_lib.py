@@ -37,6 +37,8 @@ SIGNATURES = {
     "moca_unet_load_many": (i32, [vp, i32, C.POINTER(cp), C.POINTER(vp), pi64, vp]),
     "moca_unet_finalize": (i32, [vp]),
     "moca_unet_forward": (i32, [vp, vp, vp, vp, vp, i32, vp, i32, i32, i32, i32, vp, vp]),
+    "moca_unet_layer_forward": (i32, [vp, cp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp]),
+    "moca_unet_layer_channels": (i32, [vp, cp, pi32, pi32]),
     "moca_unet_set_taps": (i32, [vp, i32]),
     "moca_unet_num_taps": (i32, [vp]),
     "moca_unet_tap_info": (i32, [vp, i32, cp, i32, pi64, pi64]),
@@ -55,6 +57,11 @@ SIGNATURES = {
     "moca_groupnorm_op16": (i32, [vp, vp, vp, vp, i64, i32, i32, f32, i32, vp, vp]),
     "moca_layernorm_op16": (i32, [vp, vp, vp, vp, i64, i32, vp, vp]),
     "moca_attention_op16": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, i32, i32, vp]),
+    "moca_comm_unique_id": (i32, [vp]),
+    "moca_comm_init": (i32, [vp, vp, i32, i32]),
+    "moca_queue_handoff": (i32, [vp, vp, vp, i64, vp]),
+    "moca_comm_destroy": (i32, [vp]),
+    "moca_comm_size": (i32, [vp]),
     "moca_halfwin_pack": (i32, [vp, vp, i32, i32, i32, i32, i32, i32, vp, vp]),
     "moca_halfwin_unpack": (i32, [vp, vp, i32, vp, i32, i32, i32, i32, i32, i32, vp, vp]),
 }

@@ -21,7 +21,7 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler",
 EXTRA = {"step_kernels.cu": ["-fmad=false"]}
 if os.environ.get("MOCA_DEBUG_HANG") == "1":
     COMMON = COMMON + ["-DMOCA_DEBUG_HANG"]
-SOURCES = ["abi.cu", "step_kernels.cu", "freeinit.cu", "gemm_tc.cu", "norm.cu", "attn.cu", "attn_tc.cu", "unet.cu", "unet_plan.cu", "ops_abi.cu"]
+SOURCES = ["abi.cu", "step_kernels.cu", "freeinit.cu", "gemm_tc.cu", "norm.cu", "attn.cu", "attn_tc.cu", "unet.cu", "unet_plan.cu", "ops_abi.cu", "comm.cu"]
 
 
 def _nvcc():
@@ -73,7 +73,7 @@ def build(force=False, verbose=False):
         with ThreadPoolExecutor(max_workers=min(8, len(jobs))) as ex:
             list(ex.map(run, jobs))
     if jobs or not os.path.exists(LIB):
-        cmd = [nvcc] + ARCH + ["-shared", "-o", LIB] + objs
+        cmd = [nvcc] + ARCH + ["-shared", "-o", LIB] + objs + ["-ldl"]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")

@@ -58,8 +58,11 @@ extern "C" int32_t moca_ctx_create(int32_t device, moca_ctx** out) {
     return MOCA_OK;
 }
 
+extern "C" int32_t moca_comm_destroy(moca_ctx* ctx);
+
 extern "C" int32_t moca_ctx_destroy(moca_ctx* ctx) {
     if (!ctx) return MOCA_OK;
+    moca_comm_destroy(ctx);
     cudaFree(ctx->c.d_mask_sums);
     cudaFree(ctx->c.d_sk_ws);
     cudaFree(ctx->c.d_sk_flags);

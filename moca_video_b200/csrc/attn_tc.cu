@@ -531,12 +531,9 @@ int attention_tc_plan(const AttnArgs& a, AttnTcLaunch* out) {
     static const int forced = [] { const char* e = getenv("MOCA_ATTN_TC"); return e ? atoi(e) : 0; }();      // 1 / 2 pins the kernel shape
     L.version = forced == 1 || forced == 2 ? forced : (a.Lq >= 256 && a.Lk >= 256 ? 2 : 1);
     L.grid = dim3(cdiv(a.Lq, L.version == 2 ? 2 * kTileQ : kTileQ), a.n_outer * a.heads);
-    static bool attr_done = false;
-    if (!attr_done) {
-        MOCA_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
-        MOCA_CHECK_CUDA(cudaFuncSetAttribute(attn_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem2));
-        attr_done = true;
-    }
+    // per-device attribute, set at plan time (once per plan, not per launch)
+    MOCA_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
+    MOCA_CHECK_CUDA(cudaFuncSetAttribute(attn_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem2));
     memcpy(out->storage, &L, sizeof(L));
     return MOCA_OK;
 }

@@ -203,12 +203,10 @@ extern "C" int32_t moca_freeinit_mix(moca_ctx* ctx, const float* x, const float*
     const size_t smemC = (size_t)H * W * 2 * sizeof(float2) + (size_t)(H + W) * sizeof(float2);
     MOCA_REQUIRE(smemC <= 200 * 1024, MOCA_E_SHAPE, "moca_freeinit_mix: slice %dx%d does not fit shared memory", H, W);
     cudaStream_t st = (cudaStream_t)stream;
-    static bool attr_set = false;
-    if (!attr_set) {
-        MOCA_CHECK_CUDA(cudaFuncSetAttribute(freeinit_fwd_hw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        MOCA_CHECK_CUDA(cudaFuncSetAttribute(freeinit_inv_hw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr_set = true;
-    }
+    // the attribute is per device and the call is cheap: set it on every launch (a process-wide "done" flag would leave the
+    // second device of a process without the opt-in)
+    MOCA_CHECK_CUDA(cudaFuncSetAttribute(freeinit_fwd_hw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    MOCA_CHECK_CUDA(cudaFuncSetAttribute(freeinit_inv_hw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     float2* Z = (float2*)work;
     freeinit_fwd_hw_kernel<<<NV * T, 256, smemA, st>>>(x, noise, Z, H, W);
     MOCA_LAUNCH_CHECK();

@@ -1186,9 +1186,13 @@ static int pick_bn(const GemmDesc& d, int num_sms) {
     return best;
 }
 
+// dynamic shared memory opt-in: a per-device attribute, so "done" is kept per device (16 devices per process at most)
+static int cur_device() { int d = 0; cudaGetDevice(&d); return d < 0 || d >= 16 ? 0 : d; }
+
 template <int BN, int EPI, bool STATS = false, bool TEPI = false>
 static int set_attr() {
-    static bool done = false;
+    static bool done_dev[16] = {false};
+    bool& done = done_dev[cur_device()];
     if (!done) {
         MOCA_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI, STATS, TEPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)GemmCfg<BN, TEPI, EPI, 1, TEPI && EPI == EPI_BF16 && STATS>::SMEM));
@@ -1199,7 +1203,8 @@ static int set_attr() {
 
 template <int BN, bool STATS>
 static int set_attr_pair() {
-    static bool done = false;
+    static bool done_dev[16] = {false};
+    bool& done = done_dev[cur_device()];
     if (!done) {
         MOCA_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI_F32, STATS, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)GemmCfg<BN, false, EPI_F32, 2>::SMEM));

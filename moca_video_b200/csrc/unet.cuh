@@ -106,5 +106,6 @@ struct moca_unet {
     bool taps = false;
     std::map<std::vector<int>, std::shared_ptr<moca::Plan>> plans;
     moca::Plan* last = nullptr;
+    uint64_t use_clock = 0;
     size_t weight_bytes = 0;
 };

@@ -24,6 +24,7 @@ struct Plan {
     std::vector<std::string> labels;      // one per op (profiling: moca_unet_profile)
     std::vector<double> op_flops;
     int launches = 0;
+    uint64_t last_use = 0;                // LRU stamp of the plan cache
     double flops = 0;
     std::vector<void*> allocs;
     float* x_in = nullptr;
@@ -32,6 +33,8 @@ struct Plan {
     int* d_fps = nullptr;
     int* d_ctxlen = nullptr;
     float* out_tok = nullptr;
+    float* emb_in = nullptr;              // layer plans: [NF, 4 mc] time (+ fps) embedding input of a ResBlock
+    int out_C = 0;                        // layer plans: channels of out_tok
     double* stats = nullptr;
     size_t stats_bytes = 0;
     float2* ab_table = nullptr;       // (scale, shift) per (statistics group, channel) of the GroupNorm being applied (shared)
@@ -255,13 +258,15 @@ struct Builder {
         }, "tap", 0);
     }
 
-    Act res_block(const LayerW& L, const Act& x, const Act* skip, const float* embout);
-    void transformer(const LayerW& L, Act& x, const op_t* kv);
+    // rowbias [NF, rb_ld]: this block's emb_layers output; kv [B*Lmax, kv_ld]: this block's cross-attention keys | values
+    Act res_block(const LayerW& L, const Act& x, const Act* skip, const float* rowbias, int rb_ld);
+    void transformer(const LayerW& L, Act& x, const op_t* kv, int kv_ld);
     void build();
+    void build_layer(const LayerW& L);
 };
 
 // ResBlock._forward (openaimodel3d.py:208-234) followed by its TemporalConvBlock (:269-276)
-Act Builder::res_block(const LayerW& L, const Act& x, const Act* skip, const float* embout) {
+Act Builder::res_block(const LayerW& L, const Act& x, const Act* skip, const float* rowbias, int rb_ld) {
     const ResW& r = L.res;
     scope = L.name;
     const int H = x.H, W = x.W, HW = H * W;
@@ -282,7 +287,7 @@ Act Builder::res_block(const LayerW& L, const Act& x, const Act* skip, const flo
     // in_layers: GN(fp32, eps 1e-5) -> SiLU -> conv3x3 ; + emb_layers(emb)[:, :, None, None]
     gnorm(x.p, x.st, x.C, skip ? skip->p : nullptr, skip ? skip->st : StatSrc(), C2, rows, HW, r.gn1, 1e-5f, 1, conv_dst(H, W, 1), H, W, pad, raw);
     const StatSrc st_t1 = stat_alloc(r.cout, HW);
-    conv3x3(pad, H, W, Cin, r.conv1, 1, t1, embout + r.emb_off, net->n_emb, nullptr, &st_t1, 1);
+    conv3x3(pad, H, W, Cin, r.conv1, 1, t1, rowbias, rb_ld, nullptr, &st_t1, 1);
     // out_layers: GN -> SiLU -> (dropout) -> conv3x3 ; + skip_connection(x)
     gnorm(t1, st_t1, r.cout, nullptr, StatSrc(), 0, rows, HW, r.gn2, 1e-5f, 1, conv_dst(H, W, 1), H, W, pad, nullptr, 1);
     StatSrc st_cur = stat_alloc(r.cout, HW);
@@ -310,7 +315,7 @@ Act Builder::res_block(const LayerW& L, const Act& x, const Act* skip, const flo
 
 // SpatialTransformer.forward (attention.py:262-278) / TemporalTransformer.forward (:331-373) with one
 // BasicTransformerBlock (:216-220): x += attn1(LN1 x); x += attn2(LN2 x, ctx); x += ff(LN3 x).  Runs in place on x.
-void Builder::transformer(const LayerW& L, Act& x, const op_t* kv) {
+void Builder::transformer(const LayerW& L, Act& x, const op_t* kv, int kv_ld) {
     const TfW& t = L.tf;
     scope = L.name;
     const int H = x.H, W = x.W, HW = H * W;
@@ -362,7 +367,7 @@ void Builder::transformer(const LayerW& L, Act& x, const op_t* kv) {
         ln_linear(y, prod, rs, rows, I, t.q2, EPI_BF16, qkv, I, lin);
         AttnArgs ca;
         ca.q = qkv; ca.ldq = I; ca.qmap = self.qmap;
-        ca.k = kv + t.kv_off; ca.v = kv + t.kv_off + I; ca.ldkv = net->n_kv;
+        ca.k = kv; ca.v = kv + I; ca.ldkv = kv_ld;
         ca.kvmap.div = T; ca.kvmap.mul_a = Lmax; ca.kvmap.mul_b = 0; ca.kvmap.step = 1;     // frame o uses the context of sample o / T
         ca.out = att; ca.ldo = I; ca.n_outer = NF; ca.heads = t.heads; ca.Lq = HW; ca.Lk = Lmax;
         ca.kv_len = plan->d_ctxlen; ca.kv_len_div = T; ca.scale = 0.125f;
@@ -469,9 +474,9 @@ void Builder::build() {
             const LayerW& L = blk.layers[li];
             if (L.kind == "conv_in") continue;
             if (L.kind == "res") {
-                cur = res_block(L, cur, li == 0 ? skip : nullptr, embout);
+                cur = res_block(L, cur, li == 0 ? skip : nullptr, embout + L.res.emb_off, n->n_emb);
             } else if (L.kind == "st" || L.kind == "tt") {
-                transformer(L, cur, kv);
+                transformer(L, cur, kv ? kv + L.tf.kv_off : nullptr, n->n_kv);
             } else if (L.kind == "down") {
                 scope = L.name;
                 const int64_t rows = (int64_t)NF * cur.H * cur.W;
@@ -520,14 +525,130 @@ void Builder::build() {
     }
 }
 
+
+// ---- one module of the UNet on its own (the per-module entry points of the boundary) --------------------------
+// {sum, sumsq} doubles per (frame, channel) of a token matrix that no GEMM epilogue produced (the module's input)
+__global__ void token_stats_kernel(const float* __restrict__ x, int C, int HW, double* __restrict__ cs) {
+    __shared__ double rs[8][32], rq[8][32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int f = blockIdx.y, c = blockIdx.x * 32 + lane;
+    double s = 0.0, q = 0.0;
+    if (c < C)
+        for (int r = warp; r < HW; r += 8) {
+            const double v = (double)x[((size_t)f * HW + r) * C + c];
+            s += v; q += v * v;
+        }
+    rs[warp][lane] = s; rq[warp][lane] = q;
+    __syncthreads();
+    if (warp == 0 && c < C) {
+        for (int w = 1; w < 8; ++w) { s += rs[w][lane]; q += rq[w][lane]; }
+        cs[((size_t)f * C + c) * 2] = s;
+        cs[((size_t)f * C + c) * 2 + 1] = q;
+    }
+}
+
+__global__ void ncthw_to_tokens_f32_kernel(const float* __restrict__ x, int B, int C, int T, int H, int W, float* __restrict__ tok) {
+    const int64_t total = (int64_t)B * C * T * H * W;
+    const int HW = H * W;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int c = (int)(i % C);
+        const int64_t r = i / C;                       // token row (b, t, hw)
+        const int hw = (int)(r % HW), t = (int)((r / HW) % T), b = (int)(r / ((int64_t)HW * T));
+        tok[i] = x[(((int64_t)b * C + c) * T + t) * HW + hw];
+    }
+}
+
+// ResBlock(+TemporalConvBlock) / SpatialTransformer / TemporalTransformer `L` applied to plan->x_in ([B, C, T, H, W] fp32);
+// emb_in [NF, 4 mc] is the (time + fps) embedding a ResBlock receives, ctx_in the text context of a SpatialTransformer.
+void Builder::build_layer(const LayerW& L) {
+    moca_unet* n = net;
+    const int mc = n->mc, te = 4 * mc;
+    const bool is_res = L.kind == "res", is_st = L.kind == "st";
+    const int Cin = is_res ? L.res.cin : L.tf.C;
+    const int64_t rows = (int64_t)NF * H0 * W0;
+    plan->x_in = (float*)palloc((size_t)rows * Cin * sizeof(float));
+    plan->emb_in = (float*)palloc((size_t)NF * te * sizeof(float));
+    plan->ctx_in = (float*)palloc((size_t)B * Lmax * n->ctx_dim * sizeof(float));
+    plan->d_ctxlen = (int*)palloc(16 * sizeof(int));
+    scope = L.name;
+    if (!dry) {
+        double* stats = plan->stats;
+        const size_t sb = plan->stats_bytes;
+        raw_push([=](cudaStream_t st) { return cudaMemsetAsync(stats, 0, sb, st) == cudaSuccess ? MOCA_OK : MOCA_E_CUDA; }, "memset stats", 0);
+    }
+    plan->launches += 1;
+    Act cur;
+    cur.C = Cin; cur.H = H0; cur.W = W0;
+    cur.p = (float*)palloc((size_t)rows * Cin * sizeof(float));
+    cur.st = stat_alloc(Cin, H0 * W0);
+    {
+        const float* x_in = plan->x_in;
+        float* tok = cur.p;
+        double* cs = (double*)cur.st.cs;
+        const int b = B, c = Cin, t = T, h = H0, w = W0, nf = NF;
+        push([=](cudaStream_t st) {
+            const int64_t total = (int64_t)b * c * t * h * w;
+            const int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+            ncthw_to_tokens_f32_kernel<<<blocks, 256, 0, st>>>(x_in, b, c, t, h, w, tok);
+            token_stats_kernel<<<dim3(cdiv(c, 32), nf), 256, 0, st>>>(tok, c, h * w, cs);
+            return cudaGetLastError() == cudaSuccess ? MOCA_OK : MOCA_E_CUDA;
+        }, 2, "stage input");
+    }
+    if (is_res) {
+        // emb_layers = SiLU -> Linear (openaimodel3d.py:166-172): this block's rows of the stacked projection
+        const ResW& r = L.res;
+        op_t* semb = (op_t*)palloc((size_t)NF * te * sizeof(op_t));
+        float* embout = (float*)palloc((size_t)NF * r.cout * sizeof(float));
+        const float* emb_in = plan->emb_in;
+        const int64_t ne = (int64_t)NF * te;
+        push([=](cudaStream_t st) { return silu_add_bf16(emb_in, nullptr, ne, semb, st); });
+        PackedW slice = n->emb_all;
+        slice.w = n->emb_all.w + (size_t)r.emb_off * n->emb_all.Kp; slice.b = n->emb_all.b + r.emb_off; slice.N = r.cout;
+        linear(semb, NF, te, slice, EPI_F32, embout, r.cout, nullptr);
+        cur = res_block(L, cur, nullptr, embout, r.cout);
+    } else {
+        const TfW& t = L.tf;
+        op_t* kv = nullptr;
+        if (is_st) {
+            // this block's to_k | to_v rows of the stacked context projection (attention.py:81-82)
+            const int I = t.inner;
+            const float* ctx_in = plan->ctx_in;
+            const int64_t nc = (int64_t)B * Lmax * n->ctx_dim;
+            op_t* ctx16 = (op_t*)palloc((size_t)nc * sizeof(op_t));
+            kv = (op_t*)palloc((size_t)B * Lmax * 2 * I * sizeof(op_t));
+            push([=](cudaStream_t st) { return f32_to_bf16(ctx_in, nc, ctx16, st); });
+            PackedW slice = n->kv_all;
+            slice.w = n->kv_all.w + (size_t)t.kv_off * n->kv_all.Kp; slice.b = nullptr; slice.N = 2 * I;
+            linear(ctx16, (int64_t)B * Lmax, n->ctx_dim, slice, EPI_BF16, kv, 2 * I, nullptr, 2 * I);
+        }
+        transformer(L, cur, kv, is_st ? 2 * t.inner : 0);
+    }
+    plan->out_tok = cur.p;
+    plan->out_C = cur.C;
+}
+
 }  // namespace moca
 
 using namespace moca;
 
+// bounded plan cache: a plan owns its workspace (1.5 GB at full size) and CUDA graph, so varying prompt lengths, batch sizes or
+// per-module calls must not accumulate them.  Least recently used plans go first; the one in use stays.
+static void evict_plans(moca_unet* n) {
+    static const size_t max_plans = [] { const char* e = getenv("MOCA_MAX_PLANS"); return (size_t)(e && atoi(e) > 0 ? atoi(e) : 4); }();
+    while (n->plans.size() >= max_plans) {
+        auto victim = n->plans.end();
+        for (auto it2 = n->plans.begin(); it2 != n->plans.end(); ++it2)
+            if (it2->second.get() != n->last && (victim == n->plans.end() || it2->second->last_use < victim->second->last_use)) victim = it2;
+        if (victim == n->plans.end()) break;
+        cudaDeviceSynchronize();                            // its graph / kernels may still be running
+        n->plans.erase(victim);
+    }
+}
+
 static int get_plan(moca_unet* n, int B, int T, int H, int W, int Lmax, Plan** out) {
     std::vector<int> key{B, T, H, W, Lmax, n->taps ? 1 : 0};
     auto it = n->plans.find(key);
-    if (it != n->plans.end()) { *out = it->second.get(); return MOCA_OK; }
+    if (it != n->plans.end()) { it->second->last_use = ++n->use_clock; *out = it->second.get(); return MOCA_OK; }
     int down = 1;
     for (size_t i = 1; i < n->mult.size(); ++i) down *= 2;
     MOCA_REQUIRE(H % down == 0 && W % down == 0, MOCA_E_SHAPE, "moca_unet_forward: H=%d W=%d must be multiples of %d", H, W, down);
@@ -551,6 +672,8 @@ static int get_plan(moca_unet* n, int B, int T, int H, int W, int Lmax, Plan** o
     if (real.rc) return real.rc;
     real.build();
     if (real.rc) return real.rc;
+    evict_plans(n);
+    plan->last_use = ++n->use_clock;
     n->plans[key] = plan;
     *out = plan.get();
     return MOCA_OK;
@@ -562,6 +685,7 @@ extern "C" int32_t moca_unet_forward(moca_unet* n, const float* x, const int32_t
     MOCA_REQUIRE(n && x && timesteps && context && ctx_len && fps && y, MOCA_E_ARG, "moca_unet_forward: NULL argument");
     MOCA_REQUIRE(n->finalized, MOCA_E_STATE, "moca_unet_forward: call moca_unet_finalize after loading the weights");
     MOCA_REQUIRE(B > 0 && T > 0 && H > 0 && W > 0 && Lmax > 0, MOCA_E_SHAPE, "moca_unet_forward: bad shape");
+    // fps: int32[B], one entry per sample (the Python mirror validates the length: a shorter array would be read past its end)
     MOCA_REQUIRE((Lmax * n->ctx_dim) % 8 == 0, MOCA_E_SHAPE, "moca_unet_forward: context size");
     for (int b = 0; b < B; ++b)
         MOCA_REQUIRE(ctx_len[b] >= 1 && ctx_len[b] <= Lmax, MOCA_E_ARG, "moca_unet_forward: ctx_len[%d]=%d outside 1..%d", b, ctx_len[b], Lmax);
@@ -609,6 +733,98 @@ extern "C" int32_t moca_unet_forward(moca_unet* n, const float* x, const int32_t
     }
     return tokens_to_ncthw(plan->out_tok, n->out_ch, B, n->out_ch, T, H, W, y, st);
 }
+
+// ---- per-module entry points (ResBlock.forward openaimodel3d.py:208-234 incl. its TemporalConvBlock :269-276,
+// SpatialTransformer.forward attention.py:262-278, TemporalTransformer.forward :331-373) ---------------------------------------
+static const LayerW* find_layer(moca_unet* n, const char* name) {
+    auto scan = [&](const BlockW& b) -> const LayerW* {
+        for (const LayerW& L : b.layers)
+            if (L.name == name) return &L;
+        return nullptr;
+    };
+    for (const BlockW& b : n->inp) if (const LayerW* L = scan(b)) return L;
+    if (const LayerW* L = scan(n->init_attn)) return L;
+    if (const LayerW* L = scan(n->mid)) return L;
+    for (const BlockW& b : n->outb) if (const LayerW* L = scan(b)) return L;
+    return nullptr;
+}
+
+extern "C" int32_t moca_unet_layer_forward(moca_unet* n, const char* layer, const float* x, const float* emb, const float* context,
+                                           const int32_t* ctx_len, int32_t Lmax, int32_t B, int32_t T, int32_t H, int32_t W, float* y,
+                                           void* stream) {
+    MOCA_REQUIRE(n && layer && x && y, MOCA_E_ARG, "moca_unet_layer_forward: NULL argument");
+    MOCA_REQUIRE(n->finalized, MOCA_E_STATE, "moca_unet_layer_forward: call moca_unet_finalize after loading the weights");
+    const LayerW* L = find_layer(n, layer);
+    MOCA_REQUIRE(L && (L->kind == "res" || L->kind == "st" || L->kind == "tt"), MOCA_E_ARG,
+                 "moca_unet_layer_forward: '%s' is not a ResBlock / SpatialTransformer / TemporalTransformer of this network", layer);
+    MOCA_REQUIRE(B > 0 && T > 0 && H > 0 && W > 0 && B * T <= 128 && B <= 16 && T <= 16, MOCA_E_SHAPE, "moca_unet_layer_forward: bad shape");
+    const bool is_res = L->kind == "res", is_st = L->kind == "st";
+    MOCA_REQUIRE(!is_res || emb, MOCA_E_ARG, "moca_unet_layer_forward: a ResBlock needs the embedding [B*T, %d]", 4 * n->mc);
+    MOCA_REQUIRE(!is_st || (context && ctx_len && Lmax > 0 && (Lmax * n->ctx_dim) % 8 == 0), MOCA_E_ARG,
+                 "moca_unet_layer_forward: a SpatialTransformer needs the context and its lengths");
+    if (!is_st) Lmax = 8;
+    cudaStream_t st = (cudaStream_t)stream;
+    std::vector<int> key{B, T, H, W, Lmax, 2};
+    for (const char* c = layer; *c; ++c) key.push_back((int)*c);
+    Plan* plan = nullptr;
+    auto it = n->plans.find(key);
+    if (it != n->plans.end()) {
+        it->second->last_use = ++n->use_clock;
+        plan = it->second.get();
+    } else {
+        auto np = std::make_shared<Plan>();
+        np->B = B; np->T = T; np->H = H; np->W = W; np->Lmax = Lmax;
+        Builder dry;
+        dry.net = n; dry.plan = np.get(); dry.dry = true; dry.B = B; dry.T = T; dry.H0 = H; dry.W0 = W; dry.NF = B * T; dry.Lmax = Lmax;
+        dry.build_layer(*L);
+        if (dry.rc) return dry.rc;
+        Builder real = dry;
+        real.dry = false; real.cs_doubles = 0;
+        np->launches = 0; np->flops = 0;
+        np->stats_bytes = dry.cs_doubles * sizeof(double);
+        np->stats = (double*)real.palloc(np->stats_bytes);
+        np->ab_table = (float2*)real.palloc((size_t)B * T * 3072 * sizeof(float2));
+        for (int i = 0; i < S_COUNT; ++i) real.sptr[i] = real.palloc(dry.need[i] + 256);
+        if (real.rc) return real.rc;
+        real.build_layer(*L);
+        if (real.rc) return real.rc;
+        evict_plans(n);
+        np->last_use = ++n->use_clock;
+        n->plans[key] = np;
+        plan = np.get();
+    }
+    const int Cin = is_res ? L->res.cin : L->tf.C;
+    MOCA_CHECK_CUDA(cudaMemcpyAsync(plan->x_in, x, (size_t)B * Cin * T * H * W * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    if (is_res) MOCA_CHECK_CUDA(cudaMemcpyAsync(plan->emb_in, emb, (size_t)B * T * 4 * n->mc * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    if (is_st) {
+        MOCA_CHECK_CUDA(cudaMemcpyAsync(plan->ctx_in, context, (size_t)B * Lmax * n->ctx_dim * sizeof(float), cudaMemcpyDeviceToDevice, st));
+        IntPack ip;
+        memset(&ip, 0, sizeof(ip));
+        for (int b = 0; b < B; ++b) {
+            MOCA_REQUIRE(ctx_len[b] >= 1 && ctx_len[b] <= Lmax, MOCA_E_ARG, "moca_unet_layer_forward: ctx_len[%d]=%d outside 1..%d", b, ctx_len[b], Lmax);
+            ip.ctxlen[b] = ctx_len[b];
+        }
+        int* scratch_ints = plan->d_ctxlen;        // set_ints_kernel also writes 2 x nf ints: none here (nf = 0)
+        set_ints_kernel<<<1, 128, 0, st>>>(ip, 0, B, scratch_ints, scratch_ints, plan->d_ctxlen);
+        MOCA_LAUNCH_CHECK();
+    }
+    for (auto& op : plan->ops) {
+        int rc = op(st);
+        if (rc) return rc;
+    }
+    return tokens_to_ncthw(plan->out_tok, plan->out_C, B, plan->out_C, T, H, W, y, st);
+}
+
+extern "C" int32_t moca_unet_layer_channels(moca_unet* n, const char* layer, int32_t* c_in, int32_t* c_out) {
+    MOCA_REQUIRE(n && layer && c_in && c_out, MOCA_E_ARG, "moca_unet_layer_channels: NULL argument");
+    const LayerW* L = find_layer(n, layer);
+    MOCA_REQUIRE(L, MOCA_E_ARG, "moca_unet_layer_channels: no layer '%s'", layer);
+    if (L->kind == "res") { *c_in = L->res.cin; *c_out = L->res.cout; }
+    else if (L->kind == "st" || L->kind == "tt") { *c_in = L->tf.C; *c_out = L->tf.C; }
+    else { *c_in = L->cin; *c_out = L->cout; }
+    return MOCA_OK;
+}
+
 
 extern "C" int32_t moca_unet_destroy(moca_unet* n) {
     if (!n) return MOCA_OK;

@@ -183,7 +183,12 @@ def fifo_ddim_sampling(args, model, conditioning, noise_shape, ddim_sampler, cfg
                 x_prev = onestep(start, end, nz)
                 ops.window_scatter(packed[j], x_prev, f - keep, 0, keep)
                 j += 1
-            dist.all_gather_into_tensor(gathered.view(-1), packed.view(-1), group=group)   # the queue hand-off
+            # the queue hand-off: issued by the library (moca_queue_handoff, NCCL on the current stream) once
+            # ops.comm_init(group) has created its communicator; torch.distributed carries it otherwise (gloo / CPU tests)
+            if getattr(ops, "comm_size", None) is not None and latents.is_cuda and ops.comm_size(dev) == world:
+                ops.queue_handoff(packed, gathered)
+            else:
+                dist.all_gather_into_tensor(gathered.view(-1), packed.view(-1), group=group)
             for (w, start, mid, end) in wins:
                 owner = w % world
                 slot = [x[0] for x in wins if x[0] % world == owner].index(w)       # same order as on the owner

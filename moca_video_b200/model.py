@@ -52,6 +52,12 @@ class LatentDiffusionB200:
         ts = list(t.tolist() if isinstance(t, torch.Tensor) else t)
         fps = self.default_fps if fps is None else fps
         if isinstance(fps, torch.Tensor):
-            fps = torch.cat([fps.reshape(-1)[:b], fps.reshape(-1)[:b]]) if fps.numel() >= b else fps
+            fps = fps.reshape(-1)
+            if fps.numel() == 1:
+                fps = fps.repeat(2 * b)
+            elif fps.numel() == b:
+                fps = torch.cat([fps, fps])
+            else:
+                raise ValueError(f"apply_model_cfg: fps has {fps.numel()} entries for batch {b} (1 or {b} expected)")
         e = self.unet(x2, ts + ts, context=ctx, fps=fps, ctx_len=[Lc] * b + [Lu] * b, **kwargs)
         return e[:b], e[b:]

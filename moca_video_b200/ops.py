@@ -249,3 +249,42 @@ def attention_op16(q, k, v, batch, heads, Lq, Lk, Lk_valid=None, temporal_inner=
                                         Lk if Lk_valid is None else Lk_valid, q.stride(0), k.stride(0), ptr(out), out.stride(0),
                                         int(temporal_inner), stream_ptr()))
     return out
+
+
+# ---- multi-GPU queue hand-off (include/moca_b200.h: moca_comm_*, moca_queue_handoff) ---------------------------------------
+def comm_init(group=None, device=None):
+    """Creates the library's NCCL communicator for the ranks of ``group`` (default: the world).  torch.distributed only carries
+    the 128-byte NCCL id from rank 0 to the others; the exchange itself (queue_handoff) is issued by the library."""
+    import torch.distributed as dist
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    buf = C.create_string_buffer(128)
+    if rank == 0:
+        check(lib().moca_comm_unique_id(buf))
+    box = [bytes(buf.raw)]
+    dist.broadcast_object_list(box, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+    idb = C.create_string_buffer(box[0], 128)
+    with torch.cuda.device(dev):
+        check(lib().moca_comm_init(ctx(dev.index), idb, world, rank))
+    return world
+
+
+def comm_size(device=None):
+    """Ranks of the library communicator of this device's context (0: none)."""
+    idx = torch.cuda.current_device() if device is None else torch.device(device).index
+    return int(lib().moca_comm_size(ctx(idx)))
+
+
+def queue_handoff(packed, gathered):
+    """All-gather of the ranks' updated half-windows on the current stream (replaces the mp.Queue exchange of funcs_mp.py:197-236).
+    packed: fp32 [count...] this rank's contribution; gathered: fp32 [nranks, count...]."""
+    assert packed.is_cuda and gathered.is_cuda and packed.dtype == gathered.dtype == torch.float32
+    assert packed.is_contiguous() and gathered.is_contiguous() and gathered.numel() % packed.numel() == 0
+    with torch.cuda.device(packed.device):
+        check(lib().moca_queue_handoff(ctx(packed.device.index), ptr(packed), ptr(gathered), packed.numel(), stream_ptr()))
+    return gathered
+
+
+def comm_destroy(device=None):
+    idx = torch.cuda.current_device() if device is None else torch.device(device).index
+    check(lib().moca_comm_destroy(ctx(idx)))

@@ -8,6 +8,10 @@ CrossAttention to xformers (lvdm/modules/attention.py:73-74).  Call after ``sys.
 
 Rebound (``REBOUND`` lists them; tests/test_patch.py checks each against the reference's own signature):
   lvdm.modules.networks.openaimodel3d.UNetModel.forward          -> UNet3D.forward (weights packed on first call)
+  lvdm.modules.networks.openaimodel3d.ResBlock.forward           -> UNet3D.layer_forward (moca_unet_layer_forward), incl. its
+                                                                    TemporalConvBlock
+  lvdm.modules.attention.SpatialTransformer.forward / TemporalTransformer.forward -> UNet3D.layer_forward
+      (a module reaches the engine of the UNetModel it belongs to: ``attach(unet)``, done by the first UNetModel.forward)
   lvdm.models.samplers.ddim.DDIMSampler.make_schedule / unet / fifo_onestep / ddim_step / p_sample_ddim
   utils.freeinit_utils.freq_mix_3d / get_freq_filter
   scripts.evaluation.funcs.prepare_latents / shift_latents / fifo_ddim_sampling (+ its imported FreeInit names)
@@ -25,7 +29,8 @@ from .sampler import DDIMSampler as _B200Sampler
 from .unet import UNet3D
 
 REBOUND = {
-    "lvdm.modules.networks.openaimodel3d": ["UNetModel.forward"],
+    "lvdm.modules.networks.openaimodel3d": ["UNetModel.forward", "ResBlock.forward"],
+    "lvdm.modules.attention": ["SpatialTransformer.forward", "TemporalTransformer.forward"],
     "lvdm.models.samplers.ddim": ["DDIMSampler.make_schedule", "DDIMSampler.unet", "DDIMSampler.fifo_onestep", "DDIMSampler.ddim_step",
                                   "DDIMSampler.p_sample_ddim"],
     "utils.freeinit_utils": ["freq_mix_3d", "get_freq_filter"],
@@ -63,18 +68,79 @@ def _init_attn_heads(unet):
     return 8
 
 
+_MODULE_KINDS = ("ResBlock", "SpatialTransformer", "TemporalTransformer")
+
+
+def attach(unet, device=None):
+    """Builds (once) the library engine of a reference ``UNetModel`` — weights packed from its ``state_dict`` — and tells every
+    ResBlock / SpatialTransformer / TemporalTransformer inside which engine and which layer name it is, so that the rebound module
+    ``forward``s reach the same packed weights."""
+    eng = getattr(unet, "_moca_engine", None)
+    if eng is None:
+        dev = device if device is not None else next(unet.parameters()).device
+        mult = tuple(unet.channel_mult) if hasattr(unet, "channel_mult") else (1, 2, 4, 4)
+        flags = {k: getattr(unet, k) for k in _UNET_FLAGS if hasattr(unet, k)}      # unsupported options raise in UNet3D
+        eng = UNet3D(unet.in_channels, unet.out_channels, unet.model_channels, tuple(unet.attention_resolutions),
+                     unet.num_res_blocks, mult, _head_channels(unet), _context_dim(unet), _init_attn_heads(unet), device=dev, **flags)
+        eng.load_state_dict(unet.state_dict())
+        object.__setattr__(unet, "_moca_engine", eng)
+        for name, mod in unet.named_modules():
+            if mod.__class__.__name__ in _MODULE_KINDS:
+                object.__setattr__(mod, "_moca_engine", eng)
+                object.__setattr__(mod, "_moca_name", name)
+    return eng
+
+
 def _unet_forward(self, x, timesteps, context=None, features_adapter=None, fps=16, ctx_len=None, **kwargs):
     """Replacement body of UNetModel.forward (openaimodel3d.py:534-578).  ``ctx_len`` is the one addition: true context
     lengths when the caller batches samples with different prompt lengths (the patched sampler's b=2 CFG launch)."""
-    eng = getattr(self, "_moca_engine", None)
-    if eng is None:
-        mult = tuple(self.channel_mult) if hasattr(self, "channel_mult") else (1, 2, 4, 4)
-        flags = {k: getattr(self, k) for k in _UNET_FLAGS if hasattr(self, k)}      # unsupported options raise in UNet3D
-        eng = UNet3D(self.in_channels, self.out_channels, self.model_channels, tuple(self.attention_resolutions),
-                     self.num_res_blocks, mult, _head_channels(self), _context_dim(self), _init_attn_heads(self), device=x.device, **flags)
-        eng.load_state_dict(self.state_dict())
-        object.__setattr__(self, "_moca_engine", eng)
+    eng = attach(self, x.device)
     return eng.forward(x, timesteps, context=context, features_adapter=features_adapter, fps=fps, ctx_len=ctx_len)
+
+
+def _module_engine(mod, what):
+    eng = getattr(mod, "_moca_engine", None)
+    if eng is None:
+        raise MocaError(f"{what}: this module is not attached to a library engine; call moca_video_b200.patch.attach(unet) "
+                        "on the UNetModel it belongs to (the first patched UNetModel.forward does it)")
+    return eng, mod._moca_name
+
+
+def _resblock_forward(self, x, emb, batch_size=None):
+    """ResBlock.forward (openaimodel3d.py:195-234) with its TemporalConvBlock (:269-276): x [(b t), c, h, w], emb [(b t), 4 mc]."""
+    eng, name = _module_engine(self, "ResBlock.forward")
+    if not batch_size:
+        raise MocaError("ResBlock.forward: batch_size is required (the library always runs the block's temporal convolution, "
+                        "which the reference skips without it, openaimodel3d.py:230)")
+    n, c, h, w = x.shape
+    b, t = int(batch_size), n // int(batch_size)
+    y = eng.layer_forward(name, x.reshape(b, t, c, h, w).permute(0, 2, 1, 3, 4), emb=emb)
+    return y.permute(0, 2, 1, 3, 4).reshape(n, y.shape[1], h, w)
+
+
+def _spatial_tf_forward(self, x, context=None):
+    """SpatialTransformer.forward (attention.py:262-278): x [(b t), c, h, w], context [(b t), L, d] (the same text for the frames
+    of a sample).  Frames are independent here, so any grouping into (b, t) with one context per group is equivalent."""
+    eng, name = _module_engine(self, "SpatialTransformer.forward")
+    if context is None:
+        raise MocaError("SpatialTransformer.forward: context is required (cross-attention on the text embedding)")
+    n, c, h, w = x.shape
+    t = 16 if n % 16 == 0 else 1
+    ctx = context.reshape(n // t, t, *context.shape[1:])
+    if t > 1 and not bool((ctx == ctx[:, :1]).all()):
+        t = 1
+        ctx = context.reshape(n, 1, *context.shape[1:])
+    b = n // t
+    if b > 16:
+        raise MocaError(f"SpatialTransformer.forward: {n} frames with per-frame contexts exceed one launch (16 groups)")
+    y = eng.layer_forward(name, x.reshape(b, t, c, h, w).permute(0, 2, 1, 3, 4), context=ctx[:, 0])
+    return y.permute(0, 2, 1, 3, 4).reshape(n, c, h, w)
+
+
+def _temporal_tf_forward(self, x, context=None):
+    """TemporalTransformer.forward (attention.py:331-373), temporal_selfatt_only: x [b, c, t, h, w]; context is unused there too."""
+    eng, name = _module_engine(self, "TemporalTransformer.forward")
+    return eng.layer_forward(name, x)
 
 
 def _get_freq_filter(shape, device, filter_type, n, d_s, d_t):
@@ -129,6 +195,11 @@ def patch_reference():
     m = mods["lvdm.modules.networks.openaimodel3d"]
     if m is not None:
         m.UNetModel.forward = _unet_forward
+        m.ResBlock.forward = _resblock_forward
+    m = mods["lvdm.modules.attention"]
+    if m is not None:
+        m.SpatialTransformer.forward = _spatial_tf_forward
+        m.TemporalTransformer.forward = _temporal_tf_forward
     m = mods["lvdm.models.samplers.ddim"]
     if m is not None:
         S = m.DDIMSampler

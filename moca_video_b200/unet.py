@@ -110,8 +110,11 @@ class UNet3D:
         L = context.shape[1]
         lens = [L] * b if ctx_len is None else [int(v) for v in ctx_len]
         if isinstance(fps, torch.Tensor):
-            fl = [int(v) for v in fps.tolist()]
-            fl = fl * b if len(fl) == 1 else fl[:b] if len(fl) >= b else fl
+            fl = [int(v) for v in fps.reshape(-1).tolist()]
+            if len(fl) == 1:
+                fl = fl * b
+            elif len(fl) != b:
+                raise _lib.MocaError(f"UNet3D.forward: fps has {len(fl)} entries for batch {b} (1 or {b} expected)")
         else:
             fl = [int(fps)] * b
         y = torch.empty((b, self.cfg.out_channels, t, h, w), device=self.device, dtype=torch.float32)
@@ -122,6 +125,41 @@ class UNet3D:
         return y
 
     __call__ = forward
+
+    # ---- per-module entry points (moca_unet_layer_forward) ---------------------------------------------------------
+    def layer_channels(self, name):
+        ci, co = C.c_int32(), C.c_int32()
+        check(lib().moca_unet_layer_channels(self._h, name.encode(), C.byref(ci), C.byref(co)))
+        return ci.value, co.value
+
+    def layer_forward(self, name, x, emb=None, context=None, ctx_len=None):
+        """One ResBlock (+ TemporalConvBlock), SpatialTransformer or TemporalTransformer of the loaded network, by its
+        state_dict prefix (openaimodel3d.py:208-234, 269-276; attention.py:262-278, 331-373).  x: [b, c, t, h, w] fp32;
+        emb: [b*t, 4*model_channels] (ResBlock); context: [b, L, context_dim] (SpatialTransformer).  Returns [b, c_out, t, h, w]."""
+        if not self._loaded:
+            raise _lib.MocaError("UNet3D.layer_forward: weights not loaded")
+        b, c, t, h, w = x.shape
+        ci, co = self.layer_channels(name)
+        if c != ci:
+            raise _lib.MocaError(f"UNet3D.layer_forward: {name} expects {ci} channels, got {c}")
+        x = x.to(device=self.device, dtype=torch.float32).contiguous()
+        y = torch.empty((b, co, t, h, w), device=self.device, dtype=torch.float32)
+        L, len_h = 0, None
+        if emb is not None:
+            emb = emb.to(device=self.device, dtype=torch.float32).contiguous()
+            if tuple(emb.shape) != (b * t, 4 * self.cfg.model_channels):
+                raise _lib.MocaError(f"UNet3D.layer_forward: emb must be [{b * t}, {4 * self.cfg.model_channels}], got {tuple(emb.shape)}")
+        if context is not None:
+            context = context.to(device=self.device, dtype=torch.float32).contiguous()
+            if context.shape[0] != b:
+                raise _lib.MocaError(f"UNet3D.layer_forward: context batch {context.shape[0]} != {b}")
+            L = context.shape[1]
+            len_h = host_i32([L] * b if ctx_len is None else [int(v) for v in ctx_len])
+        with torch.cuda.device(self.device):
+            check(lib().moca_unet_layer_forward(self._h, name.encode(), ptr(x), ptr(emb), ptr(context),
+                                                C.cast(len_h, C.c_void_p) if len_h is not None else None, L, b, t, h, w, ptr(y),
+                                                stream_ptr()))
+        return y
 
     # ---- parity taps / accounting -------------------------------------------------------------------------------
     def set_taps(self, enable=True):

@@ -245,3 +245,24 @@ def test_freq_mix_3d():
     # linearity in (x, noise)
     y2 = ops.freq_mix_3d(_t(2 * x), _t(2 * n), lp)
     assert _rel(y2.cpu().numpy(), 2 * y.cpu().numpy()) < 1e-5
+
+
+def test_queue_handoff_single_rank_communicator():
+    """moca_comm_unique_id -> moca_comm_init -> moca_queue_handoff on a 1-rank NCCL communicator (the multi-rank exchange is
+    checked on hardware by bench.py's one_vs_n record and on CPU by the gloo tests of test_host_logic.py)."""
+    import ctypes as C
+    from moca_video_b200 import _lib, ops
+    dev = torch.device("cuda", 0)
+    if ops.comm_size(dev) == 0:
+        buf = C.create_string_buffer(128)
+        _lib.check(_lib.lib().moca_comm_unique_id(buf))
+        _lib.check(_lib.lib().moca_comm_init(_lib.ctx(0), buf, 1, 0))
+    assert ops.comm_size(dev) == 1
+    g = torch.Generator(device=dev).manual_seed(4)
+    packed = torch.randn((2, 1, 4, 8, 40, 64), device=dev, generator=g)
+    gathered = torch.zeros((1,) + tuple(packed.shape), device=dev)
+    ops.queue_handoff(packed, gathered)
+    torch.cuda.synchronize()
+    assert torch.equal(gathered[0], packed)
+    ops.comm_destroy(dev)
+    assert ops.comm_size(dev) == 0

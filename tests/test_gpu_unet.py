@@ -86,6 +86,36 @@ def test_unet_small_taps_vs_oracle(small):
     assert rel(y2, y) < 1e-6
 
 
+@pytest.mark.parametrize("name,kind", [("input_blocks.1.0", "res"), ("input_blocks.4.0", "res"), ("output_blocks.2.0", "res"),
+                                       ("input_blocks.1.1", "st"), ("input_blocks.4.2", "tt"), ("middle_block.1", "st"), ("init_attn.0", "tt")])
+def test_module_entry_points_vs_oracle(small, name, kind):
+    """moca_unet_layer_forward: one ResBlock (+ TemporalConvBlock, incl. a channel-changing one and a skip-concat
+    one), SpatialTransformer or TemporalTransformer on its own against the oracle's module functions."""
+    from oracle import unet_ref as O
+    cfg, sd, net = small
+    ci, co = net.layer_channels(name)
+    b, t = 1, 16
+    res = {"input_blocks.1": 16, "input_blocks.4": 8, "output_blocks.2": 2, "middle_block": 2, "init_attn": 16}[name.rsplit(".", 1)[0]]
+    h = w = res
+    g = torch.Generator(device=DEV).manual_seed(len(name))
+    x = torch.randn(b, ci, t, h, w, device=DEV, generator=g)
+    heads = ci // cfg.num_head_channels if name != "init_attn.0" else 8
+    if kind == "res":
+        emb = torch.randn(b * t, 4 * cfg.model_channels, device=DEV, generator=g)
+        y = net.layer_forward(name, x, emb=emb)
+        x4 = x.permute(0, 2, 1, 3, 4).reshape(b * t, ci, h, w)
+        ref = O.resblock(x4, emb, sd, name, b).reshape(b, t, co, h, w).permute(0, 2, 1, 3, 4)
+    elif kind == "st":
+        ctx = torch.randn(b, 11, cfg.context_dim, device=DEV, generator=g)
+        y = net.layer_forward(name, x, context=ctx)
+        x4 = x.permute(0, 2, 1, 3, 4).reshape(b * t, ci, h, w)
+        ref = O.spatial_transformer(x4, ctx.repeat_interleave(t, 0), sd, name, heads).reshape(b, t, co, h, w).permute(0, 2, 1, 3, 4)
+    else:
+        y = net.layer_forward(name, x)
+        ref = O.temporal_transformer(x, sd, name, heads)
+    assert y.shape == ref.shape and rel(y, ref) < 5e-3, (name, rel(y, ref))      # one module: far inside the 2e-2 end-to-end bar
+
+
 def test_unet_full_vs_oracle_fp32(full):
     """inference_t2v_512_v2.0 architecture at [1,4,16,40,64], ctx 77, FIFO per-frame timesteps (BASELINE config 1/3)."""
     from oracle.unet_ref import unet_forward

@@ -16,6 +16,9 @@ pytestmark = pytest.mark.skipif(not refimport.available(), reason="reference tre
 
 ORIGINAL_AT = {                                   # reference definitions the replacements stand in for (file:line)
     "lvdm.modules.networks.openaimodel3d:UNetModel.forward": "openaimodel3d.py:534",
+    "lvdm.modules.networks.openaimodel3d:ResBlock.forward": "openaimodel3d.py:195",
+    "lvdm.modules.attention:SpatialTransformer.forward": "attention.py:262",
+    "lvdm.modules.attention:TemporalTransformer.forward": "attention.py:331",
     "lvdm.models.samplers.ddim:DDIMSampler.make_schedule": "ddim.py:62",
     "lvdm.models.samplers.ddim:DDIMSampler.unet": "ddim.py:362",
     "lvdm.models.samplers.ddim:DDIMSampler.fifo_onestep": "ddim.py:255",
@@ -94,6 +97,14 @@ def test_patched_calls_reach_the_device_boundary(patched):
     x = torch.zeros(1, 4, 16, 8, 8)
     with pytest.raises(MocaError):
         net(x, torch.arange(16), context=torch.zeros(1, 7, 64), fps=10, gamma=0.9, clean_cond=True)   # stray sampler kwargs
+    # module-level drop-ins: a module that was never attached to an engine says so; the reference's call shapes are accepted
+    rb = net.input_blocks[1][0]
+    with pytest.raises(MocaError, match="not attached"):
+        rb(torch.zeros(16, 64, 8, 8), torch.zeros(16, 256), batch_size=1)
+    with pytest.raises(MocaError, match="not attached"):
+        net.input_blocks[1][1](torch.zeros(16, 64, 8, 8), context=torch.zeros(16, 7, 64))
+    with pytest.raises(MocaError, match="not attached"):
+        net.input_blocks[1][2](torch.zeros(1, 64, 16, 8, 8))
     # sampler through the reference's own constructor path (oracle/refimport's CPU subclass) and LatentDiffusion-like apply_model
     seen = []
 
