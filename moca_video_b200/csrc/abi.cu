@@ -45,9 +45,6 @@ extern "C" int32_t moca_ctx_create(int32_t device, moca_ctx** out) {
     c->c.cc_minor = prop.minor;
     cudaError_t e1 = cudaMalloc(&c->c.d_mask_sums, sizeof(double) * MOCA_MAX_MASKS);
     cudaError_t e2 = e1 == cudaSuccess ? cudaMemset(c->c.d_mask_sums, 0, sizeof(double) * MOCA_MAX_MASKS) : e1;
-    if (e2 == cudaSuccess) e2 = cudaMalloc(&c->c.d_sk_ws, (size_t)c->c.num_sms * 128 * 256 * sizeof(float));
-    if (e2 == cudaSuccess) e2 = cudaMalloc(&c->c.d_sk_flags, (size_t)c->c.num_sms * sizeof(unsigned));
-    if (e2 == cudaSuccess) e2 = cudaMemset(c->c.d_sk_flags, 0, (size_t)c->c.num_sms * sizeof(unsigned));
     cudaSetDevice(prev_dev);
     if (e2 != cudaSuccess) {
         set_error("moca_ctx_create: scratch allocation failed: %s", cudaGetErrorString(e2));
@@ -64,8 +61,6 @@ extern "C" int32_t moca_ctx_destroy(moca_ctx* ctx) {
     if (!ctx) return MOCA_OK;
     moca_comm_destroy(ctx);
     cudaFree(ctx->c.d_mask_sums);
-    cudaFree(ctx->c.d_sk_ws);
-    cudaFree(ctx->c.d_sk_flags);
     delete ctx;
     return MOCA_OK;
 }

@@ -73,8 +73,6 @@ struct Ctx {
     int num_sms = 148;
     int cc_major = 0, cc_minor = 0;
     double* d_mask_sums = nullptr;      // [MOCA_MAX_FRAMES] scratch of the K13 mask pre-pass
-    float* d_sk_ws = nullptr;           // stream-K partial accumulators of the GEMM tail tiles: [num_sms][128][256] fp32
-    unsigned* d_sk_flags = nullptr;     // [num_sms] arrival counters, zero between launches
     void* nccl_comm = nullptr;          // queue hand-off communicator (comm.cu), NULL on a single GPU
     int nranks = 1, rank = 0;
     float* d_twiddle = nullptr;         // FreeInit DFT twiddles (cos,sin) for up to 3 axes

@@ -110,129 +110,6 @@ __device__ __forceinline__ bool map_row(const GemmParams& P, int row, int& out_r
     return true;
 }
 
-// ---- stream-K tail -------------------------------------------------------------------------------------------------
-// A persistent grid of G CTAs runs floor(ntiles / G) full waves data-parallel (CTA g: tiles g, g + G, ..).  The R < G tiles
-// that remain would cost a whole wave; with sk_on their R * kiters k-block iterations are dealt out evenly instead, CTA g
-// taking units [g U / G, (g + 1) U / G) of U = R * kiters.  Such a range touches at most two tiles.  The part that reaches
-// the END of a tile makes its CTA that tile's OWNER (it runs the normal epilogue, after adding the partial accumulators of
-// the CTAs that hold the earlier k ranges of the tile: CTAs g_lo .. g - 1); any other part is a CONTRIBUTION: the raw fp32
-// accumulator goes to sk_ws[g] and every epilogue warp bumps sk_flags[g].  A CTA has at most one contribution and does it
-// before its owner part, so an owner only ever waits for CTAs that are not waiting themselves.  The owner's warps bump the
-// counters again when they have read the partials; the last one resets them to zero for the next launch.
-struct SkPlan {
-    int n_dp = 0;                       // data-parallel tiles of this CTA: tile0 + i * tstep
-    bool has_c = false, has_o = false;
-    int c_tile = 0, c_k0 = 0, c_k1 = 0;  // contribution: k-block iterations [c_k0, c_k1) of c_tile
-    int o_tile = 0, o_k0 = 0;            // owner part: iterations [o_k0, kiters) of o_tile (o_k0 == 0: a whole tile)
-    int g_lo = 0;                       // contributors of o_tile: CTAs g_lo .. g - 1
-};
-
-__device__ __forceinline__ SkPlan sk_decompose(const GemmParams& P, int g, int G, int ntiles, int kiters) {
-    SkPlan s;
-    if (!P.sk_on) {
-        s.n_dp = g < ntiles ? (ntiles - g + G - 1) / G : 0;
-        return s;
-    }
-    const int n_full = ntiles / G, tail0 = n_full * G, R = ntiles - tail0;
-    s.n_dp = n_full;
-    const long long U = (long long)R * kiters;
-    const long long b0 = (long long)g * U / G, b1 = (long long)(g + 1) * U / G;
-    if (b1 > b0) {
-        const int ta = (int)(b0 / kiters), ka = (int)(b0 - (long long)ta * kiters), len = (int)(b1 - b0);
-        const int enda = min(kiters, ka + len);
-        if (enda == kiters) { s.has_o = true; s.o_tile = tail0 + ta; s.o_k0 = ka; }
-        else { s.has_c = true; s.c_tile = tail0 + ta; s.c_k0 = ka; s.c_k1 = enda; }
-        const int rem = len - (enda - ka);
-        if (rem > 0) { s.has_c = true; s.c_tile = tail0 + ta + 1; s.c_k0 = 0; s.c_k1 = rem; }
-        if (s.has_o && s.o_k0 > 0) {
-            const long long tu = (long long)ta * kiters;          // first unit of the owner's tile
-            int gl = (int)(tu * G / U);
-            while ((long long)(gl + 1) * U / G <= tu) ++gl;
-            while (gl > 0 && (long long)gl * U / G > tu) --gl;
-            s.g_lo = gl;
-        }
-    }
-    return s;
-}
-
-__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
-    unsigned v;
-    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-
-// contribution of one epilogue warp (lane quarter q, warp widx of the nwq warps that share the quarter): its 32 accumulator rows,
-// every nwq-th 32-column chunk, raw fp32 into sk_ws[g]; then the warp announces itself
-// Workspace layout of one slot: [BN / 4 column quads][128 rows] float4 — a warp's store / load of one quad for its 32 rows is 512
-// contiguous bytes.
-template <int BN, int EPI_WARPS>
-__device__ __forceinline__ void sk_contribute(const GemmParams& P, uint32_t t_row, int g, int q, int widx, int lane) {
-    float4* wsq = reinterpret_cast<float4*>(P.sk_ws + (size_t)g * kBM * BN) + q * 32 + lane;
-    constexpr int nwq = EPI_WARPS / 4;
-    for (int c = widx; c < BN / 32; c += nwq) {
-        uint32_t r[32];
-        tmem_ld32(t_row + (uint32_t)(c * 32), r);
-        tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-            wsq[(size_t)(c * 8 + j) * kBM] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
-    }
-    __threadfence();
-    __syncwarp();
-    if (lane == 0) atomicAdd(P.sk_flags + g, 1u);
-}
-// owner: wait until every epilogue warp of the contributing CTAs g_lo .. g - 1 has written its part
-template <int EPI_WARPS>
-__device__ __forceinline__ void sk_wait(const GemmParams& P, int g_lo, int g, int lane) {
-    if (lane == 0)
-        for (int gp = g_lo; gp < g; ++gp)
-            while (ld_acquire_u32(P.sk_flags + gp) < (unsigned)EPI_WARPS) __nanosleep(64);
-    __syncwarp();
-    __threadfence();
-}
-// owner: r[0..31] (thread = accumulator row `row` of the tile, columns col .. col + 31) += the partials, in CTA order
-template <int BN>
-__device__ __forceinline__ void sk_add32(const GemmParams& P, int g_lo, int g, int row, int col, uint32_t* r) {
-    for (int gp = g_lo; gp < g; ++gp) {
-        const float4* src = reinterpret_cast<const float4*>(P.sk_ws + (size_t)gp * kBM * BN) + (size_t)(col >> 2) * kBM + row;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const float4 t = __ldcg(src + (size_t)j * kBM);
-            r[4 * j] = __float_as_uint(__uint_as_float(r[4 * j]) + t.x);
-            r[4 * j + 1] = __float_as_uint(__uint_as_float(r[4 * j + 1]) + t.y);
-            r[4 * j + 2] = __float_as_uint(__uint_as_float(r[4 * j + 2]) + t.z);
-            r[4 * j + 3] = __float_as_uint(__uint_as_float(r[4 * j + 3]) + t.w);
-        }
-    }
-}
-// owner, when the tile is done: the last of the 2 * EPI_WARPS arrivals (contributors + readers) clears the counter
-template <int EPI_WARPS>
-__device__ __forceinline__ void sk_release(const GemmParams& P, int g_lo, int g, int lane) {
-    __syncwarp();
-    if (lane == 0)
-        for (int gp = g_lo; gp < g; ++gp)
-            if (atomicAdd(P.sk_flags + gp, 1u) == 2u * EPI_WARPS - 1u) atomicExch(P.sk_flags + gp, 0u);
-}
-
-// LayerNorm fold, consumer side: mean and rstd of accumulator row `row` from the producer's partial sums.  Split in two so that
-// the loads (all issued back to back: the slot count is even and at most 10, gemm_plan) run one tile ahead of their use.
-struct LnRow { float4 v[5]; };
-__device__ __forceinline__ void ln_row_load(const GemmParams& P, int row, LnRow& t) {
-    const float4* src = reinterpret_cast<const float4*>(P.ln_rs + (size_t)row * P.ln_slots);
-    const int nq = row < P.M ? (P.ln_slots >> 1) : 0;
-#pragma unroll
-    for (int i = 0; i < 5; ++i) t.v[i] = i < nq ? __ldcg(src + i) : make_float4(0.f, 0.f, 0.f, 0.f);
-}
-__device__ __forceinline__ void ln_row_finish(const GemmParams& P, const LnRow& t, float& rstd, float& nmr) {
-    float sx = 0.f, sq = 0.f;
-#pragma unroll
-    for (int i = 0; i < 5; ++i) { sx += t.v[i].x + t.v[i].z; sq += t.v[i].y + t.v[i].w; }
-    const float mean = sx * P.ln_inv_c;
-    const float var = fmaxf(sq * P.ln_inv_c - mean * mean, 0.f);
-    rstd = rsqrtf(var + P.ln_eps);
-    nmr = -mean * rstd;
-}
-
 // STATS: GroupNorm statistics of the stored values (EPI_F32); for the bf16 thread = row epilogue (TEPI && EPI_BF16) the same
 // flag selects the variant that adds a 16-bit residual (RES16).
 template <int BN, int EPI, bool STATS, bool TEPI = false, int NCTA = 1>
@@ -261,7 +138,6 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
     const int ntiles = NCTA == 2 ? ((P.num_m_tiles + 1) >> 1) * P.num_n_tiles : P.num_m_tiles * P.num_n_tiles;
     auto MT = [&](int tile) { return NCTA == 2 ? 2 * (tile / P.num_n_tiles) + cta_rank : tile / P.num_n_tiles; };
     const int kiters = P.ntaps * P.kblocks;
-    const SkPlan sk = sk_decompose(P, tile0, tstep, ntiles, kiters);      // NCTA == 2 never runs with sk_on
 
     if (threadIdx.x == 0) {
         prefetch_tmap(&P.tmA);
@@ -299,38 +175,35 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
             // ===== TMA producer =====
             int stage = 0;
             uint32_t phase = 0;
-            auto produce = [&](int tile, int k0, int k1) {
+            for (int tile = tile0; tile < ntiles; tile += tstep) {
                 const int mt = MT(tile), nt = tile % P.num_n_tiles;
-                int tap = k0 / P.kblocks, kb = k0 - tap * P.kblocks;
                 // GEMM_SPATIAL_4D: first frame / first input image row of the tile
                 const int c4_fg = P.mode == GEMM_SPATIAL_4D ? mt / P.c4_th : 0;
                 const int c4_f0 = c4_fg * P.c4_bf, c4_h0 = (mt - c4_fg * P.c4_th) * P.c4_bh * P.stride;
-                for (int it = k0; it < k1; ++it) {
+                for (int tap = 0; tap < P.ntaps; ++tap) {
                     const int arow = mt * kBM + P.tap_shift[tap];
-                    mbar_wait(&empty[stage], phase ^ 1);
-                    uint8_t* sa = base + (size_t)stage * Cfg::STAGE_BYTES;
-                    if (NCTA == 1 && P.mode == GEMM_SPATIAL_4D) {
-                        const int dy = tap / 3, dx = tap - dy * 3;
-                        mbar_expect_tx(&full[stage], Cfg::STAGE_BYTES);
-                        tma_load_4d(sa, &P.tmA, &full[stage], kb * kBK, dx - 1, c4_h0 + dy - 1, c4_f0);
-                        tma_load_2d(sa + kABytes, &P.tmB, &full[stage], tap * P.Kp + kb * kBK, nt * BN);
-                    } else if constexpr (NCTA == 2) {
-                        // both CTAs load their A rows and their half of the B rows; all bytes are counted on the leader's barrier
-                        if (cta_rank == 0) mbar_expect_tx(&full[stage], 2 * Cfg::STAGE_BYTES);
-                        tma_load_2d_pair(sa, &P.tmA, &full[stage], kb * kBK, arow);
-                        tma_load_2d_pair(sa + kABytes, &P.tmB, &full[stage], tap * P.Kp + kb * kBK, nt * BN + cta_rank * (BN / 2));
-                    } else {
-                        mbar_expect_tx(&full[stage], Cfg::STAGE_BYTES);
-                        tma_load_2d(sa, &P.tmA, &full[stage], kb * kBK, arow);
-                        tma_load_2d(sa + kABytes, &P.tmB, &full[stage], tap * P.Kp + kb * kBK, nt * BN);
+                    const int dy = tap / 3, dx = tap - dy * 3;
+                    for (int kb = 0; kb < P.kblocks; ++kb) {
+                        mbar_wait(&empty[stage], phase ^ 1);
+                        uint8_t* sa = base + (size_t)stage * Cfg::STAGE_BYTES;
+                        if (NCTA == 1 && P.mode == GEMM_SPATIAL_4D) {
+                            mbar_expect_tx(&full[stage], Cfg::STAGE_BYTES);
+                            tma_load_4d(sa, &P.tmA, &full[stage], kb * kBK, dx - 1, c4_h0 + dy - 1, c4_f0);
+                            tma_load_2d(sa + kABytes, &P.tmB, &full[stage], tap * P.Kp + kb * kBK, nt * BN);
+                        } else if constexpr (NCTA == 2) {
+                            // both CTAs load their A rows and their half of the B rows; all bytes are counted on the leader's barrier
+                            if (cta_rank == 0) mbar_expect_tx(&full[stage], 2 * Cfg::STAGE_BYTES);
+                            tma_load_2d_pair(sa, &P.tmA, &full[stage], kb * kBK, arow);
+                            tma_load_2d_pair(sa + kABytes, &P.tmB, &full[stage], tap * P.Kp + kb * kBK, nt * BN + cta_rank * (BN / 2));
+                        } else {
+                            mbar_expect_tx(&full[stage], Cfg::STAGE_BYTES);
+                            tma_load_2d(sa, &P.tmA, &full[stage], kb * kBK, arow);
+                            tma_load_2d(sa + kABytes, &P.tmB, &full[stage], tap * P.Kp + kb * kBK, nt * BN);
+                        }
+                        if (++stage == STAGES) { stage = 0; phase ^= 1; }
                     }
-                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
-                    if (++kb == P.kblocks) { kb = 0; ++tap; }
                 }
-            };
-            for (int i = 0; i < sk.n_dp; ++i) produce(tile0 + i * tstep, 0, kiters);
-            if (sk.has_c) produce(sk.c_tile, sk.c_k0, sk.c_k1);
-            if (sk.has_o) produce(sk.o_tile, sk.o_k0, kiters);
+            }
         }
     } else if (warp == 1) {
         if (lane == 0 && cta_rank == 0) {
@@ -340,11 +213,11 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
             uint32_t phase = 0;
             int as = 0;
             uint32_t aphase = 0;
-            auto mma_part = [&](int nk) {
+            for (int tile = tile0; tile < ntiles; tile += tstep) {
                 mbar_wait(&tempty[as], aphase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + (uint32_t)(as * BN);
-                for (int it = 0; it < nk; ++it) {
+                for (int it = 0; it < kiters; ++it) {
                     mbar_wait(&full[stage], phase);
                     tc_fence_after();
                     const uint32_t sa = smem_u32(base + (size_t)stage * Cfg::STAGE_BYTES);
@@ -364,10 +237,7 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
                 else umma_commit(&tfull[as]);
                 as ^= 1;
                 if (as == 0) aphase ^= 1;
-            };
-            for (int i = 0; i < sk.n_dp; ++i) mma_part(kiters);
-            if (sk.has_c) mma_part(sk.c_k1 - sk.c_k0);
-            if (sk.has_o) mma_part(kiters - sk.o_k0);
+            }
         }
     } else if constexpr (TEPI && EPI == EPI_GEGLU) {
         // ===== GEGLU, thread = row, 16 warps: warp (q, c) owns output columns c*32 .. +31 of the tile's 128 for the rows of
@@ -378,17 +248,10 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
         const int ncols_total = P.N >> 1;
         int as = 0;
         uint32_t aphase = 0;
-        LnRow lnr;                                             // LayerNorm fold: row statistics, requested one tile ahead
-        if (P.ln_s && tile0 < ntiles) ln_row_load(P, MT(tile0) * kBM + q * 32 + lane, lnr);
         for (int tile = tile0; tile < ntiles; tile += tstep) {
             const int mt = MT(tile), nt = tile % P.num_n_tiles;
             const int row0 = mt * kBM + q * 32;
             const int n0 = nt * (BN / 2) + c * 32;
-            float rstd = 1.f, nmr = 0.f;
-            if (P.ln_s) {
-                ln_row_finish(P, lnr, rstd, nmr);
-                if (tile + tstep < ntiles) ln_row_load(P, MT(tile + tstep) * kBM + q * 32 + lane, lnr);
-            }
             mbar_wait(&tfull[as], aphase);
             tc_fence_after();
             const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN);
@@ -404,21 +267,13 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
                     const float4* bg = reinterpret_cast<const float4*>(P.bias + (size_t)nt * BN + BN / 2 + c * 32 + h * 16);
                     tmem_ld_wait();
                     uint32_t pk[8];
-                    const float4* sv = reinterpret_cast<const float4*>(P.ln_s + (size_t)nt * BN + c * 32 + h * 16);
-                    const float4* sg = reinterpret_cast<const float4*>(P.ln_s + (size_t)nt * BN + BN / 2 + c * 32 + h * 16);
 #pragma unroll
                     for (int u = 0; u < 4; ++u) {
-                        float4 b1 = __ldg(bv + u), b2 = __ldg(bg + u);
-                        if (P.ln_s) {
-                            // LayerNorm fold: rstd * (acc - mean s[n]) + bias[n] = fma(rstd, acc, fma(-mean rstd, s[n], bias[n]))
-                            const float4 s1 = __ldg(sv + u), s2 = __ldg(sg + u);
-                            b1.x = fmaf(nmr, s1.x, b1.x); b1.y = fmaf(nmr, s1.y, b1.y); b1.z = fmaf(nmr, s1.z, b1.z); b1.w = fmaf(nmr, s1.w, b1.w);
-                            b2.x = fmaf(nmr, s2.x, b2.x); b2.y = fmaf(nmr, s2.y, b2.y); b2.z = fmaf(nmr, s2.z, b2.z); b2.w = fmaf(nmr, s2.w, b2.w);
-                        }
-                        const float o0 = fmaf(rstd, __uint_as_float(rv[4 * u]), b1.x) * gelu_fast(fmaf(rstd, __uint_as_float(rg[4 * u]), b2.x));
-                        const float o1 = fmaf(rstd, __uint_as_float(rv[4 * u + 1]), b1.y) * gelu_fast(fmaf(rstd, __uint_as_float(rg[4 * u + 1]), b2.y));
-                        const float o2 = fmaf(rstd, __uint_as_float(rv[4 * u + 2]), b1.z) * gelu_fast(fmaf(rstd, __uint_as_float(rg[4 * u + 2]), b2.z));
-                        const float o3 = fmaf(rstd, __uint_as_float(rv[4 * u + 3]), b1.w) * gelu_fast(fmaf(rstd, __uint_as_float(rg[4 * u + 3]), b2.w));
+                        const float4 b1 = __ldg(bv + u), b2 = __ldg(bg + u);
+                        const float o0 = (__uint_as_float(rv[4 * u]) + b1.x) * gelu_fast(__uint_as_float(rg[4 * u]) + b2.x);
+                        const float o1 = (__uint_as_float(rv[4 * u + 1]) + b1.y) * gelu_fast(__uint_as_float(rg[4 * u + 1]) + b2.y);
+                        const float o2 = (__uint_as_float(rv[4 * u + 2]) + b1.z) * gelu_fast(__uint_as_float(rg[4 * u + 2]) + b2.z);
+                        const float o3 = (__uint_as_float(rv[4 * u + 3]) + b1.w) * gelu_fast(__uint_as_float(rg[4 * u + 3]) + b2.w);
                         pk[2 * u] = pack_bf16(o0, o1);
                         pk[2 * u + 1] = pack_bf16(o2, o3);
                     }
@@ -451,21 +306,17 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
         constexpr int kChunks = BN / 32;
         // the two warps of a lane quarter take alternate 32-column chunks; with an odd chunk count (BN = 160: 3 + 2) they swap
         // roles from one tile of this CTA to the next, so that over two tiles (= the two accumulator stages) both do 5 chunks
-        // epilogue items of this CTA: its data-parallel tiles, then (stream-K) the tile it owns the end of
-        const int n_items = sk.n_dp + (sk.has_o ? 1 : 0);
-        auto item_tile = [&](int i) { return i < sk.n_dp ? tile0 + i * tstep : sk.o_tile; };
-        auto first_chunk = [&](int i) { return (kChunks & 1) ? (half ^ (i & 1)) : half; };
-        int pi = 0, pc = first_chunk(0);
+        auto first_chunk = [&](int t) { return (kChunks & 1) ? (half ^ (((t - tile0) / tstep) & 1)) : half; };
+        int pt = tile0, pc = first_chunk(tile0);
         uint32_t n_issued = 0, n_waited = 0;
-        auto norm = [&](int& i, int& c) {
-            while (i < n_items && !(c < kChunks && (item_tile(i) % P.num_n_tiles) * BN + c * 32 < P.N)) { ++i; c = first_chunk(i); }
+        auto norm = [&](int& t, int& c) {
+            while (t < ntiles && !(c < kChunks && (t % P.num_n_tiles) * BN + c * 32 < P.N)) { t += tstep; c = first_chunk(t); }
         };
         auto issue_res = [&]() {                               // lane 0 only
-            while (pi < n_items) {
-                const int pt = item_tile(pi);
+            while (pt < ntiles) {
                 const int prow0 = MT(pt) * kBM + q * 32;
                 const int pn0 = (pt % P.num_n_tiles) * BN + pc * 32;
-                pc += 2; norm(pi, pc);
+                pc += 2; norm(pt, pc);
                 if (prow0 >= P.M) continue;
                 const uint32_t slot = n_issued & 1u;
                 mbar_expect_tx(&rbar[slot], 2048);
@@ -475,43 +326,19 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
             }
         };
         if constexpr (RES16) {
-            norm(pi, pc);
+            norm(pt, pc);
             if (lane == 0) { issue_res(); issue_res(); }
         }
         int as = 0;
         uint32_t aphase = 0, nst = 0;
-        bool contrib_pending = sk.has_c;
-        auto do_contrib = [&]() {
-            mbar_wait(&tfull[as], aphase);
-            tc_fence_after();
-            sk_contribute<BN, Cfg::EPI_WARPS>(P, tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN), tile0, q, half, lane);
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&tempty[as]);
-            as ^= 1;
-            if (as == 0) aphase ^= 1;
-            contrib_pending = false;
-        };
-        LnRow lnr;                                             // LayerNorm fold, consumer: row statistics, requested one tile ahead
-        if (P.ln_s && n_items > 0) ln_row_load(P, MT(item_tile(0)) * kBM + q * 32 + lane, lnr);
-        for (int ii = 0; ii < n_items; ++ii) {
-            if (ii == sk.n_dp && contrib_pending) do_contrib();
-            const int tile = item_tile(ii);
-            const bool fix = ii == sk.n_dp && sk.o_k0 > 0;
+        for (int tile = tile0; tile < ntiles; tile += tstep) {
             const int mt = MT(tile), nt = tile % P.num_n_tiles;
             const int row0 = mt * kBM + q * 32;
-            float rstd = 1.f, nmr = 0.f;
-            if (P.ln_s) {
-                ln_row_finish(P, lnr, rstd, nmr);
-                if (ii + 1 < n_items) ln_row_load(P, MT(item_tile(ii + 1)) * kBM + q * 32 + lane, lnr);
-            }
-            float rs_sum = 0.f, rs_sq = 0.f;                   // LayerNorm fold, producer: this thread's row, this warp's columns
             mbar_wait(&tfull[as], aphase);
             tc_fence_after();
-            if (fix) sk_wait<Cfg::EPI_WARPS>(P, sk.g_lo, tile0, lane);
             const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN);
             if (row0 < P.M) {
-                for (int c = first_chunk(ii); c < kChunks; c += 2) {
+                for (int c = first_chunk(tile); c < kChunks; c += 2) {
                     const int n0 = nt * BN + c * 32;
                     if (n0 >= P.N) break;
                     uint32_t r[32];
@@ -521,24 +348,13 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
                     if (lane == 0) bulk_wait_read1();          // the store issued two chunks ago has released this box
                     __syncwarp();
                     tmem_ld_wait();
-                    if (fix) sk_add32<BN>(P, sk.g_lo, tile0, q * 32 + lane, c * 32, r);
                     uint4* dst = reinterpret_cast<uint4*>(stgb + (nst & 1u) * 2048 + lane * 64);
 #pragma unroll
                     for (int u = 0; u < 4; ++u) {
                         float v[8];
 #pragma unroll
                         for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[8 * u + e]);
-                        if (P.ln_s) {
-                            // LayerNorm fold: rstd * (acc - mean s[n]) + bias[n] = fma(rstd, acc, fma(-mean rstd, s[n], bias[n]))
-                            const float4 s1 = __ldg(reinterpret_cast<const float4*>(P.ln_s + n0) + 2 * u);
-                            const float4 s2 = __ldg(reinterpret_cast<const float4*>(P.ln_s + n0) + 2 * u + 1);
-                            const float4 b1 = __ldg(reinterpret_cast<const float4*>(P.bias + n0) + 2 * u);
-                            const float4 b2 = __ldg(reinterpret_cast<const float4*>(P.bias + n0) + 2 * u + 1);
-                            v[0] = fmaf(rstd, v[0], fmaf(nmr, s1.x, b1.x)); v[1] = fmaf(rstd, v[1], fmaf(nmr, s1.y, b1.y));
-                            v[2] = fmaf(rstd, v[2], fmaf(nmr, s1.z, b1.z)); v[3] = fmaf(rstd, v[3], fmaf(nmr, s1.w, b1.w));
-                            v[4] = fmaf(rstd, v[4], fmaf(nmr, s2.x, b2.x)); v[5] = fmaf(rstd, v[5], fmaf(nmr, s2.y, b2.y));
-                            v[6] = fmaf(rstd, v[6], fmaf(nmr, s2.z, b2.z)); v[7] = fmaf(rstd, v[7], fmaf(nmr, s2.w, b2.w));
-                        } else if (P.bias) {
+                        if (P.bias) {
                             const float4 b1 = __ldg(reinterpret_cast<const float4*>(P.bias + n0) + 2 * u);
                             const float4 b2 = __ldg(reinterpret_cast<const float4*>(P.bias + n0) + 2 * u + 1);
                             v[0] += b1.x; v[1] += b1.y; v[2] += b1.z; v[3] += b1.w;
@@ -551,18 +367,7 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
                             v[0] += f0.x; v[1] += f0.y; v[2] += f1.x; v[3] += f1.y;
                             v[4] += f2.x; v[5] += f2.y; v[6] += f3.x; v[7] += f3.y;
                         }
-                        const uint4 pk = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
-                        dst[u] = pk;
-                        if (P.rs_out) {
-                            // statistics of the values before their 16-bit rounding: over a row of C >= 64 values the rounding
-                            // moves the mean by 2^-12 rms / sqrt(C), far below the rounding of the stored values themselves
-                            rs_sum += ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
-                            float q0 = v[0] * v[0], q1 = v[1] * v[1];
-                            q0 = fmaf(v[2], v[2], q0); q1 = fmaf(v[3], v[3], q1);
-                            q0 = fmaf(v[4], v[4], q0); q1 = fmaf(v[5], v[5], q1);
-                            q0 = fmaf(v[6], v[6], q0); q1 = fmaf(v[7], v[7], q1);
-                            rs_sq += q0 + q1;
-                        }
+                        dst[u] = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
                     }
                     fence_proxy_async_smem();
                     __syncwarp();
@@ -574,16 +379,13 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
                     ++nst;
                     if constexpr (RES16) ++n_waited;
                 }
-                if (P.rs_out) P.rs_out[(size_t)(row0 + lane) * P.rs_slots + 2 * nt + half] = make_float2(rs_sum, rs_sq);
             }
-            if (fix) sk_release<Cfg::EPI_WARPS>(P, sk.g_lo, tile0, lane);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&tempty[as]);
             as ^= 1;
             if (as == 0) aphase ^= 1;
         }
-        if (contrib_pending) do_contrib();
         if (lane == 0) bulk_wait0();
     } else if constexpr (TEPI) {
         // ===== TMA-store epilogue (linear / time-padded rows, 32-row slices that map to 32 consecutive output rows) =====
@@ -778,47 +580,26 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
             }
         };
 
-        // epilogue items of this CTA: its data-parallel tiles, then (stream-K) the tile it owns the end of; a contribution to
-        // another tile's owner, if any, is dumped between the two
-        const int n_items = sk.n_dp + (sk.has_o ? 1 : 0);
-        auto item_tile = [&](int i) { return i < sk.n_dp ? tile0 + i * tstep : sk.o_tile; };
-        bool contrib_pending = sk.has_c;
-        auto do_contrib = [&]() {
-            mbar_wait(&tfull[as], aphase);
-            tc_fence_after();
-            sk_contribute<BN, Cfg::EPI_WARPS>(P, tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN), tile0, q, half, lane);
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&tempty[as]);
-            as ^= 1;
-            if (as == 0) aphase ^= 1;
-            contrib_pending = false;
-        };
+        int tile = tile0;
         int out_row = 0, nxt_row = 0;
         int frame_u = -1, nxt_frame = -1;
         uint32_t vmask = 0, nxt_mask = 0;
         float4 pre[8];
         bool have_pre = false;
-        if (n_items > 0) {
-            const int tile = item_tile(0);
+        if (tile < ntiles) {
             tile_rows(tile, out_row, vmask, frame_u);
             if (EPI == EPI_F32 && col0_of(tile) + half * 32 < ncols_total) {
                 prefetch(pre, out_row, vmask, col0_of(tile) + half * 32);
                 have_pre = true;
             }
         }
-        for (int ii = 0; ii < n_items; ++ii) {
-            if (ii == sk.n_dp && contrib_pending) do_contrib();
-            const int tile = item_tile(ii);
-            const bool fix = ii == sk.n_dp && sk.o_k0 > 0;
+        for (; tile < ntiles; tile += tstep) {
             const int nt = tile % P.num_n_tiles;
             const int col_tile0 = col0_of(tile);
-            const bool has_next = ii + 1 < n_items;
-            const int ntile = has_next ? item_tile(ii + 1) : 0;
+            const int ntile = tile + tstep;
             bool nxt_ready = false;
             mbar_wait(&tfull[as], aphase);
             tc_fence_after();
-            if (fix) sk_wait<Cfg::EPI_WARPS>(P, sk.g_lo, tile0, lane);
             const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN);
             for (int c = half; c < kChunks; c += 2) {
                 const int n0 = col_tile0 + c * 32;                 // first output column of this chunk
@@ -832,7 +613,7 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
                     if (c + 2 < kChunks && n0 + 64 < ncols_total) {
                         prefetch(nxt, out_row, vmask, n0 + 64);
                         have_nxt = true;
-                    } else if (has_next) {
+                    } else if (ntile < ntiles) {
                         if (!nxt_ready) { tile_rows(ntile, nxt_row, nxt_mask, nxt_frame); nxt_ready = true; }
                         if (col0_of(ntile) + half * 32 < ncols_total) {
                             prefetch(nxt, nxt_row, nxt_mask, col0_of(ntile) + half * 32);
@@ -840,7 +621,6 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
                         }
                     }
                     tmem_ld_wait();
-                    if (fix) sk_add32<BN>(P, sk.g_lo, tile0, q * 32 + lane, c * 32, r);
 #pragma unroll
                     for (int j = 0; j < 8; ++j)
                         *reinterpret_cast<uint4*>(stg + lane * 32 + ((j ^ (lane & 7)) << 2)) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
@@ -981,7 +761,6 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
                         for (int e = 0; e < 8; ++e) { bb[e] = __ldg(bvp + e); bg[e] = __ldg(bvp + BN / 2 + e); }
                     } else {
                         tmem_ld_wait();
-                        if (fix) sk_add32<BN>(P, sk.g_lo, tile0, q * 32 + lane, c * 32, r);
 #pragma unroll
                         for (int e = 0; e < 8; ++e) bb[e] = (P.bias && e < nvalid) ? P.bias[col + e] : 0.f;
                     }
@@ -1020,7 +799,6 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
                     __syncwarp();
                 }
             }
-            if (fix) sk_release<Cfg::EPI_WARPS>(P, sk.g_lo, tile0, lane);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) {
@@ -1030,13 +808,12 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
             as ^= 1;
             if (as == 0) aphase ^= 1;
             if (EPI == EPI_F32) {
-                if (!nxt_ready && has_next) tile_rows(ntile, nxt_row, nxt_mask, nxt_frame);
+                if (!nxt_ready && ntile < ntiles) tile_rows(ntile, nxt_row, nxt_mask, nxt_frame);
                 out_row = nxt_row; vmask = nxt_mask; frame_u = nxt_frame;
-            } else if (has_next) {
+            } else if (ntile < ntiles) {
                 tile_rows(ntile, out_row, vmask, frame_u);
             }
         }
-        if (contrib_pending) do_contrib();
     }
     tc_fence_before();
     if constexpr (NCTA == 2) cluster_sync_all();             // no CTA of the pair exits while its peer can still reach its smem / TMEM
@@ -1344,11 +1121,6 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
                     d.ldo % 8 == 0 && (((uintptr_t)d.out | (uintptr_t)d.bias) & 15) == 0;
     const bool bt = tepi_on && d.epi == EPI_BF16 && d.mode == GEMM_LINEAR && d.M % 32 == 0 && d.N % 32 == 0 && d.ldo % 8 == 0 &&
                     (((uintptr_t)d.out | (uintptr_t)d.bias | (uintptr_t)d.residual16) & 15) == 0;
-    // LayerNorm fold: only the thread = row epilogues implement it; the caller reads rs_ok / ln_ok
-    L.rs_ok = d.rowstat_out && bt;
-    L.ln_ok = d.ln_s && d.ln_rowstat && d.ln_slots > 0 && d.ln_slots <= 10 && d.ln_slots % 2 == 0 && d.ln_C > 0 && (bt || gt) && d.bias;
-    if (L.rs_ok) { p.rs_out = d.rowstat_out; p.rs_slots = 2 * p.num_n_tiles; }
-    if (L.ln_ok) { p.ln_s = d.ln_s; p.ln_rs = d.ln_rowstat; p.ln_slots = d.ln_slots; p.ln_inv_c = 1.0f / (float)d.ln_C; p.ln_eps = d.ln_eps; }
     if (bt) {
         p.tepi = 1;
         rc = make_tmap_bf16_chunk(&p.tmOut, d.out, d.M, d.N, d.ldo);
@@ -1375,26 +1147,6 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
         L.smem = L.BN == 160 ? GemmCfg<160, true>::SMEM : GemmCfg<128, true>::SMEM;
     } else {
         L.smem = L.BN == 256 ? GemmCfg<256>::SMEM : (L.BN == 160 ? GemmCfg<160>::SMEM : GemmCfg<128>::SMEM);
-    }
-    // stream-K tail (see SkPlan): staged fp32 / 16-bit epilogues and the 16-bit thread = row epilogue, main loops long enough
-    // that a tile is worth splitting, a tail that leaves at least 20 % of the last wave idle, and at least 4 k-block
-    // iterations per CTA in the tail.  Off under programmatic dependent launch (two GEMMs could share the workspace).
-    // OFF BY DEFAULT (MOCA_GEMM_STREAMK=1 turns it on): measured on the b=2 forward it loses.  The fix-up (contributor dump,
-    // fence, flag, owner's wait and 128 KB reads per contributor) is a serial ~15-20 us at the end of the kernel, more than the
-    // fraction of a 13-150 us wave it saves: 200 tiles x K 1280: 25.1 -> 34.7 us, 225-tile (3,1,1) conv 60.4 -> 74.3 us,
-    // 561-tile 3x3 conv 153.8 -> 166.3 us, forward 41.3 -> 41.9 ms (profiles/README.md, round 2 negative results).
-    {
-        static const int sk_env = [] { const char* e = getenv("MOCA_GEMM_STREAMK"); return e ? atoi(e) : 0; }();
-        static const int sk_mink = [] { const char* e = getenv("MOCA_GEMM_STREAMK_MINK"); return e ? atoi(e) : 16; }();
-        const int kiters = d.ntaps * p.kblocks, G = ctx.num_sms, R = ntiles % G;
-        const bool epi_ok = ncta == 1 && ((d.epi == EPI_F32 && !p.tepi) || (d.epi == EPI_BF16 && (bt || !p.tepi)));
-        p.sk_on = sk_env && pdl_level() == 0 && epi_ok && ctx.d_sk_ws && kiters >= sk_mink && R > 0 && R * 10 <= G * 8 &&
-                  (long long)R * kiters >= 4ll * G;
-        if (p.sk_on) {
-            L.grid = G;
-            p.sk_ws = ctx.d_sk_ws;
-            p.sk_flags = ctx.d_sk_flags;
-        }
     }
     L.flops = 2.0 * (double)d.M * d.N * d.ntaps * d.a_cols;
     if (ncta == 2) {

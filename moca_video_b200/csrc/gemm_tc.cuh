@@ -51,21 +51,6 @@ struct GemmParams {
     const op_t* res16;        // EPI_BF16 only: 16-bit residual [out_rows, ldo] or null (may alias the output: in-place stream update)
     int epi;
     int out16;                // EPI_F32 epilogues: store the result as op_t (outb) instead of fp32; statistics unchanged
-    // LayerNorm folded into the GEMMs around it (16-bit thread = row epilogues only, see gemm_tc.cu):
-    //   producer: rs_out[row][2 nt + half] = {sum, sum of squares} of the stored (rounded) values of the columns this epilogue warp
-    //             wrote for the row (rs_slots slots per row, every slot rewritten by every launch)
-    //   consumer: A holds the raw rows, the weight carries gamma (W' = gamma W), ln_s[n] = sum_k W'[n][k], bias = beta W + b:
-    //             out = rstd (acc - mean ln_s[n]) + bias[n] with mean / rstd of the row from ln_rs (ln_slots slots, C = 1 / ln_inv_c)
-    float2* rs_out;
-    int rs_slots;
-    const float* ln_s;
-    const float2* ln_rs;
-    int ln_slots;
-    float ln_inv_c, ln_eps;
-    // stream-K tail (gemm_tc.cu): the tiles beyond the last full wave are split along K over all CTAs of the grid
-    int sk_on;
-    float* sk_ws;             // [grid][128][BN] fp32 partial accumulators, one slot per contributing CTA
-    unsigned* sk_flags;       // [grid] arrival counters (zero between launches)
     int num_m_tiles, num_n_tiles;
     double* cstat;            // optional per-(frame, output channel) {sum, sum of squares} of the stored fp32 values
     int stat_rpf;             // output rows per frame (frame = out_row / stat_rpf)
@@ -91,13 +76,6 @@ struct GemmDesc {
     int rb_ld = 0, rows_per_frame = 1;
     const float* residual = nullptr;
     const op_t* residual16 = nullptr; // EPI_BF16 only: out = op16(acc + bias + residual16); may alias out
-    // LayerNorm fold (GemmParams): both are honoured only by the thread = row epilogues; gemm_plan reports what it could do in
-    // GemmLaunch::rs_ok / ln_ok and the caller falls back to a separate normalisation pass otherwise
-    float2* rowstat_out = nullptr;    // EPI_BF16 producer: per-row {sum, sumsq} partials, [M][2 * num_n_tiles]
-    const float* ln_s = nullptr;      // EPI_BF16 / EPI_GEGLU consumer: column sums of the gamma-folded weight (packed row order)
-    const float2* ln_rowstat = nullptr;
-    int ln_slots = 0, ln_C = 0;
-    float ln_eps = 1e-5f;
     // EPI_F32 only: accumulate {sum, sumsq} of the stored values into chan_stats[frame][N][2] (doubles, zeroed by the
     // caller) — the GroupNorm that consumes this tensor needs no statistics pass of its own.
     double* chan_stats = nullptr;
@@ -106,7 +84,6 @@ struct GemmDesc {
 };
 
 struct GemmLaunch {
-    bool rs_ok = false, ln_ok = false;   // the requested row statistics are written / the LayerNorm correction is applied
     GemmParams p;
     int BN = 128;
     int grid = 0;

@@ -64,16 +64,6 @@ static PackedW reg_linear(moca_unet* n, const std::string& prefix, int N, int K,
     return w;
 }
 
-// the LayerNorm (gamma, beta) in front of linear layer pw is folded into a second copy of its weight at finalize
-static void reg_fold(moca_unet* n, PackedW& pw, const NormW& ln) {
-    pw.wf = (op_t*)dalloc(n, (size_t)pw.N * pw.taps * pw.Kp * sizeof(op_t));
-    pw.bf = (float*)dalloc(n, (size_t)pw.N * sizeof(float));
-    pw.sf = (float*)dalloc(n, (size_t)pw.N * sizeof(float));
-    FoldJob j;
-    j.w = pw; j.gamma = ln.g; j.beta = ln.b;
-    n->folds.push_back(j);
-}
-
 static void build_res(moca_unet* n, LayerW& L, int te) {
     ResW& r = L.res;
     const std::string& p = L.name;
@@ -123,10 +113,6 @@ static void build_tf(moca_unet* n, LayerW& L, bool spatial, int heads, int inner
     t.out2 = reg_linear(n, b + ".attn2.to_out.0", inner, inner, 1, true);
     t.ff1 = reg_linear(n, b + ".ff.net.0.proj", 8 * inner, inner, 1, true, 256);
     t.ff2 = reg_linear(n, b + ".ff.net.2", inner, 4 * inner, 1, true);
-    // norm1 -> attn1 q|k|v, norm2 -> attn2 q (spatial) or q|k|v (temporal), norm3 -> GEGLU projection
-    reg_fold(n, t.qkv1, t.ln1);
-    if (spatial) reg_fold(n, t.q2, t.ln2); else reg_fold(n, t.qkv2, t.ln2);
-    reg_fold(n, t.ff1, t.ln3);
 }
 
 static bool has(const std::vector<int>& v, int x) {
@@ -420,42 +406,10 @@ extern "C" int32_t moca_unet_load_many(moca_unet* n, int32_t count, const char* 
     return MOCA_OK;
 }
 
-// LayerNorm fold: one warp per packed weight row (rows are in packed order, so the GEGLU row permutation carries over)
-__global__ void fold_ln_kernel(const op_t* __restrict__ w, const float* __restrict__ b, const float* __restrict__ gamma,
-                               const float* __restrict__ beta, int N, int K, int Kp, op_t* __restrict__ wf, float* __restrict__ bf,
-                               float* __restrict__ sf) {
-    const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-    if (row >= N) return;
-    float s = 0.f, bb = 0.f;
-    for (int k = lane; k < Kp; k += 32) {
-        float wk = 0.f, wg = 0.f;
-        if (k < K) {
-            wk = op2float(w[(size_t)row * Kp + k]);
-            const op_t h = float2op(wk * gamma[k]);
-            wf[(size_t)row * Kp + k] = h;
-            wg = op2float(h);
-            bb = fmaf(beta[k], wk, bb);
-        } else {
-            wf[(size_t)row * Kp + k] = float2op(0.f);
-        }
-        s += wg;
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) { s += __shfl_xor_sync(0xffffffffu, s, o); bb += __shfl_xor_sync(0xffffffffu, bb, o); }
-    if (lane == 0) { sf[row] = s; bf[row] = bb + (b ? b[row] : 0.f); }
-}
-
 extern "C" int32_t moca_unet_finalize(moca_unet* n) {
     MOCA_REQUIRE(n, MOCA_E_ARG, "moca_unet_finalize: NULL");
     for (auto& kv : n->slots)
         MOCA_REQUIRE(kv.second.loaded, MOCA_E_STATE, "moca_unet_finalize: parameter '%s' was never loaded", kv.first.c_str());
-    // (re)build the LayerNorm-folded copies from the weights as loaded (idempotent: safe after a partial reload)
-    if (!n->dry) {
-        for (const FoldJob& j : n->folds) {
-            fold_ln_kernel<<<cdiv(j.w.N, 8), 256>>>(j.w.w, j.w.b, j.gamma, j.beta, j.w.N, j.w.K, j.w.Kp, j.w.wf, j.w.bf, j.w.sf);
-            MOCA_LAUNCH_CHECK();
-        }
-    }
     MOCA_CHECK_CUDA(cudaDeviceSynchronize());
     n->finalized = true;
     return MOCA_OK;

@@ -21,17 +21,6 @@ struct PackedW {               // op_t [N, taps*Kp]
     op_t* w = nullptr;
     float* b = nullptr;        // fp32 [N] or null
     int N = 0, K = 0, Kp = 0, taps = 1;
-    // LayerNorm folded into this linear layer (moca_unet_finalize): wf = op_t(w * gamma[k]), sf[n] = sum_k wf[n][k],
-    // bf[n] = b[n] + sum_k beta[k] * w[n][k]; the plan feeds wf / bf / sf to the GEMM (gemm_tc.cuh)
-    op_t* wf = nullptr;
-    float* bf = nullptr;
-    float* sf = nullptr;
-};
-
-struct FoldJob {               // one LayerNorm -> Linear pair
-    PackedW w;
-    const float* gamma = nullptr;
-    const float* beta = nullptr;
 };
 
 struct NormW {
@@ -99,7 +88,6 @@ struct moca_unet {
     moca::NormW gn_out;
     int n_emb = 0, n_kv = 0;
     std::unordered_map<std::string, moca::LoadSlot> slots;
-    std::vector<moca::FoldJob> folds;
     std::vector<void*> allocs;
     bool finalized = false;
     bool dry = false;

@@ -54,7 +54,7 @@ struct Act {
     StatSrc st;               // GroupNorm statistics material left by the GEMM epilogue that wrote p
 };
 
-enum ScratchId { S_PAD = 0, S_RAW, S_LIN, S_QKV, S_ATT, S_FFH, S_F32A, S_F32B, S_Y, S_RS, S_COUNT };
+enum ScratchId { S_PAD = 0, S_RAW, S_LIN, S_QKV, S_ATT, S_FFH, S_F32A, S_F32B, S_Y, S_COUNT };
 
 struct Builder {
     moca_unet* net;
@@ -107,52 +107,35 @@ struct Builder {
     }
 
     // ---- GEMM flavours -------------------------------------------------------------------------------------
-    // returns what the planned launch does about the LayerNorm fold (rs_ok / ln_ok / number of N tiles); in a dry run it
-    // assumes the fused path
-    GemmLaunch gemm(GemmDesc d, double useful_flops) {
-        GemmLaunch L;
-        L.rs_ok = d.rowstat_out != nullptr; L.ln_ok = d.ln_s != nullptr;
+    void gemm(GemmDesc d, double useful_flops) {
         plan->launches += 1;
         plan->flops += useful_flops;
-        if (dry || rc) return L;
+        if (dry || rc) return;
+        GemmLaunch L;
         int r = gemm_plan(net->ctx->c, d, &L);
-        if (r) { fail(r); return L; }
+        if (r) { fail(r); return; }
         char buf[192];
         snprintf(buf, sizeof(buf), "gemm M=%d N=%d K=%d taps=%d BN=%d tiles=%d epi=%d mode=%d", d.M, d.N, d.a_cols, d.ntaps, L.BN,
                  L.p.num_m_tiles * L.p.num_n_tiles, d.epi, d.mode);
         raw_push([L](cudaStream_t st) { return gemm_run(L, st); }, buf, useful_flops);
-        return L;
     }
-    struct LnFold {                  // LayerNorm folded around a linear layer (gemm_tc.cuh)
-        float2* rowstat_out = nullptr;          // producer: write the per-row partial sums here
-        const float2* rowstat = nullptr;        // consumer: read them from here (slots per row, row width C) ...
-        int slots = 0, C = 0;
-        bool folded_only = false;               // ... or: input already normalised, only use the gamma / beta folded weight and bias
-    };
-    GemmLaunch linear(const op_t* A, int64_t rows, int K, const PackedW& w, int epi, void* out, int ldo, const float* residual,
-                      int n_override = 0, const StatSrc* ss = nullptr, int rpf = 0, const op_t* residual16 = nullptr,
-                      const LnFold* ln = nullptr) {
+    void linear(const op_t* A, int64_t rows, int K, const PackedW& w, int epi, void* out, int ldo, const float* residual,
+                int n_override = 0, const StatSrc* ss = nullptr, int rpf = 0, const op_t* residual16 = nullptr) {
         GemmDesc d;
         d.A = A; d.a_rows = rows; d.a_cols = K; d.a_pitch = K;
         d.Wt = w.w; d.N = n_override ? n_override : w.N; d.ntaps = 1; d.Kp = w.Kp;
         d.mode = GEMM_LINEAR; d.M = (int)rows; d.epi = epi; d.out = out; d.ldo = ldo; d.bias = w.b; d.residual = residual; d.residual16 = residual16;
         if (ss) { d.chan_stats = (double*)ss->cs; d.stat_rows_per_frame = ss->rows; }
         d.stat_sample_rows = T * rpf;
-        if (ln && ln->rowstat_out) d.rowstat_out = ln->rowstat_out;
-        if (ln && (ln->rowstat || ln->folded_only)) { d.Wt = w.wf; d.bias = w.bf; }
-        if (ln && ln->rowstat) {
-            // the input rows are raw: gamma lives in the folded weight, beta in the folded bias, mean / rstd in the epilogue
-            d.ln_s = w.sf; d.ln_rowstat = ln->rowstat; d.ln_slots = ln->slots; d.ln_C = ln->C;
-            if (!dry && !rc) {
-                GemmLaunch probe;                          // does this shape get a thread = row epilogue?
-                if (gemm_plan(net->ctx->c, d, &probe) != MOCA_OK || !probe.ln_ok) { GemmLaunch no; no.ln_ok = false; return no; }
-            }
-        }
-        return gemm(d, 2.0 * rows * d.N * K);
+        gemm(d, 2.0 * rows * d.N * K);
     }
     // 3x3 conv of the 16-bit operand `src`: unpadded tokens [NF, H, W, Cin] through the 4-D tensor map when the geometry allows
     // (conv_dst / conv4d tell the producer of src which layout to write), else the zero-bordered [NF, H+2, W+2, Cin] buffer
-    bool conv4d(int H, int W, int stride) const { return conv4d_supported(NF, H, W, stride); }
+    // (at 5x8 the unpadded matrix has 10 M tiles: fewer CTAs than SMs and slower than the 18 padded ones, 83 vs 69 us measured;
+    // the stride-2 convolutions always win by not computing the dropped rows)
+    bool conv4d(int H, int W, int stride) const {
+        return conv4d_supported(NF, H, W, stride) && (stride == 2 || (int64_t)NF * H * W >= 4096);
+    }
     int conv_dst(int H, int W, int stride) const { return conv4d(H, W, stride) ? DST_LINEAR : DST_SPATIAL_PAD; }
     void conv3x3(const op_t* src, int H, int W, int Cin, const PackedW& w, int stride, void* out, const float* rowbias,
                  int rb_ld, const float* residual, const StatSrc* ss, int out16 = 0) {
@@ -224,23 +207,8 @@ struct Builder {
         a.NF = NF; a.H = H; a.W = W; a.B = B; a.T = T; a.HW = H * W; a.dst = dst;
         push([=](cudaStream_t st) { return gn_apply(a, st); }, 1, "convert rows=" + std::to_string(rows) + " C=" + std::to_string(C) + " dst=" + std::to_string(dst_mode));
     }
-    // LayerNorm(y) -> Linear(w), y the 16-bit stream whose producer `prod` was asked for row statistics (rs).  Fused: the GEMM
-    // reads the raw rows and normalises in its epilogue (LnFold).  Otherwise (no thread = row epilogue for one of the two
-    // shapes, or MOCA_LN_FOLD=0): a plain (x - mean) * rstd pass into `lin`, then the same folded weight and bias.
-    void ln_linear(const op_t* y, const GemmLaunch& prod, float2* rs, int64_t rows, int I, const PackedW& w, int epi, void* out,
-                   int ldo, op_t* lin) {
-        static const int fold_on = [] { const char* e = getenv("MOCA_LN_FOLD"); return e ? atoi(e) : 1; }();
-        if (fold_on && prod.rs_ok) {
-            LnFold f;
-            f.rowstat = rs; f.slots = dry ? 2 : 2 * prod.p.num_n_tiles; f.C = I;
-            const GemmLaunch L = linear(y, rows, I, w, epi, out, ldo, nullptr, 0, nullptr, 0, nullptr, &f);
-            if (L.ln_ok) return;
-        }
-        push([=](cudaStream_t st) { return layernorm_op16_in16(y, nullptr, nullptr, rows, I, lin, st); }, 1,
-             "layernorm rows=" + std::to_string(rows) + " C=" + std::to_string(I));
-        LnFold f;
-        f.folded_only = true;
-        linear(lin, rows, I, w, epi, out, ldo, nullptr, 0, nullptr, 0, nullptr, &f);
+    void lnorm(const op_t* x, const NormW& w, int64_t rows, int C, op_t* out) {
+        push([=](cudaStream_t st) { return layernorm_op16_in16(x, w.g, w.b, rows, C, out, st); }, 1, "layernorm rows=" + std::to_string(rows) + " C=" + std::to_string(C));
     }
     void tap(const std::string& name, const Act& a) {
         if (!plan->with_taps) return;
@@ -330,11 +298,7 @@ void Builder::transformer(const LayerW& L, Act& x, const op_t* kv, int kv_ld) {
     op_t* y = scratch<op_t>(S_Y, (size_t)rows * I);
     // norm (GroupNorm eps 1e-6; spatial: per frame, temporal: 5-D input so statistics span all T frames)
     gnorm(x.p, x.st, C, nullptr, StatSrc(), 0, rows, t.spatial ? HW : T * HW, t.gn, 1e-6f, 0, DST_LINEAR, H, W, lin, nullptr);
-    // per-row {sum, sumsq} partials of y written by the GEMM that produced it, read by the GEMM behind the next LayerNorm
-    float2* rs = scratch<float2>(S_RS, (size_t)rows * 2 * ((I + 127) / 128));
-    LnFold rs_out;
-    rs_out.rowstat_out = rs;
-    GemmLaunch prod = linear(lin, rows, C, t.proj_in, EPI_BF16, y, I, nullptr, 0, nullptr, 0, nullptr, &rs_out);
+    linear(lin, rows, C, t.proj_in, EPI_BF16, y, I, nullptr);
 
     AttnArgs self;
     self.q = qkv; self.k = qkv + I; self.v = qkv + 2 * I; self.ldq = 3 * I; self.ldkv = 3 * I;
@@ -359,12 +323,14 @@ void Builder::transformer(const LayerW& L, Act& x, const op_t* kv, int kv_ld) {
     };
 
     // attn1: self-attention
-    ln_linear(y, prod, rs, rows, I, t.qkv1, EPI_BF16, qkv, 3 * I, lin);
+    lnorm(y, t.ln1, rows, I, lin);
+    linear(lin, rows, I, t.qkv1, EPI_BF16, qkv, 3 * I, nullptr);
     push(run_self, 1, "attn_self", attn_flops); plan->flops += attn_flops;
-    prod = linear(att, rows, I, t.out1, EPI_BF16, y, I, nullptr, 0, nullptr, 0, y, &rs_out);
+    linear(att, rows, I, t.out1, EPI_BF16, y, I, nullptr, 0, nullptr, 0, y);
     // attn2: cross-attention on the text context (spatial) or a second self-attention (temporal_selfatt_only, attention.py:313-314)
+    lnorm(y, t.ln2, rows, I, lin);
     if (t.spatial) {
-        ln_linear(y, prod, rs, rows, I, t.q2, EPI_BF16, qkv, I, lin);
+        linear(lin, rows, I, t.q2, EPI_BF16, qkv, I, nullptr);
         AttnArgs ca;
         ca.q = qkv; ca.ldq = I; ca.qmap = self.qmap;
         ca.k = kv; ca.v = kv + I; ca.ldkv = kv_ld;
@@ -378,12 +344,13 @@ void Builder::transformer(const LayerW& L, Act& x, const op_t* kv, int kv_ld) {
         push([=](cudaStream_t st) { return ca_tc ? attention_tc_run(ca_l, st) : attention_flash(ca, st); }, 1, "attn_cross", 4.0 * (double)NF * t.heads * HW * Lmax * 64.0);
         plan->flops += 4.0 * (double)NF * t.heads * HW * Lmax * 64.0;
     } else {
-        ln_linear(y, prod, rs, rows, I, t.qkv2, EPI_BF16, qkv, 3 * I, lin);
+        linear(lin, rows, I, t.qkv2, EPI_BF16, qkv, 3 * I, nullptr);
         push(run_self, 1, "attn_self", attn_flops); plan->flops += attn_flops;
     }
-    prod = linear(att, rows, I, t.out2, EPI_BF16, y, I, nullptr, 0, nullptr, 0, y, &rs_out);
+    linear(att, rows, I, t.out2, EPI_BF16, y, I, nullptr, 0, nullptr, 0, y);
     // feed-forward: Linear(C -> 8C) with the GEGLU gate fused into the GEMM epilogue, Linear(4C -> C) + residual
-    ln_linear(y, prod, rs, rows, I, t.ff1, EPI_GEGLU, ffh, 4 * I, lin);
+    lnorm(y, t.ln3, rows, I, lin);
+    linear(lin, rows, I, t.ff1, EPI_GEGLU, ffh, 4 * I, nullptr);
     linear(ffh, rows, 4 * I, t.ff2, EPI_BF16, y, I, nullptr, 0, nullptr, 0, y);
     // proj_out + x_in (reads the 16-bit stream directly)
     x.st = stat_alloc(C, HW);

@@ -60,9 +60,7 @@ def test_loader_expects_reference_state_dict(built):
     listing = "\n".join(f"{k} {tuple(v)}" for k, v in sorted(shapes.items()))
     assert hashlib.sha256(listing.encode()).hexdigest() == str(g["shapes_sha256"])
     assert int(g["n_tensors"]) == len(exp) == 1484
-    # packed 16-bit weights + fp32 norms / biases, plus the LayerNorm-folded second copy of the three projections that follow a
-    # LayerNorm in every transformer block (attn1 q|k|v, attn2 q or q|k|v, GEGLU): between 1.0x and 1.25x of 2 bytes / parameter
-    assert 0.99 < u.weight_bytes() / (2 * int(g["n_params"])) < 1.25
+    assert abs(u.weight_bytes() - 2 * int(g["n_params"])) / (2 * int(g["n_params"])) < 0.01     # packed 16-bit + fp32 norms/biases
     small = UNet3D(model_channels=64, context_dim=64, _listing_only=True)
     assert small.expected_params() == {k: int(np.prod(v)) for k, v in param_shapes(UNetConfig(model_channels=64, context_dim=64)).items()}
 
