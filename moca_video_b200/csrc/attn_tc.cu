@@ -263,10 +263,12 @@ __global__ void __launch_bounds__(kThreads, 2) attn_tc_kernel(const __grid_const
 // pipe runs the MMAs of tile B and vice versa.
 namespace {
 constexpr int kThreads2 = 320;
-constexpr int kStages2 = 3;
-// smem: Q_A | Q_B | K[3] | V[3] | P_A (2 halves) | P_B (2 halves) | barriers
+constexpr int kStages2 = 2;
+// smem: Q_A | Q_B | K[2] | V[2] | P_A[2 buffers][2 halves] | P_B[2][2] | barriers.  P is double-buffered: the softmax threads write
+// P_X(j) while P_X(j-1) V is still in the tensor pipe (with one buffer 18 % of their samples were the wait for that MMA,
+// profiles/r02_attn2_ncu.txt); the K / V rings give up one stage each for it.
 constexpr int kOff2Q = 0, kOff2K = 2 * kTileBytes, kOff2V = kOff2K + kStages2 * kTileBytes, kOff2P = kOff2V + kStages2 * kTileBytes,
-              kOff2Bar = kOff2P + 4 * kTileBytes;
+              kOff2Bar = kOff2P + 8 * kTileBytes;
 constexpr size_t kSmem2 = (size_t)kOff2Bar + 256 + 1024;
 constexpr float kRescaleLog2 = 8.0f;
 }  // namespace
@@ -283,8 +285,8 @@ __global__ void __launch_bounds__(kThreads2, 1) attn_tc2_kernel(const __grid_con
     uint64_t* s_full = bars + 13;     // [2] S_X(j) is in TMEM
     uint64_t* s_free = bars + 15;     // [2] S_X(j) has been read into registers
     uint64_t* p_full = bars + 17;     // [2] P_X(j) is in smem (and O_X rescaled if needed)
-    uint64_t* o_done = bars + 19;     // [2] P_X(j) V_j has been accumulated
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 21);
+    uint64_t* o_done = bars + 19;     // [2 tiles][2 buffers] P_X(j) V_j has been accumulated (barrier [x][j & 1]: one completion per two key tiles)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 23);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int o = blockIdx.y / P.heads, h = blockIdx.y - o * P.heads;
@@ -301,7 +303,7 @@ __global__ void __launch_bounds__(kThreads2, 1) attn_tc2_kernel(const __grid_con
         }
         for (int x = 0; x < 2; ++x) {
             mbar_init(&s_full[x], 1); mbar_init(&s_free[x], 4);
-            mbar_init(&p_full[x], 4); mbar_init(&o_done[x], 1);
+            mbar_init(&p_full[x], 4); mbar_init(&o_done[2 * x], 1); mbar_init(&o_done[2 * x + 1], 1);
         }
         fence_mbar_init();
     }
@@ -371,7 +373,7 @@ __global__ void __launch_bounds__(kThreads2, 1) attn_tc2_kernel(const __grid_con
                     mbar_wait(&p_full[x], ph);
                     tc_fence_after();
                     const uint32_t t_o = tmem_base + (uint32_t)(256 + x * 64);
-                    const uint32_t pb = smem_u32(base + kOff2P + x * 2 * kTileBytes);
+                    const uint32_t pb = smem_u32(base + kOff2P + (x * 2 + (j & 1)) * 2 * kTileBytes);
                     const uint32_t vb = smem_u32(base + kOff2V + (j % kStages2) * kTileBytes);
 #pragma unroll
                     for (int k = 0; k < kTileK / 16; ++k) {
@@ -379,7 +381,7 @@ __global__ void __launch_bounds__(kThreads2, 1) attn_tc2_kernel(const __grid_con
                         const uint64_t dv = umma_desc_sw128(vb + k * 2048);
                         umma_bf16(t_o, dp, dv, idesc_pv, (uint32_t)((j | k) != 0));
                     }
-                    umma_commit(&o_done[x]);
+                    umma_commit(&o_done[2 * x + (j & 1)]);
                 }
                 umma_commit(&v_empty[j % kStages2]);
             }
@@ -391,7 +393,7 @@ __global__ void __launch_bounds__(kThreads2, 1) attn_tc2_kernel(const __grid_con
             const int row = wq * 32 + lane;
             const uint32_t t_lane = tmem_base + ((uint32_t)(wq * 32) << 16);
             const uint32_t t_s = t_lane + (uint32_t)(x * 128), t_o = t_lane + (uint32_t)(256 + x * 64);
-            uint8_t* prow = base + kOff2P + x * 2 * kTileBytes + row * 128;        // this row inside either 64-key half of P_X
+            uint8_t* prow0 = base + kOff2P + x * 4 * kTileBytes + row * 128;       // this row inside either 64-key half of P_X, buffer 0
             float m_ref = -INFINITY, l = 0.f;
             for (int j = 0; j < ntiles; ++j) {
                 const uint32_t ph = (uint32_t)(j & 1);
@@ -417,8 +419,9 @@ __global__ void __launch_bounds__(kThreads2, 1) attn_tc2_kernel(const __grid_con
                 const float mx = fmaxf(fmaxf(fmaxf(mxp[0], mxp[1]), fmaxf(mxp[2], mxp[3])), fmaxf(fmaxf(mxp[4], mxp[5]), fmaxf(mxp[6], mxp[7])));
                 // the reference maximum moves only when some row of the warp outgrew it by 2^8 (first tile: always)
                 const bool grow = (mx - m_ref) * P.scale_log2 > kRescaleLog2;
-                if (j > 0) {
-                    mbar_wait(&o_done[x], ph ^ 1u);                        // P_X(j-1) V has been accumulated: P_X smem and O_X are ours
+                uint8_t* prow = prow0 + (j & 1) * 2 * kTileBytes;
+                if (j >= 2) {
+                    mbar_wait(&o_done[2 * x + (j & 1)], (uint32_t)(((j >> 1) - 1) & 1));      // P_X(j-2) V is done: this P buffer is ours
                     tc_fence_after();
                 }
                 if (__any_sync(0xffffffffu, grow)) {
@@ -427,6 +430,8 @@ __global__ void __launch_bounds__(kThreads2, 1) attn_tc2_kernel(const __grid_con
                     m_ref = m_new;
                     l *= alpha;
                     if (j > 0) {
+                        mbar_wait(&o_done[2 * x + ((j - 1) & 1)], (uint32_t)(((j - 1) >> 1) & 1));   // P_X(j-1) V is done: O_X is ours
+                        tc_fence_after();
 #pragma unroll 1
                         for (int c = 0; c < 8; ++c) {                      // rare path: 8 columns at a time keeps the 128 scores in registers
                             uint32_t ov[8];
@@ -465,7 +470,7 @@ __global__ void __launch_bounds__(kThreads2, 1) attn_tc2_kernel(const __grid_con
                 if (lane == 0) mbar_arrive(&p_full[x]);
             }
             // epilogue: O_X / l -> bf16
-            mbar_wait(&o_done[x], (uint32_t)((ntiles - 1) & 1));
+            mbar_wait(&o_done[2 * x + ((ntiles - 1) & 1)], (uint32_t)(((ntiles - 1) >> 1) & 1));
             tc_fence_after();
             const int qr = q0 + x * kTileQ + row;
             const float inv = 1.0f / l;
