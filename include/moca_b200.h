@@ -189,6 +189,20 @@ int64_t moca_unet_workspace_bytes(moca_unet* net);
 int64_t moca_unet_profile(moca_unet* net, int32_t iters, char* buf, int64_t cap, void* stream);
 int64_t moca_unet_weight_bytes(moca_unet* net);
 
+/* ---- first-stage decoder: AutoencoderKL.decode (lvdm/models/autoencoder.py:104-107) = post_quant_conv + Decoder
+ * (lvdm/modules/networks/ae_modules.py:466-578: conv_in, mid ResnetBlock :151-210 / AttnBlock :26-78 / ResnetBlock, the up levels
+ * with nearest x2 Upsample :103-116, norm_out, SiLU, conv_out), called per frame by decode_first_stage_2DAE (ddpm3d.py:555-562).
+ * moca_vae_create: the yaml's ddconfig integers (configs/inference_t2v_512_v2.0.yaml:60-72); ctx == NULL lists parameters only.
+ *   The handle is a moca_unet: moca_unet_load / _load_many / _finalize / _destroy / _param_* / _launches / _flops / _profile apply,
+ *   with the first_stage_model state_dict keys ("post_quant_conv.weight", "decoder.mid.attn_1.q.weight", ...); encoder and
+ *   quant_conv keys are not part of the decode path and are not expected.
+ * moca_vae_decode: z [B, z_channels, H, W] fp32 latents as the sampler leaves them; the library applies 1 / scale_factor
+ *   (ddpm3d.py:559) and writes image [B, out_ch, H * 2^(n_mult-1), W * 2^(n_mult-1)] fp32.  B <= 16 frames per call. */
+int32_t moca_vae_create(moca_ctx* ctx, int32_t ch, const int32_t* ch_mult, int32_t n_mult, int32_t num_res_blocks,
+                        int32_t z_channels, int32_t out_ch, moca_unet** out);
+int32_t moca_vae_decode(moca_unet* vae, const float* z, int32_t B, int32_t H, int32_t W, float scale_factor, float* image,
+                        void* stream);
+
 /* ---- primitives exposed for unit parity tests (tests/test_gpu_ops.py): the same kernels the UNet plan launches ----
  * moca_gemm_op16: D[M,N] = A[M,K] * W[N,K]^T (+bias[N]) on the tcgen05 core; A, W op16 (moca_operand_dtype) row-major (K contiguous),
  *   D fp32 or op16 (out_op16).  K % 64 == 0.                                    (nn.Linear, attention.py:54-57)

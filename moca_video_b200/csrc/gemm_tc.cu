@@ -179,7 +179,8 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
                 const int mt = MT(tile), nt = tile % P.num_n_tiles;
                 // GEMM_SPATIAL_4D: first frame / first input image row of the tile
                 const int c4_fg = P.mode == GEMM_SPATIAL_4D ? mt / P.c4_th : 0;
-                const int c4_f0 = c4_fg * P.c4_bf, c4_h0 = (mt - c4_fg * P.c4_th) * P.c4_bh * P.stride;
+                const int c4_t = mt - c4_fg * P.c4_th, c4_hq = c4_t / P.c4_tw;       // c4_tw > 1: 128-pixel segments of wide rows
+                const int c4_f0 = c4_fg * P.c4_bf, c4_h0 = c4_hq * P.c4_bh * P.stride, c4_w0 = (c4_t - c4_hq * P.c4_tw) * kBM;
                 for (int tap = 0; tap < P.ntaps; ++tap) {
                     const int arow = mt * kBM + P.tap_shift[tap];
                     const int dy = tap / 3, dx = tap - dy * 3;
@@ -188,7 +189,7 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
                         uint8_t* sa = base + (size_t)stage * Cfg::STAGE_BYTES;
                         if (NCTA == 1 && P.mode == GEMM_SPATIAL_4D) {
                             mbar_expect_tx(&full[stage], Cfg::STAGE_BYTES);
-                            tma_load_4d(sa, &P.tmA, &full[stage], kb * kBK, dx - 1, c4_h0 + dy - 1, c4_f0);
+                            tma_load_4d(sa, &P.tmA, &full[stage], kb * kBK, c4_w0 + dx - 1, c4_h0 + dy - 1, c4_f0);
                             tma_load_2d(sa + kABytes, &P.tmB, &full[stage], tap * P.Kp + kb * kBK, nt * BN);
                         } else if constexpr (NCTA == 2) {
                             // both CTAs load their A rows and their half of the B rows; all bytes are counted on the leader's barrier
@@ -873,7 +874,13 @@ static bool conv4d_geometry(int NF, int H, int W, int stride, int* bh, int* bf) 
     if (stride != 1 && stride != 2) return false;
     if (H % stride || W % stride) return false;
     const int Ho = H / stride, Wo = W / stride;
-    if (Wo < 1 || Wo > 128 || (Wo & (Wo - 1)) != 0) return false;
+    if (Wo > 128) {
+        // wide images: an M tile is 128 consecutive pixels of one image row (*bh = 1, *bf = 1, Wo / 128 tiles per row)
+        if (stride != 1 || Wo % 128 != 0) return false;
+        *bh = 1; *bf = 1;
+        return true;
+    }
+    if (Wo < 1 || (Wo & (Wo - 1)) != 0) return false;
     int best = 0;
     for (int h = 1; h <= Ho && Wo * h <= 128; ++h)
         if (Ho % h == 0 && 128 % (Wo * h) == 0) best = h;
@@ -897,7 +904,7 @@ static int make_tmap_conv4d(CUtensorMap* tm, const void* ptr, int NF, int H, int
     const int Wo = W / stride;
     cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)NF};
     cuuint64_t strides[3] = {(cuuint64_t)pitch * 2, (cuuint64_t)W * pitch * 2, (cuuint64_t)H * W * pitch * 2};
-    cuuint32_t box[4] = {64, (cuuint32_t)(Wo * stride), (cuuint32_t)(bh * stride), (cuuint32_t)bf};
+    cuuint32_t box[4] = {64, (cuuint32_t)((Wo > 128 ? 128 : Wo) * stride), (cuuint32_t)(bh * stride), (cuuint32_t)bf};
     cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
     CUresult r = enc(tm, MOCA_TMAP_OP16, 4, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                      CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -1085,9 +1092,15 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
     p.M = d.M; p.N = d.N; p.ntaps = d.ntaps; p.Kp = d.Kp; p.kblocks = d.Kp / 64;
     for (int i = 0; i < 9; ++i) p.tap_shift[i] = d.tap_shift[i];
     p.mode = d.mode; p.g_rows = d.g_rows; p.g_w = d.g_w; p.g_H = d.g_H; p.g_W = d.g_W; p.stride = d.stride;
+    p.c4_tw = 1;
     if (d.mode == GEMM_SPATIAL_4D) {
         p.g_H = d.g_H / d.stride; p.g_W = d.g_W / d.stride;            // output image size from here on
-        p.c4_bh = c4_bh; p.c4_bf = c4_bf; p.c4_th = p.g_H / c4_bh;
+        p.c4_bh = c4_bh; p.c4_bf = c4_bf; p.c4_th = p.g_H / c4_bh; p.c4_tw = 1;
+        if (p.g_W > 128) {
+            // wide rows: the output rows of a tile are consecutive, which map_row reproduces for an image of 128-pixel rows
+            p.c4_tw = p.g_W / 128; p.c4_th = p.g_H * p.c4_tw;
+            p.g_H = p.c4_th; p.g_W = 128;
+        }
     }
     p.outf = (float*)d.out; p.outb = (op_t*)d.out; p.ldo = d.ldo;
     p.bias = d.bias; p.rowbias = d.rowbias; p.rb_ld = d.rb_ld; p.rows_per_frame = d.rows_per_frame > 0 ? d.rows_per_frame : 1;

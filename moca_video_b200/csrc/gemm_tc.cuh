@@ -40,7 +40,7 @@ struct GemmParams {
     int g_w;                  // SPATIAL: W+2           TIME: HW
     int g_H, g_W;             // SPATIAL: H, W          TIME: g_H = T
     int stride;               // SPATIAL: 1 or 2 (Downsample)
-    int c4_bh, c4_bf, c4_th;  // SPATIAL_4D: output image rows / frames per M tile, M tiles per frame group (Ho / bh); g_H, g_W = Ho, Wo
+    int c4_bh, c4_bf, c4_th, c4_tw;  // SPATIAL_4D: output image rows / frames per M tile, M tiles per frame group (Ho / bh); g_H, g_W = Ho, Wo
     float* outf;
     op_t* outb;
     int ldo;                  // output row pitch (elements)

@@ -302,7 +302,73 @@ __global__ void __launch_bounds__(256) load_many_kernel(const LoadJob* __restric
     }
 }
 
+// AutoencoderKL decode path: post_quant_conv (autoencoder.py:104-107) + Decoder (ae_modules.py:466-578), names as in the
+// first_stage_model state_dict.
+static VaeResW build_vae_res(moca_unet* n, const std::string& p, int cin, int cout) {
+    VaeResW r;
+    r.cin = cin; r.cout = cout;
+    r.n1 = reg_norm(n, p + ".norm1", cin);
+    r.conv1 = reg_linear(n, p + ".conv1", cout, cin, 9, true);
+    r.n2 = reg_norm(n, p + ".norm2", cout);
+    r.conv2 = reg_linear(n, p + ".conv2", cout, cout, 9, true);
+    r.has_nin = cin != cout;
+    if (r.has_nin) r.nin = reg_linear(n, p + ".nin_shortcut", cout, cin, 1, true);
+    return r;
+}
+
+static void build_vae_arch(moca_unet* n) {
+    VaeW& v = n->vae;
+    const int L = (int)v.mult.size();
+    int block_in = v.ch * v.mult[L - 1];
+    v.pq_w = reg_f32(n, "post_quant_conv.weight", (int64_t)v.zc * v.zc);
+    v.pq_b = reg_f32(n, "post_quant_conv.bias", v.zc);
+    v.conv_in = reg_linear(n, "decoder.conv_in", block_in, v.zc, 9, true);
+    v.mid1 = build_vae_res(n, "decoder.mid.block_1", block_in, block_in);
+    v.attn_norm = reg_norm(n, "decoder.mid.attn_1.norm", block_in);
+    v.aq = reg_linear(n, "decoder.mid.attn_1.q", block_in, block_in, 1, true);
+    v.ak = reg_linear(n, "decoder.mid.attn_1.k", block_in, block_in, 1, true);
+    v.av = reg_linear(n, "decoder.mid.attn_1.v", block_in, block_in, 1, true);
+    v.aproj = reg_linear(n, "decoder.mid.attn_1.proj_out", block_in, block_in, 1, true);
+    v.mid2 = build_vae_res(n, "decoder.mid.block_2", block_in, block_in);
+    v.up.resize(L);
+    v.upconv.resize(L);
+    for (int lvl = L - 1; lvl >= 0; --lvl) {
+        const int block_out = v.ch * v.mult[lvl];
+        for (int j = 0; j <= v.nres; ++j) {
+            v.up[lvl].push_back(build_vae_res(n, "decoder.up." + std::to_string(lvl) + ".block." + std::to_string(j), block_in, block_out));
+            block_in = block_out;
+        }
+        if (lvl != 0) v.upconv[lvl] = reg_linear(n, "decoder.up." + std::to_string(lvl) + ".upsample.conv", block_in, block_in, 9, true);
+    }
+    v.norm_out = reg_norm(n, "decoder.norm_out", block_in);
+    v.conv_out = reg_linear(n, "decoder.conv_out", v.out_ch, block_in, 9, true);
+}
+
 }  // namespace moca
+
+// VAE decoder object: the same handle type and the same moca_unet_load / _load_many / _finalize / _destroy / _param_* calls as the
+// UNet; moca_vae_decode (unet_plan.cu) runs it.  ch / ch_mult / num_res_blocks / z_channels / out_ch: the yaml's ddconfig.
+extern "C" int32_t moca_vae_create(moca_ctx* ctx, int32_t ch, const int32_t* ch_mult, int32_t n_mult, int32_t num_res_blocks,
+                                   int32_t z_channels, int32_t out_ch, moca_unet** out) {
+    MOCA_REQUIRE(out && ch_mult && n_mult >= 1 && n_mult <= 6, MOCA_E_ARG, "moca_vae_create: bad argument");
+    MOCA_REQUIRE(ch > 0 && ch % 64 == 0 && z_channels >= 1 && z_channels <= 16 && out_ch >= 1 && out_ch <= 4 && num_res_blocks >= 1, MOCA_E_SHAPE,
+                 "moca_vae_create: ch %d must be a multiple of 64 (one GEMM k-block), z_channels <= 16, out_ch <= 4", ch);
+    for (int i = 0; i < n_mult; ++i) MOCA_REQUIRE(ch_mult[i] >= 1, MOCA_E_SHAPE, "moca_vae_create: ch_mult[%d] = %d", i, ch_mult[i]);
+    moca_unet* n = new moca_unet();
+    n->ctx = ctx;
+    n->dry = (ctx == nullptr);
+    n->vae.present = true;
+    n->vae.ch = ch; n->vae.zc = z_channels; n->vae.out_ch = out_ch; n->vae.nres = num_res_blocks;
+    n->vae.mult.assign(ch_mult, ch_mult + n_mult);
+    build_vae_arch(n);
+    for (void* p : n->allocs)
+        if (!p) {
+            set_error("moca_vae_create: device allocation failed");
+            return MOCA_E_CUDA;
+        }
+    *out = n;
+    return MOCA_OK;
+}
 
 extern "C" int32_t moca_unet_create(moca_ctx* ctx, int32_t in_channels, int32_t out_channels, int32_t model_channels,
                                     int32_t num_res_blocks, const int32_t* channel_mult, int32_t n_mult,

@@ -64,6 +64,27 @@ struct BlockW {
     int skip_cin = 0;
 };
 
+// ---- SD-VAE decoder (lvdm/modules/networks/ae_modules.py:466-578, the "next" row N1) ------------------------------------
+struct VaeResW {               // ResnetBlock (:151-210), temb_channels = 0
+    int cin = 0, cout = 0;
+    NormW n1, n2;
+    PackedW conv1, conv2, nin;
+    bool has_nin = false;
+};
+struct VaeW {
+    bool present = false;
+    int ch = 128, zc = 4, out_ch = 3, nres = 2;
+    std::vector<int> mult;
+    float* pq_w = nullptr;                           // post_quant_conv [zc, zc] (1x1) and bias, applied while staging z
+    float* pq_b = nullptr;
+    PackedW conv_in, conv_out;
+    VaeResW mid1, mid2;
+    NormW attn_norm, norm_out;
+    PackedW aq, ak, av, aproj;                       // AttnBlock (:26-78): 1x1 convs, one head of block_in channels
+    std::vector<std::vector<VaeResW>> up;            // up[level][block], level as in the state_dict
+    std::vector<PackedW> upconv;                     // up[level].upsample.conv (level > 0)
+};
+
 struct LoadSlot {
     enum Kind { COPY_F32, PACK } kind = COPY_F32;
     float* dst_f32 = nullptr;
@@ -86,6 +107,7 @@ struct moca_unet {
     moca::BlockW init_attn, mid;
     moca::PackedW time0, time2, fps0, fps2, emb_all, kv_all, conv_out;
     moca::NormW gn_out;
+    moca::VaeW vae;                                  // moca_vae_create: this object is a VAE decoder, not a UNet
     int n_emb = 0, n_kv = 0;
     std::unordered_map<std::string, moca::LoadSlot> slots;
     std::vector<void*> allocs;

@@ -96,12 +96,17 @@ struct Builder {
     // of TemporalConvBlock / TemporalTransformer; the apply kernel adds the T entries): per-sample entries would put
     // every atomic of the GEMM on B*C addresses, and same-address fp64 atomics serialise at ~40 ns each in L2 (measured:
     // the 81920 x 320 proj_out GEMM went from 56 to 107 us).
+    // Large frames (the VAE decoder's 160 x 256 and 320 x 512 levels: thousands of M tiles on one or two frames) split a frame
+    // into entries of <= 2048 rows for the same reason; gn_finalize adds the entries of a group.
     StatSrc stat_alloc(int C, int HW) {
         StatSrc r;
         r.C = C;
         r.rows = HW;
+        if (HW > 4096)
+            for (int e = 2048; e >= 32; e -= 32)
+                if (HW % e == 0) { r.rows = e; break; }
         const size_t off = cs_doubles;
-        cs_doubles += (size_t)NF * C * 2;
+        cs_doubles += (size_t)NF * (HW / r.rows) * C * 2;
         r.cs = dry ? (const double*)16 : plan->stats + off;
         return r;
     }
@@ -231,6 +236,9 @@ struct Builder {
     void transformer(const LayerW& L, Act& x, const op_t* kv, int kv_ld);
     void build();
     void build_layer(const LayerW& L);
+    Act vae_res(const VaeResW& r, const Act& x, const std::string& name);
+    void vae_attn(Act& x);
+    void build_vae(float inv_scale);
 };
 
 // ResBlock._forward (openaimodel3d.py:208-234) followed by its TemporalConvBlock (:269-276)
@@ -594,6 +602,179 @@ void Builder::build_layer(const LayerW& L) {
     plan->out_C = cur.C;
 }
 
+// ---- SD-VAE decoder (row N1): decode_first_stage_2DAE (ddpm3d.py:555-562) = post_quant_conv + Decoder.forward
+// (autoencoder.py:104-107, ae_modules.py:536-578), one frame = one "frame" of the token matrix (NF = B, T = 1) ------------------
+__global__ void vae_stage_kernel(const float* __restrict__ z, int B, int C, int HW, float inv_scale, const float* __restrict__ w,
+                                 const float* __restrict__ b, float* __restrict__ tok) {
+    // tok[(f, hw)][c] = post_quant_conv(z / scale_factor); columns C .. 63 zero (conv_in's K is padded to one 64-wide k-block)
+    const int64_t total = (int64_t)B * HW * 64;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int c = (int)(i & 63);
+        const int64_t r = i >> 6;
+        const int hw = (int)(r % HW), f = (int)(r / HW);
+        float v = 0.f;
+        if (c < C) {
+            v = b[c];
+            for (int k = 0; k < C; ++k) v = fmaf(w[c * C + k], z[((int64_t)f * C + k) * HW + hw] * inv_scale, v);
+        }
+        tok[i] = v;
+    }
+}
+
+// softmax(scale * S) over the rows of an fp32 matrix -> 16-bit P (AttnBlock, ae_modules.py:64-66); one block per row
+__global__ void __launch_bounds__(256) softmax_rows_kernel(const float* __restrict__ S, int cols, int ld, float scale, op_t* __restrict__ Pm) {
+    __shared__ float red[8];
+    const float* row = S + (size_t)blockIdx.x * ld;
+    op_t* out = Pm + (size_t)blockIdx.x * ld;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float mx = -INFINITY;
+    for (int c = threadIdx.x; c < cols; c += 256) mx = fmaxf(mx, row[c]);
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (lane == 0) red[warp] = mx;
+    __syncthreads();
+    mx = red[0];
+    for (int w = 1; w < 8; ++w) mx = fmaxf(mx, red[w]);
+    __syncthreads();
+    float sum = 0.f;
+    for (int c = threadIdx.x; c < cols; c += 256) sum += __expf((row[c] - mx) * scale);
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if (lane == 0) red[warp] = sum;
+    __syncthreads();
+    sum = 0.f;
+    for (int w = 0; w < 8; ++w) sum += red[w];
+    const float inv = 1.0f / sum;
+    for (int c = threadIdx.x; c < cols; c += 256) out[c] = float2op(__expf((row[c] - mx) * scale) * inv);
+}
+
+// ResnetBlock.forward with temb = None (ae_modules.py:189-210)
+Act Builder::vae_res(const VaeResW& r, const Act& x, const std::string& name) {
+    scope = name;
+    const int H = x.H, W = x.W, HW = H * W;
+    const int64_t rows = (int64_t)NF * HW;
+    if (x.C != r.cin) { set_error("plan: %s expects %d input channels, got %d", name.c_str(), r.cin, x.C); fail(MOCA_E_SHAPE); }
+    const size_t pad_elems = (size_t)NF * (H + 2) * (W + 2);
+    op_t* pad = scratch<op_t>(S_PAD, pad_elems * (r.cin > r.cout ? r.cin : r.cout));
+    op_t* raw = r.has_nin ? scratch<op_t>(S_RAW, (size_t)rows * r.cin) : nullptr;
+    op_t* t1 = scratch<op_t>(S_F32A, (size_t)rows * r.cout);
+    Act out;
+    out.C = r.cout; out.H = H; out.W = W;
+    out.p = (float*)palloc((size_t)rows * r.cout * sizeof(float));
+    gnorm(x.p, x.st, x.C, nullptr, StatSrc(), 0, rows, HW, r.n1, 1e-6f, 1, conv_dst(H, W, 1), H, W, pad, raw);
+    const StatSrc st1 = stat_alloc(r.cout, HW);
+    conv3x3(pad, H, W, r.cin, r.conv1, 1, t1, nullptr, 0, nullptr, &st1, 1);
+    gnorm(t1, st1, r.cout, nullptr, StatSrc(), 0, rows, HW, r.n2, 1e-6f, 1, conv_dst(H, W, 1), H, W, pad, nullptr, 1);
+    out.st = stat_alloc(r.cout, HW);
+    if (r.has_nin) {
+        linear(raw, rows, r.cin, r.nin, EPI_F32, out.p, r.cout, nullptr);
+        conv3x3(pad, H, W, r.cout, r.conv2, 1, out.p, nullptr, 0, out.p, &out.st);
+    } else {
+        conv3x3(pad, H, W, r.cout, r.conv2, 1, out.p, nullptr, 0, x.p, &out.st);
+    }
+    return out;
+}
+
+// AttnBlock.forward (ae_modules.py:52-78): one head of C channels over the H*W tokens of a frame.  S = q k^T and O = P v run on the
+// GEMM core with the keys / the transposed values in the weight operand's place; v's bias is added after the product (the rows of P
+// sum to one); in place on x.
+void Builder::vae_attn(Act& x) {
+    const VaeW& v = net->vae;
+    scope = "decoder.mid.attn_1";
+    const int C = x.C, HW = x.H * x.W;
+    const int64_t rows = (int64_t)NF * HW;
+    if (HW % 64 != 0 || C % 64 != 0) { set_error("plan: the VAE attention needs H*W (%d) and C (%d) to be multiples of 64", HW, C); fail(MOCA_E_SHAPE); }
+    op_t* xn = scratch<op_t>(S_LIN, (size_t)rows * C);
+    op_t* q = scratch<op_t>(S_QKV, (size_t)rows * C * 2);
+    op_t* k = dry ? nullptr : q + (size_t)rows * C;
+    op_t* vT = scratch<op_t>(S_ATT, (size_t)C * HW);
+    float* Sm = scratch<float>(S_Y, (size_t)HW * HW);
+    op_t* Pm = scratch<op_t>(S_FFH, (size_t)HW * HW);
+    op_t* att = scratch<op_t>(S_RAW, (size_t)rows * C);
+    gnorm(x.p, x.st, C, nullptr, StatSrc(), 0, rows, HW, v.attn_norm, 1e-6f, 0, DST_LINEAR, x.H, x.W, xn, nullptr);
+    linear(xn, rows, C, v.aq, EPI_BF16, q, C, nullptr);
+    linear(xn, rows, C, v.ak, EPI_BF16, k, C, nullptr);
+    const float scale = 1.0f / sqrtf((float)C);
+    for (int f = 0; f < NF; ++f) {
+        const op_t* xf = dry ? nullptr : xn + (size_t)f * HW * C;
+        const op_t* qf = dry ? nullptr : q + (size_t)f * HW * C;
+        const op_t* kf = dry ? nullptr : k + (size_t)f * HW * C;
+        PackedW wx; wx.w = (op_t*)xf; wx.N = HW; wx.K = C; wx.Kp = C;               // v^T = W_v x^T (no bias here)
+        linear(v.av.w, C, C, wx, EPI_BF16, vT, HW, nullptr);
+        PackedW wk; wk.w = (op_t*)kf; wk.N = HW; wk.K = C; wk.Kp = C;
+        linear(qf, HW, C, wk, EPI_F32, Sm, HW, nullptr);
+        push([=](cudaStream_t st) {
+            softmax_rows_kernel<<<HW, 256, 0, st>>>(Sm, HW, HW, scale, Pm);
+            return cudaGetLastError() == cudaSuccess ? MOCA_OK : MOCA_E_CUDA;
+        }, 1, "vae softmax");
+        PackedW wv; wv.w = vT; wv.b = v.av.b; wv.N = C; wv.K = HW; wv.Kp = HW;
+        linear(Pm, HW, HW, wv, EPI_BF16, dry ? nullptr : att + (size_t)f * HW * C, C, nullptr);
+    }
+    x.st = stat_alloc(C, HW);
+    linear(att, rows, C, v.aproj, EPI_F32, x.p, C, x.p, 0, &x.st, HW);
+}
+
+void Builder::build_vae(float inv_scale) {
+    moca_unet* n = net;
+    const VaeW& v = n->vae;
+    const int L = (int)v.mult.size();
+    const int64_t rows0 = (int64_t)NF * H0 * W0;
+    plan->x_in = (float*)palloc((size_t)rows0 * v.zc * sizeof(float));
+    scope = "vae";
+    if (!dry) {
+        double* stats = plan->stats;
+        const size_t sb = plan->stats_bytes;
+        raw_push([=](cudaStream_t st) { return cudaMemsetAsync(stats, 0, sb, st) == cudaSuccess ? MOCA_OK : MOCA_E_CUDA; }, "memset stats", 0);
+    }
+    plan->launches += 1;
+    Act h;
+    h.H = H0; h.W = W0;
+    {
+        float* tok = (float*)palloc((size_t)rows0 * 64 * sizeof(float));
+        op_t* pad = scratch<op_t>(S_PAD, (size_t)NF * (H0 + 2) * (W0 + 2) * 64);
+        const float* z = plan->x_in;
+        const float* pw = v.pq_w; const float* pb = v.pq_b;
+        const int b = NF, c = v.zc, hw = H0 * W0;
+        push([=](cudaStream_t st) {
+            const int64_t total = (int64_t)b * hw * 64;
+            const int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+            vae_stage_kernel<<<blocks, 256, 0, st>>>(z, b, c, hw, inv_scale, pw, pb, tok);
+            return cudaGetLastError() == cudaSuccess ? MOCA_OK : MOCA_E_CUDA;
+        }, 1, "vae stage");
+        convert(tok, 64, rows0, conv_dst(H0, W0, 1), H0, W0, pad);
+        h.C = v.ch * v.mult[L - 1];
+        h.p = (float*)palloc((size_t)rows0 * h.C * sizeof(float));
+        h.st = stat_alloc(h.C, H0 * W0);
+        conv3x3(pad, H0, W0, 64, v.conv_in, 1, h.p, nullptr, 0, nullptr, &h.st);
+    }
+    h = vae_res(v.mid1, h, "decoder.mid.block_1");
+    vae_attn(h);
+    h = vae_res(v.mid2, h, "decoder.mid.block_2");
+    for (int lvl = L - 1; lvl >= 0; --lvl) {
+        for (size_t j = 0; j < v.up[lvl].size(); ++j)
+            h = vae_res(v.up[lvl][j], h, "decoder.up." + std::to_string(lvl) + ".block." + std::to_string(j));
+        if (lvl != 0) {
+            scope = "decoder.up." + std::to_string(lvl) + ".upsample";
+            const int64_t rows = (int64_t)NF * h.H * h.W;
+            const int H2 = h.H * 2, W2 = h.W * 2;
+            op_t* pad = scratch<op_t>(S_PAD, (size_t)NF * (H2 + 2) * (W2 + 2) * h.C);
+            convert(h.p, h.C, rows, conv4d(H2, W2, 1) ? DST_UP2 : DST_SPATIAL_PAD_UP2, h.H, h.W, pad);
+            Act o; o.C = h.C; o.H = H2; o.W = W2;
+            o.p = (float*)palloc((size_t)NF * H2 * W2 * o.C * sizeof(float));
+            o.st = stat_alloc(o.C, H2 * W2);
+            conv3x3(pad, H2, W2, h.C, v.upconv[lvl], 1, o.p, nullptr, 0, nullptr, &o.st);
+            h = o;
+        }
+    }
+    scope = "decoder.out";
+    {
+        const int64_t rows = (int64_t)NF * h.H * h.W;
+        op_t* pad = scratch<op_t>(S_PAD, (size_t)NF * (h.H + 2) * (h.W + 2) * h.C);
+        gnorm(h.p, h.st, h.C, nullptr, StatSrc(), 0, rows, h.H * h.W, v.norm_out, 1e-6f, 1, conv_dst(h.H, h.W, 1), h.H, h.W, pad, nullptr);
+        plan->out_tok = (float*)palloc((size_t)rows * v.out_ch * sizeof(float));
+        plan->out_C = v.out_ch;
+        conv3x3(pad, h.H, h.W, h.C, v.conv_out, 1, plan->out_tok, nullptr, 0, nullptr, nullptr);
+    }
+}
+
 }  // namespace moca
 
 using namespace moca;
@@ -612,19 +793,14 @@ static void evict_plans(moca_unet* n) {
     }
 }
 
-static int get_plan(moca_unet* n, int B, int T, int H, int W, int Lmax, Plan** out) {
-    std::vector<int> key{B, T, H, W, Lmax, n->taps ? 1 : 0};
-    auto it = n->plans.find(key);
-    if (it != n->plans.end()) { it->second->last_use = ++n->use_clock; *out = it->second.get(); return MOCA_OK; }
-    int down = 1;
-    for (size_t i = 1; i < n->mult.size(); ++i) down *= 2;
-    MOCA_REQUIRE(H % down == 0 && W % down == 0, MOCA_E_SHAPE, "moca_unet_forward: H=%d W=%d must be multiples of %d", H, W, down);
-    MOCA_REQUIRE(B * T <= 128 && B <= 16 && T <= 16, MOCA_E_SHAPE, "moca_unet_forward: B=%d T=%d unsupported (B*T <= 128, T <= 16)", B, T);
+// dry pass (sizes) -> allocation -> real pass; `build` runs the same Builder method both times
+template <typename F>
+static int make_plan(moca_unet* n, const std::vector<int>& key, int B, int T, int H, int W, int Lmax, bool taps, F build, Plan** out) {
     auto plan = std::make_shared<Plan>();
-    plan->B = B; plan->T = T; plan->H = H; plan->W = W; plan->Lmax = Lmax; plan->with_taps = n->taps;
+    plan->B = B; plan->T = T; plan->H = H; plan->W = W; plan->Lmax = Lmax; plan->with_taps = taps;
     Builder dry;
     dry.net = n; dry.plan = plan.get(); dry.dry = true; dry.B = B; dry.T = T; dry.H0 = H; dry.W0 = W; dry.NF = B * T; dry.Lmax = Lmax;
-    dry.build();
+    build(dry);
     if (dry.rc) return dry.rc;
     Builder real = dry;
     real.dry = false; real.cs_doubles = 0;
@@ -637,13 +813,86 @@ static int get_plan(moca_unet* n, int B, int T, int H, int W, int Lmax, Plan** o
         plan->workspace_bytes += dry.need[i];
     }
     if (real.rc) return real.rc;
-    real.build();
+    build(real);
     if (real.rc) return real.rc;
     evict_plans(n);
     plan->last_use = ++n->use_clock;
     n->plans[key] = plan;
     *out = plan.get();
     return MOCA_OK;
+}
+
+static int get_plan(moca_unet* n, int B, int T, int H, int W, int Lmax, Plan** out) {
+    std::vector<int> key{B, T, H, W, Lmax, n->taps ? 1 : 0};
+    auto it = n->plans.find(key);
+    if (it != n->plans.end()) { it->second->last_use = ++n->use_clock; *out = it->second.get(); return MOCA_OK; }
+    int down = 1;
+    for (size_t i = 1; i < n->mult.size(); ++i) down *= 2;
+    MOCA_REQUIRE(H % down == 0 && W % down == 0, MOCA_E_SHAPE, "moca_unet_forward: H=%d W=%d must be multiples of %d", H, W, down);
+    MOCA_REQUIRE(B * T <= 128 && B <= 16 && T <= 16, MOCA_E_SHAPE, "moca_unet_forward: B=%d T=%d unsupported (B*T <= 128, T <= 16)", B, T);
+    return make_plan(n, key, B, T, H, W, Lmax, n->taps, [](Builder& b) { b.build(); }, out);
+}
+
+// launch a plan's ops: as one CUDA graph (captured on first use) unless taps are collected or MOCA_NO_GRAPH is set
+static int run_plan(Plan* plan, cudaStream_t st, const char* who) {
+    const bool use_graph = !plan->with_taps && getenv("MOCA_NO_GRAPH") == nullptr;
+    if (!use_graph) {
+        for (auto& op : plan->ops) {
+            int rc = op(st);
+            if (rc) return rc;
+        }
+        return MOCA_OK;
+    }
+    if (!plan->gexec) {
+        // capture on a private stream (the caller's may be the legacy default stream, which cannot be captured)
+        cudaGraph_t graph = nullptr;
+        cudaStream_t cs = nullptr;
+        MOCA_CHECK_CUDA(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
+        MOCA_CHECK_CUDA(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
+        int orc = MOCA_OK;
+        for (auto& op : plan->ops) {
+            orc = op(cs);
+            if (orc) break;
+        }
+        cudaError_t ce = cudaStreamEndCapture(cs, &graph);
+        cudaStreamDestroy(cs);
+        if (orc) { if (graph) cudaGraphDestroy(graph); return orc; }
+        MOCA_REQUIRE(ce == cudaSuccess, MOCA_E_CUDA, "%s: stream capture failed: %s", who, cudaGetErrorString(ce));
+        ce = cudaGraphInstantiate(&plan->gexec, graph, 0);
+        cudaGraphDestroy(graph);
+        MOCA_REQUIRE(ce == cudaSuccess, MOCA_E_CUDA, "%s: graph instantiate failed: %s", who, cudaGetErrorString(ce));
+    }
+    MOCA_CHECK_CUDA(cudaGraphLaunch(plan->gexec, st));
+    return MOCA_OK;
+}
+
+// AutoencoderKL.decode of B latent frames (autoencoder.py:104-107) with the 1 / scale_factor of decode_first_stage_2DAE
+// (ddpm3d.py:555-562) folded into the staging kernel: z [B, zc, H, W] fp32 -> image [B, out_ch, H * 2^(L-1), W * 2^(L-1)] fp32
+extern "C" int32_t moca_vae_decode(moca_unet* n, const float* z, int32_t B, int32_t H, int32_t W, float scale_factor, float* image,
+                                   void* stream) {
+    MOCA_REQUIRE(n && z && image, MOCA_E_ARG, "moca_vae_decode: NULL argument");
+    MOCA_REQUIRE(n->vae.present, MOCA_E_STATE, "moca_vae_decode: handle was not made by moca_vae_create");
+    MOCA_REQUIRE(n->finalized, MOCA_E_STATE, "moca_vae_decode: call moca_unet_finalize after loading the weights");
+    MOCA_REQUIRE(B > 0 && B <= 16 && H > 0 && W > 0 && scale_factor != 0.f, MOCA_E_SHAPE, "moca_vae_decode: bad shape B=%d H=%d W=%d", B, H, W);
+    const int up = 1 << ((int)n->vae.mult.size() - 1);
+    MOCA_REQUIRE((int64_t)B * (H * up + 2) * (W * up + 2) < (1ll << 31) / 64, MOCA_E_SHAPE, "moca_vae_decode: B=%d frames of %d x %d are too many rows", B, H * up, W * up);
+    cudaStream_t st = (cudaStream_t)stream;
+    int sbits;
+    memcpy(&sbits, &scale_factor, sizeof(int));
+    std::vector<int> key{B, 1, H, W, -1, sbits};
+    Plan* plan = nullptr;
+    auto it = n->plans.find(key);
+    if (it != n->plans.end()) { it->second->last_use = ++n->use_clock; plan = it->second.get(); }
+    else {
+        const float inv = 1.0f / scale_factor;
+        int rc = make_plan(n, key, B, 1, H, W, 0, false, [inv](Builder& b) { b.build_vae(inv); }, &plan);
+        if (rc) return rc;
+    }
+    n->last = plan;
+    MOCA_CHECK_CUDA(cudaMemcpyAsync(plan->x_in, z, (size_t)B * n->vae.zc * H * W * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    int rc = run_plan(plan, st, "moca_vae_decode");
+    if (rc) return rc;
+    return tokens_to_ncthw(plan->out_tok, n->vae.out_ch, B, n->vae.out_ch, 1, H * up, W * up, image, st);
 }
 
 extern "C" int32_t moca_unet_forward(moca_unet* n, const float* x, const int32_t* timesteps, const float* context,
@@ -670,34 +919,8 @@ extern "C" int32_t moca_unet_forward(moca_unet* n, const float* x, const int32_t
     MOCA_LAUNCH_CHECK();
     MOCA_CHECK_CUDA(cudaMemcpyAsync(plan->x_in, x, (size_t)B * n->in_ch * T * H * W * sizeof(float), cudaMemcpyDeviceToDevice, st));
     MOCA_CHECK_CUDA(cudaMemcpyAsync(plan->ctx_in, context, (size_t)B * Lmax * n->ctx_dim * sizeof(float), cudaMemcpyDeviceToDevice, st));
-    const bool use_graph = !plan->with_taps && getenv("MOCA_NO_GRAPH") == nullptr;
-    if (use_graph) {
-        if (!plan->gexec) {
-            // capture on a private stream (the caller's may be the legacy default stream, which cannot be captured)
-            cudaGraph_t graph = nullptr;
-            cudaStream_t cs = nullptr;
-            MOCA_CHECK_CUDA(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
-            MOCA_CHECK_CUDA(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
-            int orc = MOCA_OK;
-            for (auto& op : plan->ops) {
-                orc = op(cs);
-                if (orc) break;
-            }
-            cudaError_t ce = cudaStreamEndCapture(cs, &graph);
-            cudaStreamDestroy(cs);
-            if (orc) { if (graph) cudaGraphDestroy(graph); return orc; }
-            MOCA_REQUIRE(ce == cudaSuccess, MOCA_E_CUDA, "moca_unet_forward: stream capture failed: %s", cudaGetErrorString(ce));
-            ce = cudaGraphInstantiate(&plan->gexec, graph, 0);
-            cudaGraphDestroy(graph);
-            MOCA_REQUIRE(ce == cudaSuccess, MOCA_E_CUDA, "moca_unet_forward: graph instantiate failed: %s", cudaGetErrorString(ce));
-        }
-        MOCA_CHECK_CUDA(cudaGraphLaunch(plan->gexec, st));
-    } else {
-        for (auto& op : plan->ops) {
-            rc = op(st);
-            if (rc) return rc;
-        }
-    }
+    rc = run_plan(plan, st, "moca_unet_forward");
+    if (rc) return rc;
     return tokens_to_ncthw(plan->out_tok, n->out_ch, B, n->out_ch, T, H, W, y, st);
 }
 

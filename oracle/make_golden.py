@@ -418,9 +418,64 @@ def gen_unet_full():
     np.savez_compressed(os.path.join(GOLD, "unet_full_meta.npz"), **out)
 
 
+VAE_SMALL = dict(ch=64, ch_mult=(1, 2, 2), num_res_blocks=1, z_channels=4, out_ch=3)
+
+
+def gen_vae_small():
+    """Reference Decoder + post_quant_conv (ae_modules.py:466-578, autoencoder.py:104-107) vs oracle.vae_ref on seeded weights:
+    a shrunk ddconfig (64 channels, three levels), then the key / shape listing of the shipped ddconfig."""
+    import hashlib
+    import yaml
+    refimport.setup()
+    from lvdm.modules.networks.ae_modules import Decoder
+    from moca_video_b200.vae import decoder_param_shapes
+    from oracle.vae_ref import random_vae_state_dict, vae_decode
+
+    def ref_model(dd):
+        dec = Decoder(ch=dd["ch"], out_ch=dd["out_ch"], ch_mult=dd["ch_mult"], num_res_blocks=dd["num_res_blocks"], attn_resolutions=[],
+                      in_channels=3, resolution=64, z_channels=dd["z_channels"])
+        pq = torch.nn.Conv2d(dd["z_channels"], dd["z_channels"], 1)
+        return dec, pq
+
+    dd = VAE_SMALL
+    dec, pq = ref_model(dd)
+    shapes = decoder_param_shapes(**dd)
+    ref_shapes = {"post_quant_conv." + k: tuple(v.shape) for k, v in pq.state_dict().items()}
+    ref_shapes.update({"decoder." + k: tuple(v.shape) for k, v in dec.state_dict().items()})
+    assert ref_shapes == {k: tuple(v) for k, v in shapes.items()}, set(ref_shapes) ^ set(shapes)
+    sd = random_vae_state_dict(shapes, seed=3)
+    dec.load_state_dict({k[len("decoder."):]: v for k, v in sd.items() if k.startswith("decoder.")}, strict=True)
+    pq.load_state_dict({k[len("post_quant_conv."):]: v for k, v in sd.items() if k.startswith("post_quant_conv.")}, strict=True)
+    rng = np.random.default_rng(31)
+    out = {}
+    for tag, (n, h, w) in {"a": (2, 8, 8), "b": (1, 8, 16)}.items():
+        z = torch.from_numpy(rng.standard_normal((n, 4, h, w)).astype(np.float32))
+        with torch.no_grad():
+            y_ref = dec(pq(z))
+            y = vae_decode(sd, z, len(dd["ch_mult"]), dd["num_res_blocks"])
+        err = float((y - y_ref).norm() / y_ref.norm())
+        print(f"vae_small[{tag}] restatement vs reference rel-L2 = {err:.3e}, |y| = {float(y_ref.abs().mean()):.3f}")
+        assert err < 1e-5
+        out.update({f"{tag}_z": _np(z), f"{tag}_y": _np(y_ref)})
+    # shipped ddconfig: listing equality on the meta device (no forward: 49.5 M parameters at 320 x 512 take minutes on CPU)
+    with open(os.path.join(refimport.REF, "configs/inference_t2v_512_v2.0.yaml")) as f:
+        full = yaml.safe_load(f)["model"]["params"]["first_stage_config"]["params"]["ddconfig"]
+    with torch.device("meta"):
+        fdec = Decoder(**full)
+    fshapes = {"decoder." + k: tuple(v.shape) for k, v in fdec.state_dict().items()}
+    fshapes.update({"post_quant_conv.weight": (4, 4, 1, 1), "post_quant_conv.bias": (4,)})
+    mine = decoder_param_shapes(full["ch"], tuple(full["ch_mult"]), full["num_res_blocks"], full["z_channels"], full["out_ch"])
+    assert fshapes == {k: tuple(v) for k, v in mine.items()}
+    listing = "\n".join(f"{k} {v}" for k, v in sorted(fshapes.items()))
+    out["full_shapes_sha256"] = np.array(hashlib.sha256(listing.encode()).hexdigest())
+    out["full_n_params"] = np.int64(sum(int(np.prod(v)) for v in fshapes.values()))
+    print("full decoder:", len(fshapes), "tensors,", int(out["full_n_params"]), "params")
+    np.savez_compressed(os.path.join(GOLD, "vae_small.npz"), **out)
+
+
 if __name__ == "__main__":
     os.makedirs(GOLD, exist_ok=True)
-    which = sys.argv[1:] or ["tables", "ddim_step", "ddim_step_sam", "p_sample", "queue", "unet_small", "unet_small64", "unet_full"]
+    which = sys.argv[1:] or ["tables", "ddim_step", "ddim_step_sam", "p_sample", "queue", "unet_small", "unet_small64", "unet_full", "vae_small"]
     for w in which:
         print("==", w)
         globals()["gen_" + w]()

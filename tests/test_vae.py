@@ -1,0 +1,135 @@
+"""First-stage decoder: oracle pinned to the reference fixture, the loader's parameter table, and GPU parity of
+``AutoencoderKLDecoder`` (-> moca_vae_decode) with the fixture, the oracle and the full-size decode.
+
+Bar: rel-L2 <= 2e-2 of the 16-bit-operand path against fp32 (north_star's tolerance for the tensor-core path).
+"""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN
+
+TOL = 2e-2
+FULL = dict(ch=128, ch_mult=(1, 2, 4, 4), num_res_blocks=2, z_channels=4, out_ch=3)
+
+
+def rel(a, b):
+    a = a.float(); b = b.float()
+    return float((a - b).norm() / (b.norm() + 1e-30))
+
+
+def _small():
+    from moca_video_b200.vae import decoder_param_shapes
+    from oracle.make_golden import VAE_SMALL
+    from oracle.vae_ref import random_vae_state_dict
+    return VAE_SMALL, random_vae_state_dict(decoder_param_shapes(**VAE_SMALL), seed=3)
+
+
+@pytest.mark.parametrize("tag", ["a", "b"])
+def test_vae_restatement_matches_reference_fixture(tag):
+    from oracle.vae_ref import vae_decode
+    dd, sd = _small()
+    g = np.load(os.path.join(GOLDEN, "vae_small.npz"))
+    y = vae_decode(sd, torch.from_numpy(g[tag + "_z"]), len(dd["ch_mult"]), dd["num_res_blocks"])
+    assert rel(y, torch.from_numpy(g[tag + "_y"])) < 1e-5
+
+
+def test_vae_loader_expects_reference_state_dict():
+    """moca_vae_create(ctx=NULL) lists what the packer consumes: the reference's decode-path keys at the shipped ddconfig
+    (listing hashed from the reference's own Decoder in oracle/make_golden.py)."""
+    from moca_video_b200.vae import AutoencoderKLDecoder, decoder_param_shapes
+    g = np.load(os.path.join(GOLDEN, "vae_small.npz"))
+    shapes = decoder_param_shapes(**FULL)
+    listing = "\n".join(f"{k} {tuple(v)}" for k, v in sorted(shapes.items()))
+    assert hashlib.sha256(listing.encode()).hexdigest() == str(g["full_shapes_sha256"])
+    v = AutoencoderKLDecoder(FULL, _listing_only=True)
+    assert v.expected_params() == {k: int(np.prod(s)) for k, s in shapes.items()}
+    assert sum(v.expected_params().values()) == int(g["full_n_params"]) == 49490199
+    dd, _ = _small()
+    s = AutoencoderKLDecoder(dd, _listing_only=True)
+    assert s.expected_params() == {k: int(np.prod(x)) for k, x in decoder_param_shapes(**dd).items()}
+
+
+def test_vae_unsupported_configs_fail_loudly():
+    from moca_video_b200 import MocaError
+    from moca_video_b200.vae import AutoencoderKLDecoder
+    with pytest.raises(MocaError):
+        AutoencoderKLDecoder(dict(FULL, tanh_out=True), _listing_only=True)
+    with pytest.raises(MocaError):
+        AutoencoderKLDecoder(dict(FULL, attn_resolutions=[16]), _listing_only=True)
+    with pytest.raises(MocaError):
+        AutoencoderKLDecoder(dict(FULL, ch=96), _listing_only=True)          # not a multiple of one GEMM k-block
+    with pytest.raises(MocaError):
+        AutoencoderKLDecoder(FULL, embed_dim=8, _listing_only=True)
+
+
+# ---- GPU ---------------------------------------------------------------------------------------------------------------
+@pytest.fixture
+def _no_tf32():
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tag", ["a", "b"])
+def test_vae_small_vs_reference_fixture(tag):
+    from moca_video_b200.vae import AutoencoderKLDecoder
+    dd, sd = _small()
+    g = np.load(os.path.join(GOLDEN, "vae_small.npz"))
+    dec = AutoencoderKLDecoder(dd, device="cuda").load_state_dict(sd)
+    y = dec.decode(torch.from_numpy(g[tag + "_z"]).cuda())
+    assert y.shape == g[tag + "_y"].shape
+    assert rel(y.cpu(), torch.from_numpy(g[tag + "_y"])) < TOL
+
+
+@pytest.mark.gpu
+def test_vae_small_video_vs_oracle(_no_tf32):
+    """decode_first_stage_2DAE: [b, c, t, h, w] latents, scale factor, frames grouped 3 per call vs one per call."""
+    from moca_video_b200.vae import AutoencoderKLDecoder
+    from oracle.vae_ref import decode_first_stage_2DAE
+    dd, sd = _small()
+    sd = {k: v.cuda() for k, v in sd.items()}
+    gen = torch.Generator(device="cuda").manual_seed(9)
+    z = torch.randn(2, 4, 5, 8, 16, device="cuda", generator=gen) * 0.18215
+    ref = decode_first_stage_2DAE(sd, z, 0.18215, len(dd["ch_mult"]), dd["num_res_blocks"])
+    dec = AutoencoderKLDecoder(dd, device="cuda", frames_per_call=3).load_state_dict(sd)
+    y = dec.decode_first_stage_2DAE(z)
+    assert y.shape == ref.shape == (2, 3, 5, 32, 64)
+    assert rel(y, ref) < TOL
+    one = AutoencoderKLDecoder(dd, device="cuda", frames_per_call=1).load_state_dict(sd)
+    assert rel(one.decode_first_stage_2DAE(z), y) < 4e-3           # frames are independent; only rounding noise may differ
+
+
+@pytest.mark.gpu
+def test_vae_full_size_vs_oracle(_no_tf32):
+    """The shipped ddconfig at the 320 x 512 output of the headline config, two latent frames."""
+    from moca_video_b200.vae import AutoencoderKLDecoder, decoder_param_shapes
+    from oracle.vae_ref import random_vae_state_dict, vae_decode
+    sd = {k: v.cuda() for k, v in random_vae_state_dict(decoder_param_shapes(**FULL), seed=5).items()}
+    gen = torch.Generator(device="cuda").manual_seed(11)
+    z = torch.randn(2, 4, 40, 64, device="cuda", generator=gen)
+    dec = AutoencoderKLDecoder(FULL, device="cuda", frames_per_call=2).load_state_dict(sd)
+    y = dec.decode(z)
+    assert y.shape == (2, 3, 320, 512)
+    ref = torch.cat([vae_decode(sd, z[i:i + 1], 4, 2) for i in range(2)])
+    assert torch.isfinite(y).all()
+    assert rel(y, ref) < TOL
+    assert dec.launches() > 0 and dec.flops() > 1e12
+
+
+@pytest.mark.gpu
+def test_vae_rejects_bad_input():
+    from moca_video_b200 import MocaError
+    from moca_video_b200.vae import AutoencoderKLDecoder
+    dd, sd = _small()
+    dec = AutoencoderKLDecoder(dd, device="cuda")
+    with pytest.raises(MocaError):
+        dec.decode(torch.zeros(1, 4, 8, 8, device="cuda"))           # weights not loaded
+    dec.load_state_dict(sd)
+    with pytest.raises(MocaError):
+        dec.decode(torch.zeros(1, 3, 8, 8, device="cuda"))           # wrong channel count
+    with pytest.raises(MocaError):
+        dec.decode(torch.zeros(1, 4, 6, 6, device="cuda"))           # H * W not a multiple of 64 (attention k-blocks)
