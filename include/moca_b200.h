@@ -202,6 +202,16 @@ int32_t moca_vae_create(moca_ctx* ctx, int32_t ch, const int32_t* ch_mult, int32
                         int32_t z_channels, int32_t out_ch, moca_unet** out);
 int32_t moca_vae_decode(moca_unet* vae, const float* z, int32_t B, int32_t H, int32_t W, float scale_factor, float* image,
                         void* stream);
+/* Encode path: AutoencoderKL.encode (lvdm/models/autoencoder.py:97-102) = Encoder (ae_modules.py:364-463; its Downsample :80-100 is
+ * F.pad (0,1,0,1) + a stride-2 convolution) + quant_conv, used by encode_first_stage_2DAE (lvdm/models/ddpm3d.py:485-490) in the DAVIS
+ * branch of prepare_latents (scripts/evaluation/funcs.py:38-47).
+ * moca_vae_encoder_create: ddconfig integers; state_dict keys "encoder.*" and "quant_conv.*".
+ * moca_vae_encode: x [B, in_channels, H, W] fp32 image -> moments [B, 2 * z_channels, H / 2^(n_mult-1), W / 2^(n_mult-1)] fp32
+ *   (mean | logvar, the tensor DiagonalGaussianDistribution, lvdm/distributions.py:24-33, is constructed from; sampling the
+ *   posterior and the scale_factor, ddpm3d.py:458-465, stay with the caller: the reference draws that noise on the host). */
+int32_t moca_vae_encoder_create(moca_ctx* ctx, int32_t ch, const int32_t* ch_mult, int32_t n_mult, int32_t num_res_blocks,
+                                int32_t in_channels, int32_t z_channels, int32_t double_z, moca_unet** out);
+int32_t moca_vae_encode(moca_unet* vae, const float* x, int32_t B, int32_t H, int32_t W, float* moments, void* stream);
 
 /* ---- primitives exposed for unit parity tests (tests/test_gpu_ops.py): the same kernels the UNet plan launches ----
  * moca_gemm_op16: D[M,N] = A[M,K] * W[N,K]^T (+bias[N]) on the tcgen05 core; A, W op16 (moca_operand_dtype) row-major (K contiguous),

@@ -180,7 +180,7 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
                 // GEMM_SPATIAL_4D: first frame / first input image row of the tile
                 const int c4_fg = P.mode == GEMM_SPATIAL_4D ? mt / P.c4_th : 0;
                 const int c4_t = mt - c4_fg * P.c4_th, c4_hq = c4_t / P.c4_tw;       // c4_tw > 1: 128-pixel segments of wide rows
-                const int c4_f0 = c4_fg * P.c4_bf, c4_h0 = c4_hq * P.c4_bh * P.stride, c4_w0 = (c4_t - c4_hq * P.c4_tw) * kBM;
+                const int c4_f0 = c4_fg * P.c4_bf, c4_h0 = c4_hq * P.c4_bh * P.stride, c4_w0 = (c4_t - c4_hq * P.c4_tw) * kBM * P.stride - P.c4_pad;
                 for (int tap = 0; tap < P.ntaps; ++tap) {
                     const int arow = mt * kBM + P.tap_shift[tap];
                     const int dy = tap / 3, dx = tap - dy * 3;
@@ -189,7 +189,7 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
                         uint8_t* sa = base + (size_t)stage * Cfg::STAGE_BYTES;
                         if (NCTA == 1 && P.mode == GEMM_SPATIAL_4D) {
                             mbar_expect_tx(&full[stage], Cfg::STAGE_BYTES);
-                            tma_load_4d(sa, &P.tmA, &full[stage], kb * kBK, c4_w0 + dx - 1, c4_h0 + dy - 1, c4_f0);
+                            tma_load_4d(sa, &P.tmA, &full[stage], kb * kBK, c4_w0 + dx, c4_h0 + dy - P.c4_pad, c4_f0);
                             tma_load_2d(sa + kABytes, &P.tmB, &full[stage], tap * P.Kp + kb * kBK, nt * BN);
                         } else if constexpr (NCTA == 2) {
                             // both CTAs load their A rows and their half of the B rows; all bytes are counted on the leader's barrier
@@ -876,7 +876,7 @@ static bool conv4d_geometry(int NF, int H, int W, int stride, int* bh, int* bf) 
     const int Ho = H / stride, Wo = W / stride;
     if (Wo > 128) {
         // wide images: an M tile is 128 consecutive pixels of one image row (*bh = 1, *bf = 1, Wo / 128 tiles per row)
-        if (stride != 1 || Wo % 128 != 0) return false;
+        if (Wo % 128 != 0) return false;
         *bh = 1; *bf = 1;
         return true;
     }
@@ -1092,7 +1092,7 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
     p.M = d.M; p.N = d.N; p.ntaps = d.ntaps; p.Kp = d.Kp; p.kblocks = d.Kp / 64;
     for (int i = 0; i < 9; ++i) p.tap_shift[i] = d.tap_shift[i];
     p.mode = d.mode; p.g_rows = d.g_rows; p.g_w = d.g_w; p.g_H = d.g_H; p.g_W = d.g_W; p.stride = d.stride;
-    p.c4_tw = 1;
+    p.c4_tw = 1; p.c4_pad = d.pad_lo;
     if (d.mode == GEMM_SPATIAL_4D) {
         p.g_H = d.g_H / d.stride; p.g_W = d.g_W / d.stride;            // output image size from here on
         p.c4_bh = c4_bh; p.c4_bf = c4_bf; p.c4_th = p.g_H / c4_bh; p.c4_tw = 1;

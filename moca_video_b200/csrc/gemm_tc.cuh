@@ -40,7 +40,7 @@ struct GemmParams {
     int g_w;                  // SPATIAL: W+2           TIME: HW
     int g_H, g_W;             // SPATIAL: H, W          TIME: g_H = T
     int stride;               // SPATIAL: 1 or 2 (Downsample)
-    int c4_bh, c4_bf, c4_th, c4_tw;  // SPATIAL_4D: output image rows / frames per M tile, M tiles per frame group (Ho / bh); g_H, g_W = Ho, Wo
+    int c4_bh, c4_bf, c4_th, c4_tw, c4_pad;  // SPATIAL_4D: output image rows / frames per M tile, M tiles per frame group (Ho / bh); g_H, g_W = Ho, Wo
     float* outf;
     op_t* outb;
     int ldo;                  // output row pitch (elements)
@@ -80,6 +80,7 @@ struct GemmDesc {
     // caller) — the GroupNorm that consumes this tensor needs no statistics pass of its own.
     double* chan_stats = nullptr;
     int stat_rows_per_frame = 0;
+    int pad_lo = 1;                   // SPATIAL_4D: zero rows / columns before the image (1: padding 1; 0: the VAE Downsample's pad (0,1,0,1))
     int stat_sample_rows = 0;         // rows of one sample in the GEMM's input-row space (0: unknown -> exact double partials)
 };
 

@@ -344,7 +344,61 @@ static void build_vae_arch(moca_unet* n) {
     v.conv_out = reg_linear(n, "decoder.conv_out", v.out_ch, block_in, 9, true);
 }
 
+// AutoencoderKL encode path: Encoder (ae_modules.py:364-463) + quant_conv (autoencoder.py:97-102)
+static void build_vae_encoder_arch(moca_unet* n) {
+    VaeW& v = n->vae;
+    const int L = (int)v.mult.size();
+    v.conv_in = reg_linear(n, "encoder.conv_in", v.ch, v.in_ch, 9, true);
+    v.down.resize(L);
+    v.downconv.resize(L);
+    int block_in = v.ch;
+    for (int lvl = 0; lvl < L; ++lvl) {
+        const int block_out = v.ch * v.mult[lvl];
+        for (int j = 0; j < v.nres; ++j) {
+            v.down[lvl].push_back(build_vae_res(n, "encoder.down." + std::to_string(lvl) + ".block." + std::to_string(j), block_in, block_out));
+            block_in = block_out;
+        }
+        if (lvl != L - 1) v.downconv[lvl] = reg_linear(n, "encoder.down." + std::to_string(lvl) + ".downsample.conv", block_in, block_in, 9, true);
+    }
+    v.mid1 = build_vae_res(n, "encoder.mid.block_1", block_in, block_in);
+    v.attn_norm = reg_norm(n, "encoder.mid.attn_1.norm", block_in);
+    v.aq = reg_linear(n, "encoder.mid.attn_1.q", block_in, block_in, 1, true);
+    v.ak = reg_linear(n, "encoder.mid.attn_1.k", block_in, block_in, 1, true);
+    v.av = reg_linear(n, "encoder.mid.attn_1.v", block_in, block_in, 1, true);
+    v.aproj = reg_linear(n, "encoder.mid.attn_1.proj_out", block_in, block_in, 1, true);
+    v.mid2 = build_vae_res(n, "encoder.mid.block_2", block_in, block_in);
+    v.norm_out = reg_norm(n, "encoder.norm_out", block_in);
+    v.conv_out = reg_linear(n, "encoder.conv_out", v.mom_ch, block_in, 9, true);
+    v.q_w = reg_f32(n, "quant_conv.weight", (int64_t)v.mom_ch * v.mom_ch);
+    v.q_b = reg_f32(n, "quant_conv.bias", v.mom_ch);
+}
+
 }  // namespace moca
+
+// VAE encoder object (same handle conventions as the decoder below); moca_vae_encode (unet_plan.cu) runs it.
+extern "C" int32_t moca_vae_encoder_create(moca_ctx* ctx, int32_t ch, const int32_t* ch_mult, int32_t n_mult, int32_t num_res_blocks,
+                                           int32_t in_channels, int32_t z_channels, int32_t double_z, moca_unet** out) {
+    MOCA_REQUIRE(out && ch_mult && n_mult >= 1 && n_mult <= 6, MOCA_E_ARG, "moca_vae_encoder_create: bad argument");
+    MOCA_REQUIRE(ch > 0 && ch % 64 == 0 && z_channels >= 1 && z_channels <= 16 && in_channels >= 1 && in_channels <= 16 && num_res_blocks >= 1,
+                 MOCA_E_SHAPE, "moca_vae_encoder_create: ch %d must be a multiple of 64 (one GEMM k-block), z_channels / in_channels <= 16", ch);
+    for (int i = 0; i < n_mult; ++i) MOCA_REQUIRE(ch_mult[i] >= 1, MOCA_E_SHAPE, "moca_vae_encoder_create: ch_mult[%d] = %d", i, ch_mult[i]);
+    moca_unet* n = new moca_unet();
+    n->ctx = ctx;
+    n->dry = (ctx == nullptr);
+    n->vae.present = true;
+    n->vae.encoder = true;
+    n->vae.ch = ch; n->vae.zc = z_channels; n->vae.in_ch = in_channels; n->vae.nres = num_res_blocks;
+    n->vae.mom_ch = (double_z ? 2 : 1) * z_channels;
+    n->vae.mult.assign(ch_mult, ch_mult + n_mult);
+    build_vae_encoder_arch(n);
+    for (void* p : n->allocs)
+        if (!p) {
+            set_error("moca_vae_encoder_create: device allocation failed");
+            return MOCA_E_CUDA;
+        }
+    *out = n;
+    return MOCA_OK;
+}
 
 // VAE decoder object: the same handle type and the same moca_unet_load / _load_many / _finalize / _destroy / _param_* calls as the
 // UNet; moca_vae_decode (unet_plan.cu) runs it.  ch / ch_mult / num_res_blocks / z_channels / out_ch: the yaml's ddconfig.

@@ -83,6 +83,13 @@ struct VaeW {
     PackedW aq, ak, av, aproj;                       // AttnBlock (:26-78): 1x1 convs, one head of block_in channels
     std::vector<std::vector<VaeResW>> up;            // up[level][block], level as in the state_dict
     std::vector<PackedW> upconv;                     // up[level].upsample.conv (level > 0)
+    // Encoder (:364-463) + quant_conv (autoencoder.py:97-102): conv_in / mid* / attn* / norm_out / conv_out above are the encoder's
+    bool encoder = false;
+    int in_ch = 3, mom_ch = 8;                       // image channels; moments = 2 * z_channels (double_z)
+    std::vector<std::vector<VaeResW>> down;          // down[level][block]
+    std::vector<PackedW> downconv;                   // down[level].downsample.conv (level < L - 1): pad (0,1,0,1), stride 2
+    float* q_w = nullptr;                            // quant_conv [mom_ch, mom_ch] (1x1) and bias, applied while un-staging
+    float* q_b = nullptr;
 };
 
 struct LoadSlot {

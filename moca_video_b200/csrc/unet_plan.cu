@@ -143,8 +143,14 @@ struct Builder {
     }
     int conv_dst(int H, int W, int stride) const { return conv4d(H, W, stride) ? DST_LINEAR : DST_SPATIAL_PAD; }
     void conv3x3(const op_t* src, int H, int W, int Cin, const PackedW& w, int stride, void* out, const float* rowbias,
-                 int rb_ld, const float* residual, const StatSrc* ss, int out16 = 0) {
+                 int rb_ld, const float* residual, const StatSrc* ss, int out16 = 0, int pad_lo = 1) {
         GemmDesc d;
+        d.pad_lo = pad_lo;
+        if (pad_lo != 1 && !conv4d(H, W, stride)) {
+            set_error("plan: a convolution with padding (0,1,0,1) needs the 4-D tensor-map geometry (NF=%d H=%d W=%d stride=%d)", NF, H, W, stride);
+            fail(MOCA_E_SHAPE);
+            return;
+        }
         const int Ho = H / stride, Wo = W / stride;
         d.a_cols = Cin; d.a_pitch = Cin;
         d.Wt = w.w; d.N = w.N; d.ntaps = 9; d.Kp = w.Kp;
@@ -239,6 +245,7 @@ struct Builder {
     Act vae_res(const VaeResW& r, const Act& x, const std::string& name);
     void vae_attn(Act& x);
     void build_vae(float inv_scale);
+    void build_vae_encoder();
 };
 
 // ResBlock._forward (openaimodel3d.py:208-234) followed by its TemporalConvBlock (:269-276)
@@ -614,10 +621,29 @@ __global__ void vae_stage_kernel(const float* __restrict__ z, int B, int C, int 
         const int hw = (int)(r % HW), f = (int)(r / HW);
         float v = 0.f;
         if (c < C) {
-            v = b[c];
-            for (int k = 0; k < C; ++k) v = fmaf(w[c * C + k], z[((int64_t)f * C + k) * HW + hw] * inv_scale, v);
+            if (w) {
+                v = b[c];
+                for (int k = 0; k < C; ++k) v = fmaf(w[c * C + k], z[((int64_t)f * C + k) * HW + hw] * inv_scale, v);
+            } else {
+                v = z[((int64_t)f * C + c) * HW + hw] * inv_scale;
+            }
         }
         tok[i] = v;
+    }
+}
+
+// moments[f][c][hw] = quant_conv(tok)[c] (autoencoder.py:100): 1x1 conv of the encoder's conv_out tokens [B*HW, C], written NCHW
+__global__ void vae_moments_kernel(const float* __restrict__ tok, int B, int C, int HW, const float* __restrict__ w,
+                                   const float* __restrict__ b, float* __restrict__ out) {
+    const int64_t total = (int64_t)B * C * HW;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int hw = (int)(i % HW);
+        const int c = (int)((i / HW) % C);
+        const int f = (int)(i / ((int64_t)HW * C));
+        const float* t = tok + ((int64_t)f * HW + hw) * C;
+        float v = b[c];
+        for (int k = 0; k < C; ++k) v = fmaf(w[c * C + k], t[k], v);
+        out[i] = v;
     }
 }
 
@@ -678,7 +704,7 @@ Act Builder::vae_res(const VaeResW& r, const Act& x, const std::string& name) {
 // sum to one); in place on x.
 void Builder::vae_attn(Act& x) {
     const VaeW& v = net->vae;
-    scope = "decoder.mid.attn_1";
+    scope = v.encoder ? "encoder.mid.attn_1" : "decoder.mid.attn_1";
     const int C = x.C, HW = x.H * x.W;
     const int64_t rows = (int64_t)NF * HW;
     if (HW % 64 != 0 || C % 64 != 0) { set_error("plan: the VAE attention needs H*W (%d) and C (%d) to be multiples of 64", HW, C); fail(MOCA_E_SHAPE); }
@@ -771,6 +797,71 @@ void Builder::build_vae(float inv_scale) {
         gnorm(h.p, h.st, h.C, nullptr, StatSrc(), 0, rows, h.H * h.W, v.norm_out, 1e-6f, 1, conv_dst(h.H, h.W, 1), h.H, h.W, pad, nullptr);
         plan->out_tok = (float*)palloc((size_t)rows * v.out_ch * sizeof(float));
         plan->out_C = v.out_ch;
+        conv3x3(pad, h.H, h.W, h.C, v.conv_out, 1, plan->out_tok, nullptr, 0, nullptr, nullptr);
+    }
+}
+
+// Encoder.forward (ae_modules.py:430-463); out_tok = conv_out tokens [B*h*w, mom_ch], quant_conv is applied by moca_vae_encode
+void Builder::build_vae_encoder() {
+    moca_unet* n = net;
+    const VaeW& v = n->vae;
+    const int L = (int)v.mult.size();
+    const int64_t rows0 = (int64_t)NF * H0 * W0;
+    plan->x_in = (float*)palloc((size_t)rows0 * v.in_ch * sizeof(float));
+    scope = "vae";
+    if (!dry) {
+        double* stats = plan->stats;
+        const size_t sb = plan->stats_bytes;
+        raw_push([=](cudaStream_t st) { return cudaMemsetAsync(stats, 0, sb, st) == cudaSuccess ? MOCA_OK : MOCA_E_CUDA; }, "memset stats", 0);
+    }
+    plan->launches += 1;
+    Act h;
+    h.H = H0; h.W = W0;
+    {
+        float* tok = (float*)palloc((size_t)rows0 * 64 * sizeof(float));
+        op_t* pad = scratch<op_t>(S_PAD, (size_t)NF * (H0 + 2) * (W0 + 2) * 64);
+        const float* x = plan->x_in;
+        const int b = NF, c = v.in_ch, hw = H0 * W0;
+        push([=](cudaStream_t st) {
+            const int64_t total = (int64_t)b * hw * 64;
+            const int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+            vae_stage_kernel<<<blocks, 256, 0, st>>>(x, b, c, hw, 1.0f, nullptr, nullptr, tok);
+            return cudaGetLastError() == cudaSuccess ? MOCA_OK : MOCA_E_CUDA;
+        }, 1, "vae stage");
+        convert(tok, 64, rows0, conv_dst(H0, W0, 1), H0, W0, pad);
+        h.C = v.ch;
+        h.p = (float*)palloc((size_t)rows0 * h.C * sizeof(float));
+        h.st = stat_alloc(h.C, H0 * W0);
+        conv3x3(pad, H0, W0, 64, v.conv_in, 1, h.p, nullptr, 0, nullptr, &h.st);
+    }
+    for (int lvl = 0; lvl < L; ++lvl) {
+        for (size_t j = 0; j < v.down[lvl].size(); ++j)
+            h = vae_res(v.down[lvl][j], h, "encoder.down." + std::to_string(lvl) + ".block." + std::to_string(j));
+        if (lvl != L - 1) {
+            // Downsample (ae_modules.py:80-100): F.pad (0,1,0,1) + 3x3 stride-2 conv without padding = the stride-2 tensor-map conv
+            // with its window starting AT the output pixel (no leading zero row / column); right / bottom zeros come from the TMA fill
+            scope = "encoder.down." + std::to_string(lvl) + ".downsample";
+            if ((h.H | h.W) & 1) { set_error("plan: odd image size %d x %d at the encoder's downsample %d", h.H, h.W, lvl); fail(MOCA_E_SHAPE); return; }
+            const int64_t rows = (int64_t)NF * h.H * h.W;
+            op_t* lin = scratch<op_t>(S_PAD, (size_t)rows * h.C);
+            convert(h.p, h.C, rows, DST_LINEAR, h.H, h.W, lin);
+            Act o; o.C = h.C; o.H = h.H / 2; o.W = h.W / 2;
+            o.p = (float*)palloc((size_t)NF * o.H * o.W * o.C * sizeof(float));
+            o.st = stat_alloc(o.C, o.H * o.W);
+            conv3x3(lin, h.H, h.W, h.C, v.downconv[lvl], 2, o.p, nullptr, 0, nullptr, &o.st, 0, 0);
+            h = o;
+        }
+    }
+    h = vae_res(v.mid1, h, "encoder.mid.block_1");
+    vae_attn(h);
+    h = vae_res(v.mid2, h, "encoder.mid.block_2");
+    scope = "encoder.out";
+    {
+        const int64_t rows = (int64_t)NF * h.H * h.W;
+        op_t* pad = scratch<op_t>(S_PAD, (size_t)NF * (h.H + 2) * (h.W + 2) * h.C);
+        gnorm(h.p, h.st, h.C, nullptr, StatSrc(), 0, rows, h.H * h.W, v.norm_out, 1e-6f, 1, conv_dst(h.H, h.W, 1), h.H, h.W, pad, nullptr);
+        plan->out_tok = (float*)palloc((size_t)rows * v.mom_ch * sizeof(float));
+        plan->out_C = v.mom_ch;
         conv3x3(pad, h.H, h.W, h.C, v.conv_out, 1, plan->out_tok, nullptr, 0, nullptr, nullptr);
     }
 }
@@ -871,7 +962,7 @@ static int run_plan(Plan* plan, cudaStream_t st, const char* who) {
 extern "C" int32_t moca_vae_decode(moca_unet* n, const float* z, int32_t B, int32_t H, int32_t W, float scale_factor, float* image,
                                    void* stream) {
     MOCA_REQUIRE(n && z && image, MOCA_E_ARG, "moca_vae_decode: NULL argument");
-    MOCA_REQUIRE(n->vae.present, MOCA_E_STATE, "moca_vae_decode: handle was not made by moca_vae_create");
+    MOCA_REQUIRE(n->vae.present && !n->vae.encoder, MOCA_E_STATE, "moca_vae_decode: handle was not made by moca_vae_create");
     MOCA_REQUIRE(n->finalized, MOCA_E_STATE, "moca_vae_decode: call moca_unet_finalize after loading the weights");
     MOCA_REQUIRE(B > 0 && B <= 16 && H > 0 && W > 0 && scale_factor != 0.f, MOCA_E_SHAPE, "moca_vae_decode: bad shape B=%d H=%d W=%d", B, H, W);
     const int up = 1 << ((int)n->vae.mult.size() - 1);
@@ -895,10 +986,42 @@ extern "C" int32_t moca_vae_decode(moca_unet* n, const float* z, int32_t B, int3
     return tokens_to_ncthw(plan->out_tok, n->vae.out_ch, B, n->vae.out_ch, 1, H * up, W * up, image, st);
 }
 
+// AutoencoderKL.encode up to the posterior's parameters (autoencoder.py:97-102): x [B, in_ch, H, W] fp32 image in [-1, 1] ->
+// moments [B, 2 zc, H / 2^(L-1), W / 2^(L-1)] fp32 (mean | logvar, what DiagonalGaussianDistribution is built from)
+extern "C" int32_t moca_vae_encode(moca_unet* n, const float* x, int32_t B, int32_t H, int32_t W, float* moments, void* stream) {
+    MOCA_REQUIRE(n && x && moments, MOCA_E_ARG, "moca_vae_encode: NULL argument");
+    MOCA_REQUIRE(n->vae.present && n->vae.encoder, MOCA_E_STATE, "moca_vae_encode: handle was not made by moca_vae_encoder_create");
+    MOCA_REQUIRE(n->finalized, MOCA_E_STATE, "moca_vae_encode: call moca_unet_finalize after loading the weights");
+    const int down = 1 << ((int)n->vae.mult.size() - 1);
+    MOCA_REQUIRE(B > 0 && B <= 16 && H > 0 && W > 0 && H % down == 0 && W % down == 0, MOCA_E_SHAPE,
+                 "moca_vae_encode: bad shape B=%d H=%d W=%d (multiples of %d)", B, H, W, down);
+    MOCA_REQUIRE((int64_t)B * (H + 2) * (W + 2) < (1ll << 31) / 64, MOCA_E_SHAPE, "moca_vae_encode: B=%d frames of %d x %d are too many rows", B, H, W);
+    cudaStream_t st = (cudaStream_t)stream;
+    std::vector<int> key{B, 1, H, W, -2, 0};
+    Plan* plan = nullptr;
+    auto it = n->plans.find(key);
+    if (it != n->plans.end()) { it->second->last_use = ++n->use_clock; plan = it->second.get(); }
+    else {
+        int rc = make_plan(n, key, B, 1, H, W, 0, false, [](Builder& b) { b.build_vae_encoder(); }, &plan);
+        if (rc) return rc;
+    }
+    n->last = plan;
+    MOCA_CHECK_CUDA(cudaMemcpyAsync(plan->x_in, x, (size_t)B * n->vae.in_ch * H * W * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    int rc = run_plan(plan, st, "moca_vae_encode");
+    if (rc) return rc;
+    const int hw = (H / down) * (W / down), C = n->vae.mom_ch;
+    const int64_t total = (int64_t)B * C * hw;
+    vae_moments_kernel<<<(int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16), 256, 0, st>>>(plan->out_tok, B, C, hw, n->vae.q_w,
+                                                                                                             n->vae.q_b, moments);
+    MOCA_LAUNCH_CHECK();
+    return MOCA_OK;
+}
+
 extern "C" int32_t moca_unet_forward(moca_unet* n, const float* x, const int32_t* timesteps, const float* context,
                                      const int32_t* ctx_len, int32_t Lmax, const int32_t* fps, int32_t B, int32_t T, int32_t H,
                                      int32_t W, float* y, void* stream) {
     MOCA_REQUIRE(n && x && timesteps && context && ctx_len && fps && y, MOCA_E_ARG, "moca_unet_forward: NULL argument");
+    MOCA_REQUIRE(!n->vae.present, MOCA_E_STATE, "moca_unet_forward: this handle is a VAE (moca_vae_decode / moca_vae_encode)");
     MOCA_REQUIRE(n->finalized, MOCA_E_STATE, "moca_unet_forward: call moca_unet_finalize after loading the weights");
     MOCA_REQUIRE(B > 0 && T > 0 && H > 0 && W > 0 && Lmax > 0, MOCA_E_SHAPE, "moca_unet_forward: bad shape");
     // fps: int32[B], one entry per sample (the Python mirror validates the length: a shorter array would be read past its end)

@@ -11,8 +11,9 @@ the critical path of the FIFO loop.
 * ``FrameWriter``         frame -> uint8 image (funcs.py:626-637 ``tensor2image``) and PNG / GIF writing on a worker thread, so the
                           device loop never waits for the file system (the reference saves inside the loop, funcs.py:359-365).
 * ``run_prompts``         the per-prompt loop of ``main`` on this package's sampler + FIFO queue, for a model object that offers the
-                          reference's ``get_learned_conditioning`` / ``decode_first_stage_2DAE`` (CLIP and the VAE are rows N4 / N1:
-                          they are the reference's own modules here).
+                          reference's ``get_learned_conditioning`` / ``decode_first_stage_2DAE`` (the decoder is the library's,
+                          vae.py / row N1, after ``patch_reference()`` or as ``LatentDiffusionB200(first_stage=...)``; the text
+                          tower, row N4, is the reference's own module).
 * ``main``                ``python -m moca_video_b200.driver`` / torchrun launcher: patches the reference tree and calls its ``main``
                           unchanged, one process per GPU; ``--parallel windows`` shards the FIFO windows over the ranks (NCCL
                           hand-off inside the library), ``--parallel prompts`` shards the prompt list like the reference.
@@ -179,8 +180,8 @@ def run_prompts(args, model, sampler_cls=None, cond_image=None, decode=None, par
     """The prompt loop of videocrafter_main.py:176-232 on this package's sampler and FIFO queue.
 
     ``model``: offers ``get_learned_conditioning(list[str])`` (text tower) and, unless ``decode`` is given,
-    ``decode_first_stage_2DAE(z)`` (VAE, N1) — the reference's LatentDiffusion after ``patch_reference()``, or
-    ``LatentDiffusionB200`` with those two callables attached.  ``parallel``: "windows" — every rank works on every prompt and
+    ``decode_first_stage_2DAE(z)`` (VAE, N1) — the reference's LatentDiffusion after ``patch_reference()`` (its decode is then
+    the library's), or ``LatentDiffusionB200(first_stage=AutoencoderKLDecoder(...))`` with a text encoder attached.  ``parallel``: "windows" — every rank works on every prompt and
     the FIFO windows of an iteration are sharded over the ranks (fifo.fifo_ddim_sampling); "prompts" — the reference's
     ``indices[rank::num_processes]`` split, each rank runs whole prompts alone.  Returns {prompt index: video path} of the
     prompts this rank wrote."""

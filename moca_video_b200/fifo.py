@@ -9,8 +9,8 @@
                                           iteration (NCCL over NVLink), every rank then applies the same shift.
 RNG parity: the noise stream is the reference's (window 2n-1 .. 0, one draw per frame, then the shift's tail draw) from
 an identically seeded generator on every rank; a rank draws only the windows it owns and advances the generator's
-Philox offset past the others (``_NoiseStream``), so 1-GPU and G-GPU runs produce the same queue without 8x the launches.  VAE decode of the popped frame and PNG writing are out of scope: popped
-latent frames are returned (or handed to ``on_frame``).
+Philox offset past the others (``_NoiseStream``), so 1-GPU and G-GPU runs produce the same queue without 8x the launches.  Popped latent frames are returned (or handed to ``on_frame``: driver.run_prompts decodes them with the library's VAE
+decoder, vae.py, and writes the images on a worker thread).
 """
 import numpy as np
 import torch

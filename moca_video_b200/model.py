@@ -2,7 +2,8 @@
 
 Carries the DDPM schedule buffers (register_schedule, ddpm3d.py:113-141), ``use_scale`` / ``scale_arr`` (:362-376) and
 ``apply_model`` (:512-527 -> DiffusionWrapper.forward :702-712: concatenate ``c_crossattn`` along tokens, pass ``fps``).
-VAE and CLIP are out of scope for this path: text embeddings are inputs.
+``first_stage`` (optional): an ``AutoencoderKLDecoder`` (vae.py) behind ``decode_first_stage_2DAE`` (:555-562).
+The text tower is not part of this path: text embeddings are inputs.
 """
 import numpy as np
 import torch
@@ -12,8 +13,13 @@ from .unet import UNet3D
 
 
 class LatentDiffusionB200:
-    def __init__(self, unet: UNet3D, timesteps=1000, linear_start=0.00085, linear_end=0.012, use_scale=True, fps=10):
+    def __init__(self, unet: UNet3D, timesteps=1000, linear_start=0.00085, linear_end=0.012, use_scale=True, fps=10,
+                 first_stage=None, scale_factor=0.18215):
         self.unet = unet
+        self.first_stage_model = first_stage
+        self.scale_factor = float(scale_factor)
+        if first_stage is not None:
+            first_stage.scale_factor = self.scale_factor
         self.device = unet.device
         self.num_timesteps = timesteps
         betas = linear_betas(timesteps, linear_start, linear_end)
@@ -24,6 +30,13 @@ class LatentDiffusionB200:
         self.use_scale = use_scale
         self.scale_arr = torch.tensor(scale_array_f32(), dtype=torch.float32)
         self.default_fps = fps
+
+    def decode_first_stage_2DAE(self, z, **kwargs):
+        """ddpm3d.py:555-562: z [b, zc, t, h, w] sampler latents -> frames [b, 3, t, 8h, 8w] in [-1, 1]."""
+        if self.first_stage_model is None:
+            from ._lib import MocaError
+            raise MocaError("LatentDiffusionB200.decode_first_stage_2DAE: constructed without first_stage (an AutoencoderKLDecoder)")
+        return self.first_stage_model.decode_first_stage_2DAE(z)
 
     @staticmethod
     def _context(c):

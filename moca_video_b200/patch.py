@@ -15,8 +15,13 @@ Rebound (``REBOUND`` lists them; tests/test_patch.py checks each against the ref
   lvdm.models.samplers.ddim.DDIMSampler.make_schedule / unet / fifo_onestep / ddim_step / p_sample_ddim
   utils.freeinit_utils.freq_mix_3d / get_freq_filter
   scripts.evaluation.funcs.prepare_latents / shift_latents / fifo_ddim_sampling (+ its imported FreeInit names)
-Not rebound: VAE decode / encode (``model.decode_first_stage_2DAE``) — the rebound ``fifo_ddim_sampling`` calls
-the reference's own decoder on every popped frame, exactly where the reference does (funcs.py:359-365).
+  lvdm.models.autoencoder.AutoencoderKL.decode / .encode         -> AutoencoderKLDecoder.decode (moca_vae_decode) /
+                                                                    AutoencoderKLEncoder.encode_moments (moca_vae_encode); SURVEY N1
+  lvdm.models.ddpm3d.LatentDiffusion.decode_first_stage_2DAE     -> the same decoder, frames grouped per call instead of one
+                                                                    ``decode`` per frame (ddpm3d.py:555-562)
+      (both need pytorch_lightning to import; where it is absent they are skipped and reported False)
+The rebound ``fifo_ddim_sampling`` calls ``model.decode_first_stage_2DAE`` on every popped frame, exactly where the reference
+does (funcs.py:359-365).  Not rebound: the text encoder.
 """
 import importlib
 import os
@@ -27,12 +32,15 @@ from . import fifo, ops
 from ._lib import MocaError
 from .sampler import DDIMSampler as _B200Sampler
 from .unet import UNet3D
+from .vae import DiagonalGaussian, attach_vae, attach_vae_encoder
 
 REBOUND = {
     "lvdm.modules.networks.openaimodel3d": ["UNetModel.forward", "ResBlock.forward"],
     "lvdm.modules.attention": ["SpatialTransformer.forward", "TemporalTransformer.forward"],
     "lvdm.models.samplers.ddim": ["DDIMSampler.make_schedule", "DDIMSampler.unet", "DDIMSampler.fifo_onestep", "DDIMSampler.ddim_step",
                                   "DDIMSampler.p_sample_ddim"],
+    "lvdm.models.autoencoder": ["AutoencoderKL.decode", "AutoencoderKL.encode"],
+    "lvdm.models.ddpm3d": ["LatentDiffusion.decode_first_stage_2DAE"],
     "utils.freeinit_utils": ["freq_mix_3d", "get_freq_filter"],
     "scripts.evaluation.funcs": ["prepare_latents", "shift_latents", "fifo_ddim_sampling", "freq_mix_3d", "get_freq_filter"],
 }
@@ -143,6 +151,31 @@ def _temporal_tf_forward(self, x, context=None):
     return eng.layer_forward(name, x)
 
 
+def _ae_decode(self, z, **kwargs):
+    """Replacement body of AutoencoderKL.decode (autoencoder.py:104-107): z [n, zc, h, w], already divided by scale_factor."""
+    return attach_vae(self, device=z.device).decode(z).to(z.dtype)
+
+
+def _ae_encode(self, x, **kwargs):
+    """Replacement body of AutoencoderKL.encode (autoencoder.py:97-102): the posterior over z for images x [n, 3, H, W]; the
+    returned object has the reference distribution's ``sample`` / ``mode`` / ``parameters`` (lvdm/distributions.py:24-43), which is
+    what get_first_stage_encoding (ddpm3d.py:458-465) consumes; that function tests isinstance, so the reference class is used when it
+    imports."""
+    mom = attach_vae_encoder(self, device=x.device).encode_moments(x).to(x.dtype)
+    try:
+        from lvdm.distributions import DiagonalGaussianDistribution
+        return DiagonalGaussianDistribution(mom)
+    except ImportError:
+        return DiagonalGaussian(mom)
+
+
+def _decode_first_stage_2DAE(self, z, **kwargs):
+    """Replacement body of LatentDiffusion.decode_first_stage_2DAE (ddpm3d.py:555-562): z [b, zc, t, h, w]."""
+    eng = attach_vae(self.first_stage_model, device=z.device)
+    eng.scale_factor = float(self.scale_factor)
+    return eng.decode_first_stage_2DAE(z).to(z.dtype)
+
+
 def _get_freq_filter(shape, device, filter_type, n, d_s, d_t):
     """utils/freeinit_utils.py:51-70; returns a [T,H,W] tensor that broadcasts like the reference's mask."""
     return ops.freeinit_filter(shape, device, filter_type, n, d_s, d_t)
@@ -200,6 +233,18 @@ def patch_reference():
     if m is not None:
         m.SpatialTransformer.forward = _spatial_tf_forward
         m.TemporalTransformer.forward = _temporal_tf_forward
+    # (under a stubbed pytorch_lightning the two classes below are not real classes: leave them alone)
+    m = mods["lvdm.models.autoencoder"]
+    if m is not None and isinstance(getattr(m, "AutoencoderKL", None), type):
+        m.AutoencoderKL.decode = _ae_decode
+        m.AutoencoderKL.encode = _ae_encode
+    else:
+        mods["lvdm.models.autoencoder"] = None
+    m = mods["lvdm.models.ddpm3d"]
+    if m is not None and isinstance(getattr(m, "LatentDiffusion", None), type):
+        m.LatentDiffusion.decode_first_stage_2DAE = _decode_first_stage_2DAE
+    else:
+        mods["lvdm.models.ddpm3d"] = None
     m = mods["lvdm.models.samplers.ddim"]
     if m is not None:
         S = m.DDIMSampler

@@ -422,7 +422,7 @@ VAE_SMALL = dict(ch=64, ch_mult=(1, 2, 2), num_res_blocks=1, z_channels=4, out_c
 
 
 def gen_vae_small():
-    """Reference Decoder + post_quant_conv (ae_modules.py:466-578, autoencoder.py:104-107) vs oracle.vae_ref on seeded weights:
+    """Reference AutoencoderKL.decode (autoencoder.py:104-107; Decoder ae_modules.py:466-578) vs oracle.vae_ref on seeded weights:
     a shrunk ddconfig (64 channels, three levels), then the key / shape listing of the shipped ddconfig."""
     import hashlib
     import yaml
@@ -431,32 +431,46 @@ def gen_vae_small():
     from moca_video_b200.vae import decoder_param_shapes
     from oracle.vae_ref import random_vae_state_dict, vae_decode
 
-    def ref_model(dd):
-        dec = Decoder(ch=dd["ch"], out_ch=dd["out_ch"], ch_mult=dd["ch_mult"], num_res_blocks=dd["num_res_blocks"], attn_resolutions=[],
-                      in_channels=3, resolution=64, z_channels=dd["z_channels"])
-        pq = torch.nn.Conv2d(dd["z_channels"], dd["z_channels"], 1)
-        return dec, pq
+    from lvdm.models.autoencoder import AutoencoderKL
 
     dd = VAE_SMALL
-    dec, pq = ref_model(dd)
+    ae = AutoencoderKL(dict(dd, double_z=True, resolution=64, in_channels=3, attn_resolutions=[], dropout=0.0),
+                       {"target": "torch.nn.Identity"}, dd["z_channels"]).eval()
     shapes = decoder_param_shapes(**dd)
-    ref_shapes = {"post_quant_conv." + k: tuple(v.shape) for k, v in pq.state_dict().items()}
-    ref_shapes.update({"decoder." + k: tuple(v.shape) for k, v in dec.state_dict().items()})
+    ref_shapes = {k: tuple(v.shape) for k, v in ae.state_dict().items() if k.startswith(("decoder.", "post_quant_conv."))}
     assert ref_shapes == {k: tuple(v) for k, v in shapes.items()}, set(ref_shapes) ^ set(shapes)
     sd = random_vae_state_dict(shapes, seed=3)
-    dec.load_state_dict({k[len("decoder."):]: v for k, v in sd.items() if k.startswith("decoder.")}, strict=True)
-    pq.load_state_dict({k[len("post_quant_conv."):]: v for k, v in sd.items() if k.startswith("post_quant_conv.")}, strict=True)
+    missing, unexpected = ae.load_state_dict(sd, strict=False)
+    assert not unexpected and all(k.startswith(("encoder.", "quant_conv.", "loss.")) for k in missing), (missing[:3], unexpected[:3])
     rng = np.random.default_rng(31)
     out = {}
     for tag, (n, h, w) in {"a": (2, 8, 8), "b": (1, 8, 16)}.items():
         z = torch.from_numpy(rng.standard_normal((n, 4, h, w)).astype(np.float32))
         with torch.no_grad():
-            y_ref = dec(pq(z))
+            y_ref = ae.decode(z)                                   # the unmodified AutoencoderKL.decode (autoencoder.py:104-107)
             y = vae_decode(sd, z, len(dd["ch_mult"]), dd["num_res_blocks"])
         err = float((y - y_ref).norm() / y_ref.norm())
         print(f"vae_small[{tag}] restatement vs reference rel-L2 = {err:.3e}, |y| = {float(y_ref.abs().mean()):.3f}")
         assert err < 1e-5
         out.update({f"{tag}_z": _np(z), f"{tag}_y": _np(y_ref)})
+    # encode path: the unmodified AutoencoderKL.encode (autoencoder.py:97-102) on seeded encoder weights
+    from moca_video_b200.vae import encoder_param_shapes
+    from oracle.vae_ref import vae_encode_moments
+    eshapes = encoder_param_shapes(dd["ch"], dd["ch_mult"], dd["num_res_blocks"], dd["z_channels"])
+    ref_e = {k: tuple(v.shape) for k, v in ae.state_dict().items() if k.startswith(("encoder.", "quant_conv."))}
+    assert ref_e == {k: tuple(v) for k, v in eshapes.items()}, set(ref_e) ^ set(eshapes)
+    esd = random_vae_state_dict(eshapes, seed=4)
+    missing, unexpected = ae.load_state_dict(esd, strict=False)
+    assert not unexpected
+    for tag, (n, h, w) in {"ea": (2, 64, 64), "eb": (1, 32, 64)}.items():
+        x = torch.from_numpy(rng.uniform(-1, 1, (n, 3, h, w)).astype(np.float32))
+        with torch.no_grad():
+            post = ae.encode(x)
+            m = vae_encode_moments(esd, x, len(dd["ch_mult"]), dd["num_res_blocks"])
+        err = float((m - post.parameters).norm() / post.parameters.norm())
+        print(f"vae_small[{tag}] encoder restatement vs reference rel-L2 = {err:.3e}, |m| = {float(post.parameters.abs().mean()):.3f}")
+        assert err < 1e-5
+        out.update({f"{tag}_x": _np(x), f"{tag}_moments": _np(post.parameters)})
     # shipped ddconfig: listing equality on the meta device (no forward: 49.5 M parameters at 320 x 512 take minutes on CPU)
     with open(os.path.join(refimport.REF, "configs/inference_t2v_512_v2.0.yaml")) as f:
         full = yaml.safe_load(f)["model"]["params"]["first_stage_config"]["params"]["ddconfig"]
@@ -466,6 +480,15 @@ def gen_vae_small():
     fshapes.update({"post_quant_conv.weight": (4, 4, 1, 1), "post_quant_conv.bias": (4,)})
     mine = decoder_param_shapes(full["ch"], tuple(full["ch_mult"]), full["num_res_blocks"], full["z_channels"], full["out_ch"])
     assert fshapes == {k: tuple(v) for k, v in mine.items()}
+    from lvdm.modules.networks.ae_modules import Encoder
+    with torch.device("meta"):
+        fenc = Encoder(**full)
+    feshapes = {"encoder." + k: tuple(v.shape) for k, v in fenc.state_dict().items()}
+    feshapes.update({"quant_conv.weight": (8, 8, 1, 1), "quant_conv.bias": (8,)})
+    emine = encoder_param_shapes(full["ch"], tuple(full["ch_mult"]), full["num_res_blocks"], full["z_channels"], full["in_channels"], full["double_z"])
+    assert feshapes == {k: tuple(v) for k, v in emine.items()}
+    out["full_enc_shapes_sha256"] = np.array(hashlib.sha256("\n".join(f"{k} {v}" for k, v in sorted(feshapes.items())).encode()).hexdigest())
+    out["full_enc_n_params"] = np.int64(sum(int(np.prod(v)) for v in feshapes.values()))
     listing = "\n".join(f"{k} {v}" for k, v in sorted(fshapes.items()))
     out["full_shapes_sha256"] = np.array(hashlib.sha256(listing.encode()).hexdigest())
     out["full_n_params"] = np.int64(sum(int(np.prod(v)) for v in fshapes.values()))

@@ -81,3 +81,34 @@ def random_vae_state_dict(shapes, seed=0):
         else:
             sd[k] = 0.05 * torch.randn(shp, generator=g)
     return sd
+
+
+def vae_encode_moments(sd, x, n_levels, num_res_blocks):
+    """AutoencoderKL.encode up to the posterior's parameters (autoencoder.py:97-102; Encoder.forward ae_modules.py:430-463;
+    Downsample.forward :93-100): x [n, 3, H, W] -> moments [n, 2 zc, H / 2^(L-1), W / 2^(L-1)]."""
+    sd = {k: v.float() for k, v in sd.items()}
+    h = _conv(x.float(), sd, "encoder.conv_in", 1)
+    for lvl in range(n_levels):
+        for j in range(num_res_blocks):
+            h = _res(h, sd, f"encoder.down.{lvl}.block.{j}")
+        if lvl != n_levels - 1:
+            h = F.pad(h, (0, 1, 0, 1), mode="constant", value=0)
+            h = F.conv2d(h, sd[f"encoder.down.{lvl}.downsample.conv.weight"], sd[f"encoder.down.{lvl}.downsample.conv.bias"], stride=2)
+    h = _res(h, sd, "encoder.mid.block_1")
+    h = _attn(h, sd, "encoder.mid.attn_1")
+    h = _res(h, sd, "encoder.mid.block_2")
+    h = _conv(F.silu(_gn(h, sd, "encoder.norm_out")), sd, "encoder.conv_out", 1)
+    return _conv(h, sd, "quant_conv", 0)
+
+
+def posterior_sample(moments, noise):
+    """DiagonalGaussianDistribution.sample (lvdm/distributions.py:24-43)."""
+    mean, logvar = torch.chunk(moments, 2, dim=1)
+    return mean + torch.exp(0.5 * torch.clamp(logvar, -30.0, 20.0)) * noise
+
+
+def encode_first_stage_2DAE(sd, x, scale_factor, n_levels, num_res_blocks, noise):
+    """ddpm3d.py:485-490 with get_first_stage_encoding (:458-465): x [b, 3, t, H, W], noise [b, zc, t, h, w]."""
+    outs = [scale_factor * posterior_sample(vae_encode_moments(sd, x[:, :, i], n_levels, num_res_blocks), noise[:, :, i]).unsqueeze(2)
+            for i in range(x.shape[2])]
+    return torch.cat(outs, dim=2)

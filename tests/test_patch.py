@@ -24,6 +24,9 @@ ORIGINAL_AT = {                                   # reference definitions the re
     "lvdm.models.samplers.ddim:DDIMSampler.fifo_onestep": "ddim.py:255",
     "lvdm.models.samplers.ddim:DDIMSampler.ddim_step": "ddim.py:377",
     "lvdm.models.samplers.ddim:DDIMSampler.p_sample_ddim": "ddim.py:274",
+    "lvdm.models.autoencoder:AutoencoderKL.decode": "autoencoder.py:104",
+    "lvdm.models.autoencoder:AutoencoderKL.encode": "autoencoder.py:97",
+    "lvdm.models.ddpm3d:LatentDiffusion.decode_first_stage_2DAE": "ddpm3d.py:556",
     "utils.freeinit_utils:freq_mix_3d": "freeinit_utils.py:7",
     "utils.freeinit_utils:get_freq_filter": "freeinit_utils.py:51",
     "scripts.evaluation.funcs:prepare_latents": "funcs.py:21",
@@ -105,6 +108,17 @@ def test_patched_calls_reach_the_device_boundary(patched):
         net.input_blocks[1][1](torch.zeros(16, 64, 8, 8), context=torch.zeros(16, 7, 64))
     with pytest.raises(MocaError, match="not attached"):
         net.input_blocks[1][2](torch.zeros(1, 64, 16, 8, 8))
+    # first-stage decode through the reference's own AutoencoderKL / decode_first_stage_2DAE call shapes
+    dd = dict(double_z=True, z_channels=4, resolution=64, in_channels=3, out_ch=3, ch=64, ch_mult=(1, 2, 2), num_res_blocks=1,
+              attn_resolutions=[], dropout=0.0)
+    ae = mods["lvdm.models.autoencoder"].AutoencoderKL(dd, {"target": "torch.nn.Identity"}, 4)
+    with pytest.raises(MocaError):
+        ae.decode(torch.zeros(1, 4, 8, 8))
+    with pytest.raises(MocaError):
+        ae.encode(torch.zeros(1, 3, 64, 64))
+    ld = types.SimpleNamespace(first_stage_model=ae, scale_factor=0.18215)
+    with pytest.raises(MocaError):
+        mods["lvdm.models.ddpm3d"].LatentDiffusion.decode_first_stage_2DAE(ld, torch.zeros(1, 4, 2, 8, 8))
     # sampler through the reference's own constructor path (oracle/refimport's CPU subclass) and LatentDiffusion-like apply_model
     seen = []
 

@@ -35,7 +35,7 @@ rows = dec.profile(3)
 tot = sum(r[0] for r in rows)
 print(f"per-op sum {tot / 1e3:.2f} ms per call")
 for us, gf, label in sorted(rows, reverse=True)[:25]:
-    print(f"{us:9.1f} us {gf / us * 1e-3 if us else 0:8.1f} TF/s  {label}")
+    print(f"{us:9.1f} us {gf / us * 1e3 if us else 0:8.1f} TF/s  {label}")
 if len(sys.argv) > 2:
     with open(sys.argv[2], "w") as f:
         f.write("us,gflop,label\n")
