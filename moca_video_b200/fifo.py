@@ -23,7 +23,10 @@ def prepare_latents(args, input_path, sampler, model=None, data=None, initial_la
     """funcs.py:21-82.  ``initial_latents`` replaces the reference's torch.load(f"{input_path}/{S}.pt") when given;
     ``noise`` [B,C,Q,H,W] replaces the per-slot randn_like draws (same order: look-ahead copies first)."""
     if data is not None:
-        raise NotImplementedError("prepare_latents: the DAVIS branch needs the VAE encoder (out of scope, SURVEY N1)")
+        # DAVIS branch (funcs.py:38-47): the queue starts from the encoded video frames instead of the cached base sample
+        if model is None or not hasattr(model, "encode_first_stage_2DAE"):
+            raise ValueError("prepare_latents: data=(frames, masks) needs a model with encode_first_stage_2DAE (the VAE encoder)")
+        initial_latents = model.encode_first_stage_2DAE(_rgb(data[0]).to("cuda"))
     if initial_latents is None:
         initial_latents = torch.load(f"{input_path}/{args.num_inference_steps}.pt")
     z = initial_latents.to("cuda", dtype=torch.float32).contiguous()
@@ -38,23 +41,39 @@ def prepare_latents(args, input_path, sampler, model=None, data=None, initial_la
     return ops.renoise(z, noise, src, alpha)
 
 
+def _rgb(frames):
+    """funcs.py:43-44 / :103-104: RGBA frames lose their alpha channel."""
+    return frames[:, :3] if frames.shape[1] == 4 else frames
+
+
 _filter_cache = {}
 
 
 def shift_latents(latents, davis_data=None, model=None, new_noise=None, generator=None):
     """funcs.py:86-99 (non-DAVIS branch): anchor = frame 0; queue shifts left by one; the new tail frame is
     freq_mix_3d(anchor, N(0,1), gaussian LPF(d_s=d_t=0.25)) built for a T=1 volume."""
-    if davis_data is not None:
-        raise NotImplementedError("shift_latents: the DAVIS branch needs the VAE encoder (out of scope, SURVEY N1)")
     B, C, Q, H, W = latents.shape
-    anchor = ops.window_gather(latents, 0, 1)
+    if davis_data is not None:
+        # DAVIS branch (funcs.py:100-116): the anchor is the encoded LAST video frame, re-encoded every call like the reference
+        # (its posterior sample draws fresh host noise each time); the mask queue shifts with the latents and returns with them
+        if model is None or not hasattr(model, "encode_first_stage_2DAE"):
+            raise ValueError("shift_latents: davis_data needs a model with encode_first_stage_2DAE (the VAE encoder)")
+        frames, masks = davis_data
+        anchor = model.encode_first_stage_2DAE(_rgb(frames[:, :, -1:]).to(latents.device)).to(torch.float32).contiguous()
+    else:
+        anchor = ops.window_gather(latents, 0, 1)
     if new_noise is None:
         new_noise = torch.randn((B, C, H, W), device=latents.device, generator=generator).unsqueeze(2)
     key = (H, W, latents.device.index)
     if key not in _filter_cache:      # the reference rebuilds the filter on the CPU every call (freeinit_utils.py:73-91)
         _filter_cache[key] = ops.freeinit_filter((1, H, W), latents.device, "gaussian", 1, 0.25, 0.25)
     tail = ops.freq_mix_3d(anchor, new_noise.reshape(B, C, 1, H, W), _filter_cache[key])
-    return ops.queue_shift(latents, tail)
+    out = ops.queue_shift(latents, tail)
+    if davis_data is not None:
+        if masks is not None:
+            masks = torch.cat([masks[:, :, 1:], masks[:, :, -1:]], dim=2)     # funcs.py:114-115 (the tail keeps its own value)
+        return out, (frames, masks)
+    return out
 
 
 class _NoiseStream:
@@ -124,7 +143,8 @@ def fifo_ddim_sampling(args, model, conditioning, noise_shape, ddim_sampler, cfg
 
     ``unconditional_conditioning``: the reference encodes "" with CLIP here (funcs.py:267-276); CLIP is out of scope, so
     the embedding is an input (or ``model.get_learned_conditioning`` is used when the model has it).
-    ``masks`` [B,1,Q,H,W]: per-queue-slot masks (the reference's DAVIS masks).  ``group``: torch.distributed group to
+    ``masks`` [B,1,Q,H,W]: per-queue-slot masks (the reference's DAVIS masks); ``davis_data`` = (frames [B,3|4,T,H*8,W*8], masks): the
+    reference's DAVIS mode — the queue starts from the encoded frames and the shift anchors on the encoded last frame (VAE encoder).  ``group``: torch.distributed group to
     shard windows over (None = the default group if initialised, else single GPU).  ``queue_out``: dict that receives the
     final queue (``latents``, ``masks``) so a caller can continue the run.  ``shard=False`` runs every window on the calling
     rank even when a process group exists (the 1-GPU replay the multi-GPU equality checks compare with)."""
@@ -139,7 +159,10 @@ def fifo_ddim_sampling(args, model, conditioning, noise_shape, ddim_sampler, cfg
             uc = dict(cond)
             uc["c_crossattn"] = [uc_emb]
     if latents is None:
-        latents = prepare_latents(args, latents_dir, ddim_sampler, model, generator=generator)
+        latents = prepare_latents(args, latents_dir, ddim_sampler, model, data=davis_data, generator=generator)
+    if davis_data is not None and masks is None and davis_data[1] is not None:
+        masks = davis_data[1].to(latents.device, dtype=torch.float32).contiguous()       # funcs.py:297-301
+        davis_data = (davis_data[0], masks)
     B, C, Q, H, W = latents.shape
     f = args.video_length
     half = f // 2
@@ -199,9 +222,13 @@ def fifo_ddim_sampling(args, model, conditioning, noise_shape, ddim_sampler, cfg
             on_frame(it, frame)
         popped.append(frame)
         # funcs.py:93 draws randn_like(latents[:, :, -1]) = [B,C,H,W]; same element count and Philox consumption as one frame
-        latents = shift_latents(latents, new_noise=stream.block(1))
-        if masks is not None:
-            masks = ops.queue_shift(masks, ops.window_gather(masks, Q - 1, 1))
+        if davis_data is not None and masks is not None:
+            latents, davis_data = shift_latents(latents, davis_data, model, new_noise=stream.block(1))       # funcs.py:368-369
+            masks = davis_data[1]
+        else:
+            latents = shift_latents(latents, new_noise=stream.block(1))
+            if masks is not None:
+                masks = ops.queue_shift(masks, ops.window_gather(masks, Q - 1, 1))
     if queue_out is not None:
         queue_out["latents"], queue_out["masks"] = latents, masks
     return popped

@@ -2,7 +2,8 @@
 
 Carries the DDPM schedule buffers (register_schedule, ddpm3d.py:113-141), ``use_scale`` / ``scale_arr`` (:362-376) and
 ``apply_model`` (:512-527 -> DiffusionWrapper.forward :702-712: concatenate ``c_crossattn`` along tokens, pass ``fps``).
-``first_stage`` (optional): an ``AutoencoderKLDecoder`` (vae.py) behind ``decode_first_stage_2DAE`` (:555-562).
+``first_stage`` / ``first_stage_encoder`` (optional): ``AutoencoderKLDecoder`` / ``AutoencoderKLEncoder`` (vae.py) behind
+``decode_first_stage_2DAE`` (:555-562) and ``encode_first_stage_2DAE`` (:485-490).
 The text tower is not part of this path: text embeddings are inputs.
 """
 import numpy as np
@@ -14,12 +15,14 @@ from .unet import UNet3D
 
 class LatentDiffusionB200:
     def __init__(self, unet: UNet3D, timesteps=1000, linear_start=0.00085, linear_end=0.012, use_scale=True, fps=10,
-                 first_stage=None, scale_factor=0.18215):
+                 first_stage=None, scale_factor=0.18215, first_stage_encoder=None):
         self.unet = unet
         self.first_stage_model = first_stage
         self.scale_factor = float(scale_factor)
-        if first_stage is not None:
-            first_stage.scale_factor = self.scale_factor
+        self.first_stage_encoder = first_stage_encoder
+        for part in (first_stage, first_stage_encoder):
+            if part is not None:
+                part.scale_factor = self.scale_factor
         self.device = unet.device
         self.num_timesteps = timesteps
         betas = linear_betas(timesteps, linear_start, linear_end)
@@ -37,6 +40,13 @@ class LatentDiffusionB200:
             from ._lib import MocaError
             raise MocaError("LatentDiffusionB200.decode_first_stage_2DAE: constructed without first_stage (an AutoencoderKLDecoder)")
         return self.first_stage_model.decode_first_stage_2DAE(z)
+
+    def encode_first_stage_2DAE(self, x, noise=None):
+        """ddpm3d.py:485-490: x [b, 3, t, H, W] frames in [-1, 1] -> scale_factor * sample(posterior) [b, zc, t, H/8, W/8]."""
+        if self.first_stage_encoder is None:
+            from ._lib import MocaError
+            raise MocaError("LatentDiffusionB200.encode_first_stage_2DAE: constructed without first_stage_encoder (an AutoencoderKLEncoder)")
+        return self.first_stage_encoder.encode_first_stage_2DAE(x, noise=noise)
 
     @staticmethod
     def _context(c):

@@ -278,3 +278,42 @@ def test_vae_encoder_full_size_vs_oracle(_no_tf32):
     m = enc.encode_moments(x)
     assert m.shape == (1, 8, 40, 64)
     assert rel(m, vae_encode_moments(sd, x, 4, 2)) < TOL
+
+
+@pytest.mark.gpu
+def test_davis_branches_of_prepare_and_shift(_no_tf32):
+    """prepare_latents(data=...) and shift_latents(davis_data=...) (funcs.py:38-47, 100-116): the queue starts from the encoded
+    frames, the shift anchors on the encoded LAST frame, the mask queue moves with the latents."""
+    import types
+    from moca_video_b200 import fifo, ops
+    from moca_video_b200.vae import AutoencoderKLEncoder
+    from oracle.vae_ref import encode_first_stage_2DAE
+    dd, sd = _small_enc()
+    enc = AutoencoderKLEncoder(dict(dd, in_channels=3, double_z=True), device="cuda", scale_factor=0.18215).load_state_dict(sd)
+    model = types.SimpleNamespace(encode_first_stage_2DAE=enc.encode_first_stage_2DAE)
+    gen = torch.Generator(device="cuda").manual_seed(21)
+    frames = torch.rand(1, 4, 4, 64, 64, device="cuda", generator=gen) * 2 - 1             # RGBA: alpha is dropped
+    masks = (torch.rand(1, 1, 12, 16, 16, device="cuda", generator=gen) > 0.5).float()
+    fa = types.SimpleNamespace(num_inference_steps=8, lookahead_denoising=True, video_length=8)
+    sampler = types.SimpleNamespace(ddim_alphas=np.linspace(0.9, 0.1, 8))
+    qn = torch.randn(1, 4, 12, 16, 16, device="cuda", generator=gen)
+    torch.manual_seed(5)                                                                    # the posterior's host-side draw
+    q = fifo.prepare_latents(fa, None, sampler, model, data=(frames, masks), noise=qn)
+    torch.manual_seed(5)
+    z = enc.encode_first_stage_2DAE(frames[:, :3])
+    assert torch.equal(q, fifo.prepare_latents(fa, None, sampler, initial_latents=z, noise=qn))
+    sdc = {k: v.cuda() for k, v in sd.items()}
+    torch.manual_seed(5)
+    host_noise = torch.cat([torch.randn(1, 4, 16, 16).unsqueeze(2) for _ in range(4)], dim=2).cuda()
+    assert rel(z, encode_first_stage_2DAE(sdc, frames[:, :3], 0.18215, 3, 1, host_noise)) < TOL
+    # shift: same tail as the latent-anchored shift would give with the encoded last frame in slot 0
+    nn_ = torch.randn(1, 4, 1, 16, 16, device="cuda", generator=gen)
+    torch.manual_seed(6)
+    out, (f2, m2) = fifo.shift_latents(q.clone(), (frames, masks), model, new_noise=nn_)
+    torch.manual_seed(6)
+    anchor = enc.encode_first_stage_2DAE(frames[:, :3, -1:])
+    fake = q.clone()
+    fake[:, :, 0] = anchor[:, :, 0]
+    want = fifo.shift_latents(fake, new_noise=nn_)
+    assert torch.equal(out[:, :, -1], want[:, :, -1]) and torch.equal(out[:, :, :-1], q[:, :, 1:])
+    assert f2 is frames and torch.equal(m2[:, :, :-1], masks[:, :, 1:]) and torch.equal(m2[:, :, -1], masks[:, :, -1])
