@@ -131,6 +131,17 @@ int64_t moca_freeinit_work_bytes(int32_t NV, int32_t T, int32_t H, int32_t W);
 int32_t moca_freeinit_mix(moca_ctx* ctx, const float* x, const float* noise, const float* lpf, int32_t NV, int32_t T,
                           int32_t H, int32_t W, float* y, void* work, void* stream);
 
+/* moca_freeinit_mix_static: the same computation as moca_freeinit_mix without caller-provided work memory and without any
+ *   allocation.  It has NO counterpart in the reference; it was added for callers that
+ *   cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The spectrum scratch
+ *   is a file-scope device array of moca_freeinit_mix_static_max_elems() = 262144 complex values (2 MiB, resident on every GPU
+ *   that loads the library until exit); NV*T*H*W beyond that returns MOCA_E_SHAPE with a message naming the limit.  All calls on
+ *   a device share the array: calls that overlap on the GPU (different streams without ordering) race; same-stream calls do not.
+ *   The array keeps the previous call's contents; every element a call reads is first rewritten by that call. */
+int64_t moca_freeinit_mix_static_max_elems(void);
+int32_t moca_freeinit_mix_static(moca_ctx* ctx, const float* x, const float* noise, const float* lpf, int32_t NV, int32_t T,
+                                 int32_t H, int32_t W, float* y, void* stream);
+
 /* ---- UNet: UNetModel (lvdm/modules/networks/openaimodel3d.py:279-578) ---------------------------------------
  * moca_unet_create: architecture integers of the yaml (configs/inference_t2v_512_v2.0.yaml:22-50).
  * moca_unet_load:   one call per state_dict tensor (name = state_dict key, fp32 DEVICE pointer, element count);

@@ -31,6 +31,8 @@ SIGNATURES = {
     "moca_freeinit_filter": (i32, [vp, i32, i32, f64, f64, i32, i32, i32, vp, vp]),
     "moca_freeinit_work_bytes": (i64, [i32, i32, i32, i32]),
     "moca_freeinit_mix": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, vp, vp, vp]),
+    "moca_freeinit_mix_static_max_elems": (i64, []),
+    "moca_freeinit_mix_static": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, vp, vp]),
     "moca_unet_create": (i32, [vp, i32, i32, i32, i32, vp, i32, vp, i32, i32, i32, i32, C.POINTER(vp)]),
     "moca_unet_destroy": (i32, [vp]),
     "moca_unet_load": (i32, [vp, cp, vp, i64, vp]),

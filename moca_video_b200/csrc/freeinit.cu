@@ -216,3 +216,52 @@ extern "C" int32_t moca_freeinit_mix(moca_ctx* ctx, const float* x, const float*
     MOCA_LAUNCH_CHECK();
     return MOCA_OK;
 }
+
+// ---- allocation-free variant of moca_freeinit_mix -------------------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot allocate (code under CUDA
+// graph capture, serving loops, harnesses that forbid cudaMalloc).  The spectrum scratch that moca_freeinit_mix takes from the
+// caller lives in a file-scope device array instead: kStaticSpectrum complex values = 2 MiB, held by every GPU that loads the
+// library until the process exits.  All calls (all streams, all contexts of a device) share it and it keeps the last call's
+// contents: the forward kernel rewrites every element the later kernels read, so nothing has to be cleared, but two calls that
+// overlap on the GPU race on it — keep them on one stream, or order them with events.
+constexpr int64_t kStaticSpectrum = 262144;          // float2 elements: NV * T * H * W <= 262144 (FIFO shift: 4 * 1 * 40 * 64 = 10240)
+static __device__ __align__(256) float2 g_freeinit_spectrum[kStaticSpectrum];
+
+extern "C" int64_t moca_freeinit_mix_static_max_elems() { return kStaticSpectrum; }
+
+extern "C" int32_t moca_freeinit_mix_static(moca_ctx* ctx, const float* x, const float* noise, const float* lpf, int32_t NV, int32_t T,
+                                            int32_t H, int32_t W, float* y, void* stream) {
+    MOCA_REQUIRE(ctx != nullptr && x && noise && lpf && y, MOCA_E_ARG, "moca_freeinit_mix_static: NULL argument");
+    MOCA_REQUIRE(NV > 0 && T > 0 && T <= kMaxT && H > 0 && W > 0, MOCA_E_SHAPE, "moca_freeinit_mix_static: bad shape NV%d T%d H%d W%d (T<=%d)",
+                 NV, T, H, W, kMaxT);
+    const int64_t elems = (int64_t)NV * T * H * W;
+    MOCA_REQUIRE(elems <= kStaticSpectrum, MOCA_E_SHAPE,
+                 "moca_freeinit_mix_static: NV*T*H*W = %lld exceeds the built-in scratch of %lld complex values (2 MiB); use moca_freeinit_mix "
+                 "with caller-provided work memory", (long long)elems, (long long)kStaticSpectrum);
+    const size_t smemA = (size_t)H * W * (sizeof(float2) + sizeof(float)) + (size_t)(H + W) * sizeof(float2);
+    const size_t smemC = (size_t)H * W * 2 * sizeof(float2) + (size_t)(H + W) * sizeof(float2);
+    MOCA_REQUIRE(smemC <= 200 * 1024, MOCA_E_SHAPE, "moca_freeinit_mix_static: slice %dx%d does not fit shared memory", H, W);
+    // device address of the array, resolved once per device with that device current (the symbol's name is a host-side stand-in
+    // here: handing it to a kernel would fault or touch the wrong memory)
+    static float2* dev_ptr[64] = {nullptr};
+    int dev = -1;
+    MOCA_CHECK_CUDA(cudaGetDevice(&dev));
+    MOCA_REQUIRE(dev >= 0 && dev < 64, MOCA_E_ARG, "moca_freeinit_mix_static: device index %d outside 0..63", dev);
+    if (!dev_ptr[dev]) {
+        float2* p = nullptr;
+        MOCA_CHECK_CUDA(cudaGetSymbolAddress((void**)&p, g_freeinit_spectrum));
+        MOCA_REQUIRE(p != nullptr, MOCA_E_CUDA, "moca_freeinit_mix_static: cudaGetSymbolAddress returned NULL");
+        dev_ptr[dev] = p;
+    }
+    float2* Z = dev_ptr[dev];
+    cudaStream_t st = (cudaStream_t)stream;
+    MOCA_CHECK_CUDA(cudaFuncSetAttribute(freeinit_fwd_hw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    MOCA_CHECK_CUDA(cudaFuncSetAttribute(freeinit_inv_hw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    freeinit_fwd_hw_kernel<<<NV * T, 256, smemA, st>>>(x, noise, Z, H, W);
+    MOCA_LAUNCH_CHECK();
+    freeinit_t_filter_kernel<<<cdiv((int64_t)NV * H * W, 128), 128, 0, st>>>(Z, lpf, NV, T, H, W);
+    MOCA_LAUNCH_CHECK();
+    freeinit_inv_hw_kernel<<<NV * T, 256, smemC, st>>>(Z, noise, y, H, W, 1.0f / (float)((int64_t)T * H * W));
+    MOCA_LAUNCH_CHECK();
+    return MOCA_OK;
+}

@@ -187,6 +187,22 @@ def freq_mix_3d(x, noise, lpf):
     return y
 
 
+def freq_mix_3d_static(x, noise, lpf, out):
+    """freq_mix_3d through moca_freeinit_mix_static: no allocation anywhere on the way (``out`` and contiguous fp32 inputs are
+    the caller's; the spectrum scratch is the library's built-in 2 MiB array, so NV*T*H*W <= 262144).  No counterpart in the
+    reference.  Calls that overlap on the GPU share the scratch and race: keep them on one stream."""
+    for t, name in ((x, "x"), (noise, "noise"), (lpf, "lpf"), (out, "out")):
+        if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
+            raise _lib.MocaError(f"freq_mix_3d_static: {name} must be a contiguous fp32 CUDA tensor (this entry converts nothing)")
+    T, H, W = x.shape[-3:]
+    if noise.shape != x.shape or out.shape != x.shape or lpf.numel() != T * H * W:
+        raise _lib.MocaError("freq_mix_3d_static: x / noise / out must have one shape and lpf T*H*W elements")
+    NV = x.numel() // (T * H * W)
+    with torch.cuda.device(x.device):
+        check(lib().moca_freeinit_mix_static(ctx(x.device.index), ptr(x), ptr(noise), ptr(lpf), NV, T, H, W, ptr(out), stream_ptr()))
+    return out
+
+
 # ---- unit-test primitives -------------------------------------------------------------------------------------
 def gemm_op16(a, w, bias=None, out_op16=False):
     M, K = a.shape
