@@ -19,9 +19,9 @@ template <int BN, bool TEPI = false, int EPI = EPI_F32, int NCTA = 1, bool RES =
 struct GemmCfg {
     static constexpr bool GT = TEPI && EPI == EPI_GEGLU;
     static constexpr int B_BYTES = (BN / NCTA) * kBK * 2;                   // CTA pair: each CTA holds half of the B rows
-    static constexpr int STAGE_BYTES = kABytes + B_BYTES;                   // multiple of 1024 for BN in {128, 160, 256}
+    static constexpr int STAGE_BYTES = kABytes + B_BYTES;                   // multiple of 1024 for BN in {128, 160, 192, 256}
     static constexpr bool BT = TEPI && EPI == EPI_BF16;      // bf16 thread = row epilogue: classic ring, two 2 KB staging boxes per warp
-    static constexpr int STAGES = NCTA == 2 ? 6 : (GT ? 4 : ((TEPI && !BT) ? (BN == 128 ? 4 : 3) : ((BN == 256) ? (RES ? 3 : 4) : (BN == 160 ? (RES ? 4 : 5) : (RES ? 5 : 6)))));
+    static constexpr int STAGES = NCTA == 2 ? 6 : (GT ? 4 : ((TEPI && !BT) ? (BN == 128 ? 4 : 3) : ((BN == 256) ? (RES ? 3 : 4) : (BN == 192 ? (RES ? 3 : 4) : (BN == 160 ? (RES ? 4 : 5) : (RES ? 5 : 6))))));
     static constexpr int TMEM_COLS = (2 * BN <= 256) ? 256 : 512;
     static constexpr int EPI_WARPS = GT ? 16 : 8;
     static constexpr int THREADS = 64 + 32 * EPI_WARPS;
@@ -953,15 +953,18 @@ int make_tmap_bf16_chunk(CUtensorMap* tm, const void* ptr, int64_t rows, int64_t
 // 160 columns where 561 / 270 tiles of 256 are 15-20 % faster (1.35 ms per forward).  GEGLU weights are packed for 256.
 static int pick_bn(const GemmDesc& d, int num_sms) {
     if (d.epi == EPI_GEGLU) return 256;
-    const int cand[3] = {256, 160, 128};
+    // 192: 1280-wide outputs on 40 M tiles (the 10 x 16 level) are 200 tiles of 256 = 1.35 waves, but 280 tiles of 192 = 1.89
+    const int cand[4] = {256, 192, 160, 128};
+    static const double pen192 = [] { const char* e = getenv("MOCA_GEMM_PEN192"); return e ? atof(e) : 1.12; }();    // <= 0: never
     static const double pen160 = [] { const char* e = getenv("MOCA_GEMM_PEN160"); return e ? atof(e) : 1.20; }();
     static const double pen128 = [] { const char* e = getenv("MOCA_GEMM_PEN128"); return e ? atof(e) : 1.40; }();
-    const double pen[3] = {1.0, pen160, pen128};
+    const double pen[4] = {1.0, pen192, pen160, pen128};
     const int64_t mt = (d.M + kBM - 1) / kBM;
     int best = 128;
     double best_cost = 1e30;
-    for (int i = 0; i < 3; ++i) {
+    for (int i = 0; i < 4; ++i) {
         const int bn = cand[i];
+        if (pen[i] <= 0.0) continue;
         const int64_t tiles = mt * ((d.N + bn - 1) / bn);
         const double waves = (double)((tiles + num_sms - 1) / num_sms);
         const double cost = waves * bn * pen[i];
@@ -1037,7 +1040,7 @@ template <int BN>
 static void launch_bn(const GemmLaunch& l, cudaStream_t st) {
     const bool stats = l.p.cstat != nullptr;
     if (l.p.ncta == 2) {
-        if constexpr (BN != 128) {
+        if constexpr (BN == 256 || BN == 160) {
             if (stats) launch_pair(gemm_tc_kernel<BN, EPI_F32, true, false, 2>, l.grid, kGemmThreads, l.smem, st, l.p);
             else launch_pair(gemm_tc_kernel<BN, EPI_F32, false, false, 2>, l.grid, kGemmThreads, l.smem, st, l.p);
         }
@@ -1083,7 +1086,7 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
     // CTA-pair shape (MOCA_GEMM_2CTA=1): staged fp32 epilogue, 160- / 256-wide tiles, long main loops
     static const int pair_on = [] { const char* e = getenv("MOCA_GEMM_2CTA"); return e ? atoi(e) : 0; }();
     static const int pair_mink = [] { const char* e = getenv("MOCA_GEMM_2CTA_MINK"); return e ? atoi(e) : 16; }();
-    const int ncta = (pair_on && d.epi == EPI_F32 && L.BN != 128 && d.ntaps * (d.Kp / 64) >= pair_mink && ctx.num_sms >= 2 &&
+    const int ncta = (pair_on && d.epi == EPI_F32 && (L.BN == 256 || L.BN == 160) && d.ntaps * (d.Kp / 64) >= pair_mink && ctx.num_sms >= 2 &&
                       d.mode != GEMM_SPATIAL_4D) ? 2 : 1;
     rc = make_tmap_bf16(&L.p.tmB, d.Wt, d.N, (int64_t)d.ntaps * d.Kp, (int64_t)d.ntaps * d.Kp, L.BN / ncta);
     if (rc) return rc;
@@ -1142,9 +1145,10 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
             rc = make_tmap_bf16_chunk(&p.tmRes, d.residual16, d.M, d.N, d.ldo);
             if (rc) return rc;
             L.smem = L.BN == 256 ? GemmCfg<256, true, EPI_BF16, 1, true>::SMEM
-                                 : (L.BN == 160 ? GemmCfg<160, true, EPI_BF16, 1, true>::SMEM : GemmCfg<128, true, EPI_BF16, 1, true>::SMEM);
+                                 : (L.BN == 192 ? GemmCfg<192, true, EPI_BF16, 1, true>::SMEM
+                                 : (L.BN == 160 ? GemmCfg<160, true, EPI_BF16, 1, true>::SMEM : GemmCfg<128, true, EPI_BF16, 1, true>::SMEM));
         } else
-        L.smem = L.BN == 256 ? GemmCfg<256, true, EPI_BF16>::SMEM : (L.BN == 160 ? GemmCfg<160, true, EPI_BF16>::SMEM : GemmCfg<128, true, EPI_BF16>::SMEM);
+        L.smem = L.BN == 256 ? GemmCfg<256, true, EPI_BF16>::SMEM : (L.BN == 192 ? GemmCfg<192, true, EPI_BF16>::SMEM : (L.BN == 160 ? GemmCfg<160, true, EPI_BF16>::SMEM : GemmCfg<128, true, EPI_BF16>::SMEM));
     } else if (gt) {
         p.tepi = 1;
         rc = make_tmap_bf16_chunk(&p.tmOut, d.out, d.M, d.N / 2, d.ldo);
@@ -1157,9 +1161,9 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
         if (d.out16 && !d.residual) p.tmRes = p.tmOut;      // never loaded from; keeps the prefetched descriptor valid
         else rc = make_tmap_f32_chunk(&p.tmRes, d.residual ? (const void*)d.residual : d.out, out_rows, d.N, d.ldo);
         if (rc) return rc;
-        L.smem = L.BN == 160 ? GemmCfg<160, true>::SMEM : GemmCfg<128, true>::SMEM;
+        L.smem = L.BN == 192 ? GemmCfg<192, true>::SMEM : (L.BN == 160 ? GemmCfg<160, true>::SMEM : GemmCfg<128, true>::SMEM);
     } else {
-        L.smem = L.BN == 256 ? GemmCfg<256>::SMEM : (L.BN == 160 ? GemmCfg<160>::SMEM : GemmCfg<128>::SMEM);
+        L.smem = L.BN == 256 ? GemmCfg<256>::SMEM : (L.BN == 192 ? GemmCfg<192>::SMEM : (L.BN == 160 ? GemmCfg<160>::SMEM : GemmCfg<128>::SMEM));
     }
     L.flops = 2.0 * (double)d.M * d.N * d.ntaps * d.a_cols;
     if (ncta == 2) {
@@ -1168,7 +1172,7 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
         if (!rc) rc = L.BN == 256 ? set_attr_pair<256, false>() : set_attr_pair<160, false>();
         if (rc) return rc;
     }
-    rc = L.BN == 256 ? set_attr_bn<256>(d.epi, p.tepi) : (L.BN == 160 ? set_attr_bn<160>(d.epi, p.tepi) : set_attr_bn<128>(d.epi, p.tepi));
+    rc = L.BN == 256 ? set_attr_bn<256>(d.epi, p.tepi) : (L.BN == 192 ? set_attr_bn<192>(d.epi, p.tepi) : (L.BN == 160 ? set_attr_bn<160>(d.epi, p.tepi) : set_attr_bn<128>(d.epi, p.tepi)));
     if (rc) return rc;
     *out = L;
     return MOCA_OK;
@@ -1176,6 +1180,7 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
 
 int gemm_run(const GemmLaunch& l, cudaStream_t st) {
     if (l.BN == 256) launch_bn<256>(l, st);
+    else if (l.BN == 192) launch_bn<192>(l, st);
     else if (l.BN == 160) launch_bn<160>(l, st);
     else launch_bn<128>(l, st);
     MOCA_LAUNCH_CHECK();
