@@ -224,6 +224,20 @@ int32_t moca_vae_encoder_create(moca_ctx* ctx, int32_t ch, const int32_t* ch_mul
                                 int32_t in_channels, int32_t z_channels, int32_t double_z, moca_unet** out);
 int32_t moca_vae_encode(moca_unet* vae, const float* x, int32_t B, int32_t H, int32_t W, float* moments, void* stream);
 
+/* ---- text tower: FrozenOpenCLIPEmbedder.encode_with_transformer (lvdm/modules/encoders/condition.py:212-230) = open_clip's CLIP
+ * text transformer (open_clip_torch 2.30.0, reference requirements.txt:196; the package is not vendored in the reference): token
+ * + positional embedding, pre-LN residual blocks (nn.MultiheadAttention with the causal mask, c_fc -> GELU -> c_proj), ln_final.
+ * moca_text_create: ViT-H-14 text tower = (49408, 77, 1024, 16, 24); layers_used = layers - 1 for layer "penultimate"
+ *   (condition.py:197-202, 226-229), layers for "last".  ctx == NULL lists parameters only.  The handle is a moca_unet:
+ *   moca_unet_load / _load_many / _finalize / _destroy / _param_* apply, keys as in FrozenOpenCLIPEmbedder.state_dict()
+ *   ("model.token_embedding.weight", "model.transformer.resblocks.0.attn.in_proj_weight", ...); the unused last block,
+ *   text_projection and logit_scale are not expected.
+ * moca_text_encode: tokens DEVICE int32 [B, context_length] (open_clip.tokenize output; the BPE tokenizer is host string work and
+ *   stays with the caller) -> z [B, context_length, width] fp32, the c_crossattn entry of the sampler's conditioning.  B <= 64. */
+int32_t moca_text_create(moca_ctx* ctx, int32_t vocab, int32_t context_length, int32_t width, int32_t heads, int32_t layers,
+                         int32_t layers_used, moca_unet** out);
+int32_t moca_text_encode(moca_unet* text, const int32_t* tokens, int32_t B, float* z, void* stream);
+
 /* ---- primitives exposed for unit parity tests (tests/test_gpu_ops.py): the same kernels the UNet plan launches ----
  * moca_gemm_op16: D[M,N] = A[M,K] * W[N,K]^T (+bias[N]) on the tcgen05 core; A, W op16 (moca_operand_dtype) row-major (K contiguous),
  *   D fp32 or op16 (out_op16).  K % 64 == 0.                                    (nn.Linear, attention.py:54-57)

@@ -9,10 +9,10 @@ from ._lib import LIB_PATH, MocaError  # noqa: F401
 def __getattr__(name):
     import importlib
     table = {"UNet3D": ".unet", "DDIMSampler": ".sampler", "LatentDiffusionB200": ".model", "patch_reference": ".patch",
-             "AutoencoderKLDecoder": ".vae", "attach_vae": ".vae",
+             "AutoencoderKLDecoder": ".vae", "AutoencoderKLEncoder": ".vae", "attach_vae": ".vae", "OpenCLIPTextEncoder": ".text",
              "fifo_ddim_sampling": ".fifo", "prepare_latents": ".fifo", "shift_latents": ".fifo"}
     if name in table:
         return getattr(importlib.import_module(table[name], __name__), name)
-    if name in ("ops", "fifo", "sampler", "schedule", "unet", "model", "patch", "arch", "build", "vae", "driver"):
+    if name in ("ops", "fifo", "sampler", "schedule", "unet", "model", "patch", "arch", "build", "vae", "text", "driver"):
         return importlib.import_module("." + name, __name__)
     raise AttributeError(name)

@@ -45,6 +45,8 @@ SIGNATURES = {
     "moca_vae_decode": (i32, [vp, vp, i32, i32, i32, f32, vp, vp]),
     "moca_vae_encoder_create": (i32, [vp, i32, vp, i32, i32, i32, i32, i32, C.POINTER(vp)]),
     "moca_vae_encode": (i32, [vp, vp, i32, i32, i32, vp, vp]),
+    "moca_text_create": (i32, [vp, i32, i32, i32, i32, i32, i32, C.POINTER(vp)]),
+    "moca_text_encode": (i32, [vp, vp, i32, vp, vp]),
     "moca_unet_set_taps": (i32, [vp, i32]),
     "moca_unet_num_taps": (i32, [vp]),
     "moca_unet_tap_info": (i32, [vp, i32, cp, i32, pi64, pi64]),

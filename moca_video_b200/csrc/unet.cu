@@ -375,6 +375,47 @@ static void build_vae_encoder_arch(moca_unet* n) {
 
 }  // namespace moca
 
+// Text tower object: open_clip's CLIP text transformer as FrozenOpenCLIPEmbedder uses it (lvdm/modules/encoders/condition.py:174-235).
+// layers_used blocks are run and registered (layer = "penultimate": layers - 1, condition.py:197-202, 226-229); the unused last
+// block, text_projection and logit_scale of the state_dict are not part of the path.  moca_text_encode (unet_plan.cu) runs it.
+extern "C" int32_t moca_text_create(moca_ctx* ctx, int32_t vocab, int32_t context_length, int32_t width, int32_t heads, int32_t layers,
+                                    int32_t layers_used, moca_unet** out) {
+    MOCA_REQUIRE(out != nullptr, MOCA_E_ARG, "moca_text_create: NULL argument");
+    MOCA_REQUIRE(vocab > 0 && context_length > 0 && context_length <= 128 && width > 0 && width % 64 == 0 && width <= 1280 && heads > 0 &&
+                 width == heads * 64 && layers > 0 && layers_used > 0 && layers_used <= layers, MOCA_E_SHAPE,
+                 "moca_text_create: unsupported shape (context_length %d <= 128, width %d = 64 * heads %d <= 1280, %d of %d layers)",
+                 context_length, width, heads, layers_used, layers);
+    moca_unet* n = new moca_unet();
+    n->ctx = ctx;
+    n->dry = (ctx == nullptr);
+    TextW& t = n->text;
+    t.present = true;
+    t.vocab = vocab; t.ctx_len = context_length; t.width = width; t.heads = heads; t.layers = layers; t.used = layers_used;
+    t.tok_emb = reg_f32(n, "model.token_embedding.weight", (int64_t)vocab * width);
+    t.pos_emb = reg_f32(n, "model.positional_embedding", (int64_t)context_length * width);
+    t.blocks.resize(layers_used);
+    for (int i = 0; i < layers_used; ++i) {
+        TextLayerW& b = t.blocks[i];
+        const std::string p = "model.transformer.resblocks." + std::to_string(i);
+        b.ln1 = reg_norm(n, p + ".ln_1", width);
+        b.in_proj = alloc_packed(n, 3 * width, width, 1, true);          // nn.MultiheadAttention: q | k | v rows of one matrix
+        reg_pack(n, p + ".attn.in_proj_weight", b.in_proj, 0, 3 * width);
+        reg_f32(n, p + ".attn.in_proj_bias", 3 * width, b.in_proj.b);
+        b.out_proj = reg_linear(n, p + ".attn.out_proj", width, width, 1, true);
+        b.ln2 = reg_norm(n, p + ".ln_2", width);
+        b.c_fc = reg_linear(n, p + ".mlp.c_fc", 4 * width, width, 1, true);
+        b.c_proj = reg_linear(n, p + ".mlp.c_proj", width, 4 * width, 1, true);
+    }
+    t.ln_final = reg_norm(n, "model.ln_final", width);
+    for (void* p : n->allocs)
+        if (!p) {
+            set_error("moca_text_create: device allocation failed");
+            return MOCA_E_CUDA;
+        }
+    *out = n;
+    return MOCA_OK;
+}
+
 // VAE encoder object (same handle conventions as the decoder below); moca_vae_encode (unet_plan.cu) runs it.
 extern "C" int32_t moca_vae_encoder_create(moca_ctx* ctx, int32_t ch, const int32_t* ch_mult, int32_t n_mult, int32_t num_res_blocks,
                                            int32_t in_channels, int32_t z_channels, int32_t double_z, moca_unet** out) {

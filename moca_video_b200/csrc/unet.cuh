@@ -92,6 +92,21 @@ struct VaeW {
     float* q_b = nullptr;
 };
 
+// OpenCLIP text tower: token / positional embeddings, pre-LN residual attention blocks, ln_final; names as in
+// FrozenOpenCLIPEmbedder.state_dict() ("model.transformer.resblocks.{i}.attn.in_proj_weight", ...)
+struct TextLayerW {
+    NormW ln1, ln2;
+    PackedW in_proj, out_proj, c_fc, c_proj;
+};
+struct TextW {
+    bool present = false;
+    int vocab = 49408, ctx_len = 77, width = 1024, heads = 16, layers = 24, used = 23;   // used: blocks actually run ("penultimate": layers - 1)
+    float* tok_emb = nullptr;                        // [vocab, width] fp32
+    float* pos_emb = nullptr;                        // [ctx_len, width] fp32
+    std::vector<TextLayerW> blocks;
+    NormW ln_final;
+};
+
 struct LoadSlot {
     enum Kind { COPY_F32, PACK } kind = COPY_F32;
     float* dst_f32 = nullptr;
@@ -114,6 +129,7 @@ struct moca_unet {
     moca::BlockW init_attn, mid;
     moca::PackedW time0, time2, fps0, fps2, emb_all, kv_all, conv_out;
     moca::NormW gn_out;
+    moca::TextW text;                                // moca_text_create: this object is a text tower
     moca::VaeW vae;                                  // moca_vae_create: this object is a VAE decoder, not a UNet
     int n_emb = 0, n_kv = 0;
     std::unordered_map<std::string, moca::LoadSlot> slots;

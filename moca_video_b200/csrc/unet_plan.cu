@@ -246,6 +246,7 @@ struct Builder {
     void vae_attn(Act& x);
     void build_vae(float inv_scale);
     void build_vae_encoder();
+    void build_text();
 };
 
 // ResBlock._forward (openaimodel3d.py:208-234) followed by its TemporalConvBlock (:269-276)
@@ -866,6 +867,166 @@ void Builder::build_vae_encoder() {
     }
 }
 
+// ---- OpenCLIP text tower (row N4): FrozenOpenCLIPEmbedder.encode_with_transformer (condition.py:212-230) -----------------------
+// x[r] = token_embedding[tokens[r]] + positional_embedding[r mod L] (condition.py:213-214)
+__global__ void text_embed_kernel(const int* __restrict__ tokens, const float* __restrict__ tok_emb, const float* __restrict__ pos_emb,
+                                  int rows, int L, int W, int vocab, float* __restrict__ x) {
+    const int r = blockIdx.x;
+    if (r >= rows) return;
+    int t = tokens[r];
+    t = t < 0 ? 0 : (t >= vocab ? vocab - 1 : t);              // ids are validated on the host; never read outside the table
+    const float4* e = reinterpret_cast<const float4*>(tok_emb + (size_t)t * W);
+    const float4* p = reinterpret_cast<const float4*>(pos_emb + (size_t)(r % L) * W);
+    float4* o = reinterpret_cast<float4*>(x + (size_t)r * W);
+    for (int i = threadIdx.x; i < W / 4; i += blockDim.x) {
+        const float4 a = e[i], b = p[i];
+        o[i] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+    }
+}
+
+// nn.MultiheadAttention with the causal additive mask of the text tower (open_clip build_attention_mask: -inf above the diagonal),
+// head dim 64, L <= 128 keys: blocks of a (sample, head) hold its K / V in shared memory, one warp per query row.
+__global__ void __launch_bounds__(128) text_attn_kernel(const op_t* __restrict__ qkv, int L, int W, int heads, op_t* __restrict__ out) {
+    extern __shared__ float sm[];
+    float* Ks = sm;
+    float* Vs = sm + (size_t)L * 65;
+    float* Qs = Vs + (size_t)L * 65;                           // [4 warps][64]
+    const int b = blockIdx.x / heads, h = blockIdx.x % heads;
+    const op_t* base = qkv + (size_t)b * L * 3 * W + h * 64;
+    for (int i = threadIdx.x; i < L * 64; i += blockDim.x) {
+        const int j = i >> 6, d = i & 63;
+        Ks[j * 65 + d] = op2float(base[(size_t)j * 3 * W + W + d]);
+        Vs[j * 65 + d] = op2float(base[(size_t)j * 3 * W + 2 * W + d]);
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float* qs = Qs + warp * 64;
+    // gridDim.y blocks share a (sample, head): query rows interleaved over them (K / V are re-read, 20 KB from L2)
+    for (int qi = warp + 4 * blockIdx.y; qi < L; qi += 4 * gridDim.y) {
+        qs[lane] = op2float(base[(size_t)qi * 3 * W + lane]) * 0.125f;
+        qs[lane + 32] = op2float(base[(size_t)qi * 3 * W + lane + 32]) * 0.125f;
+        __syncwarp();
+        float sc[4], mx = -INFINITY;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const int j = lane + 32 * c;
+            float a = -INFINITY;
+            if (j <= qi) {
+                a = 0.f;
+                for (int d = 0; d < 64; ++d) a = fmaf(qs[d], Ks[j * 65 + d], a);
+            }
+            sc[c] = a;
+            mx = fmaxf(mx, a);
+        }
+        for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        float sum = 0.f;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            sc[c] = (lane + 32 * c <= qi) ? __expf(sc[c] - mx) : 0.f;
+            sum += sc[c];
+        }
+        for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            if (32 * c > qi) break;                              // warp-uniform
+            const int jn = min(32, qi + 1 - 32 * c);
+            for (int jj = 0; jj < jn; ++jj) {
+                const float pj = __shfl_sync(0xffffffffu, sc[c], jj);
+                const float* vr = Vs + (32 * c + jj) * 65;
+                a0 = fmaf(pj, vr[lane], a0);
+                a1 = fmaf(pj, vr[lane + 32], a1);
+            }
+        }
+        const float inv = 1.0f / sum;
+        op_t* o = out + ((size_t)b * L + qi) * W + h * 64;
+        o[lane] = float2op(a0 * inv);
+        o[lane + 32] = float2op(a1 * inv);
+        __syncwarp();
+    }
+}
+
+// nn.GELU() (exact erf form; open_clip's ViT-H-14 text config has quick_gelu = false): fp32 -> 16-bit GEMM operand
+__global__ void gelu_op16_kernel(const float* __restrict__ x, int64_t n, op_t* __restrict__ y) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const float g = x[i];
+        y[i] = float2op(0.5f * g * (1.0f + erff(g * 0.70710678118654752f)));
+    }
+}
+
+// nn.LayerNorm(W), eps 1e-5, fp32 out (ln_final, condition.py:218): one warp per row, two passes over registers-in-cache
+__global__ void __launch_bounds__(128) layernorm_f32_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                                                            const float* __restrict__ beta, int rows, int W, float* __restrict__ y) {
+    const int r = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (r >= rows) return;
+    const float* xr = x + (size_t)r * W;
+    float s = 0.f;
+    for (int i = lane; i < W; i += 32) s += xr[i];
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    const float mean = s / (float)W;
+    float q = 0.f;
+    for (int i = lane; i < W; i += 32) { const float d = xr[i] - mean; q = fmaf(d, d, q); }
+    for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+    const float rstd = rsqrtf(q / (float)W + 1e-5f);
+    for (int i = lane; i < W; i += 32) y[(size_t)r * W + i] = (xr[i] - mean) * rstd * gamma[i] + beta[i];
+}
+
+void Builder::build_text() {
+    const TextW& t = net->text;
+    const int L = t.ctx_len, W = t.width;
+    const int rows = B * L;
+    plan->d_ts = (int*)palloc((size_t)rows * sizeof(int));                 // token ids [B, L]
+    float* x = (float*)palloc((size_t)rows * W * sizeof(float));           // fp32 residual stream
+    plan->out_tok = (float*)palloc((size_t)rows * W * sizeof(float));
+    plan->out_C = W;
+    op_t* ln = scratch<op_t>(S_LIN, (size_t)rows * W);
+    op_t* qkv = scratch<op_t>(S_QKV, (size_t)rows * 3 * W);
+    op_t* att = scratch<op_t>(S_ATT, (size_t)rows * W);
+    float* fc = scratch<float>(S_F32A, (size_t)rows * 4 * W);
+    op_t* act = scratch<op_t>(S_FFH, (size_t)rows * 4 * W);
+    scope = "text";
+    {
+        const int* tok = plan->d_ts;
+        const float* te = t.tok_emb; const float* pe = t.pos_emb;
+        const int vocab = t.vocab;
+        push([=](cudaStream_t st) {
+            text_embed_kernel<<<rows, 128, 0, st>>>(tok, te, pe, rows, L, W, vocab, x);
+            return cudaGetLastError() == cudaSuccess ? MOCA_OK : MOCA_E_CUDA;
+        }, 1, "embed");
+    }
+    const int heads = t.heads, nb = B;
+    const size_t attn_smem = ((size_t)2 * L * 65 + 4 * 64) * sizeof(float);
+    for (int i = 0; i < t.used; ++i) {
+        const TextLayerW& b = t.blocks[i];
+        scope = "model.transformer.resblocks." + std::to_string(i);
+        // x = x + attn(ln_1(x)); x = x + mlp(ln_2(x))   (open_clip ResidualAttentionBlock.forward)
+        push([=](cudaStream_t st) { return layernorm_op16(x, b.ln1.g, b.ln1.b, rows, W, ln, st); }, 1, "layernorm");
+        linear(ln, rows, W, b.in_proj, EPI_BF16, qkv, 3 * W, nullptr);
+        push([=](cudaStream_t st) {
+            text_attn_kernel<<<dim3(nb * heads, 4), 128, attn_smem, st>>>(qkv, L, W, heads, att);
+            return cudaGetLastError() == cudaSuccess ? MOCA_OK : MOCA_E_CUDA;
+        }, 1, "causal attention");
+        linear(att, rows, W, b.out_proj, EPI_F32, x, W, x);
+        push([=](cudaStream_t st) { return layernorm_op16(x, b.ln2.g, b.ln2.b, rows, W, ln, st); }, 1, "layernorm");
+        linear(ln, rows, W, b.c_fc, EPI_F32, fc, 4 * W, nullptr);
+        push([=](cudaStream_t st) {
+            const int64_t n = (int64_t)rows * 4 * W;
+            gelu_op16_kernel<<<(int)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8), 256, 0, st>>>(fc, n, act);
+            return cudaGetLastError() == cudaSuccess ? MOCA_OK : MOCA_E_CUDA;
+        }, 1, "gelu");
+        linear(act, rows, 4 * W, b.c_proj, EPI_F32, x, W, x);
+    }
+    scope = "model.ln_final";
+    {
+        const float* g = t.ln_final.g; const float* bb = t.ln_final.b;
+        float* y = plan->out_tok;
+        push([=](cudaStream_t st) {
+            layernorm_f32_kernel<<<(rows + 3) / 4, 128, 0, st>>>(x, g, bb, rows, W, y);
+            return cudaGetLastError() == cudaSuccess ? MOCA_OK : MOCA_E_CUDA;
+        }, 1, "layernorm f32");
+    }
+}
+
 }  // namespace moca
 
 using namespace moca;
@@ -986,6 +1147,32 @@ extern "C" int32_t moca_vae_decode(moca_unet* n, const float* z, int32_t B, int3
     return tokens_to_ncthw(plan->out_tok, n->vae.out_ch, B, n->vae.out_ch, 1, H * up, W * up, image, st);
 }
 
+// FrozenOpenCLIPEmbedder.encode_with_transformer (condition.py:212-219): tokens DEVICE int32 [B, context_length] (open_clip.tokenize
+// output; the BPE tokenizer itself is host string work and stays with the caller) -> z [B, context_length, width] fp32
+extern "C" int32_t moca_text_encode(moca_unet* n, const int32_t* tokens, int32_t B, float* z, void* stream) {
+    MOCA_REQUIRE(n && tokens && z, MOCA_E_ARG, "moca_text_encode: NULL argument");
+    MOCA_REQUIRE(n->text.present, MOCA_E_STATE, "moca_text_encode: handle was not made by moca_text_create");
+    MOCA_REQUIRE(n->finalized, MOCA_E_STATE, "moca_text_encode: call moca_unet_finalize after loading the weights");
+    MOCA_REQUIRE(B > 0 && B <= 64, MOCA_E_SHAPE, "moca_text_encode: B=%d outside 1..64", B);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int L = n->text.ctx_len, W = n->text.width;
+    std::vector<int> key{B, 1, L, 1, -3, 0};
+    Plan* plan = nullptr;
+    auto it = n->plans.find(key);
+    if (it != n->plans.end()) { it->second->last_use = ++n->use_clock; plan = it->second.get(); }
+    else {
+        int rc = make_plan(n, key, B, 1, L, 1, 0, false, [](Builder& b) { b.build_text(); }, &plan);
+        if (rc) return rc;
+        MOCA_CHECK_CUDA(cudaFuncSetAttribute(text_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 80 * 1024));
+    }
+    n->last = plan;
+    MOCA_CHECK_CUDA(cudaMemcpyAsync(plan->d_ts, tokens, (size_t)B * L * sizeof(int), cudaMemcpyDeviceToDevice, st));
+    int rc = run_plan(plan, st, "moca_text_encode");
+    if (rc) return rc;
+    MOCA_CHECK_CUDA(cudaMemcpyAsync(z, plan->out_tok, (size_t)B * L * W * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    return MOCA_OK;
+}
+
 // AutoencoderKL.encode up to the posterior's parameters (autoencoder.py:97-102): x [B, in_ch, H, W] fp32 image in [-1, 1] ->
 // moments [B, 2 zc, H / 2^(L-1), W / 2^(L-1)] fp32 (mean | logvar, what DiagonalGaussianDistribution is built from)
 extern "C" int32_t moca_vae_encode(moca_unet* n, const float* x, int32_t B, int32_t H, int32_t W, float* moments, void* stream) {
@@ -1021,7 +1208,7 @@ extern "C" int32_t moca_unet_forward(moca_unet* n, const float* x, const int32_t
                                      const int32_t* ctx_len, int32_t Lmax, const int32_t* fps, int32_t B, int32_t T, int32_t H,
                                      int32_t W, float* y, void* stream) {
     MOCA_REQUIRE(n && x && timesteps && context && ctx_len && fps && y, MOCA_E_ARG, "moca_unet_forward: NULL argument");
-    MOCA_REQUIRE(!n->vae.present, MOCA_E_STATE, "moca_unet_forward: this handle is a VAE (moca_vae_decode / moca_vae_encode)");
+    MOCA_REQUIRE(!n->vae.present && !n->text.present, MOCA_E_STATE, "moca_unet_forward: this handle is a VAE or a text tower (moca_vae_decode / moca_vae_encode / moca_text_encode)");
     MOCA_REQUIRE(n->finalized, MOCA_E_STATE, "moca_unet_forward: call moca_unet_finalize after loading the weights");
     MOCA_REQUIRE(B > 0 && T > 0 && H > 0 && W > 0 && Lmax > 0, MOCA_E_SHAPE, "moca_unet_forward: bad shape");
     // fps: int32[B], one entry per sample (the Python mirror validates the length: a shorter array would be read past its end)

@@ -4,7 +4,7 @@ Carries the DDPM schedule buffers (register_schedule, ddpm3d.py:113-141), ``use_
 ``apply_model`` (:512-527 -> DiffusionWrapper.forward :702-712: concatenate ``c_crossattn`` along tokens, pass ``fps``).
 ``first_stage`` / ``first_stage_encoder`` (optional): ``AutoencoderKLDecoder`` / ``AutoencoderKLEncoder`` (vae.py) behind
 ``decode_first_stage_2DAE`` (:555-562) and ``encode_first_stage_2DAE`` (:485-490).
-The text tower is not part of this path: text embeddings are inputs.
+``cond_stage`` (optional): an ``OpenCLIPTextEncoder`` (text.py) behind ``get_learned_conditioning`` (:445-456).
 """
 import numpy as np
 import torch
@@ -15,11 +15,12 @@ from .unet import UNet3D
 
 class LatentDiffusionB200:
     def __init__(self, unet: UNet3D, timesteps=1000, linear_start=0.00085, linear_end=0.012, use_scale=True, fps=10,
-                 first_stage=None, scale_factor=0.18215, first_stage_encoder=None):
+                 first_stage=None, scale_factor=0.18215, first_stage_encoder=None, cond_stage=None):
         self.unet = unet
         self.first_stage_model = first_stage
         self.scale_factor = float(scale_factor)
         self.first_stage_encoder = first_stage_encoder
+        self.cond_stage_model = cond_stage
         for part in (first_stage, first_stage_encoder):
             if part is not None:
                 part.scale_factor = self.scale_factor
@@ -40,6 +41,15 @@ class LatentDiffusionB200:
             from ._lib import MocaError
             raise MocaError("LatentDiffusionB200.decode_first_stage_2DAE: constructed without first_stage (an AutoencoderKLDecoder)")
         return self.first_stage_model.decode_first_stage_2DAE(z)
+
+    def get_learned_conditioning(self, c):
+        """ddpm3d.py:445-456: list of prompts (or token ids [b, 77]) -> text embedding [b, 77, 1024]."""
+        if self.cond_stage_model is None:
+            from ._lib import MocaError
+            raise MocaError("LatentDiffusionB200.get_learned_conditioning: constructed without cond_stage (an OpenCLIPTextEncoder)")
+        if isinstance(c, torch.Tensor):
+            return self.cond_stage_model.encode_with_transformer(c)
+        return self.cond_stage_model.encode(c)
 
     def encode_first_stage_2DAE(self, x, noise=None):
         """ddpm3d.py:485-490: x [b, 3, t, H, W] frames in [-1, 1] -> scale_factor * sample(posterior) [b, zc, t, H/8, W/8]."""

@@ -20,8 +20,10 @@ Rebound (``REBOUND`` lists them; tests/test_patch.py checks each against the ref
   lvdm.models.ddpm3d.LatentDiffusion.decode_first_stage_2DAE     -> the same decoder, frames grouped per call instead of one
                                                                     ``decode`` per frame (ddpm3d.py:555-562)
       (both need pytorch_lightning to import; where it is absent they are skipped and reported False)
+  lvdm.modules.encoders.condition.FrozenOpenCLIPEmbedder.encode_with_transformer -> OpenCLIPTextEncoder (moca_text_encode; SURVEY N4);
+      tokenisation (``forward`` -> open_clip.tokenize) stays the reference's
 The rebound ``fifo_ddim_sampling`` calls ``model.decode_first_stage_2DAE`` on every popped frame, exactly where the reference
-does (funcs.py:359-365).  Not rebound: the text encoder.
+does (funcs.py:359-365).  
 """
 import importlib
 import os
@@ -32,6 +34,7 @@ from . import fifo, ops
 from ._lib import MocaError
 from .sampler import DDIMSampler as _B200Sampler
 from .unet import UNet3D
+from .text import attach_text
 from .vae import DiagonalGaussian, attach_vae, attach_vae_encoder
 
 REBOUND = {
@@ -41,6 +44,7 @@ REBOUND = {
                                   "DDIMSampler.p_sample_ddim"],
     "lvdm.models.autoencoder": ["AutoencoderKL.decode", "AutoencoderKL.encode"],
     "lvdm.models.ddpm3d": ["LatentDiffusion.decode_first_stage_2DAE"],
+    "lvdm.modules.encoders.condition": ["FrozenOpenCLIPEmbedder.encode_with_transformer"],
     "utils.freeinit_utils": ["freq_mix_3d", "get_freq_filter"],
     "scripts.evaluation.funcs": ["prepare_latents", "shift_latents", "fifo_ddim_sampling", "freq_mix_3d", "get_freq_filter"],
 }
@@ -156,6 +160,12 @@ def _ae_decode(self, z, **kwargs):
     return attach_vae(self, device=z.device).decode(z).to(z.dtype)
 
 
+def _clip_encode_with_transformer(self, text):
+    """Replacement body of FrozenOpenCLIPEmbedder.encode_with_transformer (condition.py:212-219): token ids [b, 77] -> [b, 77, 1024].
+    ``forward`` (tokenisation with open_clip.tokenize, condition.py:205-210) stays the reference's."""
+    return attach_text(self, device=text.device if text.is_cuda else None).encode_with_transformer(text)
+
+
 def _ae_encode(self, x, **kwargs):
     """Replacement body of AutoencoderKL.encode (autoencoder.py:97-102): the posterior over z for images x [n, 3, H, W]; the
     returned object has the reference distribution's ``sample`` / ``mode`` / ``parameters`` (lvdm/distributions.py:24-43), which is
@@ -245,6 +255,11 @@ def patch_reference():
         m.LatentDiffusion.decode_first_stage_2DAE = _decode_first_stage_2DAE
     else:
         mods["lvdm.models.ddpm3d"] = None
+    m = mods["lvdm.modules.encoders.condition"]
+    if m is not None and isinstance(getattr(m, "FrozenOpenCLIPEmbedder", None), type):
+        m.FrozenOpenCLIPEmbedder.encode_with_transformer = _clip_encode_with_transformer
+    else:
+        mods["lvdm.modules.encoders.condition"] = None
     m = mods["lvdm.models.samplers.ddim"]
     if m is not None:
         S = m.DDIMSampler

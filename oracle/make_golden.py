@@ -496,9 +496,46 @@ def gen_vae_small():
     np.savez_compressed(os.path.join(GOLD, "vae_small.npz"), **out)
 
 
+TEXT_SMALL = (1000, 77, 128, 2, 4)          # vocab, context, width, heads, layers
+
+
+def gen_text_small():
+    """oracle.text_ref (open_clip's published text transformer behind condition.py:212-230) vs transformers.CLIPTextModel with the
+    same weights: open_clip itself is not installed here, so this fixture pins the restatement to an INDEPENDENT implementation of
+    the same model, not to the reference's dependency ("parity unpinned" in oracle/text_ref.py)."""
+    from transformers import CLIPTextConfig, CLIPTextModel
+    from moca_video_b200.text import text_param_shapes
+    from oracle.text_ref import random_text_state_dict, text_encode, to_hf_state_dict
+    vocab, L, W, heads, layers = TEXT_SMALL
+    sd = random_text_state_dict(text_param_shapes(vocab, L, W, heads, layers), seed=8)
+    cfg = CLIPTextConfig(vocab_size=vocab, hidden_size=W, intermediate_size=4 * W, num_hidden_layers=layers, num_attention_heads=heads,
+                         max_position_embeddings=L, hidden_act="gelu", layer_norm_eps=1e-5, attn_implementation="eager")
+    hf = CLIPTextModel(cfg).eval()
+    missing, unexpected = hf.load_state_dict(to_hf_state_dict(sd, layers), strict=False)
+    assert not unexpected and all("position_ids" in k for k in missing), (missing, unexpected)
+    rng = np.random.default_rng(33)
+    tokens = torch.from_numpy(rng.integers(1, vocab - 2, size=(3, L))).long()
+    tokens[:, 0] = vocab - 2
+    for r, n in enumerate((5, 20, 77)):                       # padded like open_clip.tokenize: <sot> words <eot> 0 0 ...
+        if n < L:
+            tokens[r, n] = vocab - 1
+            tokens[r, n + 1:] = 0
+    out = {"tokens": _np(tokens)}
+    with torch.no_grad():
+        o = hf(input_ids=tokens, output_hidden_states=True)
+        ref = {"last": o.last_hidden_state, "penultimate": hf.text_model.final_layer_norm(o.hidden_states[-2])}
+    for layer, idx in (("last", 0), ("penultimate", 1)):
+        z = text_encode(sd, tokens, heads, layers - idx)
+        err = float((z - ref[layer]).norm() / ref[layer].norm())
+        print(f"text_small[{layer}] restatement vs transformers.CLIPTextModel rel-L2 = {err:.3e}, |z| = {float(ref[layer].abs().mean()):.3f}")
+        assert err < 1e-5
+        out["z_" + layer] = _np(ref[layer])
+    np.savez_compressed(os.path.join(GOLD, "text_small.npz"), **out)
+
+
 if __name__ == "__main__":
     os.makedirs(GOLD, exist_ok=True)
-    which = sys.argv[1:] or ["tables", "ddim_step", "ddim_step_sam", "p_sample", "queue", "unet_small", "unet_small64", "unet_full", "vae_small"]
+    which = sys.argv[1:] or ["tables", "ddim_step", "ddim_step_sam", "p_sample", "queue", "unet_small", "unet_small64", "unet_full", "vae_small", "text_small"]
     for w in which:
         print("==", w)
         globals()["gen_" + w]()

@@ -27,6 +27,7 @@ ORIGINAL_AT = {                                   # reference definitions the re
     "lvdm.models.autoencoder:AutoencoderKL.decode": "autoencoder.py:104",
     "lvdm.models.autoencoder:AutoencoderKL.encode": "autoencoder.py:97",
     "lvdm.models.ddpm3d:LatentDiffusion.decode_first_stage_2DAE": "ddpm3d.py:556",
+    "lvdm.modules.encoders.condition:FrozenOpenCLIPEmbedder.encode_with_transformer": "condition.py:212",
     "utils.freeinit_utils:freq_mix_3d": "freeinit_utils.py:7",
     "utils.freeinit_utils:get_freq_filter": "freeinit_utils.py:51",
     "scripts.evaluation.funcs:prepare_latents": "funcs.py:21",
@@ -119,6 +120,19 @@ def test_patched_calls_reach_the_device_boundary(patched):
     ld = types.SimpleNamespace(first_stage_model=ae, scale_factor=0.18215)
     with pytest.raises(MocaError):
         mods["lvdm.models.ddpm3d"].LatentDiffusion.decode_first_stage_2DAE(ld, torch.zeros(1, 4, 2, 8, 8))
+    # text tower: an object shaped like FrozenOpenCLIPEmbedder after open_clip built its model (open_clip itself is not installed)
+    class _Attn(torch.nn.Module):
+        num_heads = 2
+    blk = torch.nn.Module(); blk.attn = _Attn()
+    clip = torch.nn.Module()
+    clip.token_embedding = torch.nn.Embedding(100, 128)
+    clip.positional_embedding = torch.nn.Parameter(torch.zeros(77, 128))
+    clip.transformer = torch.nn.Module(); clip.transformer.resblocks = torch.nn.ModuleList([blk, blk])
+    emb = object.__new__(mods["lvdm.modules.encoders.condition"].FrozenOpenCLIPEmbedder)
+    torch.nn.Module.__init__(emb)
+    emb.model, emb.layer_idx = clip, 1
+    with pytest.raises(MocaError):
+        emb.encode_with_transformer(torch.zeros(1, 77, dtype=torch.long))
     # sampler through the reference's own constructor path (oracle/refimport's CPU subclass) and LatentDiffusion-like apply_model
     seen = []
 
