@@ -19,9 +19,9 @@ template <int BN, bool TEPI = false, int EPI = EPI_F32, int NCTA = 1, bool RES =
 struct GemmCfg {
     static constexpr bool GT = TEPI && EPI == EPI_GEGLU;
     static constexpr int B_BYTES = (BN / NCTA) * kBK * 2;                   // CTA pair: each CTA holds half of the B rows
-    static constexpr int STAGE_BYTES = kABytes + B_BYTES;                   // multiple of 1024 for BN in {128, 160, 192, 256}
+    static constexpr int STAGE_BYTES = kABytes + B_BYTES;                   // multiple of 1024 for BN in {32, 128, 160, 192, 256}
     static constexpr bool BT = TEPI && EPI == EPI_BF16;      // bf16 thread = row epilogue: classic ring, two 2 KB staging boxes per warp
-    static constexpr int STAGES = NCTA == 2 ? 6 : (GT ? 4 : ((TEPI && !BT) ? (BN == 128 ? 4 : 3) : ((BN == 256) ? (RES ? 3 : 4) : (BN == 192 ? (RES ? 3 : 4) : (BN == 160 ? (RES ? 4 : 5) : (RES ? 5 : 6))))));
+    static constexpr int STAGES = NCTA == 2 ? 6 : (GT ? 4 : ((TEPI && !BT) ? (BN == 128 ? 4 : 3) : ((BN == 256) ? (RES ? 3 : 4) : (BN == 192 ? (RES ? 3 : 4) : (BN == 160 ? (RES ? 4 : 5) : (BN == 32 ? 8 : (RES ? 5 : 6)))))));
     static constexpr int TMEM_COLS = (2 * BN <= 256) ? 256 : 512;
     static constexpr int EPI_WARPS = GT ? 16 : 8;
     static constexpr int THREADS = 64 + 32 * EPI_WARPS;
@@ -953,6 +953,10 @@ int make_tmap_bf16_chunk(CUtensorMap* tm, const void* ptr, int64_t rows, int64_t
 // 160 columns where 561 / 270 tiles of 256 are 15-20 % faster (1.35 ms per forward).  GEGLU weights are packed for 256.
 static int pick_bn(const GemmDesc& d, int num_sms) {
     if (d.epi == EPI_GEGLU) return 256;
+    // outputs of a few channels (the UNet's `out` conv, N = 4; the VAE's conv_out, N = 3): a 32-wide tile instead of 128 columns of
+    // zeros; the launch is then bound by streaming A through shared memory (staged fp32 epilogue only)
+    static const int bn32 = [] { const char* e = getenv("MOCA_GEMM_BN32"); return e ? atoi(e) : 1; }();
+    if (bn32 && d.epi == EPI_F32 && d.N <= 32) return 32;
     // 192: 1280-wide outputs on 40 M tiles (the 10 x 16 level) are 200 tiles of 256 = 1.35 waves, but 280 tiles of 192 = 1.89
     const int cand[4] = {256, 192, 160, 128};
     static const double pen192 = [] { const char* e = getenv("MOCA_GEMM_PEN192"); return e ? atof(e) : 1.12; }();    // <= 0: never
@@ -1131,7 +1135,7 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
     static const int tepi_maxk128 = [] { const char* e = getenv("MOCA_GEMM_TEPI_MAXK128"); return e ? atoi(e) : 15; }();    // 4-stage ring
     const int tepi_maxk = L.BN == 128 ? tepi_maxk128 : tepi_maxk160;
     const bool rows_ok = (d.mode == GEMM_LINEAR && d.M % 32 == 0) || (d.mode == GEMM_TIME_PAD && d.g_w % 32 == 0 && d.g_rows % 32 == 0);
-    p.tepi = tepi_on && ncta == 1 && d.epi == EPI_F32 && L.BN != 256 && rows_ok && d.N % 32 == 0 && d.ldo % 4 == 0 && (!d.out16 || d.ldo % 8 == 0) && !d.rowbias && (!d.chan_stats || d.stat_rows_per_frame % 32 == 0) &&
+    p.tepi = tepi_on && ncta == 1 && d.epi == EPI_F32 && L.BN != 256 && L.BN != 32 && rows_ok && d.N % 32 == 0 && d.ldo % 4 == 0 && (!d.out16 || d.ldo % 8 == 0) && !d.rowbias && (!d.chan_stats || d.stat_rows_per_frame % 32 == 0) &&
              d.ntaps * p.kblocks <= tepi_maxk && (((uintptr_t)d.out | (uintptr_t)d.residual | (uintptr_t)d.bias) & 15) == 0;
     const bool gt = tepi_on && d.epi == EPI_GEGLU && L.BN == 256 && d.mode == GEMM_LINEAR && d.M % 32 == 0 && (d.N / 2) % 32 == 0 &&
                     d.ldo % 8 == 0 && (((uintptr_t)d.out | (uintptr_t)d.bias) & 15) == 0;
@@ -1163,7 +1167,7 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
         if (rc) return rc;
         L.smem = L.BN == 192 ? GemmCfg<192, true>::SMEM : (L.BN == 160 ? GemmCfg<160, true>::SMEM : GemmCfg<128, true>::SMEM);
     } else {
-        L.smem = L.BN == 256 ? GemmCfg<256>::SMEM : (L.BN == 192 ? GemmCfg<192>::SMEM : (L.BN == 160 ? GemmCfg<160>::SMEM : GemmCfg<128>::SMEM));
+        L.smem = L.BN == 32 ? GemmCfg<32>::SMEM : L.BN == 256 ? GemmCfg<256>::SMEM : (L.BN == 192 ? GemmCfg<192>::SMEM : (L.BN == 160 ? GemmCfg<160>::SMEM : GemmCfg<128>::SMEM));
     }
     L.flops = 2.0 * (double)d.M * d.N * d.ntaps * d.a_cols;
     if (ncta == 2) {
@@ -1172,14 +1176,18 @@ int gemm_plan(const Ctx& ctx, const GemmDesc& d, GemmLaunch* out) {
         if (!rc) rc = L.BN == 256 ? set_attr_pair<256, false>() : set_attr_pair<160, false>();
         if (rc) return rc;
     }
-    rc = L.BN == 256 ? set_attr_bn<256>(d.epi, p.tepi) : (L.BN == 192 ? set_attr_bn<192>(d.epi, p.tepi) : (L.BN == 160 ? set_attr_bn<160>(d.epi, p.tepi) : set_attr_bn<128>(d.epi, p.tepi)));
+    if (L.BN == 32) { rc = set_attr<32, EPI_F32, true>(); if (!rc) rc = set_attr<32, EPI_F32>(); }
+    else rc = L.BN == 256 ? set_attr_bn<256>(d.epi, p.tepi) : (L.BN == 192 ? set_attr_bn<192>(d.epi, p.tepi) : (L.BN == 160 ? set_attr_bn<160>(d.epi, p.tepi) : set_attr_bn<128>(d.epi, p.tepi)));
     if (rc) return rc;
     *out = L;
     return MOCA_OK;
 }
 
 int gemm_run(const GemmLaunch& l, cudaStream_t st) {
-    if (l.BN == 256) launch_bn<256>(l, st);
+    if (l.BN == 32) {
+        if (l.p.cstat) launch_pdl_tc(gemm_tc_kernel<32, EPI_F32, true>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
+        else launch_pdl_tc(gemm_tc_kernel<32, EPI_F32, false>, dim3(l.grid), dim3(kGemmThreads), l.smem, st, l.p);
+    } else if (l.BN == 256) launch_bn<256>(l, st);
     else if (l.BN == 192) launch_bn<192>(l, st);
     else if (l.BN == 160) launch_bn<160>(l, st);
     else launch_bn<128>(l, st);

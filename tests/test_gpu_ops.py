@@ -68,7 +68,9 @@ def test_geglu_epilogue(M, N, K):
 CONV_CASES = [(2, 8, 8, 64, 64, 1), (3, 10, 16, 64, 128, 1), (16, 40, 64, 320, 320, 1), (4, 20, 32, 960, 640, 1), (2, 5, 8, 1280, 1280, 1),
               (4, 40, 64, 320, 320, 2), (2, 10, 16, 1280, 1280, 2), (16, 10, 16, 64, 4, 1), (2, 8, 8, 8, 64, 1), (1, 2, 2, 64, 64, 1),
               # 4-D tensor-map path with several frames per M tile (bf = 4 / 16) and stride 2 (element strides of the tensor map)
-              (32, 10, 16, 256, 256, 1), (16, 5, 8, 128, 192, 1), (32, 20, 32, 128, 128, 2), (16, 10, 16, 64, 64, 2)]
+              (32, 10, 16, 256, 256, 1), (16, 5, 8, 128, 192, 1), (32, 20, 32, 128, 128, 2), (16, 10, 16, 64, 64, 2),
+              # few output channels: the 32-wide tile (UNet `out` conv N = 4 at full size, VAE conv_out N = 3, a ragged 20, exactly 32)
+              (32, 40, 64, 320, 4, 1), (2, 64, 128, 128, 3, 1), (4, 20, 32, 64, 20, 1), (2, 8, 8, 64, 32, 1)]
 
 
 @pytest.mark.parametrize("NF,H,W,Ci,Co,s", CONV_CASES)
