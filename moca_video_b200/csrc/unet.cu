@@ -134,7 +134,10 @@ static void build_arch(moca_unet* n) {
     {
         BlockW b;
         LayerW L = mk("conv_in", "input_blocks.0.0", n->in_ch, mc);
-        L.conv = reg_linear(n, L.name, mc, n->in_ch, 9, true);
+        // the stem's [mc, in_ch, 3, 3] weight read as a Linear over k = c * 9 + tap when the 9 * in_ch patch fits one 64-wide k-block
+        // (unet_plan.cu gathers the patches while it converts the input layout), else as a 9-tap convolution
+        if (n->in_ch * 9 <= 64) L.conv = reg_linear(n, L.name, mc, n->in_ch * 9, 1, true);
+        else L.conv = reg_linear(n, L.name, mc, n->in_ch, 9, true);
         b.layers.push_back(L);
         n->inp.push_back(b);
     }

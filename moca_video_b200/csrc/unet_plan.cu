@@ -54,6 +54,24 @@ struct Act {
     StatSrc st;               // GroupNorm statistics material left by the GEMM epilogue that wrote p
 };
 
+// x [B, C, T, H, W] fp32 -> 3x3 patches as 16-bit rows [B*T*H*W, 64]: column c * 9 + ky * 3 + kx = x[b, c, t, h + ky - 1, w + kx - 1]
+// (zero outside the image and for columns >= 9 C): the stem convolution (openaimodel3d.py:375-379) becomes one k-block of a Linear
+__global__ void ncthw_patches_kernel(const float* __restrict__ x, int B, int C, int T, int H, int W, op_t* __restrict__ dst) {
+    const int64_t total = (int64_t)B * T * H * W * 64;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int k = (int)(i & 63);
+        const int64_t r = i >> 6;
+        const int w = (int)(r % W), h = (int)((r / W) % H), f = (int)(r / ((int64_t)W * H));
+        float v = 0.f;
+        if (k < 9 * C) {
+            const int c = k / 9, tap = k - 9 * c;
+            const int hh = h + tap / 3 - 1, ww = w + tap % 3 - 1;
+            if (hh >= 0 && hh < H && ww >= 0 && ww < W) v = x[((((int64_t)(f / T) * C + c) * T + (f % T)) * H + hh) * W + ww];
+        }
+        dst[i] = float2op(v);
+    }
+}
+
 enum ScratchId { S_PAD = 0, S_RAW, S_LIN, S_QKV, S_ATT, S_FFH, S_F32A, S_F32B, S_Y, S_COUNT };
 
 struct Builder {
@@ -446,10 +464,26 @@ void Builder::build() {
         const float* x_in = plan->x_in;
         const int b = B, c = n->in_ch, t = T, h = H0, w = W0;
         const bool c4 = conv4d(H0, W0, 1);
-        push([=](cudaStream_t st) { return c4 ? ncthw_to_tokens(x_in, b, c, t, h, w, 64, pad, st) : ncthw_to_pad(x_in, b, c, t, h, w, 64, pad, st); });
+        const PackedW& cw = n->inp[0].layers[0].conv;
         cur.p = (float*)palloc((size_t)rows0 * mc * 4);
         cur.st = stat_alloc(mc, H0 * W0);
-        conv3x3(pad, H0, W0, 64, n->inp[0].layers[0].conv, 1, cur.p, nullptr, 0, nullptr, &cur.st);
+        if (cw.taps == 1) {
+            // patches gathered by the layout conversion: 81920 x 320 x 64 instead of nine taps of 60 zero channels each (85 -> 30 us)
+            push([=](cudaStream_t st) {
+                const int64_t total = (int64_t)b * t * h * w * 64;
+                ncthw_patches_kernel<<<(int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16), 256, 0, st>>>(x_in, b, c, t, h, w, pad);
+                return cudaGetLastError() == cudaSuccess ? MOCA_OK : MOCA_E_CUDA;
+            }, 1, "stem patches");
+            GemmDesc d;
+            d.A = pad; d.a_rows = rows0; d.a_cols = 64; d.a_pitch = 64;
+            d.Wt = cw.w; d.N = cw.N; d.ntaps = 1; d.Kp = cw.Kp;
+            d.mode = GEMM_LINEAR; d.M = (int)rows0; d.epi = EPI_F32; d.out = cur.p; d.ldo = cw.N; d.bias = cw.b;
+            d.chan_stats = (double*)cur.st.cs; d.stat_rows_per_frame = cur.st.rows; d.stat_sample_rows = T * H0 * W0;
+            gemm(d, 2.0 * rows0 * cw.N * 9.0 * c);
+        } else {
+            push([=](cudaStream_t st) { return c4 ? ncthw_to_tokens(x_in, b, c, t, h, w, 64, pad, st) : ncthw_to_pad(x_in, b, c, t, h, w, 64, pad, st); });
+            conv3x3(pad, H0, W0, 64, cw, 1, cur.p, nullptr, 0, nullptr, &cur.st);
+        }
         tap("input_blocks.0.0", cur);
     }
     auto run_layers = [&](const BlockW& blk, const Act* skip) {
