@@ -41,6 +41,24 @@ __device__ __forceinline__ float ex2(float x) {
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
+// packed fp32 pairs (sm_100 fma.rn.f32x2 / add.rn.f32x2): the softmax threads are bound by their own instruction stream, and the
+// scale-and-subtract and the row sum are one instruction per two scores this way
+__device__ __forceinline__ uint64_t f2_pack(float a, float b) {
+    uint64_t d;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(a), "f"(b));
+    return d;
+}
+__device__ __forceinline__ void f2_unpack(uint64_t v, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ uint64_t f2_fma(uint64_t a, uint64_t b, uint64_t c) {
+    uint64_t d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ uint64_t f2_add(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ uint32_t pack2(float a, float b) {
     op2_t v = floats2op2(a, b);
@@ -180,7 +198,8 @@ __global__ void __launch_bounds__(kThreads, 2) attn_tc_kernel(const __grid_const
             const float alpha = ex2(m * P.scale_log2 - ms);      // m = -inf on the first tile -> 0
             m = mx;
             // pass 2: p = exp2(s * scale - max * scale), row sum, bf16 P into the swizzled smem tile
-            float rs = 0.f;
+            const uint64_t sc2 = f2_pack(P.scale_log2, P.scale_log2), nms2 = f2_pack(-ms, -ms);
+            uint64_t rs2[2] = {0ull, 0ull};
 #pragma unroll 1
             for (int c = 0; c < 4; ++c) {
                 uint32_t pk[16];
@@ -190,11 +209,12 @@ __global__ void __launch_bounds__(kThreads, 2) attn_tc_kernel(const __grid_const
                     tmem_ld_wait();
 #pragma unroll
                     for (int i = 0; i < 32; i += 2) {
-                        float p0 = ex2(fmaf(__uint_as_float(r[i]), P.scale_log2, -ms));
-                        float p1 = ex2(fmaf(__uint_as_float(r[i + 1]), P.scale_log2, -ms));
+                        float x0, x1;
+                        f2_unpack(f2_fma(f2_pack(__uint_as_float(r[i]), __uint_as_float(r[i + 1])), sc2, nms2), x0, x1);
+                        float p0 = ex2(x0), p1 = ex2(x1);
                         if (c * 32 + i >= nvalid) p0 = 0.f;
                         if (c * 32 + i + 1 >= nvalid) p1 = 0.f;
-                        rs += p0 + p1;
+                        rs2[(i >> 1) & 1] = f2_add(rs2[(i >> 1) & 1], f2_pack(p0, p1));
                         pk[i >> 1] = pack2(p0, p1);
                     }
                 } else {
@@ -208,6 +228,12 @@ __global__ void __launch_bounds__(kThreads, 2) attn_tc_kernel(const __grid_const
                     const int chunk = ((c & 1) * 4 + u) ^ (row & 7);
                     *reinterpret_cast<uint4*>(dst + chunk * 16) = make_uint4(pk[4 * u], pk[4 * u + 1], pk[4 * u + 2], pk[4 * u + 3]);
                 }
+            }
+            float rs;
+            {
+                float a, b;
+                f2_unpack(f2_add(rs2[0], rs2[1]), a, b);
+                rs = a + b;
             }
             l = l * alpha + rs;
             tc_fence_before();
@@ -445,15 +471,17 @@ __global__ void __launch_bounds__(kThreads2, 1) attn_tc2_kernel(const __grid_con
                     }
                 }
                 const float ms = m_ref * P.scale_log2;
-                float rsp[4] = {0.f, 0.f, 0.f, 0.f};
+                const uint64_t sc2 = f2_pack(P.scale_log2, P.scale_log2), nms2 = f2_pack(-ms, -ms);
+                uint64_t rsp[4] = {0ull, 0ull, 0ull, 0ull};              // four chains of (even, odd) partial row sums
 #pragma unroll
                 for (int c = 0; c < 4; ++c) {
                     uint32_t pk[16];
 #pragma unroll
                     for (int i = 0; i < 32; i += 2) {
-                        const float p0 = ex2(fmaf(__uint_as_float(r[c * 32 + i]), P.scale_log2, -ms));
-                        const float p1 = ex2(fmaf(__uint_as_float(r[c * 32 + i + 1]), P.scale_log2, -ms));
-                        rsp[(i >> 1) & 3] += p0 + p1;
+                        float x0, x1;
+                        f2_unpack(f2_fma(f2_pack(__uint_as_float(r[c * 32 + i]), __uint_as_float(r[c * 32 + i + 1])), sc2, nms2), x0, x1);
+                        const float p0 = ex2(x0), p1 = ex2(x1);
+                        rsp[(i >> 1) & 3] = f2_add(rsp[(i >> 1) & 3], f2_pack(p0, p1));
                         pk[i >> 1] = pack2(p0, p1);
                     }
                     uint8_t* dst = prow + (c >> 1) * kTileBytes;
@@ -463,7 +491,11 @@ __global__ void __launch_bounds__(kThreads2, 1) attn_tc2_kernel(const __grid_con
                         *reinterpret_cast<uint4*>(dst + chunk * 16) = make_uint4(pk[4 * u], pk[4 * u + 1], pk[4 * u + 2], pk[4 * u + 3]);
                     }
                 }
-                l += (rsp[0] + rsp[1]) + (rsp[2] + rsp[3]);
+                {
+                    float a, b;
+                    f2_unpack(f2_add(f2_add(rsp[0], rsp[1]), f2_add(rsp[2], rsp[3])), a, b);
+                    l += a + b;
+                }
                 tc_fence_before();
                 fence_async_smem();
                 __syncwarp();
