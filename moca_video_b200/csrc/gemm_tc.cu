@@ -49,6 +49,45 @@ __device__ __forceinline__ float gelu_fast(float g) {
     const float h = 0.5f * g;
     return fmaf(h, th, h);
 }
+// the same on packed fp32 pairs (sm_100 f32x2 arithmetic): the 16-warp GEGLU epilogue is bound by its instruction stream, and all
+// but the clamp and the tanh are one instruction per two outputs this way.  Bit-identical to gelu_fast per element.
+__device__ __forceinline__ uint64_t f2_pack(float a, float b) {
+    uint64_t d;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(a), "f"(b));
+    return d;
+}
+__device__ __forceinline__ void f2_unpack(uint64_t v, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ uint64_t f2_fma(uint64_t a, uint64_t b, uint64_t c) {
+    uint64_t d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ uint64_t f2_add(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ uint64_t f2_mul(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+// (value + bias_v) * gelu_fast(gate + bias_g) for two adjacent columns
+__device__ __forceinline__ void geglu_pair(float v0, float v1, float g0, float g1, float bv0, float bv1, float bg0, float bg1, float& o0, float& o1) {
+    const uint64_t g = f2_add(f2_pack(g0, g1), f2_pack(bg0, bg1));
+    float q0, q1;
+    f2_unpack(f2_mul(g, g), q0, q1);
+    const uint64_t g2 = f2_pack(fminf(q0, 64.0f), fminf(q1, 64.0f));
+    uint64_t u = f2_fma(g2, f2_pack(-3.51516789e-04f, -3.51516789e-04f), f2_pack(3.70056460e-02f, 3.70056460e-02f));
+    u = f2_fma(g2, u, f2_pack(7.97507884e-01f, 7.97507884e-01f));
+    float a0, a1, t0, t1;
+    f2_unpack(f2_mul(g, u), a0, a1);
+    asm("tanh.approx.f32 %0, %1;" : "=f"(t0) : "f"(a0));
+    asm("tanh.approx.f32 %0, %1;" : "=f"(t1) : "f"(a1));
+    const uint64_t h = f2_mul(g, f2_pack(0.5f, 0.5f));
+    const uint64_t ge = f2_fma(h, f2_pack(t0, t1), h);
+    f2_unpack(f2_mul(f2_add(f2_pack(v0, v1), f2_pack(bv0, bv1)), ge), o0, o1);
+}
 #else
 __device__ __forceinline__ float gelu_fast(float g) {
     const float z = g * 0.70710678118654752f;
@@ -271,10 +310,18 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
 #pragma unroll
                     for (int u = 0; u < 4; ++u) {
                         const float4 b1 = __ldg(bv + u), b2 = __ldg(bg + u);
+#ifndef MOCA_GELU_ERFC_POLY
+                        float o0, o1, o2, o3;
+                        geglu_pair(__uint_as_float(rv[4 * u]), __uint_as_float(rv[4 * u + 1]), __uint_as_float(rg[4 * u]), __uint_as_float(rg[4 * u + 1]),
+                                   b1.x, b1.y, b2.x, b2.y, o0, o1);
+                        geglu_pair(__uint_as_float(rv[4 * u + 2]), __uint_as_float(rv[4 * u + 3]), __uint_as_float(rg[4 * u + 2]), __uint_as_float(rg[4 * u + 3]),
+                                   b1.z, b1.w, b2.z, b2.w, o2, o3);
+#else
                         const float o0 = (__uint_as_float(rv[4 * u]) + b1.x) * gelu_fast(__uint_as_float(rg[4 * u]) + b2.x);
                         const float o1 = (__uint_as_float(rv[4 * u + 1]) + b1.y) * gelu_fast(__uint_as_float(rg[4 * u + 1]) + b2.y);
                         const float o2 = (__uint_as_float(rv[4 * u + 2]) + b1.z) * gelu_fast(__uint_as_float(rg[4 * u + 2]) + b2.z);
                         const float o3 = (__uint_as_float(rv[4 * u + 3]) + b1.w) * gelu_fast(__uint_as_float(rg[4 * u + 3]) + b2.w);
+#endif
                         pk[2 * u] = pack_bf16(o0, o1);
                         pk[2 * u + 1] = pack_bf16(o2, o3);
                     }
