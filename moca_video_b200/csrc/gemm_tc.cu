@@ -31,26 +31,8 @@ struct GemmCfg {
     static constexpr size_t SMEM = (size_t)OFF_BAR + 512 /*barriers*/ + 1024 /*align slack*/;
 };
 
-__device__ __forceinline__ float gelu_erf(float g) { return 0.5f * g * (1.0f + erff(g * 0.70710678118654752f)); }
-
-// erf-GELU (attention.py:383 uses F.gelu's default) for the GEGLU epilogues.  ncu showed the 16-warp GEGLU kernel issue-bound
-// (70 % issue-active, 32 warp instructions per output), so the activation is the cheapest form that stays below the bf16
-// rounding of the output: 0.5 g (1 + tanh(g (a0 + a1 g^2 + a2 g^4))) with the three coefficients fitted (minimax over
-// [-8, 8], g^2 clamped at 64 so the odd polynomial stays monotone) to the erf form: |error| <= 2.6e-5 for the fit plus
-// 2^-11 relative for tanh.approx — 8 instructions and one MUFU op, against 17 and two for the Abramowitz-Stegun
-// erfc polynomial (|error| 2e-7; build with -DMOCA_GELU_ERFC_POLY to get it back).
-#ifndef MOCA_GELU_ERFC_POLY
-__device__ __forceinline__ float gelu_fast(float g) {
-    const float g2 = fminf(g * g, 64.0f);
-    float u = fmaf(g2, -3.51516789e-04f, 3.70056460e-02f);
-    u = fmaf(g2, u, 7.97507884e-01f);
-    float th;
-    asm("tanh.approx.f32 %0, %1;" : "=f"(th) : "f"(g * u));
-    const float h = 0.5f * g;
-    return fmaf(h, th, h);
-}
-// the same on packed fp32 pairs (sm_100 f32x2 arithmetic): the 16-warp GEGLU epilogue is bound by its instruction stream, and all
-// but the clamp and the tanh are one instruction per two outputs this way.  Bit-identical to gelu_fast per element.
+// packed fp32 pairs (sm_100 f32x2 arithmetic): the thread = row epilogues are bound by their instruction streams, and adds / multiplies /
+// FMAs on two adjacent columns are one instruction this way (bit-identical to the scalar forms)
 __device__ __forceinline__ uint64_t f2_pack(float a, float b) {
     uint64_t d;
     asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(a), "f"(b));
@@ -72,7 +54,26 @@ __device__ __forceinline__ uint64_t f2_mul(uint64_t a, uint64_t b) {
     asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
     return d;
 }
-// (value + bias_v) * gelu_fast(gate + bias_g) for two adjacent columns
+__device__ __forceinline__ float gelu_erf(float g) { return 0.5f * g * (1.0f + erff(g * 0.70710678118654752f)); }
+
+// erf-GELU (attention.py:383 uses F.gelu's default) for the GEGLU epilogues.  ncu showed the 16-warp GEGLU kernel issue-bound
+// (70 % issue-active, 32 warp instructions per output), so the activation is the cheapest form that stays below the bf16
+// rounding of the output: 0.5 g (1 + tanh(g (a0 + a1 g^2 + a2 g^4))) with the three coefficients fitted (minimax over
+// [-8, 8], g^2 clamped at 64 so the odd polynomial stays monotone) to the erf form: |error| <= 2.6e-5 for the fit plus
+// 2^-11 relative for tanh.approx — 8 instructions and one MUFU op, against 17 and two for the Abramowitz-Stegun
+// erfc polynomial (|error| 2e-7; build with -DMOCA_GELU_ERFC_POLY to get it back).
+#ifndef MOCA_GELU_ERFC_POLY
+__device__ __forceinline__ float gelu_fast(float g) {
+    const float g2 = fminf(g * g, 64.0f);
+    float u = fmaf(g2, -3.51516789e-04f, 3.70056460e-02f);
+    u = fmaf(g2, u, 7.97507884e-01f);
+    float th;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(th) : "f"(g * u));
+    const float h = 0.5f * g;
+    return fmaf(h, th, h);
+}
+// (value + bias_v) * gelu_fast(gate + bias_g) for two adjacent columns, on packed pairs: all but the clamp and the tanh are one
+// instruction per two outputs (the 16-warp GEGLU epilogue is bound by its instruction stream)
 __device__ __forceinline__ void geglu_pair(float v0, float v1, float g0, float g1, float bv0, float bv1, float bg0, float bg1, float& o0, float& o1) {
     const uint64_t g = f2_add(f2_pack(g0, g1), f2_pack(bg0, bg1));
     float q0, q1;
@@ -399,23 +400,27 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
                     uint4* dst = reinterpret_cast<uint4*>(stgb + (nst & 1u) * 2048 + lane * 64);
 #pragma unroll
                     for (int u = 0; u < 4; ++u) {
-                        float v[8];
+                        // packed fp32 pairs: one add per two columns for the bias and for the residual (same values as scalar adds)
+                        uint64_t v[4];
 #pragma unroll
-                        for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[8 * u + e]);
+                        for (int e = 0; e < 4; ++e) v[e] = f2_pack(__uint_as_float(r[8 * u + 2 * e]), __uint_as_float(r[8 * u + 2 * e + 1]));
                         if (P.bias) {
                             const float4 b1 = __ldg(reinterpret_cast<const float4*>(P.bias + n0) + 2 * u);
                             const float4 b2 = __ldg(reinterpret_cast<const float4*>(P.bias + n0) + 2 * u + 1);
-                            v[0] += b1.x; v[1] += b1.y; v[2] += b1.z; v[3] += b1.w;
-                            v[4] += b2.x; v[5] += b2.y; v[6] += b2.z; v[7] += b2.w;
+                            v[0] = f2_add(v[0], f2_pack(b1.x, b1.y)); v[1] = f2_add(v[1], f2_pack(b1.z, b1.w));
+                            v[2] = f2_add(v[2], f2_pack(b2.x, b2.y)); v[3] = f2_add(v[3], f2_pack(b2.z, b2.w));
                         }
                         if constexpr (RES16) {
                             const uint4 t4 = rsrc[u];
                             const float2 f0 = op22float2(*reinterpret_cast<const op2_t*>(&t4.x)), f1 = op22float2(*reinterpret_cast<const op2_t*>(&t4.y));
                             const float2 f2 = op22float2(*reinterpret_cast<const op2_t*>(&t4.z)), f3 = op22float2(*reinterpret_cast<const op2_t*>(&t4.w));
-                            v[0] += f0.x; v[1] += f0.y; v[2] += f1.x; v[3] += f1.y;
-                            v[4] += f2.x; v[5] += f2.y; v[6] += f3.x; v[7] += f3.y;
+                            v[0] = f2_add(v[0], f2_pack(f0.x, f0.y)); v[1] = f2_add(v[1], f2_pack(f1.x, f1.y));
+                            v[2] = f2_add(v[2], f2_pack(f2.x, f2.y)); v[3] = f2_add(v[3], f2_pack(f3.x, f3.y));
                         }
-                        dst[u] = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+                        float o[8];
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) f2_unpack(v[e], o[2 * e], o[2 * e + 1]);
+                        dst[u] = make_uint4(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]), pack_bf16(o[4], o[5]), pack_bf16(o[6], o[7]));
                     }
                     fence_proxy_async_smem();
                     __syncwarp();
@@ -505,17 +510,21 @@ __global__ void __launch_bounds__((GemmCfg<BN, TEPI, EPI, NCTA, TEPI && EPI == E
                     uint8_t* dst = wbuf + (out16 ? lane * 64 : lane * 128);
 #pragma unroll
                     for (int j = 0; j < 8; ++j) {
-                        float4 v = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]),
-                                               __uint_as_float(r[4 * j + 3]));
+                        // bias and residual as packed-pair adds (same values as scalar adds)
+                        uint64_t lo = f2_pack(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]));
+                        uint64_t hi = f2_pack(__uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
                         if (P.bias) {
                             const float4 b4 = __ldg(reinterpret_cast<const float4*>(P.bias + n0) + j);
-                            v.x += b4.x; v.y += b4.y; v.z += b4.z; v.w += b4.w;
+                            lo = f2_add(lo, f2_pack(b4.x, b4.y)); hi = f2_add(hi, f2_pack(b4.z, b4.w));
                         }
                         const int sw = (j ^ (lane & 7)) << 4;
                         if (has_res) {
                             const float4 t4 = *reinterpret_cast<const float4*>(rsrc + sw);
-                            v.x += t4.x; v.y += t4.y; v.z += t4.z; v.w += t4.w;
+                            lo = f2_add(lo, f2_pack(t4.x, t4.y)); hi = f2_add(hi, f2_pack(t4.z, t4.w));
                         }
+                        float4 v;
+                        f2_unpack(lo, v.x, v.y);
+                        f2_unpack(hi, v.z, v.w);
                         // 16-bit output: plain 32 x 64-byte box (row = 32 op_t), else the 128-byte-swizzled fp32 box
                         if (out16) *reinterpret_cast<uint2*>(dst + j * 8) = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
                         else *reinterpret_cast<float4*>(dst + sw) = v;
