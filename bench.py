@@ -10,6 +10,7 @@ step kernel.
                              the MoCA concept blend is inside the timed region) — the like-for-like base of the N>1 lines
          roofline_hbm        the HBM-bound kernels north_star names (K13 fused step, K14 FreeInit mix, K15 re-noise)
          gpu_eager_baseline  the same modules in torch eager on this B200 (bf16 autocast, TF32 on): SURVEY §8(d)'s speed bar
+         aux_rows            SURVEY N1 / N4 next to the step: VAE decode / encode of 320x512 frames, text tower per prompt pair
          cpu_baseline        the CPU path on the box's host cores (one real full-size forward)
   N>1  runs configs[3]: the same FIFO queue with its 8 windows per iteration sharded over the ranks (window r on rank r mod N,
        one NCCL all_gather of the updated half-windows per iteration), K iterations = 8K steps; rank 0 then replays the same
@@ -123,6 +124,56 @@ def run_reference(args, rank):
            "cpu_baseline": cb, "e2e": {"value": cb["value"], "unit": "steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
            "gpu_launches": 0}
     print(json.dumps(out))
+
+
+def aux_rows(dev):
+    """Rows either side of the step, random-init weights of the shipped configs, device timing outside the headline's
+    timed region: first-stage decode / encode of 320x512 frames and the ViT-H-14 text tower for a CFG prompt pair."""
+    from moca_video_b200.text import OpenCLIPTextEncoder
+    from moca_video_b200.vae import AutoencoderKLDecoder, AutoencoderKLEncoder
+
+    def rand_sd(shapes, seed):
+        g = torch.Generator(device=dev).manual_seed(seed)
+        sd = {}
+        for k, shp in shapes.items():
+            t = torch.randn(shp, device=dev, generator=g)
+            if len(shp) >= 2:
+                fan = int(np.prod(shp[1:]))
+                sd[k] = t * fan ** -0.5
+            else:
+                sd[k] = (1.0 + 0.1 * t) if (k.endswith(".weight") and ("norm" in k or ".ln_" in k)) else 0.02 * t
+        return sd
+
+    def timed(fn, n):
+        fn(); torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record(); torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / n
+
+    dd = dict(ch=128, ch_mult=(1, 2, 4, 4), num_res_blocks=2, z_channels=4, out_ch=3, in_channels=3, double_z=True)
+    out = {}
+    dec = AutoencoderKLDecoder(dd, device=dev, frames_per_call=2)
+    dec.load_state_dict(rand_sd(dec.shapes, 5))
+    z = torch.randn((1, 4, 16, 40, 64), device=dev) * 0.18215
+    ms = timed(lambda: dec.decode_first_stage_2DAE(z), 3)
+    out["vae_decode"] = {"ms_per_frame": ms / 16, "frames_per_s": 16e3 / ms, "tflops": dec.flops() / 2 * 16 / ms / 1e9, "frame": "320x512"}
+    dec.close()
+    enc = AutoencoderKLEncoder(dd, device=dev, frames_per_call=2)
+    enc.load_state_dict(rand_sd(enc.shapes, 6))
+    x = torch.rand((4, 3, 320, 512), device=dev) * 2 - 1
+    ms = timed(lambda: enc.encode_moments(x), 3)
+    out["vae_encode"] = {"ms_per_frame": ms / 4, "frames_per_s": 4e3 / ms, "frame": "320x512"}
+    enc.close()
+    txt = OpenCLIPTextEncoder(device=dev, layer="penultimate")
+    txt.load_state_dict(rand_sd(txt.shapes, 7))
+    tok = torch.randint(1, 49405, (2, 77), device=dev)
+    out["text_tower"] = {"ms_per_prompt_pair": timed(lambda: txt.encode_with_transformer(tok), 10), "arch": "ViT-H-14 text, penultimate"}
+    txt.close()
+    torch.cuda.empty_cache()
+    return out
 
 
 def gpu_eager_baseline(dev, iters=3):
@@ -447,6 +498,10 @@ def main():
     if world == 1 and not args.no_extras:
         del net
         torch.cuda.empty_cache()
+        try:
+            out["aux_rows"] = aux_rows(dev)
+        except Exception as e:  # noqa: BLE001  (informational rows must not take the headline line down)
+            out["aux_rows"] = {"error": str(e)[:200]}
         out["gpu_eager_baseline"] = gpu_eager_baseline(dev)
         if not args.no_cpu_baseline:
             out["cpu_baseline"], _ = cpu_reference(1, 0)
