@@ -223,9 +223,22 @@ def run_prompts(args, model, sampler_cls=None, cond_image=None, decode=None, par
         keep_frames = rank == 0 or parallel == "prompts"
         writer = FrameWriter(os.path.join(output_dir, "fifo") if keep_frames else None, save_frames=bool(args.save_frames) and keep_frames)
 
+        # the popped frame is decoded on a side stream: the next iteration's windows do not wait for the VAE (2.4 ms of a 40 ms
+        # iteration at 8 GPUs); the frame tensor is a copy the queue never writes again
+        side = torch.cuda.Stream(device=model.device) if keep_frames and torch.device(model.device).type == "cuda" else None
+
         def on_frame(i, z):
-            if keep_frames:
+            if not keep_frames:
+                return
+            if side is None:
                 writer.put(i, decode(z))
+                return
+            ready = torch.cuda.Event()
+            ready.record(torch.cuda.current_stream(z.device))
+            with torch.cuda.stream(side):
+                side.wait_event(ready)
+                z.record_stream(side)
+                writer.put(i, decode(z))                             # FrameWriter records its event on the side stream
         fifo.fifo_ddim_sampling(args, model, cond, noise_shape, sampler, cfg_scale=args.unconditional_guidance_scale,
                                 output_dir=output_dir, latents_dir=latents_dir, conditioned_image=cond_image,
                                 targets=d["conditioned_object"] + ".", gamma=d["gamma"],
